@@ -1,0 +1,107 @@
+#!/usr/bin/env python
+"""Build recipe for oracle/_ref/: the UNMODIFIED reference CUDA extensions.
+
+TEST INFRASTRUCTURE ONLY.  Nothing under oracle/ is imported by the product
+package; only tests/, __graft_entry__.smoke() and bench.py's reference /
+cpu_baseline legs may touch it.
+
+The three reference extensions are compiled straight from the sources where
+they lie under /root/reference/submodules (no source is copied into this repo);
+the only outputs are the three shared objects and ninja scratch under
+oracle/_ref/ (git-ignored, NOT gpurun-ignored, so the .so files travel to the
+GPU box, where /root/reference does not exist).
+
+  ref_surfel_C   <- diff-surfel-rasterization   (S/setup.py:21-30 source list)
+  ref_gauss_C    <- diff-gaussian-rasterization (G/setup.py:21-29)
+  ref_cubemap_C  <- cubemapencoder              (C/setup.py:19-27, -use_fast_math)
+
+`-include cstdint` is required on gcc 13: S|G/cuda_rasterizer/rasterizer_impl.h
+uses std::uintptr_t / uint32_t without including <cstdint>.
+"""
+import os
+import sys
+
+REF = os.environ.get("B200GS_REFERENCE_ROOT", "/root/reference")
+HERE = os.path.dirname(os.path.abspath(__file__))
+OUT = os.path.join(HERE, "_ref")
+
+ARCH = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo"]
+
+TARGETS = {
+    "ref_surfel_C": dict(
+        root="submodules/diff-surfel-rasterization",
+        sources=["cuda_rasterizer/rasterizer_impl.cu", "cuda_rasterizer/forward.cu",
+                 "cuda_rasterizer/backward.cu", "rasterize_points.cu", "ext.cpp"],
+        include=["third_party/glm"],
+        nvcc=["-include", "cstdint"],
+        cxx=[],
+    ),
+    "ref_gauss_C": dict(
+        root="submodules/diff-gaussian-rasterization",
+        sources=["cuda_rasterizer/rasterizer_impl.cu", "cuda_rasterizer/forward.cu",
+                 "cuda_rasterizer/backward.cu", "rasterize_points.cu", "ext.cpp"],
+        include=["third_party/glm"],
+        nvcc=["-include", "cstdint"],
+        cxx=[],
+    ),
+    "ref_cubemap_C": dict(
+        root="submodules/cubemapencoder",
+        sources=["src/cubemapencoder.cu", "src/bindings.cpp"],
+        include=[],
+        nvcc=["-O3", "-std=c++17", "-DCUDA_HAS_FP16=1", "-D__CUDA_NO_HALF_OPERATORS__",
+              "-D__CUDA_NO_HALF_CONVERSIONS__", "-D__CUDA_NO_HALF2_OPERATORS__", "-use_fast_math"],
+        cxx=["-O3", "-std=c++17"],
+    ),
+}
+
+
+def built(name):
+    return os.path.exists(os.path.join(OUT, name, name + ".so"))
+
+
+def build(names=None, verbose=False):
+    """Build the requested reference extensions (all by default).  Returns the
+    list of names that are available afterwards.  A missing /root/reference is
+    not an error: prebuilt .so files (if any) are used as they are."""
+    names = list(names or TARGETS)
+    if not os.path.isdir(REF):
+        return [n for n in names if built(n)]
+    os.environ.setdefault("TORCH_CUDA_ARCH_LIST", "10.0a")
+    from torch.utils.cpp_extension import load
+    ok = []
+    for name in names:
+        t = TARGETS[name]
+        root = os.path.join(REF, t["root"])
+        bdir = os.path.join(OUT, name)
+        os.makedirs(bdir, exist_ok=True)
+        try:
+            load(name=name,
+                 sources=[os.path.join(root, s) for s in t["sources"]],
+                 extra_include_paths=[os.path.join(root, i) for i in t["include"]],
+                 extra_cuda_cflags=ARCH + t["nvcc"],
+                 extra_cflags=t["cxx"],
+                 build_directory=bdir,
+                 is_python_module=False,   # build only; importing needs no GPU but keep it lazy
+                 verbose=verbose)
+            ok.append(name)
+        except Exception as ex:  # noqa: BLE001 - report and carry on with the others
+            print(f"[build_ref] {name}: FAILED: {ex}", file=sys.stderr)
+    return ok
+
+
+def load_ref(name):
+    """Import a prebuilt reference extension from oracle/_ref (GPU box or here)."""
+    import importlib.util
+    import torch  # noqa: F401  (libtorch symbols must be resident first)
+    path = os.path.join(OUT, name, name + ".so")
+    if not os.path.exists(path):
+        return None
+    spec = importlib.util.spec_from_file_location(name, path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+if __name__ == "__main__":
+    got = build(sys.argv[1:] or None, verbose=True)
+    print("built:", got)
