@@ -1,0 +1,161 @@
+// api.cu -- the extern "C" surface of libb200gs.so (see include/b200gs.h):
+// argument checks, scratch carving, stage sequencing.  No torch, no CPU fallback.
+#include "common.cuh"
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+namespace b200gs {
+
+static thread_local char t_err[512] = "";
+std::atomic<unsigned long long> g_launches{0};
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(t_err, sizeof(t_err), fmt, ap);
+  va_end(ap);
+}
+int cuda_fail(cudaError_t e, const char* what) {
+  set_error("CUDA error in %s: %s", what, cudaGetErrorString(e));
+  return B200GS_ECUDA;
+}
+
+size_t scan_state_words(int n);  // binning.cu
+
+SurfelGeom SurfelGeom::carve(void* base, size_t P, size_t* bytes) {
+  Carver c(base);
+  SurfelGeom g;
+  g.depths = c.take<float>(P);
+  g.tiles_touched = c.take<uint32_t>(P);
+  g.point_offsets = c.take<uint32_t>(P);
+  g.clamped = c.take<uint8_t>(P);
+  g.rects = c.take<uint2>(P);
+  g.rec = c.take<SurfelRec>(P);
+  g.scan_state = c.take<uint32_t>(scan_state_words((int)P));
+  g.flags = c.take<int>(4);
+  if (bytes) *bytes = c.used + 128;
+  return g;
+}
+
+SurfelImage SurfelImage::carve(void* base, int W, int H, size_t* bytes) {
+  Carver c(base);
+  SurfelImage im;
+  const size_t N = (size_t)W * H;
+  const size_t tiles = (size_t)((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
+  im.accum = c.take<float>(3 * N);
+  im.n_contrib = c.take<uint32_t>(2 * N);
+  im.ranges = c.take<uint2>(tiles);
+  if (bytes) *bytes = c.used + 128;
+  return im;
+}
+
+// Scratch handed in by the caller may start at any address; carve from the next
+// 128-B boundary (the carve sizes include that slack).
+static inline void* align128(const void* p) {
+  return reinterpret_cast<void*>((reinterpret_cast<uintptr_t>(p) + 127) & ~uintptr_t(127));
+}
+
+static int check_fwd(const b200gs_surfel_fwd* a) {
+  if (!a) { set_error("null argument struct"); return B200GS_EINVAL; }
+  if (a->P < 0 || a->width <= 0 || a->height <= 0) { set_error("bad sizes P=%d W=%d H=%d", a->P, a->width, a->height); return B200GS_EINVAL; }
+  if ((a->shs == nullptr) == (a->colors_precomp == nullptr)) {
+    set_error("provide exactly one of shs / colors_precomp"); return B200GS_EINVAL; }
+  const bool sr = a->scales && a->rotations;
+  if (sr == (a->transMat_precomp != nullptr) || (!sr && (a->scales || a->rotations))) {
+    set_error("provide exactly one of scale/rotation pair or transMat_precomp"); return B200GS_EINVAL; }
+  if (a->shs && (a->sh_degree < 0 || a->sh_degree > 3 || (a->sh_degree + 1) * (a->sh_degree + 1) > a->sh_coeffs)) {
+    set_error("sh_degree %d needs %d coefficients, shs has %d", a->sh_degree, (a->sh_degree + 1) * (a->sh_degree + 1), a->sh_coeffs);
+    return B200GS_EINVAL; }
+  if (!a->means3D || !a->opacities || !a->viewmatrix || !a->projmatrix || !a->campos || !a->background) {
+    set_error("missing required input pointer"); return B200GS_EINVAL; }
+  if (!a->out_color || !a->out_others || !a->out_refl || !a->radii || !a->gaussian_weights || !a->geom || !a->img) {
+    set_error("missing output / scratch pointer"); return B200GS_EINVAL; }
+  if (a->geom_bytes < b200gs_surfel_geom_bytes(a->P) || a->img_bytes < b200gs_surfel_image_bytes(a->width, a->height)) {
+    set_error("geom/img scratch too small"); return B200GS_ESIZE; }
+  return B200GS_OK;
+}
+
+}  // namespace b200gs
+
+using namespace b200gs;
+
+extern "C" {
+
+const char* b200gs_last_error(void) { return t_err; }
+int b200gs_version(void) { return 1; }
+int b200gs_sm_arch(void) { return 100; }
+unsigned long long b200gs_launch_count(void) { return g_launches.load(); }
+
+size_t b200gs_surfel_geom_bytes(int P) {
+  size_t b = 0;
+  SurfelGeom::carve(nullptr, (size_t)(P > 0 ? P : 0), &b);
+  return b;
+}
+size_t b200gs_surfel_image_bytes(int width, int height) {
+  size_t b = 0;
+  SurfelImage::carve(nullptr, width, height, &b);
+  return b;
+}
+size_t b200gs_binning_bytes(int num_rendered) {
+  size_t b = 0;
+  Binning::carve(nullptr, (size_t)(num_rendered > 0 ? num_rendered : 0), &b);
+  return b;
+}
+size_t b200gs_surfel_accum_bytes(int P) { return (size_t)(P > 0 ? P : 0) * ACC_STRIDE * sizeof(float) + 128; }
+
+int b200gs_surfel_forward_stage1(const b200gs_surfel_fwd* a, int* num_rendered, void* stream) {
+  int rc = check_fwd(a);
+  if (rc) return rc;
+  if (!num_rendered) { set_error("num_rendered is null"); return B200GS_EINVAL; }
+  cudaStream_t s = (cudaStream_t)stream;
+  *num_rendered = 0;
+  if (a->P == 0) return B200GS_OK;
+  SurfelGeom g = SurfelGeom::carve(align128(a->geom), a->P, nullptr);
+  rc = surfel_preprocess(*a, g, s);
+  if (rc) return rc;
+  rc = inclusive_scan_u32(g.tiles_touched, g.point_offsets, a->P, g.scan_state, s, a->debug != 0);
+  if (rc) return rc;
+  int host[2] = {0, 0};
+  B200GS_CUDA(cudaMemcpyAsync(&host[0], g.point_offsets + a->P - 1, sizeof(int), cudaMemcpyDeviceToHost, s));
+  B200GS_CUDA(cudaMemcpyAsync(&host[1], g.flags, sizeof(int), cudaMemcpyDeviceToHost, s));
+  B200GS_CUDA(cudaStreamSynchronize(s));
+  *num_rendered = host[0];
+  if (host[1]) { set_error("Point is filtered although prefiltered is set. This shouldn't happen!"); return B200GS_EINVAL; }
+  return B200GS_OK;
+}
+
+int b200gs_surfel_forward_stage2(const b200gs_surfel_fwd* a, int R, void* stream) {
+  int rc = check_fwd(a);
+  if (rc) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (a->P == 0) return B200GS_OK;
+  if (R < 0) { set_error("negative num_rendered"); return B200GS_EINVAL; }
+  if (R > 0 && (!a->binning || a->binning_bytes < b200gs_binning_bytes(R))) { set_error("binning scratch too small"); return B200GS_ESIZE; }
+  SurfelGeom g = SurfelGeom::carve(align128(a->geom), a->P, nullptr);
+  SurfelImage im = SurfelImage::carve(align128(a->img), a->width, a->height, nullptr);
+  Binning b = Binning::carve(R > 0 ? align128(a->binning) : nullptr, R, nullptr);
+  rc = bin_and_sort(g.depths, g.rects, g.point_offsets, a->P, R, a->width, a->height, b, im.ranges, s, a->debug != 0);
+  if (rc) return rc;
+  return surfel_composite_forward(*a, g, im, b, s);
+}
+
+int b200gs_surfel_backward(const b200gs_surfel_bwd* a, void* stream) {
+  if (!a) { set_error("null argument struct"); return B200GS_EINVAL; }
+  cudaStream_t s = (cudaStream_t)stream;
+  if (a->P <= 0) return B200GS_OK;
+  if (!a->geom || !a->img || !a->accum || a->accum_bytes < b200gs_surfel_accum_bytes(a->P)) {
+    set_error("missing scratch / accum too small"); return B200GS_ESIZE; }
+  if (!a->dL_dout_color || !a->dL_dout_others || !a->dL_dmeans2D || !a->dL_dnormal || !a->dL_dopacity || !a->dL_dcolors ||
+      !a->dL_dmeans3D || !a->dL_dtransMat || !a->dL_dscales || !a->dL_drotations || !a->radii || !a->means3D) {
+    set_error("missing gradient pointer"); return B200GS_EINVAL; }
+  SurfelGeom g = SurfelGeom::carve(align128(a->geom), a->P, nullptr);
+  SurfelImage im = SurfelImage::carve(align128(a->img), a->width, a->height, nullptr);
+  Binning b = Binning::carve(a->num_rendered > 0 ? align128(a->binning) : nullptr, a->num_rendered > 0 ? a->num_rendered : 0, nullptr);
+  float* acc = reinterpret_cast<float*>(align128(a->accum));
+  int rc = surfel_composite_backward(*a, g, im, b, acc, s);
+  if (rc) return rc;
+  return surfel_preprocess_backward(*a, g, acc, s);
+}
+
+}  // extern "C"

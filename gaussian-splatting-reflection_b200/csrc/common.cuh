@@ -1,0 +1,153 @@
+// common.cuh -- shared device helpers, scratch layouts and error plumbing of
+// libb200gs (sm_100a).  Not part of the public ABI (that is include/b200gs.h).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+#include <atomic>
+#include "../../include/b200gs.h"
+
+namespace b200gs {
+
+// ---------------------------------------------------------------- constants
+// Tile = 16x16 pixels (S/cuda_rasterizer/config.h:15-17).
+constexpr int TILE_X = 16;
+constexpr int TILE_Y = 16;
+constexpr int TILE_PIX = TILE_X * TILE_Y;
+// S/cuda_rasterizer/auxiliary.h:41-44
+constexpr float NEAR_N = 0.2f;
+constexpr float FAR_N = 100.0f;
+constexpr float FILTER_INV_SQUARE = 2.0f;
+
+// ---------------------------------------------------------------- errors
+void set_error(const char* fmt, ...);
+int cuda_fail(cudaError_t e, const char* what);
+extern std::atomic<unsigned long long> g_launches;
+
+#define B200GS_CUDA(expr)                                          \
+  do {                                                             \
+    cudaError_t _e = (expr);                                       \
+    if (_e != cudaSuccess) return ::b200gs::cuda_fail(_e, #expr);  \
+  } while (0)
+
+// After a kernel launch: count it, pick up launch errors; in debug mode also
+// drain the stream (the reference's CHECK_CUDA, S/cuda_rasterizer/auxiliary.h:300-307).
+#define B200GS_LAUNCHED(what, debug, stream)                                   \
+  do {                                                                         \
+    ::b200gs::g_launches.fetch_add(1, std::memory_order_relaxed);              \
+    cudaError_t _e = cudaGetLastError();                                       \
+    if (_e == cudaSuccess && (debug)) _e = cudaStreamSynchronize(stream);      \
+    if (_e != cudaSuccess) return ::b200gs::cuda_fail(_e, what);               \
+  } while (0)
+
+// ---------------------------------------------------------------- scratch carving
+// Same idea as the reference's obtain() (S/cuda_rasterizer/rasterizer_impl.h:21-27):
+// carve typed arrays out of one byte buffer, each start aligned.
+struct Carver {
+  char* p;
+  size_t used;
+  explicit Carver(void* base) : p(reinterpret_cast<char*>(base)), used(0) {}
+  template <typename T>
+  T* take(size_t count, size_t align = 128) {
+    used = (used + align - 1) / align * align;
+    T* r = p ? reinterpret_cast<T*>(p + used) : nullptr;
+    used += count * sizeof(T);
+    return r;
+  }
+};
+
+// Per-Gaussian packed record written by preprocess and staged (5 x 16 B) by the
+// compositing kernels.  80 B, 16-B aligned.
+//   q0 = Tu.x Tu.y Tu.z Tv.x      q1 = Tv.y Tv.z Tw.x Tw.y
+//   q2 = Tw.z xy.x xy.y opacity   q3 = n.x  n.y  n.z  refl
+//   q4 = r    g    b    mask(float 0/1)
+struct __align__(16) SurfelRec {
+  float4 q[5];
+};
+static_assert(sizeof(SurfelRec) == 80, "record must be 80 B");
+
+struct SurfelGeom {
+  float* depths;            // [P]
+  uint32_t* tiles_touched;  // [P]
+  uint32_t* point_offsets;  // [P] inclusive prefix sum
+  uint8_t* clamped;         // [P] bit c = colour channel c clamped at 0
+  uint2* rects;             // [P] tile rect: x = x0 | x1<<16, y = y0 | y1<<16 (only valid if tiles_touched>0)
+  SurfelRec* rec;           // [P]
+  uint32_t* scan_state;     // decoupled look-back tile states
+  int* flags;               // [4] error flags (prefiltered violation, ...)
+  static SurfelGeom carve(void* base, size_t P, size_t* bytes);
+};
+
+struct SurfelImage {
+  float* accum;        // [3,N]: final T, M1, M2
+  uint32_t* n_contrib; // [2,N]: last contributor, median contributor
+  uint2* ranges;       // [tiles]
+  static SurfelImage carve(void* base, int W, int H, size_t* bytes);
+};
+
+struct Binning {
+  uint32_t* point_list;           // [R] sorted Gaussian ids
+  uint32_t* point_list_unsorted;  // [R]
+  uint64_t* keys;                 // [R] sorted keys
+  uint64_t* keys_unsorted;        // [R]
+  void* sort_temp;
+  size_t sort_temp_bytes;
+  static Binning carve(void* base, size_t R, size_t* bytes);
+};
+
+// Backward accumulator: 20 floats per Gaussian, one contiguous 80-B segment so a
+// (tile, Gaussian) partial is flushed with one vector of RED.ADD.F32.
+//   0..8 dL_dtransMat   9,10 dL_dmean2D.xy   11 dL_dopacity
+//   12..14 dL_dcolor    15 dL_drefl          16..18 dL_dnormal   19 pad
+constexpr int ACC_STRIDE = 20;
+
+// ---------------------------------------------------------------- device helpers
+__device__ __forceinline__ int imin(int a, int b) { return a < b ? a : b; }
+__device__ __forceinline__ int imax(int a, int b) { return a > b ? a : b; }
+
+// getRect (S/cuda_rasterizer/auxiliary.h:71-81), with the exact fp32 operation
+// order nvcc emits for it: (p - r) * (1/16) and ((p + r) + 16) + (-1)) * (1/16),
+// truncation toward zero, clamp to [0, grid].
+__device__ __forceinline__ void get_rect(float px, float py, int radius, int gx, int gy,
+                                         int& x0, int& y0, int& x1, int& y1) {
+  const float r = (float)radius;
+  x0 = imin(gx, imax(0, (int)__fmul_rn(__fsub_rn(px, r), 0.0625f)));
+  y0 = imin(gy, imax(0, (int)__fmul_rn(__fsub_rn(py, r), 0.0625f)));
+  x1 = imin(gx, imax(0, (int)__fmul_rn(__fadd_rn(__fadd_rn(__fadd_rn(px, r), 16.0f), -1.0f), 0.0625f)));
+  y1 = imin(gy, imax(0, (int)__fmul_rn(__fadd_rn(__fadd_rn(__fadd_rn(py, r), 16.0f), -1.0f), 0.0625f)));
+}
+
+// transformPoint4x3 / transformVec4x3 (S/cuda_rasterizer/auxiliary.h:83-112) with
+// the contraction the reference build has:  m12 + fma(z,m8, fma(x,m0, y*m4)).
+__device__ __forceinline__ float dot3_ref(float x, float m0, float y, float m4, float z, float m8) {
+  return __fmaf_rn(z, m8, __fmaf_rn(x, m0, __fmul_rn(y, m4)));
+}
+
+// SH basis constants (S/cuda_rasterizer/auxiliary.h:46-64).
+__device__ constexpr float SH_C0 = 0.28209479177387814f;
+__device__ constexpr float SH_C1 = 0.4886025119029199f;
+__device__ constexpr float SH_C2_0 = 1.0925484305920792f;
+__device__ constexpr float SH_C2_1 = -1.0925484305920792f;
+__device__ constexpr float SH_C2_2 = 0.31539156525252005f;
+__device__ constexpr float SH_C2_3 = -1.0925484305920792f;
+__device__ constexpr float SH_C2_4 = 0.5462742152960396f;
+__device__ constexpr float SH_C3_0 = -0.5900435899266435f;
+__device__ constexpr float SH_C3_1 = 2.890611442640554f;
+__device__ constexpr float SH_C3_2 = -0.4570457994644658f;
+__device__ constexpr float SH_C3_3 = 0.3731763325901154f;
+__device__ constexpr float SH_C3_4 = -0.4570457994644658f;
+__device__ constexpr float SH_C3_5 = 1.445305721320277f;
+__device__ constexpr float SH_C3_6 = -0.5900435899266435f;
+
+// ---------------------------------------------------------------- stage launchers (internal)
+int surfel_preprocess(const b200gs_surfel_fwd& a, const SurfelGeom& g, cudaStream_t s);
+int inclusive_scan_u32(const uint32_t* in, uint32_t* out, int n, uint32_t* state, cudaStream_t s, bool debug);
+int bin_and_sort(const float* depths, const uint2* rects, const uint32_t* offsets,
+                 int P, int R, int W, int H, const Binning& b, uint2* ranges, cudaStream_t s, bool debug);
+int surfel_composite_forward(const b200gs_surfel_fwd& a, const SurfelGeom& g, const SurfelImage& im,
+                             const Binning& b, cudaStream_t s);
+int surfel_composite_backward(const b200gs_surfel_bwd& a, const SurfelGeom& g, const SurfelImage& im,
+                              const Binning& b, float* acc, cudaStream_t s);
+int surfel_preprocess_backward(const b200gs_surfel_bwd& a, const SurfelGeom& g, const float* acc, cudaStream_t s);
+
+}  // namespace b200gs

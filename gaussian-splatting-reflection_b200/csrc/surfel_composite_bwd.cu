@@ -1,0 +1,244 @@
+// surfel_composite_bwd.cu -- K4s: reverse-order (back-to-front) backward of the
+// surfel compositing.
+//
+// Restates BACKWARD::renderCUDA (S/cuda_rasterizer/backward.cu:143-470).  Same
+// tiling and staging as the forward kernel.  Where the reference issues up to 17
+// global atomicAdds per contributing (pixel, Gaussian) pair, this kernel keeps
+// the per-pixel recurrences in registers, forms the 19 per-Gaussian partials of
+// every lane, and sums them over the warp with a 21-shuffle recursive-halving
+// reduce-scatter, so that 19 lanes each own one component and flush the warp's
+// contribution with ONE vector RED.ADD.F32 into a contiguous 80-B accumulator
+// row (ACC_STRIDE floats per Gaussian).  Warps none of whose pixels touch a
+// Gaussian skip the reduction altogether.
+#include "surfel_composite.cuh"
+
+namespace b200gs {
+
+struct CompBwdArgs {
+  int W, H, gx;
+  const uint2* ranges;
+  const uint32_t* point_list;
+  const SurfelRec* rec;
+  const float* bg;
+  const float* accum;         // [3,N] final T, M1, M2
+  const uint32_t* n_contrib;  // [2,N]
+  const float* dL_dpix;       // [3,N]
+  const float* dL_dothers;    // [8,N]
+  const float* dL_drefl;      // [N] or NULL
+  float* acc;                 // [P, ACC_STRIDE]
+};
+
+constexpr int BATCH = 256;
+
+// One recursive-halving step: lanes whose `m` bit is set keep the upper half.
+template <int H>
+__device__ __forceinline__ void rs_step(float* v, int m, bool upper) {
+#pragma unroll
+  for (int i = 0; i < H; ++i) {
+    const float send = upper ? v[i] : v[i + H];
+    const float keep = upper ? v[i + H] : v[i];
+    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, m);
+  }
+}
+
+__global__ void __launch_bounds__(BATCH, 2) surfel_composite_bwd_kernel(const CompBwdArgs a) {
+  __shared__ SurfelRec s_rec[2][BATCH];
+  __shared__ int s_id[2][BATCH];
+
+  const int t = threadIdx.x, lane = t & 31;
+  const int tile = blockIdx.x;
+  const int tile_x = tile % a.gx, tile_y = tile / a.gx;
+  int lx, ly;
+  tile_pixel(t, lx, ly);
+  const int pxi = tile_x * TILE_X + lx, pyi = tile_y * TILE_Y + ly;
+  const bool inside = pxi < a.W && pyi < a.H;
+  const float fx = (float)pxi, fy = (float)pyi;
+  const size_t N = (size_t)a.W * a.H;
+  const size_t pix_id = (size_t)a.W * pyi + pxi;
+
+  const uint2 range = a.ranges[tile];
+  const int n = (int)(range.y - range.x);
+  const int rounds = (n + BATCH - 1) / BATCH;
+  if (n == 0) return;
+
+  // lane -> accumulator component owned after the reduce-scatter
+  const int b16 = (lane >> 4) & 1, b8 = (lane >> 3) & 1, b4 = (lane >> 2) & 1, b2 = (lane >> 1) & 1, b1 = lane & 1;
+  const int loc3 = b2 * 2 + b1, loc5 = b4 * 3 + loc3;
+  const int comp = b16 * 10 + b8 * 5 + loc5;
+  const bool comp_valid = loc3 <= 2 && loc5 <= 4 && comp < 19;
+
+  const float T_final = inside ? a.accum[pix_id] : 0.0f;
+  float T = T_final;
+  uint32_t contributor = (uint32_t)n;
+  const uint32_t last_contributor = inside ? a.n_contrib[pix_id] : 0u;
+  const uint32_t median_contributor = inside ? a.n_contrib[pix_id + N] : 0u;
+  const float final_D = inside ? a.accum[pix_id + N] : 0.0f;
+  const float final_D2 = inside ? a.accum[pix_id + 2 * N] : 0.0f;
+  const float final_A = 1.0f - T_final;
+
+  float dpix0 = 0.f, dpix1 = 0.f, dpix2 = 0.f, drefl = 0.f;
+  float ddepth = 0.f, daccum = 0.f, dreg = 0.f, dn0 = 0.f, dn1 = 0.f, dn2 = 0.f, dmedian = 0.f;
+  if (inside) {
+    dpix0 = a.dL_dpix[pix_id]; dpix1 = a.dL_dpix[pix_id + N]; dpix2 = a.dL_dpix[pix_id + 2 * N];
+    drefl = a.dL_drefl ? a.dL_drefl[pix_id] : 0.0f;
+    ddepth = a.dL_dothers[pix_id + 0 * N];
+    daccum = a.dL_dothers[pix_id + 1 * N];
+    dn0 = a.dL_dothers[pix_id + 2 * N]; dn1 = a.dL_dothers[pix_id + 3 * N]; dn2 = a.dL_dothers[pix_id + 4 * N];
+    dmedian = a.dL_dothers[pix_id + 5 * N];
+    dreg = a.dL_dothers[pix_id + 6 * N];
+  }
+  float bg_dot_dpixel = 0.0f;
+  bg_dot_dpixel += a.bg[0] * dpix0;
+  bg_dot_dpixel += a.bg[1] * dpix1;
+  bg_dot_dpixel += a.bg[2] * dpix2;
+
+  float acc_c0 = 0.f, acc_c1 = 0.f, acc_c2 = 0.f, last_c0 = 0.f, last_c1 = 0.f, last_c2 = 0.f;
+  float acc_refl = 0.f, last_refl = 0.f;
+  float last_depth = 0.f, acc_depth = 0.f, acc_alpha = 0.f;
+  float acc_n0 = 0.f, acc_n1 = 0.f, acc_n2 = 0.f, last_n0 = 0.f, last_n1 = 0.f, last_n2 = 0.f;
+  float last_dL_dT = 0.f, last_alpha = 0.f;
+
+  // The reference leaves the entry loop per thread (`!done`); here `done` pixels
+  // (outside the image) simply never contribute.
+  const bool live = inside;
+
+  const uint32_t* pl = a.point_list + range.x;
+  auto stage = [&](int buf, int id) {
+    if (id >= 0) {
+      const SurfelRec* g = a.rec + id;
+      SurfelRec* d = &s_rec[buf][t];
+#pragma unroll
+      for (int k = 0; k < 5; ++k) cp_async16(&d->q[k], &g->q[k]);
+      s_id[buf][t] = id;
+    }
+    cp_async_commit();
+  };
+  int id_next = (t < n) ? (int)pl[n - 1 - t] : -1;
+  stage(0, id_next);
+  id_next = (BATCH + t < n) ? (int)pl[n - 1 - (BATCH + t)] : -1;
+
+  // Warps whose pixels all have last_contributor == 0 have nothing to do, but they
+  // still take part in the staging and barriers.
+  const uint32_t warp_last = __reduce_max_sync(0xffffffffu, live ? last_contributor : 0u);
+
+  for (int i = 0; i < rounds; ++i) {
+    cp_async_wait_all();
+    __syncthreads();
+    if (i + 1 < rounds) {
+      stage((i + 1) & 1, id_next);
+      const int nx = (i + 2) * BATCH + t;
+      id_next = (nx < n) ? (int)pl[n - 1 - nx] : -1;
+    }
+    const int buf = i & 1;
+    const int count = min(BATCH, n - i * BATCH);
+    const SurfelRec* rb = s_rec[buf];
+    // entries behind every pixel's last contributor: skip the whole prefix at once
+    int j0 = 0;
+    {
+      const int first_pos = n - i * BATCH;  // `contributor` value before this batch
+      if ((uint32_t)first_pos > warp_last) j0 = min(count, first_pos - (int)warp_last);
+    }
+    contributor -= (uint32_t)j0;
+    for (int j = j0; j < count; ++j) {
+      contributor--;
+      const float4 q0 = rb[j].q[0], q1 = rb[j].q[1], q2 = rb[j].q[2];
+      SurfelHit h;
+      bool c = live && contributor < last_contributor;
+      c = surfel_eval<true>(q0, q1, q2, fx, fy, h) && c;
+      if (!__any_sync(0xffffffffu, c)) continue;
+
+      float g[20];
+#pragma unroll
+      for (int k = 0; k < 20; ++k) g[k] = 0.0f;
+      if (c) {
+        const float4 q3 = rb[j].q[3], q4 = rb[j].q[4];
+        const float alpha = h.alpha, G = h.G;
+        T = __fdiv_rn(T, __fsub_rn(1.0f, alpha));
+        const float w = alpha * T;
+        float dL_dalpha = 0.0f;
+        const float om = 1.0f - last_alpha;
+        // colour (backward.cu:346-359)
+        acc_c0 = last_alpha * last_c0 + om * acc_c0; last_c0 = q4.x; dL_dalpha += (q4.x - acc_c0) * dpix0; g[12] = w * dpix0;
+        acc_c1 = last_alpha * last_c1 + om * acc_c1; last_c1 = q4.y; dL_dalpha += (q4.y - acc_c1) * dpix1; g[13] = w * dpix1;
+        acc_c2 = last_alpha * last_c2 + om * acc_c2; last_c2 = q4.z; dL_dalpha += (q4.z - acc_c2) * dpix2; g[14] = w * dpix2;
+        // reflection strength (:361-364)
+        acc_refl = last_alpha * last_refl + om * acc_refl; last_refl = q3.w;
+        dL_dalpha += (q3.w - acc_refl) * drefl; g[15] = w * drefl;
+        // distortion / depth / alpha / normal (:366-402)
+        const float c_d = h.depth;
+        const float m_d = ndc_depth(c_d);
+        const float dmd_dd = (FAR_N * NEAR_N) / ((FAR_N - NEAR_N) * c_d * c_d);
+        float dL_dz = 0.0f;
+        if (contributor == median_contributor - 1u) dL_dz += dmedian;
+        const float dL_dweight = (final_D2 + m_d * m_d * final_A - 2.0f * m_d * final_D) * dreg;
+        dL_dalpha += dL_dweight - last_dL_dT;
+        last_dL_dT = dL_dweight * alpha + (1.0f - alpha) * last_dL_dT;
+        const float dL_dmd = 2.0f * (T * alpha) * (m_d * final_A - final_D) * dreg;
+        dL_dz += dL_dmd * dmd_dd;
+        acc_depth = last_alpha * last_depth + om * acc_depth; last_depth = c_d;
+        dL_dalpha += (c_d - acc_depth) * ddepth;
+        acc_alpha = last_alpha + om * acc_alpha;
+        dL_dalpha += (1.0f - acc_alpha) * daccum;
+        acc_n0 = last_alpha * last_n0 + om * acc_n0; last_n0 = q3.x; dL_dalpha += (q3.x - acc_n0) * dn0; g[16] = w * dn0;
+        acc_n1 = last_alpha * last_n1 + om * acc_n1; last_n1 = q3.y; dL_dalpha += (q3.y - acc_n1) * dn1; g[17] = w * dn1;
+        acc_n2 = last_alpha * last_n2 + om * acc_n2; last_n2 = q3.z; dL_dalpha += (q3.z - acc_n2) * dn2; g[18] = w * dn2;
+
+        dL_dalpha *= T;
+        last_alpha = alpha;
+        dL_dalpha += (-T_final / (1.0f - alpha)) * bg_dot_dpixel;  // :411-414
+        const float dL_dG = h.opa * dL_dalpha;
+        dL_dz += w * ddepth;
+        if (h.rho3d <= h.rho2d) {  // :423-453
+          const float dsx = dL_dG * -G * h.sx + dL_dz * h.Twx;
+          const float dsy = dL_dG * -G * h.sy + dL_dz * h.Twy;
+          const float dsx_pz = dsx / h.pz, dsy_pz = dsy / h.pz;
+          const float dpx = dsx_pz, dpy = dsy_pz, dpz = -(dsx_pz * h.sx + dsy_pz * h.sy);
+          // dL_dk = cross(l, dL_dp), dL_dl = cross(dL_dp, k)
+          const float dkx = h.ly * dpz - h.lz * dpy, dky = h.lz * dpx - h.lx * dpz, dkz = h.lx * dpy - h.ly * dpx;
+          const float dlx = dpy * h.kz - dpz * h.ky, dly = dpz * h.kx - dpx * h.kz, dlz = dpx * h.ky - dpy * h.kx;
+          g[0] = -dkx; g[1] = -dky; g[2] = -dkz;
+          g[3] = -dlx; g[4] = -dly; g[5] = -dlz;
+          g[6] = fx * dkx + fy * dlx + dL_dz * h.sx;
+          g[7] = fx * dky + fy * dly + dL_dz * h.sy;
+          g[8] = fx * dkz + fy * dlz + dL_dz * 1.0f;
+        } else {  // :454-464
+          g[9] = dL_dG * (-G * FILTER_INV_SQUARE * h.dx);
+          g[10] = dL_dG * (-G * FILTER_INV_SQUARE * h.dy);
+          g[6] = h.sx * dL_dz;
+          g[7] = h.sy * dL_dz;
+          g[8] = dL_dz;
+        }
+        g[11] = G * dL_dalpha;  // :467
+      }
+
+      // warp reduce-scatter 20 -> 10 -> 5 -> 3 -> 2 -> 1
+      rs_step<10>(g, 16, b16);
+      rs_step<5>(g, 8, b8);
+      g[5] = 0.0f;
+      rs_step<3>(g, 4, b4);
+      g[3] = 0.0f;
+      rs_step<2>(g, 2, b2);
+      rs_step<1>(g, 1, b1);
+      if (comp_valid) atomicAdd(a.acc + (size_t)s_id[buf][j] * ACC_STRIDE + comp, g[0]);
+    }
+  }
+  cp_async_wait_all();
+}
+
+int surfel_composite_backward(const b200gs_surfel_bwd& f, const SurfelGeom& g, const SurfelImage& im, const Binning& b,
+                              float* acc, cudaStream_t s) {
+  CompBwdArgs a;
+  a.W = f.width; a.H = f.height;
+  a.gx = (f.width + TILE_X - 1) / TILE_X;
+  const int gy = (f.height + TILE_Y - 1) / TILE_Y;
+  a.ranges = im.ranges; a.point_list = b.point_list; a.rec = g.rec; a.bg = f.background;
+  a.accum = im.accum; a.n_contrib = im.n_contrib;
+  a.dL_dpix = f.dL_dout_color; a.dL_dothers = f.dL_dout_others; a.dL_drefl = f.dL_dout_refl;
+  a.acc = acc;
+  B200GS_CUDA(cudaMemsetAsync(acc, 0, (size_t)f.P * ACC_STRIDE * sizeof(float), s));
+  surfel_composite_bwd_kernel<<<a.gx * gy, BATCH, 0, s>>>(a);
+  B200GS_LAUNCHED("surfel_composite_bwd_kernel", f.debug, s);
+  return B200GS_OK;
+}
+
+}  // namespace b200gs

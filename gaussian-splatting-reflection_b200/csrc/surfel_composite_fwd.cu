@@ -1,0 +1,180 @@
+// surfel_composite_fwd.cu -- K3s: per-tile front-to-back compositing of colour,
+// reflection strength and the 8 auxiliary planes of the surfel path.
+//
+// Restates FORWARD::renderCUDA (S/cuda_rasterizer/forward.cu:258-489).  One CTA
+// per 16x16 tile, one pixel per thread.  Batches of 256 packed 80-B Gaussian
+// records are gathered with cp.async into a double-buffered shared-memory ring
+// (the gather of batch i+1 and the id load of batch i+2 overlap the blending of
+// batch i); the inner loop is warp-synchronous so whole warps leave as soon as
+// all their pixels are saturated, and the per-Gaussian max blending weight is
+// reduced with redux.sync + one shared atomicMax per (warp, Gaussian) instead of
+// the reference's racy global compare/exchange per pixel.
+#include "surfel_composite.cuh"
+
+namespace b200gs {
+
+struct CompFwdArgs {
+  int W, H, gx;
+  const uint2* ranges;
+  const uint32_t* point_list;
+  const SurfelRec* rec;
+  const float* bg;
+  float* accum;         // [3,N]
+  uint32_t* n_contrib;  // [2,N]
+  float* out_color;
+  float* out_others;
+  float* out_refl;
+  float* gaussian_weights;
+};
+
+constexpr int BATCH = 256;
+
+__global__ void __launch_bounds__(BATCH) surfel_composite_fwd_kernel(const CompFwdArgs a) {
+  __shared__ SurfelRec s_rec[2][BATCH];
+  __shared__ int s_id[2][BATCH];
+  __shared__ int s_wmax[2][BATCH];
+
+  const int t = threadIdx.x, lane = t & 31;
+  const int tile = blockIdx.x;
+  const int tile_x = tile % a.gx, tile_y = tile / a.gx;
+  int lx, ly;
+  tile_pixel(t, lx, ly);
+  const int pxi = tile_x * TILE_X + lx, pyi = tile_y * TILE_Y + ly;
+  const bool inside = pxi < a.W && pyi < a.H;
+  const float fx = (float)pxi, fy = (float)pyi;
+  const size_t N = (size_t)a.W * a.H;
+  const size_t pix_id = (size_t)a.W * pyi + pxi;
+
+  const uint2 range = a.ranges[tile];
+  const int n = (int)(range.y - range.x);
+  const int rounds = (n + BATCH - 1) / BATCH;
+
+  bool done = !inside;
+  float T = 1.0f;
+  uint32_t contributor = 0, last_contributor = 0;
+  float C0 = 0.f, C1 = 0.f, C2 = 0.f, refl = 0.f, mask = 0.f;
+  float N0 = 0.f, N1 = 0.f, N2 = 0.f, D = 0.f, M1 = 0.f, M2 = 0.f, distortion = 0.f, median_depth = 0.f;
+  float median_contributor = -1.0f;
+
+  s_wmax[0][t] = 0;
+  s_wmax[1][t] = 0;
+
+  const uint32_t* pl = a.point_list + range.x;
+  auto stage = [&](int buf, int id) {
+    if (id >= 0) {
+      const SurfelRec* g = a.rec + id;
+      SurfelRec* d = &s_rec[buf][t];
+#pragma unroll
+      for (int k = 0; k < 5; ++k) cp_async16(&d->q[k], &g->q[k]);
+      s_id[buf][t] = id;
+    }
+    cp_async_commit();
+  };
+  int id_next = (t < n) ? (int)pl[t] : -1;
+  stage(0, id_next);
+  id_next = (BATCH + t < n) ? (int)pl[BATCH + t] : -1;
+
+  int last_batch = -1;
+  for (int i = 0; i < rounds; ++i) {
+    cp_async_wait_all();
+    // batch i has landed for everyone, and everyone is past batch i-1
+    if (__syncthreads_count(done) == BATCH) break;
+    if (i > 0) {  // publish and clear the per-Gaussian weight maxima of batch i-1
+      const int b = (i - 1) & 1;
+      const int v = s_wmax[b][t];
+      if (v > 0) { atomicMax(reinterpret_cast<int*>(a.gaussian_weights) + s_id[b][t], v); s_wmax[b][t] = 0; }
+    }
+    if (i + 1 < rounds) {
+      stage((i + 1) & 1, id_next);
+      const int nx = (i + 2) * BATCH + t;
+      id_next = (nx < n) ? (int)pl[nx] : -1;
+    }
+    last_batch = i;
+    const int buf = i & 1;
+    const int count = min(BATCH, n - i * BATCH);
+    const SurfelRec* rb = s_rec[buf];
+    for (int j = 0; j < count; ++j) {
+      if (__all_sync(0xffffffffu, done)) break;
+      contributor++;  // for finished pixels this is never read again
+      const float4 q0 = rb[j].q[0], q1 = rb[j].q[1], q2 = rb[j].q[2];
+      SurfelHit h;
+      bool c = surfel_eval<false>(q0, q1, q2, fx, fy, h) && !done;
+      float w = 0.0f;
+      if (c) {
+        const float test_T = __fmul_rn(T, __fsub_rn(1.0f, h.alpha));
+        if (test_T < 0.0001f) {
+          done = true;
+          c = false;
+        } else {
+          const float4 q3 = rb[j].q[3], q4 = rb[j].q[4];
+          w = __fmul_rn(T, h.alpha);
+          const float A = __fsub_rn(1.0f, T);
+          const float m = ndc_depth(h.depth);
+          const float mm = __fmul_rn(m, m);
+          // distortion += (m*m*A + M2 - 2*m*M1) * w   (forward.cu:424)
+          const float e = __fsub_rn(__fmaf_rn(A, mm, M2), __fmul_rn(M1, __fadd_rn(m, m)));
+          distortion = __fmaf_rn(e, w, distortion);
+          D = __fmaf_rn(h.depth, w, D);
+          M1 = __fmaf_rn(m, w, M1);
+          M2 = __fmaf_rn(mm, w, M2);
+          if (T > 0.5f) { median_depth = h.depth; median_contributor = (float)contributor; }
+          N0 = __fmaf_rn(w, q3.x, N0); N1 = __fmaf_rn(w, q3.y, N1); N2 = __fmaf_rn(w, q3.z, N2);
+          C0 = __fmaf_rn(w, q4.x, C0); C1 = __fmaf_rn(w, q4.y, C1); C2 = __fmaf_rn(w, q4.z, C2);
+          refl = __fmaf_rn(w, q3.w, refl);
+          if (q4.w != 0.0f) mask = 1.0f;
+          T = test_T;
+          last_contributor = contributor;
+        }
+      }
+      // gaussian_weights[id] = max over pixels of w  (forward.cu:457-459, made exact)
+      if (__any_sync(0xffffffffu, c)) {
+        const int wm = __reduce_max_sync(0xffffffffu, __float_as_int(w));
+        if (lane == 0) atomicMax(&s_wmax[buf][j], wm);
+      }
+    }
+  }
+  __syncthreads();
+  if (last_batch >= 0) {
+    const int b = last_batch & 1;
+    const int v = s_wmax[b][t];
+    if (v > 0) atomicMax(reinterpret_cast<int*>(a.gaussian_weights) + s_id[b][t], v);
+  }
+  cp_async_wait_all();
+
+  if (inside) {  // forward.cu:465-488
+    a.accum[pix_id] = T;
+    a.accum[pix_id + N] = M1;
+    a.accum[pix_id + 2 * N] = M2;
+    a.n_contrib[pix_id] = last_contributor;
+    a.n_contrib[pix_id + N] = (uint32_t)median_contributor;  // -1 saturates to 0 (cvt.rzi.u32.f32)
+    a.out_color[pix_id] = __fmaf_rn(T, a.bg[0], C0);
+    a.out_color[pix_id + N] = __fmaf_rn(T, a.bg[1], C1);
+    a.out_color[pix_id + 2 * N] = __fmaf_rn(T, a.bg[2], C2);
+    a.out_refl[pix_id] = refl;
+    a.out_others[pix_id + 0 * N] = D;
+    a.out_others[pix_id + 1 * N] = __fsub_rn(1.0f, T);
+    a.out_others[pix_id + 2 * N] = N0;
+    a.out_others[pix_id + 3 * N] = N1;
+    a.out_others[pix_id + 4 * N] = N2;
+    a.out_others[pix_id + 5 * N] = median_depth;
+    a.out_others[pix_id + 6 * N] = distortion;
+    a.out_others[pix_id + 7 * N] = mask;
+  }
+}
+
+int surfel_composite_forward(const b200gs_surfel_fwd& f, const SurfelGeom& g, const SurfelImage& im, const Binning& b,
+                             cudaStream_t s) {
+  CompFwdArgs a;
+  a.W = f.width; a.H = f.height;
+  a.gx = (f.width + TILE_X - 1) / TILE_X;
+  const int gy = (f.height + TILE_Y - 1) / TILE_Y;
+  a.ranges = im.ranges; a.point_list = b.point_list; a.rec = g.rec; a.bg = f.background;
+  a.accum = im.accum; a.n_contrib = im.n_contrib;
+  a.out_color = f.out_color; a.out_others = f.out_others; a.out_refl = f.out_refl;
+  a.gaussian_weights = f.gaussian_weights;
+  surfel_composite_fwd_kernel<<<a.gx * gy, BATCH, 0, s>>>(a);
+  B200GS_LAUNCHED("surfel_composite_fwd_kernel", f.debug, s);
+  return B200GS_OK;
+}
+
+}  // namespace b200gs

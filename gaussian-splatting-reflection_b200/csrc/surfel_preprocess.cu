@@ -1,0 +1,253 @@
+// surfel_preprocess.cu -- K1s: per-Gaussian preprocess of the 2DGS/surfel path.
+//
+// Restates FORWARD::preprocessCUDA (S/cuda_rasterizer/forward.cu:148-253) with
+// compute_transmat (:75-115), compute_aabb (:119-145), quat_to_rotmat
+// (auxiliary.h:217-239), getRect (auxiliary.h:71-81), in_frustum (:189-214) and
+// computeColorFromSH (forward.cu:20-71).
+//
+// Everything that feeds an integer output (radii, tiles_touched, the depth bits
+// of the sort keys, the tile rect) is written with explicit __fmaf_rn/__fmul_rn/
+// __fadd_rn in the exact fused/unfused shape nvcc 12.9 produces for the
+// reference's glm expression trees (fp-contract on, no fast-math), so those
+// outputs are bit-identical to the reference extension built with the same
+// toolkit, independent of how this file is optimised.  Terms the reference
+// multiplies by a literal 0 (glm's dense mat products with the sparse S and
+// ndc2pix matrices) are dropped: for finite inputs fma(x, 0, y) == y.
+//
+// Output is one packed 80-B record per visible Gaussian (see common.cuh) instead
+// of the reference's six SoA arrays, so the compositing kernels stage a Gaussian
+// with five 16-B copies.
+#include "common.cuh"
+
+namespace b200gs {
+
+struct SurfelPreArgs {
+  int P, D, M, W, H, gx, gy;
+  float mod;
+  int prefiltered;
+  const float* means3D;
+  const float* scales;
+  const float* rotations;
+  const float* opacities;
+  const float* shs;
+  const float* colors_precomp;
+  const float* transMat_precomp;
+  const float* refl;
+  const uint8_t* mask;
+  const float* viewmatrix;
+  const float* projmatrix;
+  const float* campos;
+  int* radii;
+  float* depths;
+  uint32_t* tiles_touched;
+  uint8_t* clamped;
+  uint2* rects;
+  SurfelRec* rec;
+  int* flags;
+};
+
+// SH degree<=3 colour (forward.cu:20-71).  sh is this Gaussian's [M][3] block.
+__device__ __forceinline__ void sh_to_rgb(int deg, const float* __restrict__ sh, float dx, float dy, float dz,
+                                          float out[3], unsigned& clamp_bits) {
+  // glm: dir / length(dir) is a component-wise division; keep it a division for the same rounding.
+  const float len = sqrtf(dx * dx + dy * dy + dz * dz);
+  const float x = dx / len, y = dy / len, z = dz / len;
+  float r[3];
+#pragma unroll
+  for (int c = 0; c < 3; ++c) r[c] = SH_C0 * sh[c];
+  if (deg > 0) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+      r[c] = r[c] - SH_C1 * y * sh[3 + c] + SH_C1 * z * sh[6 + c] - SH_C1 * x * sh[9 + c];
+    if (deg > 1) {
+      const float xx = x * x, yy = y * y, zz = z * z;
+      const float xy = x * y, yz = y * z, xz = x * z;
+#pragma unroll
+      for (int c = 0; c < 3; ++c)
+        r[c] = r[c] + SH_C2_0 * xy * sh[12 + c] + SH_C2_1 * yz * sh[15 + c] +
+               SH_C2_2 * (2.0f * zz - xx - yy) * sh[18 + c] + SH_C2_3 * xz * sh[21 + c] +
+               SH_C2_4 * (xx - yy) * sh[24 + c];
+      if (deg > 2) {
+#pragma unroll
+        for (int c = 0; c < 3; ++c)
+          r[c] = r[c] + SH_C3_0 * y * (3.0f * xx - yy) * sh[27 + c] + SH_C3_1 * xy * z * sh[30 + c] +
+                 SH_C3_2 * y * (4.0f * zz - xx - yy) * sh[33 + c] +
+                 SH_C3_3 * z * (2.0f * zz - 3.0f * xx - 3.0f * yy) * sh[36 + c] +
+                 SH_C3_4 * x * (4.0f * zz - xx - yy) * sh[39 + c] + SH_C3_5 * z * (xx - yy) * sh[42 + c] +
+                 SH_C3_6 * x * (xx - 3.0f * yy) * sh[45 + c];
+      }
+    }
+  }
+  clamp_bits = 0;
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    r[c] += 0.5f;
+    if (r[c] < 0.0f) clamp_bits |= 1u << c;
+    out[c] = fmaxf(r[c], 0.0f);
+  }
+}
+
+__global__ void __launch_bounds__(256) surfel_preprocess_kernel(const SurfelPreArgs a) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= a.P) return;
+
+  // "If this isn't changed, this Gaussian will not be processed further" (forward.cu:180-183)
+  int radius_out = 0;
+  uint32_t tiles = 0;
+
+  const float px = a.means3D[3 * idx + 0], py = a.means3D[3 * idx + 1], pz = a.means3D[3 * idx + 2];
+  const float* __restrict__ vm = a.viewmatrix;
+  const float* __restrict__ pm = a.projmatrix;
+
+  // in_frustum (auxiliary.h:189-214): p_view = transformPoint4x3(p, view); cull z <= 0.2
+  const float vx = __fadd_rn(vm[12], dot3_ref(px, vm[0], py, vm[4], pz, vm[8]));
+  const float vy = __fadd_rn(vm[13], dot3_ref(px, vm[1], py, vm[5], pz, vm[9]));
+  const float vz = __fadd_rn(vm[14], dot3_ref(px, vm[2], py, vm[6], pz, vm[10]));
+
+  bool alive = vz > 0.2f;
+  if (!alive && a.prefiltered) atomicExch(&a.flags[0], 1);
+
+  float Tu[3], Tv[3], Tw[3], nrm[3];
+  if (alive) {
+    if (a.transMat_precomp == nullptr) {
+      // quat_to_rotmat (auxiliary.h:217-239); storage (w,x,y,z) = q0..q3
+      const float4 q = reinterpret_cast<const float4*>(a.rotations)[idx];
+      const float q0 = q.x, q1 = q.y, q2 = q.z, q3 = q.w;
+      const float n2 = __fmaf_rn(q2, q2, __fmaf_rn(q1, q1, __fmaf_rn(q0, q0, __fmul_rn(q3, q3))));
+      const float s = rsqrtf(n2);
+      const float w = __fmul_rn(q0, s), x = __fmul_rn(q1, s), y = __fmul_rn(q2, s), z = __fmul_rn(q3, s);
+      const float yy = __fmul_rn(y, y), zz = __fmul_rn(z, z);
+      const float xy = __fmul_rn(x, y), wz = __fmul_rn(w, z);
+      const float xz = __fmul_rn(x, z), wy = __fmul_rn(w, y);
+      const float yz = __fmul_rn(y, z), wx = __fmul_rn(w, x);
+      const float xx_zz = __fmaf_rn(x, x, zz), xx_yy = __fmaf_rn(x, x, yy);
+      // glm column-major R[c][r]
+      const float R00 = __fsub_rn(1.0f, __fmul_rn(2.0f, __fadd_rn(yy, zz)));
+      const float R01 = __fmul_rn(2.0f, __fadd_rn(xy, wz));
+      const float R02 = __fmul_rn(2.0f, __fsub_rn(xz, wy));
+      const float R10 = __fmul_rn(2.0f, __fsub_rn(xy, wz));
+      const float R11 = __fsub_rn(1.0f, __fmul_rn(2.0f, xx_zz));
+      const float R12 = __fmul_rn(2.0f, __fadd_rn(yz, wx));
+      const float R20 = __fmul_rn(2.0f, __fadd_rn(xz, wy));
+      const float R21 = __fmul_rn(2.0f, __fsub_rn(yz, wx));
+      const float R22 = __fsub_rn(1.0f, __fmul_rn(2.0f, xx_yy));
+      // L = R * diag(mod*sx, mod*sy, 1)   (forward.cu:88-90)
+      const float2 sc = reinterpret_cast<const float2*>(a.scales)[idx];
+      const float S00 = __fmul_rn(a.mod, sc.x), S11 = __fmul_rn(a.mod, sc.y);
+      const float L0[3] = {__fmul_rn(S00, R00), __fmul_rn(S00, R01), __fmul_rn(S00, R02)};
+      const float L1[3] = {__fmul_rn(S11, R10), __fmul_rn(S11, R11), __fmul_rn(S11, R12)};
+      // M = transpose(splat2world) * world2ndc  (forward.cu:93-112); M[c][r], c = clip component
+      float M0[4], M1[4], M2[4];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        M0[c] = __fmaf_rn(L0[2], pm[8 + c], __fmaf_rn(L0[0], pm[c], __fmul_rn(L0[1], pm[4 + c])));
+        M1[c] = __fmaf_rn(L1[2], pm[8 + c], __fmaf_rn(L1[0], pm[c], __fmul_rn(L1[1], pm[4 + c])));
+        M2[c] = __fadd_rn(pm[12 + c], __fmaf_rn(pz, pm[8 + c], __fmaf_rn(px, pm[c], __fmul_rn(py, pm[4 + c]))));
+      }
+      // T = M * ndc2pix: T[0][r] = fma((W-1)/2, M[3][r], W/2 * M[0][r]) etc.
+      const float hw = __fmul_rn((float)a.W, 0.5f), hw1 = __fmul_rn((float)(a.W - 1), 0.5f);
+      const float hh = __fmul_rn((float)a.H, 0.5f), hh1 = __fmul_rn((float)(a.H - 1), 0.5f);
+      Tu[0] = __fmaf_rn(hw1, M0[3], __fmul_rn(hw, M0[0]));
+      Tu[1] = __fmaf_rn(hw1, M1[3], __fmul_rn(hw, M1[0]));
+      Tu[2] = __fmaf_rn(hw1, M2[3], __fmul_rn(hw, M2[0]));
+      Tv[0] = __fmaf_rn(hh1, M0[3], __fmul_rn(hh, M0[1]));
+      Tv[1] = __fmaf_rn(hh1, M1[3], __fmul_rn(hh, M1[1]));
+      Tv[2] = __fmaf_rn(hh1, M2[3], __fmul_rn(hh, M2[1]));
+      Tw[0] = M0[3]; Tw[1] = M1[3]; Tw[2] = M2[3];
+      // normal = transformVec4x3(L[2] = R[2], viewmatrix)  (forward.cu:113)
+      nrm[0] = dot3_ref(R20, vm[0], R21, vm[4], R22, vm[8]);
+      nrm[1] = dot3_ref(R20, vm[1], R21, vm[5], R22, vm[9]);
+      nrm[2] = dot3_ref(R20, vm[2], R21, vm[6], R22, vm[10]);
+    } else {
+      const float* tp = a.transMat_precomp + 9 * (size_t)idx;  // forward.cu:200-208
+      Tu[0] = tp[0]; Tu[1] = tp[1]; Tu[2] = tp[2];
+      Tv[0] = tp[3]; Tv[1] = tp[4]; Tv[2] = tp[5];
+      Tw[0] = tp[6]; Tw[1] = tp[7]; Tw[2] = tp[8];
+      nrm[0] = 0.0f; nrm[1] = 0.0f; nrm[2] = 1.0f;
+    }
+    // DUAL_VISIABLE (forward.cu:211-216): cos = -(p_view . normal); cos == 0 -> drop
+    const float pn = __fmaf_rn(vz, nrm[2], __fmaf_rn(vx, nrm[0], __fmul_rn(vy, nrm[1])));
+    if (pn == 0.0f) alive = false;
+    const float mult = pn < 0.0f ? 1.0f : -1.0f;
+    nrm[0] = __fmul_rn(nrm[0], mult); nrm[1] = __fmul_rn(nrm[1], mult); nrm[2] = __fmul_rn(nrm[2], mult);
+  }
+
+  float cx = 0.f, cy = 0.f;
+  int x0 = 0, y0 = 0, x1 = 0, y1 = 0;
+  if (alive) {
+    // compute_aabb (forward.cu:119-145), cutoff = 3
+    const float d = __fsub_rn(__fmaf_rn(__fmul_rn(Tw[0], Tw[0]), 9.0f, __fmul_rn(__fmul_rn(Tw[1], Tw[1]), 9.0f)),
+                              __fmul_rn(Tw[2], Tw[2]));
+    if (d == 0.0f) {
+      alive = false;
+    } else {
+      const float fz = __frcp_rn(d);          // f = (1/d) * (9, 9, -1)
+      const float fxy = __fmul_rn(fz, 9.0f);
+      cx = __fsub_rn(__fmaf_rn(fxy, __fmul_rn(Tu[0], Tw[0]), __fmul_rn(fxy, __fmul_rn(Tu[1], Tw[1]))),
+                     __fmul_rn(fz, __fmul_rn(Tu[2], Tw[2])));
+      cy = __fsub_rn(__fmaf_rn(fxy, __fmul_rn(Tv[0], Tw[0]), __fmul_rn(fxy, __fmul_rn(Tv[1], Tw[1]))),
+                     __fmul_rn(fz, __fmul_rn(Tv[2], Tw[2])));
+      const float du = __fmaf_rn(fxy, __fmul_rn(Tu[0], Tu[0]), __fmul_rn(fxy, __fmul_rn(Tu[1], Tu[1])));
+      const float dv = __fmaf_rn(fxy, __fmul_rn(Tv[0], Tv[0]), __fmul_rn(fxy, __fmul_rn(Tv[1], Tv[1])));
+      const float h0x = __fmaf_rn(cx, cx, __fsub_rn(__fmul_rn(fz, __fmul_rn(Tu[2], Tu[2])), du));
+      const float h0y = __fmaf_rn(cy, cy, __fsub_rn(__fmul_rn(fz, __fmul_rn(Tv[2], Tv[2])), dv));
+      const float hx = __fsqrt_rn(fmaxf(h0x, 1e-4f));
+      const float hy = __fsqrt_rn(fmaxf(h0y, 1e-4f));
+      // radius = ceil(max(max(hx, hy), 3 * 0.707106))  (forward.cu:232)
+      const float radius = ceilf(fmaxf(fmaxf(hx, hy), 2.12131786346435546875f));
+      const int ri = (int)radius;
+      get_rect(cx, cy, ri, a.gx, a.gy, x0, y0, x1, y1);
+      tiles = (uint32_t)((x1 - x0) * (y1 - y0));
+      if (tiles == 0) alive = false;
+      else radius_out = ri;
+    }
+  }
+
+  a.radii[idx] = radius_out;
+  a.tiles_touched[idx] = alive ? tiles : 0u;
+  if (!alive) return;
+
+  // Colour (forward.cu:240-246)
+  float rgb[3];
+  unsigned cb = 0;
+  if (a.colors_precomp == nullptr) {
+    const float* cp = a.campos;
+    sh_to_rgb(a.D, a.shs + (size_t)idx * a.M * 3, px - cp[0], py - cp[1], pz - cp[2], rgb, cb);
+  } else {
+    rgb[0] = a.colors_precomp[3 * idx + 0];
+    rgb[1] = a.colors_precomp[3 * idx + 1];
+    rgb[2] = a.colors_precomp[3 * idx + 2];
+  }
+  a.clamped[idx] = (uint8_t)cb;
+  a.depths[idx] = vz;
+  a.rects[idx] = make_uint2((uint32_t)x0 | ((uint32_t)x1 << 16), (uint32_t)y0 | ((uint32_t)y1 << 16));
+
+  const float opa = a.opacities[idx];
+  const float refl = a.refl ? a.refl[idx] : 0.0f;
+  const float mk = (a.mask && a.mask[idx]) ? 1.0f : 0.0f;
+  SurfelRec* r = a.rec + idx;
+  r->q[0] = make_float4(Tu[0], Tu[1], Tu[2], Tv[0]);
+  r->q[1] = make_float4(Tv[1], Tv[2], Tw[0], Tw[1]);
+  r->q[2] = make_float4(Tw[2], cx, cy, opa);
+  r->q[3] = make_float4(nrm[0], nrm[1], nrm[2], refl);
+  r->q[4] = make_float4(rgb[0], rgb[1], rgb[2], mk);
+}
+
+int surfel_preprocess(const b200gs_surfel_fwd& a, const SurfelGeom& g, cudaStream_t s) {
+  SurfelPreArgs k;
+  k.P = a.P; k.D = a.sh_degree; k.M = a.sh_coeffs; k.W = a.width; k.H = a.height;
+  k.gx = (a.width + TILE_X - 1) / TILE_X; k.gy = (a.height + TILE_Y - 1) / TILE_Y;
+  k.mod = a.scale_modifier; k.prefiltered = a.prefiltered;
+  k.means3D = a.means3D; k.scales = a.scales; k.rotations = a.rotations; k.opacities = a.opacities;
+  k.shs = a.shs; k.colors_precomp = a.colors_precomp; k.transMat_precomp = a.transMat_precomp;
+  k.refl = a.refl_strengths; k.mask = a.env_scope_mask;
+  k.viewmatrix = a.viewmatrix; k.projmatrix = a.projmatrix; k.campos = a.campos;
+  k.radii = a.radii; k.depths = g.depths; k.tiles_touched = g.tiles_touched; k.clamped = g.clamped;
+  k.rects = g.rects; k.rec = g.rec; k.flags = g.flags;
+  B200GS_CUDA(cudaMemsetAsync(g.flags, 0, 4 * sizeof(int), s));
+  surfel_preprocess_kernel<<<(a.P + 255) / 256, 256, 0, s>>>(k);
+  B200GS_LAUNCHED("surfel_preprocess_kernel", a.debug, s);
+  return B200GS_OK;
+}
+
+}  // namespace b200gs

@@ -1,0 +1,102 @@
+"""ctypes binding of libb200gs.so (the C ABI declared in include/b200gs.h).
+
+This is the only place the shared library is loaded.  There is no fallback of
+any kind: if the library is missing or a call fails, an exception is raised.
+PyTorch is used by the callers of this module for device memory and streams
+only; nothing here imports it.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.environ.get(
+    "B200GS_LIB", os.path.normpath(os.path.join(_HERE, "..", "..", "lib", "libb200gs.so")))
+
+
+class B200gsError(RuntimeError):
+    pass
+
+
+if not os.path.exists(_LIB_PATH):
+    raise ImportError(
+        f"libb200gs.so not found at {_LIB_PATH}; build it with "
+        "`python gaussian-splatting-reflection_b200/build.py` (there is no CPU fallback)")
+lib = C.CDLL(_LIB_PATH)
+
+_p = C.c_void_p
+_f = C.c_float
+_i = C.c_int
+_sz = C.c_size_t
+
+
+class SurfelFwd(C.Structure):
+    """struct b200gs_surfel_fwd"""
+    _fields_ = [
+        ("P", _i), ("sh_degree", _i), ("sh_coeffs", _i), ("width", _i), ("height", _i),
+        ("tan_fovx", _f), ("tan_fovy", _f), ("scale_modifier", _f),
+        ("prefiltered", _i), ("debug", _i),
+        ("background", _p), ("means3D", _p), ("env_scope_mask", _p), ("shs", _p),
+        ("colors_precomp", _p), ("refl_strengths", _p), ("opacities", _p), ("scales", _p),
+        ("rotations", _p), ("transMat_precomp", _p), ("viewmatrix", _p), ("projmatrix", _p),
+        ("campos", _p),
+        ("geom", _p), ("geom_bytes", _sz), ("img", _p), ("img_bytes", _sz),
+        ("binning", _p), ("binning_bytes", _sz),
+        ("out_color", _p), ("out_others", _p), ("out_refl", _p), ("radii", _p),
+        ("gaussian_weights", _p),
+    ]
+
+
+class SurfelBwd(C.Structure):
+    """struct b200gs_surfel_bwd"""
+    _fields_ = [
+        ("P", _i), ("sh_degree", _i), ("sh_coeffs", _i), ("num_rendered", _i),
+        ("width", _i), ("height", _i),
+        ("tan_fovx", _f), ("tan_fovy", _f), ("scale_modifier", _f), ("debug", _i),
+        ("background", _p), ("means3D", _p), ("shs", _p), ("colors_precomp", _p), ("scales", _p),
+        ("rotations", _p), ("transMat_precomp", _p), ("viewmatrix", _p), ("projmatrix", _p),
+        ("campos", _p), ("radii", _p), ("geom", _p), ("binning", _p), ("img", _p),
+        ("dL_dout_color", _p), ("dL_dout_others", _p), ("dL_dout_refl", _p),
+        ("accum", _p), ("accum_bytes", _sz),
+        ("dL_dmeans2D", _p), ("dL_dnormal", _p), ("dL_dopacity", _p), ("dL_dcolors", _p),
+        ("dL_drefl", _p), ("dL_dmeans3D", _p), ("dL_dtransMat", _p), ("dL_dsh", _p),
+        ("dL_dscales", _p), ("dL_drotations", _p),
+    ]
+
+
+def _sig(name, restype, *argtypes):
+    fn = getattr(lib, name)
+    fn.restype = restype
+    fn.argtypes = list(argtypes)
+    return fn
+
+
+last_error = _sig("b200gs_last_error", C.c_char_p)
+version = _sig("b200gs_version", _i)
+sm_arch = _sig("b200gs_sm_arch", _i)
+launch_count = _sig("b200gs_launch_count", C.c_ulonglong)
+mark_visible = _sig("b200gs_mark_visible", _i, _i, _p, _p, _p, _p, _p)
+surfel_geom_bytes = _sig("b200gs_surfel_geom_bytes", _sz, _i)
+surfel_image_bytes = _sig("b200gs_surfel_image_bytes", _sz, _i, _i)
+binning_bytes = _sig("b200gs_binning_bytes", _sz, _i)
+surfel_accum_bytes = _sig("b200gs_surfel_accum_bytes", _sz, _i)
+surfel_forward_stage1 = _sig("b200gs_surfel_forward_stage1", _i, C.POINTER(SurfelFwd), C.POINTER(_i), _p)
+surfel_forward_stage2 = _sig("b200gs_surfel_forward_stage2", _i, C.POINTER(SurfelFwd), _i, _p)
+surfel_backward = _sig("b200gs_surfel_backward", _i, C.POINTER(SurfelBwd), _p)
+surfel_inspect_geom = _sig("b200gs_surfel_inspect_geom", _i, _p, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p)
+inspect_binning = _sig("b200gs_inspect_binning", _i, _p, _i, _p, _p, _p)
+surfel_inspect_image = _sig("b200gs_surfel_inspect_image", _i, _p, _i, _i, _p, _p, _p, _p)
+
+
+def check(rc):
+    """Map a C return code to an exception (the reference throws std::runtime_error
+    -> Python RuntimeError; S/rasterize_points.cu:63-65, auxiliary.h:300-307)."""
+    if rc != 0:
+        raise B200gsError(last_error().decode("utf-8", "replace"))
+
+
+def ptr(t):
+    """Device pointer of a tensor, or None for a missing / empty one (the reference
+    treats an empty tensor as 'not provided': S/diff_surfel_rasterization/__init__.py:210-223)."""
+    if t is None or t.numel() == 0:
+        return None
+    return t.data_ptr()

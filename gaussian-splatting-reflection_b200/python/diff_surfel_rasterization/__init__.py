@@ -1,0 +1,121 @@
+"""Drop-in `diff_surfel_rasterization` package over libb200gs.so (sm_100a).
+
+Public surface and behaviour follow the reference package
+(S/diff_surfel_rasterization/__init__.py): `GaussianRasterizationSettings`
+(:170-182), `GaussianRasterizer` with `.markVisible` and `.forward` (:184-239),
+`rasterize_gaussians` (:21-46) and the autograd function behind it (:48-168), so
+the reference's gaussian_renderer/__init__.py, train.py and render.py import and
+call it unchanged.
+"""
+from typing import NamedTuple
+
+import torch
+import torch.nn as nn
+
+from . import _C
+
+__all__ = ["GaussianRasterizationSettings", "GaussianRasterizer", "rasterize_gaussians"]
+
+
+class GaussianRasterizationSettings(NamedTuple):
+    image_height: int
+    image_width: int
+    tanfovx: float
+    tanfovy: float
+    bg: torch.Tensor
+    scale_modifier: float
+    viewmatrix: torch.Tensor
+    projmatrix: torch.Tensor
+    sh_degree: int
+    campos: torch.Tensor
+    prefiltered: bool
+    debug: bool
+
+
+def _snapshot(args):
+    """CPU copy of the call arguments, taken before a debug-mode call so a failing
+    call can be dumped (reference: cpu_deep_copy_tuple, :17-19)."""
+    return tuple(a.detach().cpu().clone() if isinstance(a, torch.Tensor) else a for a in args)
+
+
+def _call_with_dump(fn, args, debug, dump_path, what):
+    if not debug:
+        return fn(*args)
+    saved = _snapshot(args)
+    try:
+        return fn(*args)
+    except Exception:
+        torch.save(saved, dump_path)
+        print(f"\nAn error occured in {what}. Please forward {dump_path} for debugging.")
+        raise
+
+
+class _RasterizeGaussians(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, means3D, means2D, sh, colors_precomp, refl_strengths, opacities, scales, rotations,
+                cov3Ds_precomp, raster_settings, env_scope_mask):
+        rs = raster_settings
+        args = (rs.bg, means3D, env_scope_mask, colors_precomp, refl_strengths, opacities, scales, rotations,
+                rs.scale_modifier, cov3Ds_precomp, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy,
+                rs.image_height, rs.image_width, sh, rs.sh_degree, rs.campos, rs.prefiltered, rs.debug)
+        (num_rendered, color, depth, radii, geomBuffer, binningBuffer, imgBuffer, refl_strength_map,
+         gaussian_weights) = _call_with_dump(_C.rasterize_gaussians, args, rs.debug, "snapshot_fw.dump", "forward")
+        ctx.raster_settings = rs
+        ctx.num_rendered = num_rendered
+        ctx.save_for_backward(colors_precomp, refl_strengths, means3D, scales, rotations, cov3Ds_precomp, radii, sh,
+                              geomBuffer, binningBuffer, imgBuffer)
+        return color, radii, depth, refl_strength_map, gaussian_weights
+
+    @staticmethod
+    def backward(ctx, grad_out_color, _grad_radii, grad_depth, grad_out_strength_map, _grad_weights):
+        rs = ctx.raster_settings
+        (colors_precomp, refl_strengths, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geomBuffer,
+         binningBuffer, imgBuffer) = ctx.saved_tensors
+        args = (rs.bg, means3D, radii, colors_precomp, refl_strengths, scales, rotations, rs.scale_modifier,
+                cov3Ds_precomp, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, grad_out_color, grad_depth,
+                grad_out_strength_map, sh, rs.sh_degree, rs.campos, geomBuffer, ctx.num_rendered, binningBuffer,
+                imgBuffer, rs.debug)
+        (grad_means2D, grad_colors_precomp, grad_refl, grad_opacities, grad_means3D, grad_cov3Ds_precomp, grad_sh,
+         grad_scales, grad_rotations) = _call_with_dump(_C.rasterize_gaussians_backward, args, rs.debug,
+                                                        "snapshot_bw.dump", "backward")
+        # input order of forward(); None for raster_settings and env_scope_mask
+        return (grad_means3D, grad_means2D, grad_sh, grad_colors_precomp, grad_refl, grad_opacities, grad_scales,
+                grad_rotations, grad_cov3Ds_precomp, None, None)
+
+
+def rasterize_gaussians(means3D, means2D, sh, colors_precomp, refl_strengths, opacities, scales, rotations,
+                        cov3Ds_precomp, raster_settings, env_scope_mask):
+    return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, refl_strengths, opacities, scales,
+                                     rotations, cov3Ds_precomp, raster_settings, env_scope_mask)
+
+
+class GaussianRasterizer(nn.Module):
+    def __init__(self, raster_settings):
+        super().__init__()
+        self.raster_settings = raster_settings
+
+    def markVisible(self, positions):
+        """Boolean mask of the points in front of the camera's near plane."""
+        with torch.no_grad():
+            rs = self.raster_settings
+            return _C.mark_visible(positions, rs.viewmatrix, rs.projmatrix)
+
+    def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, refl_strengths=None, scales=None,
+                rotations=None, cov3D_precomp=None, env_scope_mask=None):
+        if (shs is None) == (colors_precomp is None):
+            raise Exception('Please provide excatly one of either SHs or precomputed colors!')
+        have_sr = scales is not None or rotations is not None
+        if ((scales is None or rotations is None) and cov3D_precomp is None) or (have_sr and cov3D_precomp is not None):
+            raise Exception('Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!')
+
+        def empty():
+            return torch.empty((0,), dtype=torch.float32, device=means3D.device)
+
+        shs = empty() if shs is None else shs
+        colors_precomp = empty() if colors_precomp is None else colors_precomp
+        scales = empty() if scales is None else scales
+        rotations = empty() if rotations is None else rotations
+        cov3D_precomp = empty() if cov3D_precomp is None else cov3D_precomp
+        env_scope_mask = empty() if env_scope_mask is None else env_scope_mask
+        return rasterize_gaussians(means3D, means2D, shs, colors_precomp, refl_strengths, opacities, scales, rotations,
+                                   cov3D_precomp, self.raster_settings, env_scope_mask)

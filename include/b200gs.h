@@ -1,0 +1,161 @@
+/*
+ * b200gs.h -- C ABI of libb200gs.so, the sm_100a implementation of the
+ * differentiable rendering hot path of gssales/gaussian-splatting-reflection.
+ *
+ * Every entry point takes plain device pointers, sizes and a CUDA stream
+ * (passed as void*; NULL = legacy default stream, which is what the reference
+ * launches on).  No torch types cross this boundary.  All functions return 0 on
+ * success and a negative B200GS_E* code on failure; b200gs_last_error() gives
+ * the message of the calling thread's last failure.
+ *
+ * Reference interfaces replaced (paths relative to the reference's
+ * submodules/):
+ *   surfel:  diff-surfel-rasterization/cuda_rasterizer/rasterizer.h:20-94
+ *            (CudaRasterizer::Rasterizer::{markVisible,forward,backward}) as
+ *            called from rasterize_points.cu:39-288
+ *   3DGS:    diff-gaussian-rasterization/cuda_rasterizer/rasterizer.h:20-102
+ *   cubemap: cubemapencoder/src/cubemapencoder.h:6-17
+ *
+ * Scratch ("geom", "img", "binning") is caller-allocated device memory whose
+ * layout is private to this library (it is NOT the reference's fromChunk
+ * layout); the *_bytes functions give the sizes and the *_inspect_* functions
+ * unpack it into the reference's SoA arrays for parity checks.
+ */
+#ifndef B200GS_H_INCLUDED
+#define B200GS_H_INCLUDED
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200GS_OK 0
+#define B200GS_EINVAL (-1)   /* bad argument (message says which)            */
+#define B200GS_ECUDA (-2)    /* CUDA runtime error (message = cudaGetErrorString) */
+#define B200GS_ESIZE (-3)    /* scratch buffer too small                      */
+
+const char* b200gs_last_error(void);
+/* Library/ABI version and the SM architecture the kernels were built for. */
+int b200gs_version(void);
+int b200gs_sm_arch(void);
+/* Number of kernel launches this library has issued since load (all threads);
+ * bench.py reads it around the timed region for its "gpu_launches" claim.    */
+unsigned long long b200gs_launch_count(void);
+
+/* ------------------------------------------------------------------------ */
+/* markVisible  (S/rasterize_points.cu:269-288, rasterizer_impl.cu:54-66)     */
+int b200gs_mark_visible(int P, const float* means3D, const float* viewmatrix,
+                        const float* projmatrix, uint8_t* present, void* stream);
+
+/* ------------------------------------------------------------------------ */
+/* Surfel (2DGS) rasterizer                                                   */
+
+/* Inputs of one forward view; mirrors the argument list of
+ * CudaRasterizer::Rasterizer::forward (S/cuda_rasterizer/rasterizer_impl.cu:198-225).
+ * Optional pointers are NULL when "not provided" (the reference tests
+ * data_ptr()==nullptr of an empty tensor).                                   */
+typedef struct b200gs_surfel_fwd {
+  int P;                 /* #Gaussians                                        */
+  int sh_degree;         /* D: active SH degree 0..3                          */
+  int sh_coeffs;         /* M: coefficients per channel stored in shs (<=16)  */
+  int width, height;
+  float tan_fovx, tan_fovy;
+  float scale_modifier;
+  int prefiltered;       /* !=0: a culled point is an error (B200GS_EINVAL after the stage) */
+  int debug;             /* !=0: synchronise + check after every stage        */
+  const float* background;        /* [3]                                      */
+  const float* means3D;           /* [P,3]                                    */
+  const uint8_t* env_scope_mask;  /* bool, indexed by Gaussian id (>=P entries) or NULL */
+  const float* shs;               /* [P,M,3] or NULL                          */
+  const float* colors_precomp;    /* [P,3]  or NULL                           */
+  const float* refl_strengths;    /* [P]    or NULL (=0)                      */
+  const float* opacities;         /* [P]                                      */
+  const float* scales;            /* [P,2]  or NULL                           */
+  const float* rotations;         /* [P,4] (w,x,y,z) or NULL                  */
+  const float* transMat_precomp;  /* [P,9]  or NULL                           */
+  const float* viewmatrix;        /* [16]                                     */
+  const float* projmatrix;        /* [16]                                     */
+  const float* campos;            /* [3]                                      */
+  void* geom;   size_t geom_bytes;     /* >= b200gs_surfel_geom_bytes(P)      */
+  void* img;    size_t img_bytes;      /* >= b200gs_surfel_image_bytes(W,H)   */
+  void* binning; size_t binning_bytes; /* >= b200gs_binning_bytes(R); stage 2 */
+  float* out_color;        /* [3,H,W]                                         */
+  float* out_others;       /* [8,H,W] depth,alpha,normal xyz,median,distortion,mask */
+  float* out_refl;         /* [1,H,W]                                         */
+  int* radii;              /* [P]                                             */
+  float* gaussian_weights; /* [P], must be zero-filled by the caller          */
+} b200gs_surfel_fwd;
+
+size_t b200gs_surfel_geom_bytes(int P);
+size_t b200gs_surfel_image_bytes(int width, int height);
+size_t b200gs_binning_bytes(int num_rendered);
+
+/* Stage 1: preprocess + tiles_touched prefix sum.  Writes the total number of
+ * (Gaussian,tile) instances to *num_rendered (host memory) and returns after
+ * the stream has drained -- the same single host sync the reference has at
+ * rasterizer_impl.cu:285-286.  Needs geom + img only.                        */
+int b200gs_surfel_forward_stage1(const b200gs_surfel_fwd* a, int* num_rendered, void* stream);
+/* Stage 2: duplicate-with-keys, 64-bit tile|depth sort, tile ranges, per-tile
+ * compositing.  Needs binning sized for num_rendered.  Asynchronous.         */
+int b200gs_surfel_forward_stage2(const b200gs_surfel_fwd* a, int num_rendered, void* stream);
+
+/* Backward; mirrors CudaRasterizer::Rasterizer::backward
+ * (S/cuda_rasterizer/rasterizer_impl.cu:358-466).  All dL_d* outputs must be
+ * zero-filled by the caller (the reference shim does torch::zeros,
+ * S/rasterize_points.cu:207-226).  `accum` is library scratch.               */
+typedef struct b200gs_surfel_bwd {
+  int P, sh_degree, sh_coeffs, num_rendered;
+  int width, height;
+  float tan_fovx, tan_fovy, scale_modifier;
+  int debug;
+  const float* background;
+  const float* means3D;
+  const float* shs;               /* or NULL */
+  const float* colors_precomp;    /* or NULL */
+  const float* scales;            /* or NULL */
+  const float* rotations;         /* or NULL */
+  const float* transMat_precomp;  /* or NULL */
+  const float* viewmatrix;
+  const float* projmatrix;
+  const float* campos;
+  const int* radii;
+  const void* geom; const void* binning; const void* img;  /* from the forward */
+  const float* dL_dout_color;   /* [3,H,W] */
+  const float* dL_dout_others;  /* [8,H,W] */
+  const float* dL_dout_refl;    /* [1,H,W] or NULL (=0; the reference dereferences it unconditionally) */
+  void* accum; size_t accum_bytes;  /* >= b200gs_surfel_accum_bytes(P); need not be zeroed */
+  float* dL_dmeans2D;    /* [P,3] */
+  float* dL_dnormal;     /* [P,3] */
+  float* dL_dopacity;    /* [P]   */
+  float* dL_dcolors;     /* [P,3] */
+  float* dL_drefl;       /* [P] or NULL */
+  float* dL_dmeans3D;    /* [P,3] */
+  float* dL_dtransMat;   /* [P,9] */
+  float* dL_dsh;         /* [P,M,3] or NULL */
+  float* dL_dscales;     /* [P,2] */
+  float* dL_drotations;  /* [P,4] */
+} b200gs_surfel_bwd;
+
+size_t b200gs_surfel_accum_bytes(int P);
+int b200gs_surfel_backward(const b200gs_surfel_bwd* a, void* stream);
+
+/* Parity-check helpers: unpack the private scratch layouts into the SoA arrays
+ * the reference keeps in GeometryState / BinningState / ImageState
+ * (S/cuda_rasterizer/rasterizer_impl.h:33-69).  Any output may be NULL.      */
+int b200gs_surfel_inspect_geom(const void* geom, int P,
+                               float* depths, float* means2D /*[P,2]*/, float* transMat /*[P,9]*/,
+                               float* normal_opacity /*[P,4]*/, float* rgb /*[P,3]*/,
+                               uint32_t* tiles_touched, uint32_t* point_offsets,
+                               uint8_t* clamped /*[P,3]*/, void* stream);
+int b200gs_inspect_binning(const void* binning, int num_rendered,
+                           uint64_t* point_list_keys, uint32_t* point_list, void* stream);
+int b200gs_surfel_inspect_image(const void* img, int width, int height,
+                                float* accum_alpha /*[3,N]*/, uint32_t* n_contrib /*[2,N]*/,
+                                uint32_t* ranges /*[T,2]*/, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200GS_H_INCLUDED */

@@ -1,0 +1,168 @@
+"""Shared drivers for the GPU parity tests, smoke() and bench.py.
+
+`run_surfel` drives ANY module that has the reference's `_C` signature
+(rasterize_gaussians / rasterize_gaussians_backward), so exactly the same call
+runs this repo's sm_100a path and the unmodified reference extension from
+oracle/_ref on identical inputs.
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PKG_PY = os.path.join(ROOT, "gaussian-splatting-reflection_b200", "python")
+for p in (ROOT, PKG_PY):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+
+def new_surfel_C():
+    import diff_surfel_rasterization
+    return diff_surfel_rasterization._C
+
+
+def ref_module(name):
+    """Prebuilt reference extension from oracle/_ref, or None."""
+    from oracle import build_ref
+    try:
+        return build_ref.load_ref(name)
+    except Exception as ex:  # noqa: BLE001
+        print(f"[harness] cannot load {name}: {ex}")
+        return None
+
+
+def to_dev(d, device="cuda"):
+    return {k: (torch.from_numpy(np.ascontiguousarray(v)).to(device) if isinstance(v, np.ndarray) else v)
+            for k, v in d.items()}
+
+
+def surfel_forward(Cmod, scene, cam, bg=(0.0, 0.0, 0.0), sh_degree=3, mask=None, scale_modifier=1.0,
+                   colors_precomp=None, transMat_precomp=None, debug=False):
+    """scene/cam: dicts of CUDA tensors (see scenes.py).  Returns the 9-tuple as a dict."""
+    dev = scene["means3D"].device
+    e = torch.empty((0,), dtype=torch.float32, device=dev)
+    P = scene["means3D"].shape[0]
+    if mask is None:
+        mask = torch.ones((P, 3), dtype=torch.bool, device=dev)
+    bgt = torch.tensor(bg, dtype=torch.float32, device=dev)
+    use_sh = colors_precomp is None
+    out = Cmod.rasterize_gaussians(
+        bgt, scene["means3D"], mask, e if use_sh else colors_precomp, scene["refl"], scene["opacities"],
+        e if transMat_precomp is not None else scene["scales"], e if transMat_precomp is not None else scene["rotations"],
+        scale_modifier, e if transMat_precomp is None else transMat_precomp, cam["viewmatrix"], cam["projmatrix"],
+        cam["tanfovx"], cam["tanfovy"], cam["height"], cam["width"], scene["shs"] if use_sh else e, sh_degree,
+        cam["campos"], False, debug)
+    keys = ("rendered", "color", "others", "radii", "geom", "binning", "img", "refl_map", "weights")
+    r = dict(zip(keys, out))
+    r.update(bg=bgt, sh_degree=sh_degree, scale_modifier=scale_modifier, colors_precomp=colors_precomp,
+             transMat_precomp=transMat_precomp)
+    return r
+
+
+def surfel_backward(Cmod, scene, cam, fwd, grads):
+    dev = scene["means3D"].device
+    e = torch.empty((0,), dtype=torch.float32, device=dev)
+    use_sh = fwd["colors_precomp"] is None
+    tp = fwd["transMat_precomp"]
+    out = Cmod.rasterize_gaussians_backward(
+        fwd["bg"], scene["means3D"], fwd["radii"], e if use_sh else fwd["colors_precomp"], scene["refl"],
+        e if tp is not None else scene["scales"], e if tp is not None else scene["rotations"], fwd["scale_modifier"],
+        e if tp is None else tp, cam["viewmatrix"], cam["projmatrix"], cam["tanfovx"], cam["tanfovy"],
+        grads["color"], grads["others"], grads["refl"], scene["shs"] if use_sh else e, fwd["sh_degree"],
+        cam["campos"], fwd["geom"], fwd["rendered"], fwd["binning"], fwd["img"], False)
+    keys = ("means2D", "colors", "refl", "opacity", "means3D", "transMat", "sh", "scales", "rotations")
+    return dict(zip(keys, out))
+
+
+# ---------------------------------------------------------------- state extraction
+def _al(off, a=128):
+    return (off + a - 1) // a * a
+
+
+def ref_surfel_state(fwd, P, W, H):
+    """Parse the reference's geomBuffer / binningBuffer / imgBuffer (SURVEY Appendix B;
+    S/cuda_rasterizer/rasterizer_impl.cu:155-194).  point_offsets lies behind the
+    CUB temp block and is recomputed from tiles_touched."""
+    g = fwd["geom"]
+    base = g.data_ptr() % 128
+    assert base == 0
+    off = 0
+    def take(buf, off, nbytes, dtype, shape):
+        off = _al(off)
+        t = buf[off:off + nbytes].view(dtype).reshape(shape)
+        return t, off + nbytes
+    depths, off = take(g, off, 4 * P, torch.float32, (P,))
+    clamped, off = take(g, off, 3 * P, torch.uint8, (P, 3))
+    iradii, off = take(g, off, 4 * P, torch.int32, (P,))
+    means2D, off = take(g, off, 8 * P, torch.float32, (P, 2))
+    transMat, off = take(g, off, 36 * P, torch.float32, (P, 9))
+    normal_opacity, off = take(g, off, 16 * P, torch.float32, (P, 4))
+    rgb, off = take(g, off, 12 * P, torch.float32, (P, 3))
+    tiles, off = take(g, off, 4 * P, torch.int32, (P,))
+    R = fwd["rendered"]
+    b = fwd["binning"]
+    off = 0
+    point_list, off = take(b, off, 4 * R, torch.int32, (R,))
+    _, off = take(b, off, 4 * R, torch.int32, (R,))
+    keys, off = take(b, off, 8 * R, torch.int64, (R,))
+    im = fwd["img"]
+    N = W * H
+    T = ((W + 15) // 16) * ((H + 15) // 16)
+    off = 0
+    accum, off = take(im, off, 12 * N, torch.float32, (3, N))
+    ncon, off = take(im, off, 8 * N, torch.int32, (2, N))
+    ranges, off = take(im, off, 8 * N, torch.int32, (N, 2))
+    return dict(depths=depths, clamped=clamped, means2D=means2D, transMat=transMat, normal_opacity=normal_opacity,
+                rgb=rgb, tiles_touched=tiles, point_offsets=torch.cumsum(tiles, 0).to(torch.int32),
+                point_list=point_list, keys=keys, accum=accum, n_contrib=ncon, ranges=ranges[:T])
+
+
+def new_surfel_state(fwd, P, W, H):
+    """Unpack this library's private scratch through the C ABI inspect helpers."""
+    import ctypes as C
+    import b200gs as _b
+    dev = fwd["geom"].device
+    f = lambda *s: torch.zeros(s, dtype=torch.float32, device=dev)  # noqa: E731
+    i = lambda *s: torch.zeros(s, dtype=torch.int32, device=dev)  # noqa: E731
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    depths, means2D, transMat, no, rgb = f(P), f(P, 2), f(P, 9), f(P, 4), f(P, 3)
+    tiles, offs = i(P), i(P)
+    clamped = torch.zeros((P, 3), dtype=torch.uint8, device=dev)
+    _b.check(_b.surfel_inspect_geom(fwd["geom"].data_ptr(), P, depths.data_ptr(), means2D.data_ptr(),
+                                    transMat.data_ptr(), no.data_ptr(), rgb.data_ptr(), tiles.data_ptr(),
+                                    offs.data_ptr(), clamped.data_ptr(), st))
+    R = fwd["rendered"]
+    keys = torch.zeros((R,), dtype=torch.int64, device=dev)
+    pl = i(R)
+    if R:
+        _b.check(_b.inspect_binning(fwd["binning"].data_ptr(), R, keys.data_ptr(), pl.data_ptr(), st))
+    N = W * H
+    T = ((W + 15) // 16) * ((H + 15) // 16)
+    accum, ncon, ranges = f(3, N), i(2, N), i(T, 2)
+    _b.check(_b.surfel_inspect_image(fwd["img"].data_ptr(), W, H, accum.data_ptr(), ncon.data_ptr(),
+                                     ranges.data_ptr(), st))
+    return dict(depths=depths, clamped=clamped, means2D=means2D, transMat=transMat, normal_opacity=no, rgb=rgb,
+                tiles_touched=tiles, point_offsets=offs, point_list=pl, keys=keys, accum=accum, n_contrib=ncon,
+                ranges=ranges)
+
+
+# ---------------------------------------------------------------- comparison metrics
+def max_abs(a, b):
+    return float((a.double() - b.double()).abs().max()) if a.numel() else 0.0
+
+
+def rel_l2(a, b):
+    d = (a.double() - b.double()).norm()
+    n = b.double().norm()
+    return float(d / n) if n > 0 else float(d)
+
+
+def grad_close_fraction(a, b, rtol=1e-4, scale_floor=1e-4):
+    """Fraction of elements with |a-b| <= rtol * max(|a|,|b|) + rtol*scale_floor*rms(b)."""
+    a, b = a.double(), b.double()
+    rms = b.pow(2).mean().sqrt() if b.numel() else torch.tensor(0.0)
+    tol = rtol * torch.maximum(a.abs(), b.abs()) + rtol * max(float(rms), 1e-30)
+    ok = (a - b).abs() <= tol
+    return float(ok.double().mean()) if ok.numel() else 1.0
