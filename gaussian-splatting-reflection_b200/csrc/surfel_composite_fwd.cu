@@ -112,7 +112,7 @@ __global__ void __launch_bounds__(BATCH) surfel_composite_fwd_kernel(const CompF
           const float m = ndc_depth(h.depth);
           const float mm = __fmul_rn(m, m);
           // distortion += (m*m*A + M2 - 2*m*M1) * w   (forward.cu:424)
-          const float e = __fsub_rn(__fmaf_rn(A, mm, M2), __fmul_rn(M1, __fadd_rn(m, m)));
+          const float e = __fmaf_rn(-M1, __fadd_rn(m, m), __fmaf_rn(A, mm, M2));
           distortion = __fmaf_rn(e, w, distortion);
           D = __fmaf_rn(h.depth, w, D);
           M1 = __fmaf_rn(m, w, M1);

@@ -50,38 +50,51 @@ struct SurfelPreArgs {
 __device__ __forceinline__ void sh_to_rgb(int deg, const float* __restrict__ sh, float dx, float dy, float dz,
                                           float out[3], unsigned& clamp_bits) {
   // glm: dir / length(dir) is a component-wise division; keep it a division for the same rounding.
-  const float len = sqrtf(dx * dx + dy * dy + dz * dz);
-  const float x = dx / len, y = dy / len, z = dz / len;
+  const float len = __fsqrt_rn(__fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy))));
+  const float x = __fdiv_rn(dx, len), y = __fdiv_rn(dy, len), z = __fdiv_rn(dz, len);
+  // Operation shapes pinned to the reference build's SASS (computeColorFromSH inlined in
+  // preprocessCUDA<3>): every basis term is rounded on its own, then one FFMA per coefficient.
   float r[3];
 #pragma unroll
-  for (int c = 0; c < 3; ++c) r[c] = SH_C0 * sh[c];
+  for (int c = 0; c < 3; ++c) r[c] = __fmul_rn(SH_C0, sh[c]);
   if (deg > 0) {
+    const float b1 = __fmul_rn(y, SH_C1), b2 = __fmul_rn(z, SH_C1), b3 = __fmul_rn(x, SH_C1);
 #pragma unroll
     for (int c = 0; c < 3; ++c)
-      r[c] = r[c] - SH_C1 * y * sh[3 + c] + SH_C1 * z * sh[6 + c] - SH_C1 * x * sh[9 + c];
+      r[c] = __fmaf_rn(-b3, sh[9 + c], __fmaf_rn(b2, sh[6 + c], __fmaf_rn(-b1, sh[3 + c], r[c])));
     if (deg > 1) {
-      const float xx = x * x, yy = y * y, zz = z * z;
-      const float xy = x * y, yz = y * z, xz = x * z;
+      const float xx = __fmul_rn(x, x), yy = __fmul_rn(y, y), zz = __fmul_rn(z, z);
+      const float xy = __fmul_rn(x, y), yz = __fmul_rn(y, z), xz = __fmul_rn(x, z);
+      const float zz2 = __fadd_rn(zz, zz);
+      const float xx_yy = __fsub_rn(xx, yy);
+      const float b4 = __fmul_rn(xy, SH_C2_0), b5 = __fmul_rn(yz, SH_C2_1);
+      const float b6 = __fmul_rn(__fsub_rn(__fsub_rn(zz2, xx), yy), SH_C2_2);
+      const float b7 = __fmul_rn(xz, SH_C2_3), b8 = __fmul_rn(xx_yy, SH_C2_4);
 #pragma unroll
       for (int c = 0; c < 3; ++c)
-        r[c] = r[c] + SH_C2_0 * xy * sh[12 + c] + SH_C2_1 * yz * sh[15 + c] +
-               SH_C2_2 * (2.0f * zz - xx - yy) * sh[18 + c] + SH_C2_3 * xz * sh[21 + c] +
-               SH_C2_4 * (xx - yy) * sh[24 + c];
+        r[c] = __fmaf_rn(b8, sh[24 + c], __fmaf_rn(b7, sh[21 + c], __fmaf_rn(b6, sh[18 + c],
+               __fmaf_rn(b5, sh[15 + c], __fmaf_rn(b4, sh[12 + c], r[c])))));
       if (deg > 2) {
+        const float a4 = __fsub_rn(__fmaf_rn(zz, 4.0f, -xx), yy);  // 4zz - xx - yy
+        const float b9 = __fmul_rn(__fmul_rn(y, SH_C3_0), __fmaf_rn(xx, 3.0f, -yy));
+        const float b10 = __fmul_rn(__fmul_rn(xy, SH_C3_1), z);
+        const float b11 = __fmul_rn(__fmul_rn(y, SH_C3_2), a4);
+        const float b12 = __fmul_rn(__fmul_rn(z, SH_C3_3), __fmaf_rn(yy, -3.0f, __fmaf_rn(xx, -3.0f, zz2)));
+        const float b13 = __fmul_rn(a4, __fmul_rn(x, SH_C3_4));
+        const float b14 = __fmul_rn(xx_yy, __fmul_rn(z, SH_C3_5));
+        const float b15 = __fmul_rn(__fmul_rn(x, SH_C3_6), __fmaf_rn(yy, -3.0f, xx));
 #pragma unroll
         for (int c = 0; c < 3; ++c)
-          r[c] = r[c] + SH_C3_0 * y * (3.0f * xx - yy) * sh[27 + c] + SH_C3_1 * xy * z * sh[30 + c] +
-                 SH_C3_2 * y * (4.0f * zz - xx - yy) * sh[33 + c] +
-                 SH_C3_3 * z * (2.0f * zz - 3.0f * xx - 3.0f * yy) * sh[36 + c] +
-                 SH_C3_4 * x * (4.0f * zz - xx - yy) * sh[39 + c] + SH_C3_5 * z * (xx - yy) * sh[42 + c] +
-                 SH_C3_6 * x * (xx - 3.0f * yy) * sh[45 + c];
+          r[c] = __fmaf_rn(b15, sh[45 + c], __fmaf_rn(b14, sh[42 + c], __fmaf_rn(b13, sh[39 + c],
+                 __fmaf_rn(b12, sh[36 + c], __fmaf_rn(b11, sh[33 + c], __fmaf_rn(b10, sh[30 + c],
+                 __fmaf_rn(b9, sh[27 + c], r[c])))))));
       }
     }
   }
   clamp_bits = 0;
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
-    r[c] += 0.5f;
+    r[c] = __fadd_rn(r[c], 0.5f);
     if (r[c] < 0.0f) clamp_bits |= 1u << c;
     out[c] = fmaxf(r[c], 0.0f);
   }
@@ -116,21 +129,20 @@ __global__ void __launch_bounds__(256) surfel_preprocess_kernel(const SurfelPreA
       const float n2 = __fmaf_rn(q2, q2, __fmaf_rn(q1, q1, __fmaf_rn(q0, q0, __fmul_rn(q3, q3))));
       const float s = rsqrtf(n2);
       const float w = __fmul_rn(q0, s), x = __fmul_rn(q1, s), y = __fmul_rn(q2, s), z = __fmul_rn(q3, s);
+      // Contraction exactly as in the reference build (SASS of preprocessCUDA<3>, nvcc 12.9):
+      // in a*b + c*d the SECOND product is rounded and the first is fused onto it.
       const float yy = __fmul_rn(y, y), zz = __fmul_rn(z, z);
-      const float xy = __fmul_rn(x, y), wz = __fmul_rn(w, z);
-      const float xz = __fmul_rn(x, z), wy = __fmul_rn(w, y);
-      const float yz = __fmul_rn(y, z), wx = __fmul_rn(w, x);
-      const float xx_zz = __fmaf_rn(x, x, zz), xx_yy = __fmaf_rn(x, x, yy);
+      const float wz = __fmul_rn(w, z), wy = __fmul_rn(w, y), wx = __fmul_rn(w, x);
       // glm column-major R[c][r]
       const float R00 = __fsub_rn(1.0f, __fmul_rn(2.0f, __fadd_rn(yy, zz)));
-      const float R01 = __fmul_rn(2.0f, __fadd_rn(xy, wz));
-      const float R02 = __fmul_rn(2.0f, __fsub_rn(xz, wy));
-      const float R10 = __fmul_rn(2.0f, __fsub_rn(xy, wz));
-      const float R11 = __fsub_rn(1.0f, __fmul_rn(2.0f, xx_zz));
-      const float R12 = __fmul_rn(2.0f, __fadd_rn(yz, wx));
-      const float R20 = __fmul_rn(2.0f, __fadd_rn(xz, wy));
-      const float R21 = __fmul_rn(2.0f, __fsub_rn(yz, wx));
-      const float R22 = __fsub_rn(1.0f, __fmul_rn(2.0f, xx_yy));
+      const float R01 = __fmul_rn(2.0f, __fmaf_rn(x, y, wz));
+      const float R02 = __fmul_rn(2.0f, __fmaf_rn(x, z, -wy));
+      const float R10 = __fmul_rn(2.0f, __fmaf_rn(x, y, -wz));
+      const float R11 = __fsub_rn(1.0f, __fmul_rn(2.0f, __fmaf_rn(x, x, zz)));
+      const float R12 = __fmul_rn(2.0f, __fmaf_rn(y, z, wx));
+      const float R20 = __fmul_rn(2.0f, __fmaf_rn(x, z, wy));
+      const float R21 = __fmul_rn(2.0f, __fmaf_rn(y, z, -wx));
+      const float R22 = __fsub_rn(1.0f, __fmul_rn(2.0f, __fmaf_rn(x, x, yy)));
       // L = R * diag(mod*sx, mod*sy, 1)   (forward.cu:88-90)
       const float2 sc = reinterpret_cast<const float2*>(a.scales)[idx];
       const float S00 = __fmul_rn(a.mod, sc.x), S11 = __fmul_rn(a.mod, sc.y);
@@ -176,21 +188,20 @@ __global__ void __launch_bounds__(256) surfel_preprocess_kernel(const SurfelPreA
   int x0 = 0, y0 = 0, x1 = 0, y1 = 0;
   if (alive) {
     // compute_aabb (forward.cu:119-145), cutoff = 3
-    const float d = __fsub_rn(__fmaf_rn(__fmul_rn(Tw[0], Tw[0]), 9.0f, __fmul_rn(__fmul_rn(Tw[1], Tw[1]), 9.0f)),
-                              __fmul_rn(Tw[2], Tw[2]));
+    const float d = __fmaf_rn(-Tw[2], Tw[2], __fmaf_rn(__fmul_rn(Tw[0], Tw[0]), 9.0f, __fmul_rn(__fmul_rn(Tw[1], Tw[1]), 9.0f)));
     if (d == 0.0f) {
       alive = false;
     } else {
       const float fz = __frcp_rn(d);          // f = (1/d) * (9, 9, -1)
       const float fxy = __fmul_rn(fz, 9.0f);
-      cx = __fsub_rn(__fmaf_rn(fxy, __fmul_rn(Tu[0], Tw[0]), __fmul_rn(fxy, __fmul_rn(Tu[1], Tw[1]))),
-                     __fmul_rn(fz, __fmul_rn(Tu[2], Tw[2])));
-      cy = __fsub_rn(__fmaf_rn(fxy, __fmul_rn(Tv[0], Tw[0]), __fmul_rn(fxy, __fmul_rn(Tv[1], Tw[1]))),
-                     __fmul_rn(fz, __fmul_rn(Tv[2], Tw[2])));
+      cx = __fmaf_rn(__fmul_rn(Tu[2], Tw[2]), -fz,
+                     __fmaf_rn(fxy, __fmul_rn(Tu[0], Tw[0]), __fmul_rn(fxy, __fmul_rn(Tu[1], Tw[1]))));
+      cy = __fmaf_rn(__fmul_rn(Tv[2], Tw[2]), -fz,
+                     __fmaf_rn(fxy, __fmul_rn(Tv[0], Tw[0]), __fmul_rn(fxy, __fmul_rn(Tv[1], Tw[1]))));
       const float du = __fmaf_rn(fxy, __fmul_rn(Tu[0], Tu[0]), __fmul_rn(fxy, __fmul_rn(Tu[1], Tu[1])));
       const float dv = __fmaf_rn(fxy, __fmul_rn(Tv[0], Tv[0]), __fmul_rn(fxy, __fmul_rn(Tv[1], Tv[1])));
-      const float h0x = __fmaf_rn(cx, cx, __fsub_rn(__fmul_rn(fz, __fmul_rn(Tu[2], Tu[2])), du));
-      const float h0y = __fmaf_rn(cy, cy, __fsub_rn(__fmul_rn(fz, __fmul_rn(Tv[2], Tv[2])), dv));
+      const float h0x = __fmaf_rn(cx, cx, __fmaf_rn(__fmul_rn(Tu[2], Tu[2]), fz, -du));
+      const float h0y = __fmaf_rn(cy, cy, __fmaf_rn(__fmul_rn(Tv[2], Tv[2]), fz, -dv));
       const float hx = __fsqrt_rn(fmaxf(h0x, 1e-4f));
       const float hy = __fsqrt_rn(fmaxf(h0y, 1e-4f));
       // radius = ceil(max(max(hx, hy), 3 * 0.707106))  (forward.cu:232)
