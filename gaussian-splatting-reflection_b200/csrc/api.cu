@@ -4,6 +4,8 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
+#include <vector>
 
 namespace b200gs {
 
@@ -22,6 +24,36 @@ int cuda_fail(cudaError_t e, const char* what) {
 }
 
 size_t scan_state_words(int n);  // binning.cu
+
+// ---- stage timing -------------------------------------------------------
+std::atomic<int> g_timing{0};
+namespace {
+struct Mark { cudaEvent_t a, b; int stage; };
+std::mutex g_tmu;
+std::vector<Mark> g_marks;        // completed or in-flight pairs
+std::vector<cudaEvent_t> g_free;  // recycled events
+cudaEvent_t get_event() {
+  if (!g_free.empty()) { cudaEvent_t e = g_free.back(); g_free.pop_back(); return e; }
+  cudaEvent_t e = nullptr;
+  cudaEventCreate(&e);
+  return e;
+}
+}  // namespace
+void stage_mark(int stage, bool begin, cudaStream_t s) {
+  std::lock_guard<std::mutex> lk(g_tmu);
+  if (begin) {
+    Mark m{get_event(), nullptr, stage};
+    cudaEventRecord(m.a, s);
+    g_marks.push_back(m);
+  } else {
+    for (size_t i = g_marks.size(); i-- > 0;)
+      if (g_marks[i].stage == stage && g_marks[i].b == nullptr) {
+        g_marks[i].b = get_event();
+        cudaEventRecord(g_marks[i].b, s);
+        break;
+      }
+  }
+}
 
 SurfelGeom SurfelGeom::carve(void* base, size_t P, size_t* bytes) {
   Carver c(base);
@@ -86,6 +118,31 @@ const char* b200gs_last_error(void) { return t_err; }
 int b200gs_version(void) { return 1; }
 int b200gs_sm_arch(void) { return 100; }
 unsigned long long b200gs_launch_count(void) { return g_launches.load(); }
+
+void b200gs_timing_enable(int on) { g_timing.store(on ? 1 : 0); }
+int b200gs_timing_stages(void) { return ST_COUNT; }
+const char* b200gs_timing_stage_name(int stage) {
+  static const char* names[ST_COUNT] = {"preprocess", "scan", "duplicate", "sort", "tile_ranges", "composite_fwd",
+                                        "composite_bwd", "preprocess_bwd", "cubemap_fwd", "cubemap_bwd"};
+  return (stage >= 0 && stage < ST_COUNT) ? names[stage] : "";
+}
+int b200gs_timing_read(float* ms, unsigned long long* counts, int n) {
+  std::lock_guard<std::mutex> lk(g_tmu);
+  for (int i = 0; i < n; ++i) { if (ms) ms[i] = 0.f; if (counts) counts[i] = 0; }
+  for (auto& m : g_marks) {
+    if (m.b) {
+      float t = 0.f;
+      if (cudaEventSynchronize(m.b) == cudaSuccess && cudaEventElapsedTime(&t, m.a, m.b) == cudaSuccess && m.stage < n) {
+        if (ms) ms[m.stage] += t;
+        if (counts) counts[m.stage] += 1;
+      }
+      g_free.push_back(m.b);
+    }
+    g_free.push_back(m.a);
+  }
+  g_marks.clear();
+  return B200GS_OK;
+}
 
 size_t b200gs_surfel_geom_bytes(int P) {
   size_t b = 0;

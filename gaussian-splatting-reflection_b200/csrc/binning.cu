@@ -110,6 +110,7 @@ size_t scan_state_words(int n) {
 int inclusive_scan_u32(const uint32_t* in, uint32_t* out, int n, uint32_t* state, cudaStream_t s, bool debug) {
   if (n <= 0) return B200GS_OK;
   const int tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
+  StageScope _t(ST_SCAN, s);
   B200GS_CUDA(cudaMemsetAsync(state, 0, scan_state_words(n) * sizeof(uint32_t), s));
   unsigned long long* st = reinterpret_cast<unsigned long long*>(state);
   scan_kernel<<<tiles, SCAN_THREADS, 0, s>>>(in, out, n, st + 1, state);  // word 0 = ticket
@@ -206,12 +207,20 @@ int bin_and_sort(const float* depths, const uint2* rects, const uint32_t* offset
   const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
   B200GS_CUDA(cudaMemsetAsync(ranges, 0, (size_t)gx * gy * sizeof(uint2), s));
   if (R <= 0) return B200GS_OK;
+  {
+  StageScope _t(ST_DUPLICATE, s);
   duplicate_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, depths, rects, offsets, b.keys_unsorted, b.point_list_unsorted, gx);
   B200GS_LAUNCHED("duplicate_kernel", debug, s);
+  }
   const int end_bit = 32 + (int)higher_msb((uint32_t)(gx * gy));
-  int rc = radix_sort_pairs(b.keys_unsorted, b.keys, b.point_list_unsorted, b.point_list, R, end_bit, b.sort_temp,
+  int rc;
+  {
+  StageScope _t(ST_SORT, s);
+  rc = radix_sort_pairs(b.keys_unsorted, b.keys, b.point_list_unsorted, b.point_list, R, end_bit, b.sort_temp,
                             b.sort_temp_bytes, s, debug);
+  }
   if (rc) return rc;
+  StageScope _t(ST_RANGES, s);
   tile_ranges_kernel<<<(R + 255) / 256, 256, 0, s>>>(R, b.keys, ranges);
   B200GS_LAUNCHED("tile_ranges_kernel", debug, s);
   return B200GS_OK;

@@ -40,6 +40,24 @@ extern std::atomic<unsigned long long> g_launches;
     if (_e != cudaSuccess) return ::b200gs::cuda_fail(_e, what);               \
   } while (0)
 
+// ---------------------------------------------------------------- stage timing
+// Optional per-stage device timing (b200gs_timing_enable / b200gs_timing_read):
+// a CUDA event pair is recorded on the LAUNCHING stream around every stage, so
+// bench.py can attribute the step time to kernels without a profiler attached.
+enum Stage {
+  ST_PREPROCESS = 0, ST_SCAN, ST_DUPLICATE, ST_SORT, ST_RANGES, ST_COMPOSITE_FWD,
+  ST_COMPOSITE_BWD, ST_PREPROCESS_BWD, ST_CUBEMAP_FWD, ST_CUBEMAP_BWD, ST_COUNT
+};
+extern std::atomic<int> g_timing;
+void stage_mark(int stage, bool begin, cudaStream_t s);
+struct StageScope {
+  int st; cudaStream_t s; bool on;
+  StageScope(int stage, cudaStream_t stream) : st(stage), s(stream), on(g_timing.load(std::memory_order_relaxed) != 0) {
+    if (on) stage_mark(st, true, s);
+  }
+  ~StageScope() { if (on) stage_mark(st, false, s); }
+};
+
 // ---------------------------------------------------------------- scratch carving
 // Same idea as the reference's obtain() (S/cuda_rasterizer/rasterizer_impl.h:21-27):
 // carve typed arrays out of one byte buffer, each start aligned.

@@ -235,6 +235,7 @@ int surfel_composite_backward(const b200gs_surfel_bwd& f, const SurfelGeom& g, c
   a.accum = im.accum; a.n_contrib = im.n_contrib;
   a.dL_dpix = f.dL_dout_color; a.dL_dothers = f.dL_dout_others; a.dL_drefl = f.dL_dout_refl;
   a.acc = acc;
+  StageScope _t(ST_COMPOSITE_BWD, s);
   B200GS_CUDA(cudaMemsetAsync(acc, 0, (size_t)f.P * ACC_STRIDE * sizeof(float), s));
   surfel_composite_bwd_kernel<<<a.gx * gy, BATCH, 0, s>>>(a);
   B200GS_LAUNCHED("surfel_composite_bwd_kernel", f.debug, s);

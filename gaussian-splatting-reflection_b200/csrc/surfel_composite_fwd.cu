@@ -172,6 +172,7 @@ int surfel_composite_forward(const b200gs_surfel_fwd& f, const SurfelGeom& g, co
   a.accum = im.accum; a.n_contrib = im.n_contrib;
   a.out_color = f.out_color; a.out_others = f.out_others; a.out_refl = f.out_refl;
   a.gaussian_weights = f.gaussian_weights;
+  StageScope _t(ST_COMPOSITE_FWD, s);
   surfel_composite_fwd_kernel<<<a.gx * gy, BATCH, 0, s>>>(a);
   B200GS_LAUNCHED("surfel_composite_fwd_kernel", f.debug, s);
   return B200GS_OK;

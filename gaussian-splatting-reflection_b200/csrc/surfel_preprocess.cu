@@ -255,6 +255,7 @@ int surfel_preprocess(const b200gs_surfel_fwd& a, const SurfelGeom& g, cudaStrea
   k.viewmatrix = a.viewmatrix; k.projmatrix = a.projmatrix; k.campos = a.campos;
   k.radii = a.radii; k.depths = g.depths; k.tiles_touched = g.tiles_touched; k.clamped = g.clamped;
   k.rects = g.rects; k.rec = g.rec; k.flags = g.flags;
+  StageScope _t(ST_PREPROCESS, s);
   B200GS_CUDA(cudaMemsetAsync(g.flags, 0, 4 * sizeof(int), s));
   surfel_preprocess_kernel<<<(a.P + 255) / 256, 256, 0, s>>>(k);
   B200GS_LAUNCHED("surfel_preprocess_kernel", a.debug, s);

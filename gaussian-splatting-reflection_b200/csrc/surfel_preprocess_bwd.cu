@@ -241,6 +241,7 @@ int surfel_preprocess_backward(const b200gs_surfel_bwd& f, const SurfelGeom& g, 
   a.dL_dcolors = f.dL_dcolors; a.dL_drefl = f.dL_drefl; a.dL_dmeans3D = f.dL_dmeans3D;
   a.dL_dtransMat = f.dL_dtransMat; a.dL_dsh = f.dL_dsh; a.dL_dscales = f.dL_dscales; a.dL_drot = f.dL_drotations;
   if (f.shs && !f.dL_dsh) { set_error("dL_dsh must be provided when shs is"); return B200GS_EINVAL; }
+  StageScope _t(ST_PREPROCESS_BWD, s);
   surfel_preprocess_bwd_kernel<<<(f.P + 255) / 256, 256, 0, s>>>(a);
   B200GS_LAUNCHED("surfel_preprocess_bwd_kernel", f.debug, s);
   return B200GS_OK;

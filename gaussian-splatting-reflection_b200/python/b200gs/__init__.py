@@ -74,6 +74,21 @@ last_error = _sig("b200gs_last_error", C.c_char_p)
 version = _sig("b200gs_version", _i)
 sm_arch = _sig("b200gs_sm_arch", _i)
 launch_count = _sig("b200gs_launch_count", C.c_ulonglong)
+timing_enable = _sig("b200gs_timing_enable", None, _i)
+timing_stages = _sig("b200gs_timing_stages", _i)
+timing_stage_name = _sig("b200gs_timing_stage_name", C.c_char_p, _i)
+_timing_read = _sig("b200gs_timing_read", _i, C.POINTER(_f), C.POINTER(C.c_ulonglong), _i)
+
+
+def timing_read():
+    """-> {stage name: (total ms, launches)} accumulated since the last read."""
+    n = timing_stages()
+    ms = (_f * n)()
+    cnt = (C.c_ulonglong * n)()
+    _timing_read(ms, cnt, n)
+    return {timing_stage_name(i).decode(): (float(ms[i]), int(cnt[i])) for i in range(n)}
+
+
 mark_visible = _sig("b200gs_mark_visible", _i, _i, _p, _p, _p, _p, _p)
 surfel_geom_bytes = _sig("b200gs_surfel_geom_bytes", _sz, _i)
 surfel_image_bytes = _sig("b200gs_surfel_image_bytes", _sz, _i, _i)

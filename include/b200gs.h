@@ -44,6 +44,15 @@ int b200gs_sm_arch(void);
  * bench.py reads it around the timed region for its "gpu_launches" claim.    */
 unsigned long long b200gs_launch_count(void);
 
+/* Per-stage device timing for bench.py: when enabled, every stage (kernel) is
+ * bracketed by a CUDA event pair on the stream it is launched on.
+ * b200gs_timing_read waits for the recorded events, adds the elapsed ms and the
+ * launch counts per stage into ms[0..n) / counts[0..n) and clears the record.   */
+void b200gs_timing_enable(int on);
+int b200gs_timing_stages(void);
+const char* b200gs_timing_stage_name(int stage);
+int b200gs_timing_read(float* ms, unsigned long long* counts, int n);
+
 /* ------------------------------------------------------------------------ */
 /* markVisible  (S/rasterize_points.cu:269-288, rasterizer_impl.cu:54-66)     */
 int b200gs_mark_visible(int P, const float* means3D, const float* viewmatrix,

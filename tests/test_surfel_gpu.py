@@ -133,3 +133,24 @@ def test_autograd_module_roundtrip():
     for k, v in leaves.items():
         assert v.grad is not None and torch.isfinite(v.grad).all(), k
     assert m2d.grad is not None and float(m2d.grad.abs().sum()) > 0
+
+
+def test_against_committed_reference_golden():
+    """tests/golden/surfel_tiny_ref.npz holds the reference extension's outputs (B200); the
+    sm_100a path must reproduce the integer structures and the images bit for bit."""
+    import os
+    import numpy as np
+    G = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "surfel_tiny_ref.npz"))
+    newC = hz.new_surfel_C()
+    sc, cam, f, b, _ = _run("tiny", newC, bg=tuple(float(x) for x in G["bg"]))
+    P, W, H = sc["means3D"].shape[0], cam["width"], cam["height"]
+    st = hz.new_surfel_state(f, P, W, H)
+    assert f["rendered"] == int(G["rendered"])
+    assert np.array_equal(f["radii"].cpu().numpy(), G["radii"])
+    for k in ("tiles_touched", "keys", "point_list", "ranges", "n_contrib"):
+        assert np.array_equal(st[k].cpu().numpy(), G["state_" + k]), k
+    for k in ("color", "others", "refl_map"):
+        assert np.array_equal(f[k].cpu().numpy(), G[k]), k
+    for k, v in b.items():
+        r = torch.from_numpy(G["grad_" + k]).cuda()
+        assert hz.rel_l2(v, r) <= GRAD_RTOL, k
