@@ -1,0 +1,358 @@
+#!/usr/bin/env python
+"""bench.py -- fwd+bwd throughput of the surfel (2DGS, reflection channels) differentiable
+rasterizer on the workload BASELINE.json's metric is quoted on: 3M Gaussians, SH degree 3,
+1920x1080, one camera view per GPU per step.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl new|reference]
+
+One process per GPU (torchrun for N>1).  A "step" = one pass of the hot path over one view per
+rank: forward (preprocess, scan, duplicate, 64-bit sort, tile ranges, compositing) + backward
+(compositing backward, preprocess backward) with non-zero upstream gradients on every
+differentiable output plane, then -- for N>1 -- one NCCL all-reduce of the per-Gaussian gradients
+(Gaussians replicated, views sharded: SURVEY.md section 8e).  Per-GPU work is fixed -> weak scaling.
+
+  value        Mpix/s over all ranks, inputs resident in HBM, CUDA-event timed, max over ranks.
+  e2e          same metric through the drop-in Python API (GaussianRasterizer autograd module)
+               with the step's host inputs (camera matrices + target image, pinned) copied
+               H2D and the loss read back D2H inside the timed region.
+  roofline     dominant kernel: algorithmic bytes per launch / its mean duration, measured with
+               CUDA event pairs recorded by the library on the launching stream during the
+               timed region (b200gs_timing_*), against MEASURED_PEAKS.json's HBM copy figure.
+  cpu_baseline the CPU oracle (oracle/surfel_oracle.py, "port": the reference has no CPU path)
+               on a bounded sample of the same view, rank 0 at N=1 only.
+  --impl reference  runs the UNMODIFIED reference CUDA extension (oracle/_ref/ref_surfel_C.so)
+               on the same inputs through the same driver: the reference's implementation of
+               this path exists only as CUDA, so "the reference on this box" is that, on the GPU.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "tests"), os.path.join(ROOT, "gaussian-splatting-reflection_b200", "python")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+METRIC = "surfel rasterizer fwd+bwd throughput, 3M Gaussians SH3 @1920x1080 (one view per GPU per step)"
+UNIT = "Mpix/s"
+WORKLOAD = "bench"   # tests/scenes.py CONFIGS["bench"]: room scene, P=3M, 1920x1080
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="new", choices=["new", "reference"])
+    ap.add_argument("--workload", default=WORKLOAD)
+    ap.add_argument("--points", type=int, default=0, help="override P (debug only; result is then not the headline)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--cpu-sample-tiles", type=int, default=3)
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.path = index, None, None
+
+    def __enter__(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix=".csv")
+            os.close(fd)
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200", "-i", str(self.index)],
+                                         stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except Exception:  # noqa: BLE001
+            self.proc = None
+        return self
+
+    def __exit__(self, *a):
+        if self.proc is not None:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:  # noqa: BLE001
+                self.proc.kill()
+
+    def summary(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if not self.path or not os.path.exists(self.path):
+            return out
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in open(self.path):
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        os.unlink(self.path)
+        if sm:
+            sm.sort()
+            out.update(sm_mhz=sm[len(sm) // 2], sm_max_mhz=max(mx), samples=len(sm))
+        out["reasons"] = sorted(reasons)
+        return out
+
+
+def algorithmic_bytes(P, V, R, N):
+    """compulsory HBM bytes per launch of each stage (surfel path, SH
+    degree 3, colours from SH), each datum moved once.  P Gaussians, V visible, R (Gaussian,tile)
+    instances, N pixels."""
+    return {
+        "preprocess": 237 * P + 87 * V + 8 * P,        # inputs; state of visible ones; radii + tiles_touched
+        "scan": 8 * P,
+        "duplicate": 12 * V + 12 * R,                   # depth + rect in, (key,value) out
+        "sort": 24 * R,                                 # read pairs once, write them once
+        "tile_ranges": 8 * R,
+        "composite_fwd": 64 * R + 68 * N,               # staged record per tile entry; 12 planes + 5 state words out
+        "composite_bwd": 80 * R + 68 * N + 60 * V,      # record + colour/refl; pixel state + 12 grad planes; partial sums
+        "preprocess_bwd": 237 * P + 60 * V + 248 * V,   # inputs again, partial sums in, final gradients out
+    }
+
+
+def cpu_baseline(scene_np, cam_np, n_tiles):
+    """Oracle (CPU, torch fp32) on a bounded sample of the same view: the full per-Gaussian
+    preprocess, then binning + compositing forward + autograd backward for `n_tiles` 16x16 tiles
+    spread over the image.  The cost of a whole view is extrapolated tile-proportionally."""
+    import numpy as np
+    import torch
+    from oracle import surfel_oracle as so
+    import scenes
+    cores = 1      # [S,256]-sized tensors: intra-op threading only adds overhead (measured 3.5x slower with 8)
+    torch.set_num_threads(cores)
+    W, H = cam_np["width"], cam_np["height"]
+    gx, gy = (W + 15) // 16, (H + 15) // 16
+    tiles = sorted({int((gy * (2 * k + 1)) // (2 * n_tiles)) * gx + int((gx * (2 * k + 1)) // (2 * n_tiles))
+                    for k in range(n_tiles)})
+    grads = scenes.upstream_grads(W, H)
+    t0 = time.time()
+    leaves = so._leaves(scene_np, torch.float32, True)
+    pre = so.preprocess(leaves, cam_np)
+    t_pre = time.time() - t0
+    t0 = time.time()
+    keys, plist, ranges = so.binning(pre, W, H, tiles=tiles)
+    comp = so.composite(pre, plist, ranges, cam_np, (0.0, 0.0, 0.0), tiles=tiles, collect_weights=False)
+    color, others, refl, _, _ = so.assemble(comp, W, H, torch.float32)
+    loss = ((color * torch.from_numpy(grads["color"])).sum() + (others[:7] * torch.from_numpy(grads["others"][:7])).sum()
+            + (refl * torch.from_numpy(grads["refl"])).sum())
+    loss.backward()
+    t_tiles = time.time() - t0
+    T = gx * gy
+    t_view = 2.0 * t_pre + t_tiles * T / len(tiles)      # preprocess forward + (about as much) backward
+    return {"value": W * H / t_view / 1e6, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"oracle/surfel_oracle.py: full preprocess of P={scene_np['means3D'].shape[0]} ({t_pre:.1f} s) + "
+                      f"binning/compositing fwd+autograd bwd of {len(tiles)} of {T} tiles ({t_tiles:.1f} s, "
+                      f"list lengths {[int(ranges[t, 1] - ranges[t, 0]) for t in tiles]}); whole view extrapolated "
+                      f"tile-proportionally to {t_view:.0f} s",
+            "seconds_measured": t_pre + t_tiles}
+
+
+def load_impl(impl):
+    """-> (module with the reference's `_C` signature, description) or (None, reason)."""
+    import harness as hz
+    if impl == "new":
+        return hz.new_surfel_C(), "libb200gs.so (sm_100a) via diff_surfel_rasterization._C"
+    m = hz.ref_module("ref_surfel_C")
+    if m is None:
+        return None, "oracle/_ref/ref_surfel_C.so not built (python oracle/build_ref.py needs /root/reference)"
+    return m, "unmodified reference CUDA extension oracle/_ref/ref_surfel_C.so (built for sm_100a)"
+
+
+def main():
+    a = parse()
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback for the product path")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    import b200gs
+    import harness as hz
+    import scenes
+    Cmod, impl_desc = load_impl(a.impl)
+    if Cmod is None:
+        if rank == 0:
+            print(json.dumps({"impl": "reference", "unavailable": impl_desc}))
+        return
+
+    # ---- synthetic workload: replicated Gaussians, one ring-camera view per rank ------------
+    sc_np, cam_np = scenes.build(a.workload, P=a.points or None, view=rank, n_views=32)
+    P, W, H = sc_np["means3D"].shape[0], cam_np["width"], cam_np["height"]
+    N = W * H
+    sc, cam = hz.to_dev(sc_np), hz.to_dev(cam_np)
+    grads = hz.to_dev(scenes.upstream_grads(W, H))
+    GRAD_KEYS = ("means3D", "sh", "opacity", "scales", "rotations", "refl")   # the 59 floats / Gaussian of the model
+
+    def step():
+        f = hz.surfel_forward(Cmod, sc, cam)
+        b = hz.surfel_backward(Cmod, sc, cam, f, grads)
+        if world > 1:
+            flat = torch.cat([b[k].reshape(P, -1) for k in GRAD_KEYS], 1)
+            dist.all_reduce(flat)
+        return f, b
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    f, _ = step()
+    R, V = int(f["rendered"]), int((f["radii"] > 0).sum())
+    del f
+
+    # ---- device-resident timing (value) with per-stage events and clock sampling -------------
+    if a.impl == "new":
+        b200gs.timing_enable(1)
+        b200gs.timing_read()
+    n0 = b200gs.launch_count()
+    with ClockSampler(local) as cs:
+        total_ms = timed(step, a.steps, a.warmup)
+    launches = b200gs.launch_count() - n0
+    stages = b200gs.timing_read() if a.impl == "new" else {}
+    b200gs.timing_enable(0)
+    clocks = cs.summary()
+    ms_per_step = total_ms / a.steps
+    value = world * N / (ms_per_step * 1e-3) / 1e6
+
+    # ---- end to end through the drop-in Python API, host inputs ------------------------------
+    e2e = None
+    if not a.no_e2e:
+        import diff_surfel_rasterization as dsr
+        saved_C = dsr._C
+        dsr._C = Cmod                                   # the reference arm drives the reference's _C
+        try:
+            leaves = {k: sc[k].clone().requires_grad_(True) for k in ("means3D", "shs", "opacities", "scales", "rotations", "refl")}
+            m2d = torch.zeros_like(leaves["means3D"], requires_grad=True)
+            mask = torch.ones((P, 3), dtype=torch.bool, device="cuda")
+            host = {k: torch.from_numpy(cam_np[k]).pin_memory() for k in ("viewmatrix", "projmatrix", "campos")}
+            host["target"] = torch.rand((3, H, W)).pin_memory()
+            host["bg"] = torch.zeros(3).pin_memory()
+            h2d = sum(t.numel() * t.element_size() for t in host.values())
+            loss_host = torch.zeros(1).pin_memory()
+
+            def e2e_step():
+                dev = {k: v.to("cuda", non_blocking=True) for k, v in host.items()}
+                rs = dsr.GaussianRasterizationSettings(
+                    image_height=H, image_width=W, tanfovx=cam_np["tanfovx"], tanfovy=cam_np["tanfovy"], bg=dev["bg"],
+                    scale_modifier=1.0, viewmatrix=dev["viewmatrix"], projmatrix=dev["projmatrix"], sh_degree=3,
+                    campos=dev["campos"], prefiltered=False, debug=False)
+                color, radii, allmap, refl_map, _ = dsr.GaussianRasterizer(rs)(
+                    means3D=leaves["means3D"], means2D=m2d, opacities=leaves["opacities"], shs=leaves["shs"],
+                    refl_strengths=leaves["refl"], scales=leaves["scales"], rotations=leaves["rotations"],
+                    env_scope_mask=mask)
+                loss = (color - dev["target"]).abs().mean() + 1e-3 * allmap[:7].mean() + 1e-3 * refl_map.mean()
+                for t in list(leaves.values()) + [m2d]:
+                    t.grad = None
+                loss.backward()
+                if world > 1:
+                    flat = torch.cat([leaves[k].grad.reshape(P, -1) for k in leaves], 1)
+                    dist.all_reduce(flat)
+                loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
+                torch.cuda.current_stream().synchronize()     # the caller reads the loss every step
+                return float(loss_host[0])
+
+            e2e_ms = timed(e2e_step, a.steps, a.warmup) / a.steps
+            e2e = {"value": world * N / (e2e_ms * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": e2e_ms,
+                   "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4,
+                   "api": "diff_surfel_rasterization.GaussianRasterizer (autograd) + L1 loss"}
+        finally:
+            dsr._C = saved_C
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- rank 0: roofline of the dominant kernel, CPU baseline, the JSON line ----------------
+    peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    try:
+        peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+        peak_src = "MEASURED_PEAKS.json hbm_gbs (measured copy bandwidth)"
+    except Exception:  # noqa: BLE001
+        pass
+    alg = algorithmic_bytes(P, V, R, N)
+    roofline, stage_table = None, {}
+    for name, (ms, cnt) in stages.items():
+        if cnt and name in alg:
+            per = ms / cnt
+            stage_table[name] = {"ms": round(per, 4), "launches_per_step": cnt / (a.steps + 0.0),
+                                 "alg_bytes": alg[name], "gbs": round(alg[name] / (per * 1e-3) / 1e9, 1),
+                                 "frac_of_hbm_peak": round(alg[name] / (per * 1e-3) / 1e9 / peak, 4)}
+    if stage_table:
+        top = max(stage_table, key=lambda k: stage_table[k]["ms"])
+        traffic = None
+        try:   # per-launch dram bytes of that kernel from the committed ncu --set full capture, if any
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(top)
+        except Exception:  # noqa: BLE001
+            pass
+        ach = stage_table[top]["gbs"]
+        roofline = {"kernel": top, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s",
+                    "frac": round(ach / peak, 4), "traffic": traffic, "peak_source": peak_src,
+                    "share_of_step": round(stage_table[top]["ms"] / ms_per_step, 3),
+                    "note": "compositing kernels are FP32/MUFU-issue bound, not HBM bound (DESIGN.md); the HBM "
+                            "fraction is reported as the contract asks, per-stage figures are under `stages`"}
+
+    cpu = None
+    if a.impl == "new" and world == 1 and not a.no_cpu_baseline:
+        cpu = cpu_baseline(sc_np, cam_np, a.cpu_sample_tiles)
+    elif a.impl == "reference":
+        cpu = {"value": value, "unit": UNIT, "cores": 0, "kind": "reference",
+               "sample": "the reference has no CPU implementation of this path (CUDA only): this arm is its "
+                         "unmodified CUDA extension on the same B200, same inputs, whole workload"}
+
+    line = {
+        "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+        "ms_per_step": round(ms_per_step, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{a.workload}: room scene, replicated Gaussians, ring camera {'0' if world == 1 else '0..%d' % (world - 1)} of 32",
+                   "gaussians": P, "width": W, "height": H, "sh_degree": 3, "visible": V, "instances": R,
+                   "views_per_step": world, "l2": "inputs (>= 0.7 GB of Gaussian data + 1.3 GB of sort keys per step) exceed the 126 MB L2; no flush",
+                   "parallelism": f"view-parallel x{world}, replicated Gaussians" + (", NCCL all-reduce of [P,59] fp32 gradients" if world > 1 else "")},
+        "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
+        "roofline": roofline, "cpu_baseline": cpu, "stages": stage_table, "implementation": impl_desc,
+    }
+    if a.impl == "reference":
+        line["impl"] = "reference"
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

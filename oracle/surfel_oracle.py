@@ -184,13 +184,21 @@ def preprocess(leaves, cam, sh_degree=3, scale_modifier=1.0, colors_precomp=None
                 grid=(gx, gy))
 
 
-def binning(pre, W, H):
+def binning(pre, W, H, tiles=None):
     """duplicateWithKeys + stable sort + identifyTileRanges (rasterizer_impl.cu:70-138, :308-313).
-    -> keys int64[R] (tile<<32 | fp32 depth bits), point_list int64[R], ranges int64[T,2]."""
+    -> keys int64[R] (tile<<32 | fp32 depth bits), point_list int64[R], ranges int64[T,2].
+    With `tiles` (bounded CPU-baseline samples) only Gaussians overlapping one of those tiles are
+    emitted; the lists and ranges of exactly those tiles are then complete, the others are not."""
     gx, gy = pre["grid"]
     alive = pre["alive"].numpy()
     rect = pre["rect"].numpy()
     dbits = pre["depths"].to(torch.float32).numpy().view(np.uint32).astype(np.int64)
+    if tiles is not None:
+        hit = np.zeros_like(alive)
+        for tl in tiles:
+            ty, tx = divmod(int(tl), gx)
+            hit |= (rect[:, 0] <= tx) & (tx < rect[:, 2]) & (rect[:, 1] <= ty) & (ty < rect[:, 3])
+        alive = alive & hit
     ids = np.nonzero(alive)[0]          # emission order: ascending id, rows outer, columns inner
     x0, y0, x1 = rect[ids, 0], rect[ids, 1], rect[ids, 2]
     wdt = x1 - x0
