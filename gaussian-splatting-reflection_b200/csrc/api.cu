@@ -64,6 +64,7 @@ SurfelGeom SurfelGeom::carve(void* base, size_t P, size_t* bytes) {
   g.clamped = c.take<uint8_t>(P);
   g.rects = c.take<uint2>(P);
   g.rec = c.take<SurfelRec>(P);
+  g.cull = c.take<uint2>(P);
   g.scan_state = c.take<uint32_t>(scan_state_words((int)P));
   g.flags = c.take<int>(4);
   if (bytes) *bytes = c.used + 128;

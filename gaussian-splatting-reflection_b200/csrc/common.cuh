@@ -91,6 +91,7 @@ struct SurfelGeom {
   uint8_t* clamped;         // [P] bit c = colour channel c clamped at 0
   uint2* rects;             // [P] tile rect: x = x0 | x1<<16, y = y0 | y1<<16 (only valid if tiles_touched>0)
   SurfelRec* rec;           // [P]
+  uint2* cull;              // [P] conservative pixel bbox of {alpha >= 1/255}: x = xmin | xmax<<16, y = ymin | ymax<<16
   uint32_t* scan_state;     // decoupled look-back tile states
   int* flags;               // [4] error flags (prefiltered violation, ...)
   static SurfelGeom carve(void* base, size_t P, size_t* bytes);

@@ -19,6 +19,7 @@ struct CompBwdArgs {
   const uint2* ranges;
   const uint32_t* point_list;
   const SurfelRec* rec;
+  const uint2* cull;
   const float* bg;
   const float* accum;         // [3,N] final T, M1, M2
   const uint32_t* n_contrib;  // [2,N]
@@ -44,8 +45,9 @@ __device__ __forceinline__ void rs_step(float* v, int m, bool upper) {
 __global__ void __launch_bounds__(BATCH, 2) surfel_composite_bwd_kernel(const CompBwdArgs a) {
   __shared__ SurfelRec s_rec[2][BATCH];
   __shared__ int s_id[2][BATCH];
+  __shared__ uint8_t s_hit[2][BATCH];   // bit w: the entry's cull box overlaps warp w's 8x4 pixel block
 
-  const int t = threadIdx.x, lane = t & 31;
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const int tile = blockIdx.x;
   const int tile_x = tile % a.gx, tile_y = tile / a.gx;
   int lx, ly;
@@ -69,7 +71,6 @@ __global__ void __launch_bounds__(BATCH, 2) surfel_composite_bwd_kernel(const Co
 
   const float T_final = inside ? a.accum[pix_id] : 0.0f;
   float T = T_final;
-  uint32_t contributor = (uint32_t)n;
   const uint32_t last_contributor = inside ? a.n_contrib[pix_id] : 0u;
   const uint32_t median_contributor = inside ? a.n_contrib[pix_id + N] : 0u;
   const float final_D = inside ? a.accum[pix_id + N] : 0.0f;
@@ -103,8 +104,11 @@ __global__ void __launch_bounds__(BATCH, 2) surfel_composite_bwd_kernel(const Co
   const bool live = inside;
 
   const uint32_t* pl = a.point_list + range.x;
+  uint2 cull_cur = make_uint2(1u, 1u);
   auto stage = [&](int buf, int id) {
+    cull_cur = make_uint2(1u, 1u);
     if (id >= 0) {
+      cull_cur = __ldg(a.cull + id);
       const SurfelRec* g = a.rec + id;
       SurfelRec* d = &s_rec[buf][t];
 #pragma unroll
@@ -121,8 +125,18 @@ __global__ void __launch_bounds__(BATCH, 2) surfel_composite_bwd_kernel(const Co
   // still take part in the staging and barriers.
   const uint32_t warp_last = __reduce_max_sync(0xffffffffu, live ? last_contributor : 0u);
 
+  const int tx0 = tile_x * TILE_X, ty0 = tile_y * TILE_Y;
   for (int i = 0; i < rounds; ++i) {
     cp_async_wait_all();
+    {
+      const uint2 cb = cull_cur;
+      const int bx0 = (int)(cb.x & 0xffffu) - tx0, bx1 = (int)(cb.x >> 16) - tx0;
+      const int by0 = (int)(cb.y & 0xffffu) - ty0, by1 = (int)(cb.y >> 16) - ty0;
+      const unsigned col = ((bx0 <= 7 && bx1 >= 0) ? 0x55u : 0u) | ((bx0 <= 15 && bx1 >= 8) ? 0xAAu : 0u);
+      const unsigned row = ((by0 <= 3 && by1 >= 0) ? 0x03u : 0u) | ((by0 <= 7 && by1 >= 4) ? 0x0Cu : 0u) |
+                           ((by0 <= 11 && by1 >= 8) ? 0x30u : 0u) | ((by0 <= 15 && by1 >= 12) ? 0xC0u : 0u);
+      s_hit[i & 1][t] = (uint8_t)(col & row);
+    }
     __syncthreads();
     if (i + 1 < rounds) {
       stage((i + 1) & 1, id_next);
@@ -138,14 +152,19 @@ __global__ void __launch_bounds__(BATCH, 2) surfel_composite_bwd_kernel(const Co
       const int first_pos = n - i * BATCH;  // `contributor` value before this batch
       if ((uint32_t)first_pos > warp_last) j0 = min(count, first_pos - (int)warp_last);
     }
-    contributor -= (uint32_t)j0;
-    for (int j = j0; j < count; ++j) {
-      contributor--;
+#pragma unroll 1
+    for (int r = j0 >> 5; r < (count + 31) >> 5; ++r) {
+      unsigned m = __ballot_sync(0xffffffffu, (s_hit[buf][r * 32 + lane] >> warp) & 1u);
+      if (r == (j0 >> 5)) m &= 0xffffffffu << (j0 & 31);   // entries behind every pixel's last contributor
+      while (m) {
+      const int j = r * 32 + __ffs(m) - 1;
+      m &= m - 1;
+      const uint32_t contributor = (uint32_t)(n - 1 - (i * BATCH + j));   // 0-based list position
       const float4 q0 = rb[j].q[0], q1 = rb[j].q[1], q2 = rb[j].q[2];
       SurfelHit h;
       bool c = live && contributor < last_contributor;
       c = surfel_eval<true>(q0, q1, q2, fx, fy, h) && c;
-      if (!__any_sync(0xffffffffu, c)) continue;
+      if (!__any_sync(0xffffffffu, c)) continue;   // next set bit of m
 
       float g[20];
 #pragma unroll
@@ -220,6 +239,7 @@ __global__ void __launch_bounds__(BATCH, 2) surfel_composite_bwd_kernel(const Co
       rs_step<2>(g, 2, b2);
       rs_step<1>(g, 1, b1);
       if (comp_valid) atomicAdd(a.acc + (size_t)s_id[buf][j] * ACC_STRIDE + comp, g[0]);
+      }
     }
   }
   cp_async_wait_all();
@@ -231,7 +251,7 @@ int surfel_composite_backward(const b200gs_surfel_bwd& f, const SurfelGeom& g, c
   a.W = f.width; a.H = f.height;
   a.gx = (f.width + TILE_X - 1) / TILE_X;
   const int gy = (f.height + TILE_Y - 1) / TILE_Y;
-  a.ranges = im.ranges; a.point_list = b.point_list; a.rec = g.rec; a.bg = f.background;
+  a.ranges = im.ranges; a.point_list = b.point_list; a.rec = g.rec; a.cull = g.cull; a.bg = f.background;
   a.accum = im.accum; a.n_contrib = im.n_contrib;
   a.dL_dpix = f.dL_dout_color; a.dL_dothers = f.dL_dout_others; a.dL_drefl = f.dL_dout_refl;
   a.acc = acc;

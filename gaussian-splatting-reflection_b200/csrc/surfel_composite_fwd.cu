@@ -18,6 +18,7 @@ struct CompFwdArgs {
   const uint2* ranges;
   const uint32_t* point_list;
   const SurfelRec* rec;
+  const uint2* cull;
   const float* bg;
   float* accum;         // [3,N]
   uint32_t* n_contrib;  // [2,N]
@@ -33,6 +34,7 @@ __global__ void __launch_bounds__(BATCH) surfel_composite_fwd_kernel(const CompF
   __shared__ SurfelRec s_rec[2][BATCH];
   __shared__ int s_id[2][BATCH];
   __shared__ int s_wmax[2][BATCH];
+  __shared__ uint8_t s_hit[2][BATCH];   // bit w: the entry's cull box overlaps warp w's 8x4 pixel block
 
   const int t = threadIdx.x, lane = t & 31;
   const int tile = blockIdx.x;
@@ -51,7 +53,7 @@ __global__ void __launch_bounds__(BATCH) surfel_composite_fwd_kernel(const CompF
 
   bool done = !inside;
   float T = 1.0f;
-  uint32_t contributor = 0, last_contributor = 0;
+  uint32_t last_contributor = 0;
   float C0 = 0.f, C1 = 0.f, C2 = 0.f, refl = 0.f, mask = 0.f;
   float N0 = 0.f, N1 = 0.f, N2 = 0.f, D = 0.f, M1 = 0.f, M2 = 0.f, distortion = 0.f, median_depth = 0.f;
   float median_contributor = -1.0f;
@@ -60,8 +62,11 @@ __global__ void __launch_bounds__(BATCH) surfel_composite_fwd_kernel(const CompF
   s_wmax[1][t] = 0;
 
   const uint32_t* pl = a.point_list + range.x;
+  uint2 cull_cur = make_uint2(1u, 1u);   // cull box of the entry this thread staged for the batch about to run
   auto stage = [&](int buf, int id) {
+    cull_cur = make_uint2(1u, 1u);       // "nothing": padding entries are never visited
     if (id >= 0) {
+      cull_cur = __ldg(a.cull + id);
       const SurfelRec* g = a.rec + id;
       SurfelRec* d = &s_rec[buf][t];
 #pragma unroll
@@ -74,9 +79,21 @@ __global__ void __launch_bounds__(BATCH) surfel_composite_fwd_kernel(const CompF
   stage(0, id_next);
   id_next = (BATCH + t < n) ? (int)pl[BATCH + t] : -1;
 
+  const int warp = t >> 5;
+  const int tx0 = tile_x * TILE_X, ty0 = tile_y * TILE_Y;
   int last_batch = -1;
   for (int i = 0; i < rounds; ++i) {
     cp_async_wait_all();
+    {  // which of the 8 warp blocks can this thread's entry reach alpha >= 1/255 in?
+      const uint2 cb = cull_cur;
+      const int bx0 = (int)(cb.x & 0xffffu) - tx0, bx1 = (int)(cb.x >> 16) - tx0;
+      const int by0 = (int)(cb.y & 0xffffu) - ty0, by1 = (int)(cb.y >> 16) - ty0;
+      const unsigned col = ((bx0 <= 7 && bx1 >= 0) ? 0x55u : 0u) | ((bx0 <= 15 && bx1 >= 8) ? 0xAAu : 0u);
+      const unsigned row = ((by0 <= 3 && by1 >= 0) ? 0x03u : 0u) | ((by0 <= 7 && by1 >= 4) ? 0x0Cu : 0u) |
+                           ((by0 <= 11 && by1 >= 8) ? 0x30u : 0u) | ((by0 <= 15 && by1 >= 12) ? 0xC0u : 0u);
+      // s_hit[i&1] was last read while blending batch i-2; everyone left that before the barrier of i-1
+      s_hit[i & 1][t] = (uint8_t)(col & row);
+    }
     // batch i has landed for everyone, and everyone is past batch i-1
     if (__syncthreads_count(done) == BATCH) break;
     if (i > 0) {  // publish and clear the per-Gaussian weight maxima of batch i-1
@@ -91,45 +108,51 @@ __global__ void __launch_bounds__(BATCH) surfel_composite_fwd_kernel(const CompF
     }
     last_batch = i;
     const int buf = i & 1;
-    const int count = min(BATCH, n - i * BATCH);
     const SurfelRec* rb = s_rec[buf];
-    for (int j = 0; j < count; ++j) {
-      if (__all_sync(0xffffffffu, done)) break;
-      contributor++;  // for finished pixels this is never read again
-      const float4 q0 = rb[j].q[0], q1 = rb[j].q[1], q2 = rb[j].q[2];
-      SurfelHit h;
-      bool c = surfel_eval<false>(q0, q1, q2, fx, fy, h) && !done;
-      float w = 0.0f;
-      if (c) {
-        const float test_T = __fmul_rn(T, __fsub_rn(1.0f, h.alpha));
-        if (test_T < 0.0001f) {
-          done = true;
-          c = false;
-        } else {
-          const float4 q3 = rb[j].q[3], q4 = rb[j].q[4];
-          w = __fmul_rn(T, h.alpha);
-          const float A = __fsub_rn(1.0f, T);
-          const float m = ndc_depth(h.depth);
-          const float mm = __fmul_rn(m, m);
-          // distortion += (m*m*A + M2 - 2*m*M1) * w   (forward.cu:424)
-          const float e = __fmaf_rn(-M1, __fadd_rn(m, m), __fmaf_rn(A, mm, M2));
-          distortion = __fmaf_rn(e, w, distortion);
-          D = __fmaf_rn(h.depth, w, D);
-          M1 = __fmaf_rn(m, w, M1);
-          M2 = __fmaf_rn(mm, w, M2);
-          if (T > 0.5f) { median_depth = h.depth; median_contributor = (float)contributor; }
-          N0 = __fmaf_rn(w, q3.x, N0); N1 = __fmaf_rn(w, q3.y, N1); N2 = __fmaf_rn(w, q3.z, N2);
-          C0 = __fmaf_rn(w, q4.x, C0); C1 = __fmaf_rn(w, q4.y, C1); C2 = __fmaf_rn(w, q4.z, C2);
-          refl = __fmaf_rn(w, q3.w, refl);
-          if (q4.w != 0.0f) mask = 1.0f;
-          T = test_T;
-          last_contributor = contributor;
+    bool warp_done = false;
+#pragma unroll 1
+    for (int r = 0; r < BATCH / 32 && !warp_done; ++r) {
+      unsigned m = __ballot_sync(0xffffffffu, (s_hit[buf][r * 32 + lane] >> warp) & 1u);
+      while (m) {
+        if (__all_sync(0xffffffffu, done)) { warp_done = true; break; }
+        const int j = r * 32 + __ffs(m) - 1;
+        m &= m - 1;
+        const uint32_t contributor = (uint32_t)(i * BATCH + j + 1);  // 1-based position in the tile's list
+        const float4 q0 = rb[j].q[0], q1 = rb[j].q[1], q2 = rb[j].q[2];
+        SurfelHit h;
+        bool c = surfel_eval<false>(q0, q1, q2, fx, fy, h) && !done;
+        float w = 0.0f;
+        if (c) {
+          const float test_T = __fmul_rn(T, __fsub_rn(1.0f, h.alpha));
+          if (test_T < 0.0001f) {
+            done = true;
+            c = false;
+          } else {
+            const float4 q3 = rb[j].q[3], q4 = rb[j].q[4];
+            w = __fmul_rn(T, h.alpha);
+            const float A = __fsub_rn(1.0f, T);
+            const float m_ = ndc_depth(h.depth);
+            const float mm = __fmul_rn(m_, m_);
+            // distortion += (m*m*A + M2 - 2*m*M1) * w   (forward.cu:424)
+            const float e = __fmaf_rn(-M1, __fadd_rn(m_, m_), __fmaf_rn(A, mm, M2));
+            distortion = __fmaf_rn(e, w, distortion);
+            D = __fmaf_rn(h.depth, w, D);
+            M1 = __fmaf_rn(m_, w, M1);
+            M2 = __fmaf_rn(mm, w, M2);
+            if (T > 0.5f) { median_depth = h.depth; median_contributor = (float)contributor; }
+            N0 = __fmaf_rn(w, q3.x, N0); N1 = __fmaf_rn(w, q3.y, N1); N2 = __fmaf_rn(w, q3.z, N2);
+            C0 = __fmaf_rn(w, q4.x, C0); C1 = __fmaf_rn(w, q4.y, C1); C2 = __fmaf_rn(w, q4.z, C2);
+            refl = __fmaf_rn(w, q3.w, refl);
+            if (q4.w != 0.0f) mask = 1.0f;
+            T = test_T;
+            last_contributor = contributor;
+          }
         }
-      }
-      // gaussian_weights[id] = max over pixels of w  (forward.cu:457-459, made exact)
-      if (__any_sync(0xffffffffu, c)) {
-        const int wm = __reduce_max_sync(0xffffffffu, __float_as_int(w));
-        if (lane == 0) atomicMax(&s_wmax[buf][j], wm);
+        // gaussian_weights[id] = max over pixels of w  (forward.cu:457-459, made exact)
+        if (__any_sync(0xffffffffu, c)) {
+          const int wm = __reduce_max_sync(0xffffffffu, __float_as_int(w));
+          if (lane == 0) atomicMax(&s_wmax[buf][j], wm);
+        }
       }
     }
   }
@@ -168,7 +191,7 @@ int surfel_composite_forward(const b200gs_surfel_fwd& f, const SurfelGeom& g, co
   a.W = f.width; a.H = f.height;
   a.gx = (f.width + TILE_X - 1) / TILE_X;
   const int gy = (f.height + TILE_Y - 1) / TILE_Y;
-  a.ranges = im.ranges; a.point_list = b.point_list; a.rec = g.rec; a.bg = f.background;
+  a.ranges = im.ranges; a.point_list = b.point_list; a.rec = g.rec; a.cull = g.cull; a.bg = f.background;
   a.accum = im.accum; a.n_contrib = im.n_contrib;
   a.out_color = f.out_color; a.out_others = f.out_others; a.out_refl = f.out_refl;
   a.gaussian_weights = f.gaussian_weights;

@@ -43,6 +43,7 @@ struct SurfelPreArgs {
   uint8_t* clamped;
   uint2* rects;
   SurfelRec* rec;
+  uint2* cull;
   int* flags;
 };
 
@@ -98,6 +99,42 @@ __device__ __forceinline__ void sh_to_rgb(int deg, const float* __restrict__ sh,
     if (r[c] < 0.0f) clamp_bits |= 1u << c;
     out[c] = fmaxf(r[c], 0.0f);
   }
+}
+
+// Conservative pixel bounding box of the region where this Gaussian can reach
+// alpha = min(0.99, opa*exp(-rho/2)) >= 1/255, i.e. rho = min(rho3d, rho2d) <= 2 ln(255 opa):
+// the union of (a) the AABB of the projected ellipse {rho3d <= c2} -- the same closed form as
+// compute_aabb (forward.cu:119-145) with cutoff^2 = c2 -- and (b) the low-pass disk
+// {2 |xy - pix|^2 <= c2}.  The compositing kernels use it only to skip (warp, Gaussian) pairs
+// none of whose 32 pixels can pass the reference's `alpha < 1/255` cut, so results stay
+// bit-identical; when the ellipse is unbounded or the arithmetic is doubtful the box is "everything".
+__device__ __forceinline__ uint2 cull_bbox(const float* Tu, const float* Tv, const float* Tw, float cx, float cy,
+                                           float opa) {
+  const uint2 everything = make_uint2(0xffff0000u, 0xffff0000u);
+  const uint2 nothing = make_uint2(0x00000001u, 0x00000001u);  // min 1 > max 0
+  if (!(opa >= 0.0f)) return everything;                        // NaN / negative: leave it to the exact test
+  if (opa < 0.0039f) return nothing;                            // opa*G <= opa < 1/255 always
+  float c2 = 2.0f * logf(255.0f * opa);
+  c2 = c2 * 1.001f + 0.01f;                                     // slack >> fp32 error of rho and expf
+  const float d = c2 * (Tw[0] * Tw[0] + Tw[1] * Tw[1]) - Tw[2] * Tw[2];
+  if (!(d < -1e-6f * Tw[2] * Tw[2])) return everything;         // ellipse not bounded (or nearly so)
+  const float f0 = c2 / d, f2 = -1.0f / d;
+  const float ex = f0 * (Tu[0] * Tw[0] + Tu[1] * Tw[1]) + f2 * Tu[2] * Tw[2];
+  const float ey = f0 * (Tv[0] * Tw[0] + Tv[1] * Tw[1]) + f2 * Tv[2] * Tw[2];
+  const float hx2 = ex * ex - (f0 * (Tu[0] * Tu[0] + Tu[1] * Tu[1]) + f2 * Tu[2] * Tu[2]);
+  const float hy2 = ey * ey - (f0 * (Tv[0] * Tv[0] + Tv[1] * Tv[1]) + f2 * Tv[2] * Tv[2]);
+  if (!(hx2 == hx2) || !(hy2 == hy2) || !(fabsf(ex) < 1e7f) || !(fabsf(ey) < 1e7f)) return everything;
+  const float hx = sqrtf(fmaxf(hx2, 0.0f)), hy = sqrtf(fmaxf(hy2, 0.0f));
+  const float r2 = sqrtf(0.5f * c2);
+  // 1-pixel geometric margin plus a relative one for large coordinates
+  const float mx = 1.0f + 1e-4f * (fabsf(ex) + hx + fabsf(cx)), my = 1.0f + 1e-4f * (fabsf(ey) + hy + fabsf(cy));
+  const float x0 = fminf(ex - hx, cx - r2) - mx, x1 = fmaxf(ex + hx, cx + r2) + mx;
+  const float y0 = fminf(ey - hy, cy - r2) - my, y1 = fmaxf(ey + hy, cy + r2) + my;
+  if (!(x0 == x0) || !(x1 == x1) || !(y0 == y0) || !(y1 == y1)) return everything;
+  if (x1 < 0.0f || y1 < 0.0f || x0 > 65535.0f || y0 > 65535.0f) return nothing;
+  const unsigned ix0 = (unsigned)fmaxf(floorf(x0), 0.0f), ix1 = (unsigned)fminf(ceilf(x1), 65535.0f);
+  const unsigned iy0 = (unsigned)fmaxf(floorf(y0), 0.0f), iy1 = (unsigned)fminf(ceilf(y1), 65535.0f);
+  return make_uint2(ix0 | (ix1 << 16), iy0 | (iy1 << 16));
 }
 
 __global__ void __launch_bounds__(256) surfel_preprocess_kernel(const SurfelPreArgs a) {
@@ -236,6 +273,7 @@ __global__ void __launch_bounds__(256) surfel_preprocess_kernel(const SurfelPreA
   const float opa = a.opacities[idx];
   const float refl = a.refl ? a.refl[idx] : 0.0f;
   const float mk = (a.mask && a.mask[idx]) ? 1.0f : 0.0f;
+  a.cull[idx] = cull_bbox(Tu, Tv, Tw, cx, cy, opa);
   SurfelRec* r = a.rec + idx;
   r->q[0] = make_float4(Tu[0], Tu[1], Tu[2], Tv[0]);
   r->q[1] = make_float4(Tv[1], Tv[2], Tw[0], Tw[1]);
@@ -254,7 +292,7 @@ int surfel_preprocess(const b200gs_surfel_fwd& a, const SurfelGeom& g, cudaStrea
   k.refl = a.refl_strengths; k.mask = a.env_scope_mask;
   k.viewmatrix = a.viewmatrix; k.projmatrix = a.projmatrix; k.campos = a.campos;
   k.radii = a.radii; k.depths = g.depths; k.tiles_touched = g.tiles_touched; k.clamped = g.clamped;
-  k.rects = g.rects; k.rec = g.rec; k.flags = g.flags;
+  k.rects = g.rects; k.rec = g.rec; k.cull = g.cull; k.flags = g.flags;
   StageScope _t(ST_PREPROCESS, s);
   B200GS_CUDA(cudaMemsetAsync(g.flags, 0, 4 * sizeof(int), s));
   surfel_preprocess_kernel<<<(a.P + 255) / 256, 256, 0, s>>>(k);
