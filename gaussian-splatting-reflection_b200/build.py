@@ -24,6 +24,9 @@ FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std
          "-DB200GS_BUILD"]
 
 
+FAST_MATH = {"cubemap.cu"}
+
+
 def _sources():
     return sorted(f for f in os.listdir(CSRC) if f.endswith(".cu"))
 
@@ -45,7 +48,8 @@ def build(force=False, verbose=False):
         o = os.path.join(OBJ, src[:-3] + ".o")
         objs.append(o)
         if force or not os.path.exists(o) or os.path.getmtime(o) < max(os.path.getmtime(s), hm):
-            jobs.append([NVCC] + FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", s, "-o", o])
+            extra = ["--use_fast_math"] if src in FAST_MATH else []   # same flag as the reference's C/setup.py:6-11
+            jobs.append([NVCC] + FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-c", s, "-o", o])
 
     def run(cmd):
         r = subprocess.run(cmd, capture_output=True, text=True)

@@ -102,6 +102,11 @@ inspect_binning = _sig("b200gs_inspect_binning", _i, _p, _i, _p, _p, _p)
 surfel_inspect_image = _sig("b200gs_surfel_inspect_image", _i, _p, _i, _i, _p, _p, _p, _p)
 
 
+_u = C.c_uint32
+cubemap_forward = _sig("b200gs_cubemap_forward", _i, _p, _p, _p, _p, _u, _u, _u, _u, _u, _p)
+cubemap_backward = _sig("b200gs_cubemap_backward", _i, _p, _p, _p, _p, _p, _p, _u, _u, _u, _u, _u, _p)
+
+
 def check(rc):
     """Map a C return code to an exception (the reference throws std::runtime_error
     -> Python RuntimeError; S/rasterize_points.cu:63-65, auxiliary.h:300-307)."""

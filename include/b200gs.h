@@ -164,6 +164,19 @@ int b200gs_surfel_inspect_image(const void* img, int width, int height,
                                 float* accum_alpha /*[3,N]*/, uint32_t* n_contrib /*[2,N]*/,
                                 uint32_t* ranges /*[T,2]*/, void* stream);
 
+/* ------------------------------------------------------------------------ */
+/* Cubemap environment lookup (C/src/cubemapencoder.h:6-17, cubemapencoder.cu:430-488,
+ * :713-779).  fp32.  inputs [B,3] directions; cubemap [6,C,L,L]; fail_value [C];
+ * outputs / grad_outputs are CHANNEL-MAJOR [C,B] like the reference's.  interp 0 =
+ * nearest, 1 = bilinear; seamless != 0 = cross-face filtering (the mode the fork uses).
+ * backward: grad_cubemap [6,C,L,L] and grad_fail [C] must be zero-filled by the caller
+ * (the reference's Python does torch.zeros_like); grad_inputs [B,3] is fully written.  */
+int b200gs_cubemap_forward(const float* inputs, const float* cubemap, const float* fail_value, float* outputs,
+                           uint32_t interp, uint32_t seamless, uint32_t B, uint32_t C, uint32_t L, void* stream);
+int b200gs_cubemap_backward(const float* grad_outputs, const float* inputs, const float* cubemap, float* grad_cubemap,
+                            float* grad_inputs, float* grad_fail, uint32_t interp, uint32_t seamless, uint32_t B,
+                            uint32_t C, uint32_t L, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

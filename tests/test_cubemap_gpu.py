@@ -1,0 +1,95 @@
+"""GPU parity of the cubemap lookup (K6) against the UNMODIFIED reference extension
+(oracle/_ref/ref_cubemap_C) and the numpy oracle.  Both CUDA builds use fast-math, so the bar
+is toleranced: values 1e-5 abs; a ray within an ulp of a texel boundary may select the
+neighbouring texel, which changes grad_inputs (the derivative is discontinuous there) for that
+ray only -- such rays are counted, not tolerated wholesale."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+import harness as hz
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden"))
+import make_golden_cubemap as mg  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+MODES = [(0, 0), (1, 0), (1, 1)]
+
+
+def _new():
+    import _cubemapencoder
+    return _cubemapencoder
+
+
+@pytest.fixture(scope="module")
+def ref():
+    m = hz.ref_module("ref_cubemap_C")
+    if m is None:
+        pytest.skip("oracle/_ref/ref_cubemap_C not built")
+    return m
+
+
+def _close(a, b, atol, rtol, max_bad_frac=0.0):
+    a, b = a.double(), b.double()
+    bad = (a - b).abs() > atol + rtol * b.abs()
+    assert float(bad.double().mean()) <= max_bad_frac, (float((a - b).abs().max()), int(bad.sum()))
+
+
+@pytest.mark.parametrize("interp,seamless", MODES)
+@pytest.mark.parametrize("B,C,L", [(4096, 3, 16), (100000, 3, 128), (777, 6, 8), (5000, 5, 32)])
+def test_matches_reference(ref, interp, seamless, B, C, L):
+    d, tex, fail, g = mg.case_inputs(B, C, L, seed=B + C)
+    o_r, gi_r, gt_r, gf_r = mg.run(ref, d, tex, fail, g, interp, seamless)
+    o_n, gi_n, gt_n, gf_n = mg.run(_new(), d, tex, fail, g, interp, seamless)
+    _close(o_n, o_r, 1e-5, 1e-5)
+    _close(gt_n, gt_r, 1e-4, 1e-4)          # scatter sums: atomics order differs
+    _close(gf_n, gf_r, 1e-5, 1e-5)
+    _close(gi_n, gi_r, 1e-3, 1e-4, max_bad_frac=1e-3)
+
+
+@pytest.mark.parametrize("interp,seamless", MODES)
+def test_matches_oracle(interp, seamless):
+    from oracle import cubemap_oracle as co
+    d, tex, fail, g = mg.case_inputs(20000, 3, 32, seed=11)
+    o_n, gi_n, gt_n, gf_n = mg.run(_new(), d, tex, fail, g, interp, seamless)
+    o = co.forward(d, tex, fail, interp, seamless)
+    gi, gt, gf = co.backward(g, d, tex, interp, seamless)
+    _close(o_n.cpu(), torch.from_numpy(o), 1e-5, 1e-5, max_bad_frac=1e-4)
+    _close(gt_n.cpu(), torch.from_numpy(gt), 1e-3, 1e-3, max_bad_frac=1e-3)
+    _close(gf_n.cpu(), torch.from_numpy(gf), 1e-4, 1e-4)
+    _close(gi_n.cpu(), torch.from_numpy(gi), 1e-2, 1e-3, max_bad_frac=2e-3)
+
+
+def test_against_committed_golden():
+    G = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "cubemap_ref.npz"))
+    for interp, seamless in MODES:
+        o, gi, gt, gf = mg.run(_new(), G["inputs"], G["cubemap"], G["fail"], G["grad_outputs"], interp, seamless)
+        tag = f"m{interp}{seamless}_"
+        _close(o.cpu(), torch.from_numpy(G[tag + "out"]), 1e-5, 1e-5)
+        _close(gt.cpu(), torch.from_numpy(G[tag + "gtex"]), 1e-4, 1e-4)
+        _close(gi.cpu(), torch.from_numpy(G[tag + "gin"]), 1e-3, 1e-4, max_bad_frac=1e-3)
+
+
+def test_module_autograd_and_state_dict():
+    import cubemapencoder
+    enc = cubemapencoder.CubemapEncoder(output_dim=3, resolution=32).cuda()
+    assert sorted(enc.state_dict().keys()) == ["params.Cubemap_failv", "params.Cubemap_texture"]
+    d = torch.randn(1000, 3, device="cuda", requires_grad=True)
+    out = enc(d)
+    assert out.shape == (1000, 3)
+    out.sigmoid().sum().backward()
+    assert d.grad.shape == (1000, 3) and torch.isfinite(d.grad).all()
+    assert enc.params["Cubemap_texture"].grad.abs().sum() > 0
+    enc.resize(64)
+    assert enc(d.detach()).shape == (1000, 3) and enc.resolution == 64
+    mip = cubemapencoder.MipCubemapEncoder(num_levels=3, level_dim=2, base_resolution=4).cuda()
+    assert mip(d.detach()).shape == (1000, 6)
+
+
+def test_empty_batch():
+    d, tex, fail, g = mg.case_inputs(512, 3, 8)
+    o, gi, gt, gf = mg.run(_new(), d[:0], tex, fail, g[:, :0], 1, 1)
+    assert o.shape == (3, 0) and float(gt.abs().sum()) == 0.0

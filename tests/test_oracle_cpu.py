@@ -85,3 +85,41 @@ def test_tile_subset_matches_full(run):
         ty, tx = divmod(t, (W + 15) // 16)
         sl = (slice(None), slice(ty * 16, ty * 16 + 16), slice(tx * 16, tx * 16 + 16))
         assert np.array_equal(sub["color"][sl], o["color"][sl])
+
+
+# ---------------------------------------------------------------- cubemap oracle vs reference golden
+CUBE_GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "cubemap_ref.npz")
+
+
+@pytest.mark.parametrize("interp,seamless", [(0, 0), (1, 0), (1, 1)])
+def test_cubemap_oracle_against_reference_golden(interp, seamless):
+    """oracle/cubemap_oracle.py vs the reference extension's outputs (B200, fast-math build)."""
+    from oracle import cubemap_oracle as co
+    G = np.load(CUBE_GOLD)
+    tag = f"m{interp}{seamless}_"
+    o = co.forward(G["inputs"], G["cubemap"], G["fail"], interp, seamless)
+    gi, gt, gf = co.backward(G["grad_outputs"], G["inputs"], G["cubemap"], interp, seamless)
+
+    def bad(a, b, atol, rtol):
+        return float((np.abs(a.astype(np.float64) - b) > atol + rtol * np.abs(b)).mean())
+    assert bad(o, G[tag + "out"], 1e-5, 1e-5) <= 1e-3
+    assert bad(gt, G[tag + "gtex"], 1e-3, 1e-3) <= 1e-3
+    assert bad(gf, G[tag + "gfail"], 1e-4, 1e-4) == 0.0
+    assert bad(gi, G[tag + "gin"], 1e-2, 1e-3) <= 2e-3     # rays on a texel boundary may pick the neighbour
+
+
+def test_cubemap_oracle_gradients_are_derivatives():
+    """finite differences of the oracle forward (fp64) against its own backward."""
+    from oracle import cubemap_oracle as co
+    rng = np.random.default_rng(3)
+    d = rng.normal(size=(400, 3)); tex = rng.uniform(-.5, .5, (6, 2, 8, 8)); fail = np.zeros(2)
+    g = rng.normal(size=(2, 400))
+    gi, gt, _ = co.backward(g, d, tex, 1, 1)
+    eps = 1e-6
+    for idx in ((0, 0, 0, 0), (3, 1, 7, 2), (5, 0, 4, 7)):
+        tp = tex.copy(); tp[idx] += eps
+        fd = ((co.forward(d, tp, fail, 1, 1) - co.forward(d, tex, fail, 1, 1)) * g).sum() / eps
+        assert abs(fd - gt[idx]) <= 1e-5 * max(1.0, abs(fd))
+    dp = d.copy(); dp[:, 1] += 1e-7
+    fd = ((co.forward(dp, tex, fail, 1, 1) - co.forward(d, tex, fail, 1, 1)) * g).sum(0) / 1e-7
+    assert np.median(np.abs(fd - gi[:, 1])) <= 1e-5
