@@ -209,12 +209,21 @@ def main():
     grads = hz.to_dev(scenes.upstream_grads(W, H))
     GRAD_KEYS = ("means3D", "sh", "opacity", "scales", "rotations", "refl")   # the 59 floats / Gaussian of the model
 
+    arena = None
+    if a.impl == "new" and world > 1:
+        from b200gs.dp import GradArena
+        arena = GradArena(P, sc["shs"].shape[1], "cuda")
+        Cmod.use_gradient_arena(arena)       # backward writes the [59 P] gradient block in place
+
     def step():
         f = hz.surfel_forward(Cmod, sc, cam)
         b = hz.surfel_backward(Cmod, sc, cam, f, grads)
         if world > 1:
-            flat = torch.cat([b[k].reshape(P, -1) for k in GRAD_KEYS], 1)
-            dist.all_reduce(flat)
+            if arena is not None:
+                arena.all_reduce()
+            else:                            # reference arm: its gradients are separate tensors
+                flat = torch.cat([b[k].reshape(P, -1) for k in GRAD_KEYS], 1)
+                dist.all_reduce(flat)
         return f, b
 
     def timed(fn, steps, warmup, after_warmup=None):
@@ -260,6 +269,8 @@ def main():
     ms_per_step = total_ms / a.steps
     value = world * N / (ms_per_step * 1e-3) / 1e6
 
+    if arena is not None:
+        Cmod.use_gradient_arena(None)
     # ---- end to end through the drop-in Python API, host inputs ------------------------------
     e2e = None
     if not a.no_e2e:

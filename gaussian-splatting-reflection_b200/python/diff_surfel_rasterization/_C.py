@@ -14,6 +14,16 @@ import b200gs as _b
 
 NUM_CHANNELS = 3
 
+# Optional destination for the parameter gradients (b200gs.dp.GradArena): when set, the backward
+# writes dL_dmeans3D / dL_dsh / dL_dopacity / dL_dscales / dL_drotations / dL_drefl into views of
+# that flat buffer (zero-copy NCCL all-reduce) instead of freshly allocated tensors.
+_grad_arena = None
+
+
+def use_gradient_arena(arena):
+    global _grad_arena
+    _grad_arena = arena
+
 
 def _cuda_f32(name, t):
     if not t.is_cuda:
@@ -126,16 +136,26 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, refl_streng
     M = sh.size(1) if sh.numel() else 0
     o = dict(dtype=torch.float32, device=means3D.device)
     with torch.cuda.device(means3D.device):
-        dL_dmeans3D = torch.zeros((P, 3), **o)
+        arena = _grad_arena
+        if arena is not None and (arena.P != P or arena.M != M or not has_refl or arena.flat.device != means3D.device):
+            raise RuntimeError("gradient arena does not match this call (P, SH coefficients, refl map or device)")
+        if arena is not None:
+            arena.zero_()
+            av = arena.views()
+        dL_dmeans3D = av["means3D"] if arena is not None else torch.zeros((P, 3), **o)
         dL_dmeans2D = torch.zeros((P, 3), **o)
         dL_dcolors = torch.zeros((P, NUM_CHANNELS), **o)
         dL_dnormal = torch.zeros((P, 3), **o)
-        dL_dopacity = torch.zeros((P, 1), **o)
         dL_dtransMat = torch.zeros((P, 9), **o)
-        dL_dsh = torch.zeros((P, M, 3), **o)
-        dL_dscales = torch.zeros((P, 2), **o)
-        dL_drotations = torch.zeros((P, 4), **o)
-        dL_drefl = torch.zeros((P, 1) if has_refl else (0, 1), **o)
+        if arena is not None:
+            dL_dopacity, dL_dsh, dL_dscales = av["opacity"], av["sh"], av["scales"]
+            dL_drotations, dL_drefl = av["rotations"], av["refl"]
+        else:
+            dL_dopacity = torch.zeros((P, 1), **o)
+            dL_dsh = torch.zeros((P, M, 3), **o)
+            dL_dscales = torch.zeros((P, 2), **o)
+            dL_drotations = torch.zeros((P, 4), **o)
+            dL_drefl = torch.zeros((P, 1) if has_refl else (0, 1), **o)
         if P != 0:
             accum = torch.empty((_b.surfel_accum_bytes(P),), dtype=torch.uint8, device=means3D.device)
             a = _b.SurfelBwd(

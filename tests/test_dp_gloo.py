@@ -1,0 +1,78 @@
+"""CPU, world_size 2, gloo: the view-parallel plumbing of b200gs.dp -- view sharding, the flat
+gradient arena and its all-reduce -- checked against a single-process sum.  Per-view gradients
+come from the CPU oracle (tests may use it); the GPU kernels are not involved here."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import scenes
+from b200gs.dp import GradArena, shard_views
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _view_grads(view, n_views, P):
+    from oracle import surfel_oracle as so
+    torch.set_num_threads(1)
+    sc, _ = scenes.build("tiny", P=P)
+    cam = scenes.ring_camera(view, n_views, 48, 32, fovx=0.9)
+    g = scenes.upstream_grads(48, 32, seed=view)
+    _, gr = so.forward_backward(sc, cam, g)
+    return gr
+
+
+def _worker(rank, world, port, n_views, P, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    arena = GradArena(P, 16, "cpu")
+    for v in shard_views(n_views, rank, world):
+        gr = _view_grads(v, n_views, P)
+        for k, dst in arena.views().items():
+            dst += torch.from_numpy(gr[k]).reshape(dst.shape)
+    arena.all_reduce()
+    np.save(os.path.join(out_dir, f"rank{rank}.npy"), arena.flat.numpy())
+    dist.destroy_process_group()
+
+
+def test_shard_views_partition():
+    for world in (1, 2, 4, 8):
+        seen = sorted(v for r in range(world) for v in shard_views(32, r, world))
+        assert seen == list(range(32))
+        assert max(len(shard_views(32, r, world)) for r in range(world)) == 32 // world
+
+
+def test_arena_layout():
+    a = GradArena(10, 16, "cpu")
+    assert a.floats_per_gaussian == 59 and a.flat.numel() == 590
+    v = a.views()
+    assert v["sh"].shape == (10, 16, 3) and v["means3D"].shape == (10, 3) and v["refl"].shape == (10, 1)
+    v["rotations"].fill_(1.0)
+    assert float(a.flat.sum()) == 40.0 and a.flat.data_ptr() == v["means3D"].data_ptr()
+
+
+@pytest.mark.timeout(600)
+def test_two_rank_allreduce_matches_single_process(tmp_path):
+    n_views, P, world = 4, 300, 2
+    port = _free_port()
+    mp.spawn(_worker, args=(world, port, n_views, P, str(tmp_path)), nprocs=world, join=True)
+    r0, r1 = np.load(tmp_path / "rank0.npy"), np.load(tmp_path / "rank1.npy")
+    assert np.array_equal(r0, r1)                      # every rank holds the same reduced gradients
+    ref = GradArena(P, 16, "cpu")
+    for v in range(n_views):
+        gr = _view_grads(v, n_views, P)
+        for k, dst in ref.views().items():
+            dst += torch.from_numpy(gr[k]).reshape(dst.shape)
+    assert np.allclose(r0, ref.flat.numpy(), rtol=1e-5, atol=1e-6)
+    assert np.abs(r0).sum() > 0
