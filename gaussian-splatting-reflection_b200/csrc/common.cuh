@@ -120,6 +120,48 @@ struct Binning {
 //   12..14 dL_dcolor    15 dL_drefl          16..18 dL_dnormal   19 pad
 constexpr int ACC_STRIDE = 20;
 
+// ---------------------------------------------------------------- 3DGS (EWA) path
+// Packed per-Gaussian record of the 3DGS path, 64 B:
+//   q0 = xy.x xy.y conic.x conic.y     q1 = conic.z opacity*h 1/depth refl
+//   q2 = r g b depth                   q3 = n.x n.y n.z 0
+struct __align__(16) GaussRec {
+  float4 q[4];
+};
+static_assert(sizeof(GaussRec) == 64, "record must be 64 B");
+
+struct GaussGeom {
+  float* depths;            // [P]
+  uint32_t* tiles_touched;  // [P]
+  uint32_t* point_offsets;  // [P]
+  uint8_t* clamped;         // [P] bit c
+  uint2* rects;             // [P]
+  GaussRec* rec;            // [P]
+  float* cov3D;             // [P,6] (computed from scale/rotation; unused with cov3D_precomp)
+  uint2* cull;              // [P]
+  uint32_t* scan_state;
+  int* flags;
+  static GaussGeom carve(void* base, size_t P, size_t* bytes);
+};
+
+struct GaussImage {
+  float* accum;         // [N] final T
+  uint32_t* n_contrib;  // [N]
+  uint2* ranges;        // [tiles]
+  static GaussImage carve(void* base, int W, int H, size_t* bytes);
+};
+
+// Backward accumulator of the 3DGS path: 16 floats (64 B) per Gaussian.
+//   0,1 dL_dmean2D.xy   2,3 dL_dmean2D_pixels.xy   4,5,6 dL_dconic x,y,w   7 dL_dopacity
+//   8..10 dL_dcolor     11..13 dL_dnormal          14 dL_drefl             15 dL_dinvdepth
+constexpr int GACC_STRIDE = 16;
+
+int gauss_preprocess(const b200gs_gauss_fwd& a, const GaussGeom& g, cudaStream_t s);
+int gauss_composite_forward(const b200gs_gauss_fwd& a, const GaussGeom& g, const GaussImage& im, const Binning& b,
+                            cudaStream_t s);
+int gauss_composite_backward(const b200gs_gauss_bwd& a, const GaussGeom& g, const GaussImage& im, const Binning& b,
+                             float* acc, cudaStream_t s);
+int gauss_preprocess_backward(const b200gs_gauss_bwd& a, const GaussGeom& g, const float* acc, cudaStream_t s);
+
 // ---------------------------------------------------------------- device helpers
 __device__ __forceinline__ int imin(int a, int b) { return a < b ? a : b; }
 __device__ __forceinline__ int imax(int a, int b) { return a > b ? a : b; }

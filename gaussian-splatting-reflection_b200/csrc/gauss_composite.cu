@@ -1,0 +1,355 @@
+// gauss_composite.cu -- K3g / K4g: per-tile compositing of the 3DGS (EWA) path, forward and
+// reverse-order backward.
+//
+// Restates FORWARD::renderCUDA (G/cuda_rasterizer/forward.cu:274-411) and BACKWARD::renderCUDA
+// (G/cuda_rasterizer/backward.cu:452-690).  Same machinery as the surfel kernels: one CTA per
+// 16x16 tile, 8x4 pixel block per warp, 256-entry batches of packed 64-B records gathered with
+// cp.async into a double-buffered ring, per-warp hit lists from conservative cull boxes, and in the
+// backward a warp reduce-scatter so each (tile, Gaussian) partial leaves as one 64-B vector of
+// RED.ADD.F32 instead of the reference's 15-16 atomicAdds per contributing pixel.
+//
+// The forward arithmetic is pinned to the reference build's contraction (SASS of renderCUDA<3>):
+//   power = fma(fma(dx, con.x*dx, (con.z*dy)*dy), -0.5, -((con.y*dx)*dy));  acc = fma(T, alpha*f, acc).
+#include "surfel_composite.cuh"
+
+namespace b200gs {
+
+constexpr int GBATCH = 256;
+
+struct GaussEval {
+  float dx, dy, G, alpha;
+};
+
+// false when the reference `continue`s (power > 0 or alpha < 1/255).
+__device__ __forceinline__ bool gauss_eval(const float4& q0, const float4& q1, float fx, float fy, GaussEval& e) {
+  e.dx = __fsub_rn(q0.x, fx);
+  e.dy = __fsub_rn(q0.y, fy);
+  const float a = __fmul_rn(__fmul_rn(e.dy, q1.x), e.dy);            // (con.z*dy)*dy
+  const float b = __fmul_rn(__fmul_rn(e.dx, q0.w), e.dy);            // (con.y*dx)*dy
+  const float s = __fmaf_rn(e.dx, __fmul_rn(e.dx, q0.z), a);         // con.x*dx*dx + ...
+  const float power = __fmaf_rn(s, -0.5f, -b);
+  if (power > 0.0f) return false;
+  e.G = expf(power);
+  e.alpha = fminf(0.99f, __fmul_rn(q1.y, e.G));
+  return !(e.alpha < 1.0f / 255.0f);
+}
+
+__device__ __forceinline__ uint8_t warp_hits(uint2 cb, int tx0, int ty0) {
+  const int bx0 = (int)(cb.x & 0xffffu) - tx0, bx1 = (int)(cb.x >> 16) - tx0;
+  const int by0 = (int)(cb.y & 0xffffu) - ty0, by1 = (int)(cb.y >> 16) - ty0;
+  const unsigned col = ((bx0 <= 7 && bx1 >= 0) ? 0x55u : 0u) | ((bx0 <= 15 && bx1 >= 8) ? 0xAAu : 0u);
+  const unsigned row = ((by0 <= 3 && by1 >= 0) ? 0x03u : 0u) | ((by0 <= 7 && by1 >= 4) ? 0x0Cu : 0u) |
+                       ((by0 <= 11 && by1 >= 8) ? 0x30u : 0u) | ((by0 <= 15 && by1 >= 12) ? 0xC0u : 0u);
+  return (uint8_t)(col & row);
+}
+
+struct GCompFwdArgs {
+  int W, H, gx;
+  const uint2* ranges;
+  const uint32_t* point_list;
+  const GaussRec* rec;
+  const uint2* cull;
+  const float* bg;
+  float* accum;
+  uint32_t* n_contrib;
+  float* out_color;
+  float* out_normal;
+  float* out_refl;
+  float* out_invdepth;
+};
+
+__global__ void __launch_bounds__(GBATCH) gauss_composite_fwd_kernel(const GCompFwdArgs a) {
+  __shared__ GaussRec s_rec[2][GBATCH];
+  __shared__ uint8_t s_hit[2][GBATCH];
+
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int tile = blockIdx.x;
+  const int tile_x = tile % a.gx, tile_y = tile / a.gx;
+  int lx, ly;
+  tile_pixel(t, lx, ly);
+  const int pxi = tile_x * TILE_X + lx, pyi = tile_y * TILE_Y + ly;
+  const bool inside = pxi < a.W && pyi < a.H;
+  const float fx = (float)pxi, fy = (float)pyi;
+  const size_t N = (size_t)a.W * a.H;
+  const size_t pix_id = (size_t)a.W * pyi + pxi;
+  const uint2 range = a.ranges[tile];
+  const int n = (int)(range.y - range.x);
+  const int rounds = (n + GBATCH - 1) / GBATCH;
+  const int tx0 = tile_x * TILE_X, ty0 = tile_y * TILE_Y;
+
+  bool done = !inside;
+  float T = 1.0f;
+  uint32_t last_contributor = 0;
+  float C0 = 0.f, C1 = 0.f, C2 = 0.f, N0 = 0.f, N1 = 0.f, N2 = 0.f, refl = 0.f, invd = 0.f;
+
+  const uint32_t* pl = a.point_list + range.x;
+  uint2 cull_cur = make_uint2(1u, 1u);
+  auto stage = [&](int buf, int id) {
+    cull_cur = make_uint2(1u, 1u);
+    if (id >= 0) {
+      cull_cur = __ldg(a.cull + id);
+      const GaussRec* g = a.rec + id;
+      GaussRec* d = &s_rec[buf][t];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) cp_async16(&d->q[k], &g->q[k]);
+    }
+    cp_async_commit();
+  };
+  int id_next = (t < n) ? (int)pl[t] : -1;
+  stage(0, id_next);
+  id_next = (GBATCH + t < n) ? (int)pl[GBATCH + t] : -1;
+
+  for (int i = 0; i < rounds; ++i) {
+    cp_async_wait_all();
+    s_hit[i & 1][t] = warp_hits(cull_cur, tx0, ty0);
+    if (__syncthreads_count(done) == GBATCH) break;
+    if (i + 1 < rounds) {
+      stage((i + 1) & 1, id_next);
+      const int nx = (i + 2) * GBATCH + t;
+      id_next = (nx < n) ? (int)pl[nx] : -1;
+    }
+    const int buf = i & 1;
+    const GaussRec* rb = s_rec[buf];
+    bool warp_done = false;
+#pragma unroll 1
+    for (int r = 0; r < GBATCH / 32 && !warp_done; ++r) {
+      unsigned m = __ballot_sync(0xffffffffu, (s_hit[buf][r * 32 + lane] >> warp) & 1u);
+      while (m) {
+        if (__all_sync(0xffffffffu, done)) { warp_done = true; break; }
+        const int j = r * 32 + __ffs(m) - 1;
+        m &= m - 1;
+        const float4 q0 = rb[j].q[0], q1 = rb[j].q[1];
+        GaussEval e;
+        if (!gauss_eval(q0, q1, fx, fy, e) || done) continue;
+        const float test_T = __fmul_rn(T, __fsub_rn(1.0f, e.alpha));
+        if (test_T < 0.0001f) { done = true; continue; }
+        const float4 q2 = rb[j].q[2], q3 = rb[j].q[3];
+        C0 = __fmaf_rn(T, __fmul_rn(e.alpha, q2.x), C0);
+        C1 = __fmaf_rn(T, __fmul_rn(e.alpha, q2.y), C1);
+        C2 = __fmaf_rn(T, __fmul_rn(e.alpha, q2.z), C2);
+        N0 = __fmaf_rn(T, __fmul_rn(e.alpha, q3.x), N0);
+        N1 = __fmaf_rn(T, __fmul_rn(e.alpha, q3.y), N1);
+        N2 = __fmaf_rn(T, __fmul_rn(e.alpha, q3.z), N2);
+        refl = __fmaf_rn(T, __fmul_rn(e.alpha, q1.w), refl);
+        invd = __fmaf_rn(T, __fmul_rn(e.alpha, q1.z), invd);
+        T = test_T;
+        last_contributor = (uint32_t)(i * GBATCH + j + 1);
+      }
+    }
+  }
+  cp_async_wait_all();
+
+  if (inside) {  // forward.cu:395-410
+    a.accum[pix_id] = T;
+    a.n_contrib[pix_id] = last_contributor;
+    a.out_color[pix_id] = __fmaf_rn(T, a.bg[0], C0);
+    a.out_color[pix_id + N] = __fmaf_rn(T, a.bg[1], C1);
+    a.out_color[pix_id + 2 * N] = __fmaf_rn(T, a.bg[2], C2);
+    a.out_normal[pix_id] = N0;
+    a.out_normal[pix_id + N] = N1;
+    a.out_normal[pix_id + 2 * N] = N2;
+    a.out_refl[pix_id] = refl;
+    if (a.out_invdepth) a.out_invdepth[pix_id] = invd;
+  }
+}
+
+int gauss_composite_forward(const b200gs_gauss_fwd& f, const GaussGeom& g, const GaussImage& im, const Binning& b,
+                            cudaStream_t s) {
+  GCompFwdArgs a;
+  a.W = f.width; a.H = f.height;
+  a.gx = (f.width + TILE_X - 1) / TILE_X;
+  const int gy = (f.height + TILE_Y - 1) / TILE_Y;
+  a.ranges = im.ranges; a.point_list = b.point_list; a.rec = g.rec; a.cull = g.cull; a.bg = f.background;
+  a.accum = im.accum; a.n_contrib = im.n_contrib;
+  a.out_color = f.out_color; a.out_normal = f.out_normal; a.out_refl = f.out_refl; a.out_invdepth = f.out_invdepth;
+  StageScope _t(ST_COMPOSITE_FWD, s);
+  gauss_composite_fwd_kernel<<<a.gx * gy, GBATCH, 0, s>>>(a);
+  B200GS_LAUNCHED("gauss_composite_fwd_kernel", f.debug, s);
+  return B200GS_OK;
+}
+
+// ------------------------------------------------------------------ backward
+struct GCompBwdArgs {
+  int W, H, gx;
+  const uint2* ranges;
+  const uint32_t* point_list;
+  const GaussRec* rec;
+  const uint2* cull;
+  const float* bg;
+  const float* accum;
+  const uint32_t* n_contrib;
+  const float* dL_dpix;      // [3,N]
+  const float* dL_dnormal;   // [3,N]
+  const float* dL_drefl;     // [N] or NULL
+  const float* dL_dinvd;     // [N] or NULL
+  float* acc;                // [P, GACC_STRIDE]
+};
+
+__global__ void __launch_bounds__(GBATCH, 2) gauss_composite_bwd_kernel(const GCompBwdArgs a) {
+  __shared__ GaussRec s_rec[2][GBATCH];
+  __shared__ int s_id[2][GBATCH];
+  __shared__ uint8_t s_hit[2][GBATCH];
+
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int tile = blockIdx.x;
+  const int tile_x = tile % a.gx, tile_y = tile / a.gx;
+  int lx, ly;
+  tile_pixel(t, lx, ly);
+  const int pxi = tile_x * TILE_X + lx, pyi = tile_y * TILE_Y + ly;
+  const bool inside = pxi < a.W && pyi < a.H;
+  const float fx = (float)pxi, fy = (float)pyi;
+  const size_t N = (size_t)a.W * a.H;
+  const size_t pix_id = (size_t)a.W * pyi + pxi;
+  const uint2 range = a.ranges[tile];
+  const int n = (int)(range.y - range.x);
+  const int rounds = (n + GBATCH - 1) / GBATCH;
+  if (n == 0) return;
+  const int tx0 = tile_x * TILE_X, ty0 = tile_y * TILE_Y;
+
+  // lane -> accumulator component owned after the reduce-scatter (16 values, 32 lanes)
+  const int b16 = (lane >> 4) & 1, b8 = (lane >> 3) & 1, b4 = (lane >> 2) & 1, b2 = (lane >> 1) & 1;
+  const int comp = b16 * 8 + b8 * 4 + b4 * 2 + b2;
+  const bool writer = (lane & 1) == 0;
+
+  const float T_final = inside ? a.accum[pix_id] : 0.0f;
+  float T = T_final;
+  const uint32_t last_contributor = inside ? a.n_contrib[pix_id] : 0u;
+  float dpix0 = 0.f, dpix1 = 0.f, dpix2 = 0.f, dn0 = 0.f, dn1 = 0.f, dn2 = 0.f, drefl = 0.f, dinv = 0.f;
+  if (inside) {
+    dpix0 = a.dL_dpix[pix_id]; dpix1 = a.dL_dpix[pix_id + N]; dpix2 = a.dL_dpix[pix_id + 2 * N];
+    dn0 = a.dL_dnormal[pix_id]; dn1 = a.dL_dnormal[pix_id + N]; dn2 = a.dL_dnormal[pix_id + 2 * N];
+    drefl = a.dL_drefl ? a.dL_drefl[pix_id] : 0.0f;
+    dinv = a.dL_dinvd ? a.dL_dinvd[pix_id] : 0.0f;
+  }
+  float bg_dot_dpixel = 0.0f;
+  bg_dot_dpixel += a.bg[0] * dpix0;
+  bg_dot_dpixel += a.bg[1] * dpix1;
+  bg_dot_dpixel += a.bg[2] * dpix2;
+  const float ddelx_dx = 0.5f * a.W, ddely_dy = 0.5f * a.H;
+
+  float acc_c0 = 0.f, acc_c1 = 0.f, acc_c2 = 0.f, last_c0 = 0.f, last_c1 = 0.f, last_c2 = 0.f;
+  float acc_n0 = 0.f, acc_n1 = 0.f, acc_n2 = 0.f, last_n0 = 0.f, last_n1 = 0.f, last_n2 = 0.f;
+  float acc_r = 0.f, last_r = 0.f, acc_i = 0.f, last_i = 0.f, last_alpha = 0.f;
+
+  const uint32_t* pl = a.point_list + range.x;
+  uint2 cull_cur = make_uint2(1u, 1u);
+  auto stage = [&](int buf, int id) {
+    cull_cur = make_uint2(1u, 1u);
+    if (id >= 0) {
+      cull_cur = __ldg(a.cull + id);
+      const GaussRec* g = a.rec + id;
+      GaussRec* d = &s_rec[buf][t];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) cp_async16(&d->q[k], &g->q[k]);
+      s_id[buf][t] = id;
+    }
+    cp_async_commit();
+  };
+  int id_next = (t < n) ? (int)pl[n - 1 - t] : -1;
+  stage(0, id_next);
+  id_next = (GBATCH + t < n) ? (int)pl[n - 1 - (GBATCH + t)] : -1;
+  const uint32_t warp_last = __reduce_max_sync(0xffffffffu, inside ? last_contributor : 0u);
+
+  for (int i = 0; i < rounds; ++i) {
+    cp_async_wait_all();
+    s_hit[i & 1][t] = warp_hits(cull_cur, tx0, ty0);
+    __syncthreads();
+    if (i + 1 < rounds) {
+      stage((i + 1) & 1, id_next);
+      const int nx = (i + 2) * GBATCH + t;
+      id_next = (nx < n) ? (int)pl[n - 1 - nx] : -1;
+    }
+    const int buf = i & 1;
+    const int count = min(GBATCH, n - i * GBATCH);
+    const GaussRec* rb = s_rec[buf];
+    int j0 = 0;
+    {
+      const int first_pos = n - i * GBATCH;
+      if ((uint32_t)first_pos > warp_last) j0 = min(count, first_pos - (int)warp_last);
+    }
+#pragma unroll 1
+    for (int r = j0 >> 5; r < (count + 31) >> 5; ++r) {
+      unsigned m = __ballot_sync(0xffffffffu, (s_hit[buf][r * 32 + lane] >> warp) & 1u);
+      if (r == (j0 >> 5)) m &= 0xffffffffu << (j0 & 31);
+      while (m) {
+        const int j = r * 32 + __ffs(m) - 1;
+        m &= m - 1;
+        const uint32_t contributor = (uint32_t)(n - 1 - (i * GBATCH + j));
+        const float4 q0 = rb[j].q[0], q1 = rb[j].q[1];
+        GaussEval e;
+        bool c = inside && contributor < last_contributor;
+        c = gauss_eval(q0, q1, fx, fy, e) && c;
+        if (!__any_sync(0xffffffffu, c)) continue;
+
+        float g[16];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) g[k] = 0.0f;
+        if (c) {
+          const float4 q2 = rb[j].q[2], q3 = rb[j].q[3];
+          const float alpha = e.alpha, G = e.G;
+          T = T / (1.f - alpha);
+          const float w = alpha * T;                      // dchannel_dcolor
+          const float om = 1.f - last_alpha;
+          float dL_dalpha = 0.0f, dL_dalpha_m = 0.0f;     // backward.cu:596-620 (incl. the running-sum quirk :614)
+          acc_c0 = last_alpha * last_c0 + om * acc_c0; last_c0 = q2.x; dL_dalpha += (q2.x - acc_c0) * dpix0; dL_dalpha_m += dL_dalpha; g[8] = w * dpix0;
+          acc_c1 = last_alpha * last_c1 + om * acc_c1; last_c1 = q2.y; dL_dalpha += (q2.y - acc_c1) * dpix1; dL_dalpha_m += dL_dalpha; g[9] = w * dpix1;
+          acc_c2 = last_alpha * last_c2 + om * acc_c2; last_c2 = q2.z; dL_dalpha += (q2.z - acc_c2) * dpix2; dL_dalpha_m += dL_dalpha; g[10] = w * dpix2;
+          acc_n0 = last_alpha * last_n0 + om * acc_n0; last_n0 = q3.x; dL_dalpha += (q3.x - acc_n0) * dn0; g[11] = w * dn0;
+          acc_n1 = last_alpha * last_n1 + om * acc_n1; last_n1 = q3.y; dL_dalpha += (q3.y - acc_n1) * dn1; g[12] = w * dn1;
+          acc_n2 = last_alpha * last_n2 + om * acc_n2; last_n2 = q3.z; dL_dalpha += (q3.z - acc_n2) * dn2; g[13] = w * dn2;
+          acc_r = last_alpha * last_r + om * acc_r; last_r = q1.w; dL_dalpha += (q1.w - acc_r) * drefl; g[14] = w * drefl;
+          if (a.dL_dinvd) {                                // :643-650
+            const float invd = q1.z;
+            acc_i = last_alpha * last_i + om * acc_i; last_i = invd; dL_dalpha += (invd - acc_i) * dinv; g[15] = w * dinv;
+          }
+          dL_dalpha *= T;
+          dL_dalpha_m *= T;
+          last_alpha = alpha;
+          const float bgterm = (-T_final / (1.f - alpha)) * bg_dot_dpixel;
+          dL_dalpha += bgterm;
+          dL_dalpha_m += bgterm;
+          const float opa = q1.y;
+          const float dL_dG = opa * dL_dalpha, dL_dG_m = opa * dL_dalpha_m;
+          const float gdx = G * e.dx, gdy = G * e.dy;
+          const float dG_ddelx = -gdx * q0.z - gdy * q0.w;
+          const float dG_ddely = -gdy * q1.x - gdx * q0.w;
+          g[0] = dL_dG * dG_ddelx * ddelx_dx;
+          g[1] = dL_dG * dG_ddely * ddely_dy;
+          g[2] = dL_dG_m * dG_ddelx * ddelx_dx;
+          g[3] = dL_dG_m * dG_ddely * ddely_dy;
+          g[4] = -0.5f * gdx * e.dx * dL_dG;
+          g[5] = -0.5f * gdx * e.dy * dL_dG;
+          g[6] = -0.5f * gdy * e.dy * dL_dG;
+          g[7] = G * dL_dalpha;
+        }
+        // warp reduce-scatter 16 -> 8 -> 4 -> 2 -> 1, then the last butterfly
+        rs_step<8>(g, 16, b16);
+        rs_step<4>(g, 8, b8);
+        rs_step<2>(g, 4, b4);
+        rs_step<1>(g, 2, b2);
+        g[0] += __shfl_xor_sync(0xffffffffu, g[0], 1);
+        if (writer) atomicAdd(a.acc + (size_t)s_id[buf][j] * GACC_STRIDE + comp, g[0]);
+      }
+    }
+  }
+  cp_async_wait_all();
+}
+
+int gauss_composite_backward(const b200gs_gauss_bwd& f, const GaussGeom& g, const GaussImage& im, const Binning& b,
+                             float* acc, cudaStream_t s) {
+  GCompBwdArgs a;
+  a.W = f.width; a.H = f.height;
+  a.gx = (f.width + TILE_X - 1) / TILE_X;
+  const int gy = (f.height + TILE_Y - 1) / TILE_Y;
+  a.ranges = im.ranges; a.point_list = b.point_list; a.rec = g.rec; a.cull = g.cull; a.bg = f.background;
+  a.accum = im.accum; a.n_contrib = im.n_contrib;
+  a.dL_dpix = f.dL_dout_color; a.dL_dnormal = f.dL_dout_normal; a.dL_drefl = f.dL_dout_refl; a.dL_dinvd = f.dL_dout_invdepth;
+  a.acc = acc;
+  StageScope _t(ST_COMPOSITE_BWD, s);
+  B200GS_CUDA(cudaMemsetAsync(acc, 0, (size_t)f.P * GACC_STRIDE * sizeof(float), s));
+  gauss_composite_bwd_kernel<<<a.gx * gy, GBATCH, 0, s>>>(a);
+  B200GS_LAUNCHED("gauss_composite_bwd_kernel", f.debug, s);
+  return B200GS_OK;
+}
+
+}  // namespace b200gs

@@ -31,17 +31,6 @@ struct CompBwdArgs {
 
 constexpr int BATCH = 256;
 
-// One recursive-halving step: lanes whose `m` bit is set keep the upper half.
-template <int H>
-__device__ __forceinline__ void rs_step(float* v, int m, bool upper) {
-#pragma unroll
-  for (int i = 0; i < H; ++i) {
-    const float send = upper ? v[i] : v[i + H];
-    const float keep = upper ? v[i + H] : v[i];
-    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, m);
-  }
-}
-
 __global__ void __launch_bounds__(BATCH, 2) surfel_composite_bwd_kernel(const CompBwdArgs a) {
   __shared__ SurfelRec s_rec[2][BATCH];
   __shared__ int s_id[2][BATCH];

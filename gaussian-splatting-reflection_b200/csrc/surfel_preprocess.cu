@@ -18,6 +18,7 @@
 // of the reference's six SoA arrays, so the compositing kernels stage a Gaussian
 // with five 16-B copies.
 #include "common.cuh"
+#include "sh.cuh"
 
 namespace b200gs {
 
@@ -46,60 +47,6 @@ struct SurfelPreArgs {
   uint2* cull;
   int* flags;
 };
-
-// SH degree<=3 colour (forward.cu:20-71).  sh is this Gaussian's [M][3] block.
-__device__ __forceinline__ void sh_to_rgb(int deg, const float* __restrict__ sh, float dx, float dy, float dz,
-                                          float out[3], unsigned& clamp_bits) {
-  // glm: dir / length(dir) is a component-wise division; keep it a division for the same rounding.
-  const float len = __fsqrt_rn(__fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy))));
-  const float x = __fdiv_rn(dx, len), y = __fdiv_rn(dy, len), z = __fdiv_rn(dz, len);
-  // Operation shapes pinned to the reference build's SASS (computeColorFromSH inlined in
-  // preprocessCUDA<3>): every basis term is rounded on its own, then one FFMA per coefficient.
-  float r[3];
-#pragma unroll
-  for (int c = 0; c < 3; ++c) r[c] = __fmul_rn(SH_C0, sh[c]);
-  if (deg > 0) {
-    const float b1 = __fmul_rn(y, SH_C1), b2 = __fmul_rn(z, SH_C1), b3 = __fmul_rn(x, SH_C1);
-#pragma unroll
-    for (int c = 0; c < 3; ++c)
-      r[c] = __fmaf_rn(-b3, sh[9 + c], __fmaf_rn(b2, sh[6 + c], __fmaf_rn(-b1, sh[3 + c], r[c])));
-    if (deg > 1) {
-      const float xx = __fmul_rn(x, x), yy = __fmul_rn(y, y), zz = __fmul_rn(z, z);
-      const float xy = __fmul_rn(x, y), yz = __fmul_rn(y, z), xz = __fmul_rn(x, z);
-      const float zz2 = __fadd_rn(zz, zz);
-      const float xx_yy = __fsub_rn(xx, yy);
-      const float b4 = __fmul_rn(xy, SH_C2_0), b5 = __fmul_rn(yz, SH_C2_1);
-      const float b6 = __fmul_rn(__fsub_rn(__fsub_rn(zz2, xx), yy), SH_C2_2);
-      const float b7 = __fmul_rn(xz, SH_C2_3), b8 = __fmul_rn(xx_yy, SH_C2_4);
-#pragma unroll
-      for (int c = 0; c < 3; ++c)
-        r[c] = __fmaf_rn(b8, sh[24 + c], __fmaf_rn(b7, sh[21 + c], __fmaf_rn(b6, sh[18 + c],
-               __fmaf_rn(b5, sh[15 + c], __fmaf_rn(b4, sh[12 + c], r[c])))));
-      if (deg > 2) {
-        const float a4 = __fsub_rn(__fmaf_rn(zz, 4.0f, -xx), yy);  // 4zz - xx - yy
-        const float b9 = __fmul_rn(__fmul_rn(y, SH_C3_0), __fmaf_rn(xx, 3.0f, -yy));
-        const float b10 = __fmul_rn(__fmul_rn(xy, SH_C3_1), z);
-        const float b11 = __fmul_rn(__fmul_rn(y, SH_C3_2), a4);
-        const float b12 = __fmul_rn(__fmul_rn(z, SH_C3_3), __fmaf_rn(yy, -3.0f, __fmaf_rn(xx, -3.0f, zz2)));
-        const float b13 = __fmul_rn(a4, __fmul_rn(x, SH_C3_4));
-        const float b14 = __fmul_rn(xx_yy, __fmul_rn(z, SH_C3_5));
-        const float b15 = __fmul_rn(__fmul_rn(x, SH_C3_6), __fmaf_rn(yy, -3.0f, xx));
-#pragma unroll
-        for (int c = 0; c < 3; ++c)
-          r[c] = __fmaf_rn(b15, sh[45 + c], __fmaf_rn(b14, sh[42 + c], __fmaf_rn(b13, sh[39 + c],
-                 __fmaf_rn(b12, sh[36 + c], __fmaf_rn(b11, sh[33 + c], __fmaf_rn(b10, sh[30 + c],
-                 __fmaf_rn(b9, sh[27 + c], r[c])))))));
-      }
-    }
-  }
-  clamp_bits = 0;
-#pragma unroll
-  for (int c = 0; c < 3; ++c) {
-    r[c] = __fadd_rn(r[c], 0.5f);
-    if (r[c] < 0.0f) clamp_bits |= 1u << c;
-    out[c] = fmaxf(r[c], 0.0f);
-  }
-}
 
 // Conservative pixel bounding box of the region where this Gaussian can reach
 // alpha = min(0.99, opa*exp(-rho/2)) >= 1/255, i.e. rho = min(rho3d, rho2d) <= 2 ln(255 opa):

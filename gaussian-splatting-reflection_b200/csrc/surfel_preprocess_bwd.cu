@@ -11,6 +11,7 @@
 // Input is the packed [P, ACC_STRIDE] accumulator written by the compositing
 // backward; this kernel unpacks it into the reference's output tensors.
 #include "common.cuh"
+#include "sh.cuh"
 
 namespace b200gs {
 
@@ -39,60 +40,6 @@ struct PreBwdArgs {
   float* dL_dscales;
   float* dL_drot;
 };
-
-struct V3 { float x, y, z; };
-__device__ __forceinline__ V3 operator*(V3 a, V3 b) { return {a.x * b.x, a.y * b.y, a.z * b.z}; }
-__device__ __forceinline__ V3 operator*(float f, V3 a) { return {f * a.x, f * a.y, f * a.z}; }
-__device__ __forceinline__ V3 operator+(V3 a, V3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
-__device__ __forceinline__ float dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
-
-// SH backward (backward.cu:20-139): writes dL_dsh rows, returns dL/d(mean) through the view direction.
-__device__ __forceinline__ V3 sh_backward(int deg, int M, const float* __restrict__ sh, V3 dir_orig, V3 dRGB,
-                                          float* __restrict__ dsh) {
-  const float len = sqrtf(dir_orig.x * dir_orig.x + dir_orig.y * dir_orig.y + dir_orig.z * dir_orig.z);
-  const float x = dir_orig.x / len, y = dir_orig.y / len, z = dir_orig.z / len;
-  V3 dx = {0, 0, 0}, dy = {0, 0, 0}, dz = {0, 0, 0};
-  auto S = [&](int k) { return V3{sh[3 * k], sh[3 * k + 1], sh[3 * k + 2]}; };
-  auto W = [&](int k, float c) { dsh[3 * k] = c * dRGB.x; dsh[3 * k + 1] = c * dRGB.y; dsh[3 * k + 2] = c * dRGB.z; };
-  W(0, SH_C0);
-  if (deg > 0) {
-    W(1, -SH_C1 * y); W(2, SH_C1 * z); W(3, -SH_C1 * x);
-    dx = -SH_C1 * S(3); dy = -SH_C1 * S(1); dz = SH_C1 * S(2);
-    if (deg > 1) {
-      const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
-      W(4, SH_C2_0 * xy); W(5, SH_C2_1 * yz); W(6, SH_C2_2 * (2.f * zz - xx - yy));
-      W(7, SH_C2_3 * xz); W(8, SH_C2_4 * (xx - yy));
-      dx = dx + (SH_C2_0 * y) * S(4) + (SH_C2_2 * 2.f * -x) * S(6) + (SH_C2_3 * z) * S(7) + (SH_C2_4 * 2.f * x) * S(8);
-      dy = dy + (SH_C2_0 * x) * S(4) + (SH_C2_1 * z) * S(5) + (SH_C2_2 * 2.f * -y) * S(6) + (SH_C2_4 * 2.f * -y) * S(8);
-      dz = dz + (SH_C2_1 * y) * S(5) + (SH_C2_2 * 2.f * 2.f * z) * S(6) + (SH_C2_3 * x) * S(7);
-      if (deg > 2) {
-        W(9, SH_C3_0 * y * (3.f * xx - yy)); W(10, SH_C3_1 * xy * z); W(11, SH_C3_2 * y * (4.f * zz - xx - yy));
-        W(12, SH_C3_3 * z * (2.f * zz - 3.f * xx - 3.f * yy)); W(13, SH_C3_4 * x * (4.f * zz - xx - yy));
-        W(14, SH_C3_5 * z * (xx - yy)); W(15, SH_C3_6 * x * (xx - 3.f * yy));
-        dx = dx + (SH_C3_0 * 3.f * 2.f * xy) * S(9) + (SH_C3_1 * yz) * S(10) + (SH_C3_2 * -2.f * xy) * S(11) +
-             (SH_C3_3 * -3.f * 2.f * xz) * S(12) + (SH_C3_4 * (-3.f * xx + 4.f * zz - yy)) * S(13) +
-             (SH_C3_5 * 2.f * xz) * S(14) + (SH_C3_6 * 3.f * (xx - yy)) * S(15);
-        dy = dy + (SH_C3_0 * 3.f * (xx - yy)) * S(9) + (SH_C3_1 * xz) * S(10) +
-             (SH_C3_2 * (-3.f * yy + 4.f * zz - xx)) * S(11) + (SH_C3_3 * -3.f * 2.f * yz) * S(12) +
-             (SH_C3_4 * -2.f * xy) * S(13) + (SH_C3_5 * -2.f * yz) * S(14) + (SH_C3_6 * -3.f * 2.f * xy) * S(15);
-        dz = dz + (SH_C3_1 * xy) * S(10) + (SH_C3_2 * 4.f * 2.f * yz) * S(11) +
-             (SH_C3_3 * 3.f * (2.f * zz - xx - yy)) * S(12) + (SH_C3_4 * 4.f * 2.f * xz) * S(13) +
-             (SH_C3_5 * (xx - yy)) * S(14);
-      }
-    }
-  }
-  (void)M;
-  const V3 ddir = {dot(dx, dRGB), dot(dy, dRGB), dot(dz, dRGB)};
-  // dnormvdv (auxiliary.h:132-142)
-  const V3 v = dir_orig;
-  const float sum2 = v.x * v.x + v.y * v.y + v.z * v.z;
-  const float inv32 = 1.0f / sqrtf(sum2 * sum2 * sum2);
-  V3 r;
-  r.x = ((+sum2 - v.x * v.x) * ddir.x - v.y * v.x * ddir.y - v.z * v.x * ddir.z) * inv32;
-  r.y = (-v.x * v.y * ddir.x + (sum2 - v.y * v.y) * ddir.y - v.z * v.y * ddir.z) * inv32;
-  r.z = (-v.x * v.z * ddir.x - v.y * v.z * ddir.y + (sum2 - v.z * v.z) * ddir.z) * inv32;
-  return r;
-}
 
 __global__ void __launch_bounds__(256) surfel_preprocess_bwd_kernel(const PreBwdArgs a) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;

@@ -63,6 +63,36 @@ class SurfelBwd(C.Structure):
     ]
 
 
+class GaussFwd(C.Structure):
+    """struct b200gs_gauss_fwd"""
+    _fields_ = [
+        ("P", _i), ("sh_degree", _i), ("sh_coeffs", _i), ("width", _i), ("height", _i),
+        ("tan_fovx", _f), ("tan_fovy", _f), ("scale_modifier", _f),
+        ("prefiltered", _i), ("antialiasing", _i), ("debug", _i),
+        ("background", _p), ("means3D", _p), ("shs", _p), ("colors_precomp", _p), ("normals", _p),
+        ("refl_strengths", _p), ("opacities", _p), ("scales", _p), ("rotations", _p), ("cov3D_precomp", _p),
+        ("viewmatrix", _p), ("projmatrix", _p), ("campos", _p),
+        ("geom", _p), ("geom_bytes", _sz), ("img", _p), ("img_bytes", _sz), ("binning", _p), ("binning_bytes", _sz),
+        ("out_color", _p), ("out_invdepth", _p), ("out_normal", _p), ("out_refl", _p), ("radii", _p),
+    ]
+
+
+class GaussBwd(C.Structure):
+    """struct b200gs_gauss_bwd"""
+    _fields_ = [
+        ("P", _i), ("sh_degree", _i), ("sh_coeffs", _i), ("num_rendered", _i), ("width", _i), ("height", _i),
+        ("tan_fovx", _f), ("tan_fovy", _f), ("scale_modifier", _f), ("antialiasing", _i), ("debug", _i),
+        ("background", _p), ("means3D", _p), ("shs", _p), ("colors_precomp", _p), ("opacities", _p), ("scales", _p),
+        ("rotations", _p), ("cov3D_precomp", _p), ("viewmatrix", _p), ("projmatrix", _p), ("campos", _p),
+        ("radii", _p), ("geom", _p), ("binning", _p), ("img", _p),
+        ("dL_dout_color", _p), ("dL_dout_invdepth", _p), ("dL_dout_normal", _p), ("dL_dout_refl", _p),
+        ("accum", _p), ("accum_bytes", _sz),
+        ("dL_dmeans2D", _p), ("dL_dconic", _p), ("dL_dopacity", _p), ("dL_dcolors", _p), ("dL_dnormals", _p),
+        ("dL_drefl", _p), ("dL_dinvdepths", _p), ("dL_dmeans3D", _p), ("dL_dcov3D", _p), ("dL_dsh", _p),
+        ("dL_dscales", _p), ("dL_drotations", _p),
+    ]
+
+
 def _sig(name, restype, *argtypes):
     fn = getattr(lib, name)
     fn.restype = restype
@@ -102,6 +132,14 @@ inspect_binning = _sig("b200gs_inspect_binning", _i, _p, _i, _p, _p, _p)
 surfel_inspect_image = _sig("b200gs_surfel_inspect_image", _i, _p, _i, _i, _p, _p, _p, _p)
 
 
+gauss_geom_bytes = _sig("b200gs_gauss_geom_bytes", _sz, _i)
+gauss_image_bytes = _sig("b200gs_gauss_image_bytes", _sz, _i, _i)
+gauss_accum_bytes = _sig("b200gs_gauss_accum_bytes", _sz, _i)
+gauss_forward_stage1 = _sig("b200gs_gauss_forward_stage1", _i, C.POINTER(GaussFwd), C.POINTER(_i), _p)
+gauss_forward_stage2 = _sig("b200gs_gauss_forward_stage2", _i, C.POINTER(GaussFwd), _i, _p)
+gauss_backward = _sig("b200gs_gauss_backward", _i, C.POINTER(GaussBwd), _p)
+gauss_inspect_geom = _sig("b200gs_gauss_inspect_geom", _i, _p, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p)
+gauss_inspect_image = _sig("b200gs_gauss_inspect_image", _i, _p, _i, _i, _p, _p, _p, _p)
 _u = C.c_uint32
 cubemap_forward = _sig("b200gs_cubemap_forward", _i, _p, _p, _p, _p, _u, _u, _u, _u, _u, _p)
 cubemap_backward = _sig("b200gs_cubemap_backward", _i, _p, _p, _p, _p, _p, _p, _u, _u, _u, _u, _u, _p)

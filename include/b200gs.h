@@ -165,6 +165,90 @@ int b200gs_surfel_inspect_image(const void* img, int width, int height,
                                 uint32_t* ranges /*[T,2]*/, void* stream);
 
 /* ------------------------------------------------------------------------ */
+/* 3DGS (EWA) rasterizer with normal / reflection-strength / inverse-depth channels.
+ * Mirrors CudaRasterizer::Rasterizer::{forward,backward} of the reference's
+ * diff-gaussian-rasterization (G/cuda_rasterizer/rasterizer_impl.cu:198-356, :358-472) as
+ * called from G/rasterize_points.cu:39-286.  Same two-stage forward as the surfel path.     */
+typedef struct b200gs_gauss_fwd {
+  int P, sh_degree, sh_coeffs, width, height;
+  float tan_fovx, tan_fovy, scale_modifier;
+  int prefiltered, antialiasing, debug;
+  const float* background;        /* [3]                                      */
+  const float* means3D;           /* [P,3]                                    */
+  const float* shs;               /* [P,M,3] or NULL                          */
+  const float* colors_precomp;    /* [P,3]  or NULL                           */
+  const float* normals;           /* [P,3]  per-Gaussian normals, composited as given */
+  const float* refl_strengths;    /* [P]                                      */
+  const float* opacities;         /* [P]                                      */
+  const float* scales;            /* [P,3]  or NULL                           */
+  const float* rotations;         /* [P,4] (w,x,y,z), NOT normalised by the kernels (G/forward.cu:123) */
+  const float* cov3D_precomp;     /* [P,6]  or NULL                           */
+  const float* viewmatrix;        /* [16] */
+  const float* projmatrix;        /* [16] */
+  const float* campos;            /* [3]  */
+  void* geom;   size_t geom_bytes;     /* >= b200gs_gauss_geom_bytes(P)       */
+  void* img;    size_t img_bytes;      /* >= b200gs_gauss_image_bytes(W,H)    */
+  void* binning; size_t binning_bytes; /* >= b200gs_binning_bytes(R); stage 2 */
+  float* out_color;       /* [3,H,W] */
+  float* out_invdepth;    /* [1,H,W] or NULL */
+  float* out_normal;      /* [3,H,W] */
+  float* out_refl;        /* [1,H,W] */
+  int* radii;             /* [P]     */
+} b200gs_gauss_fwd;
+
+size_t b200gs_gauss_geom_bytes(int P);
+size_t b200gs_gauss_image_bytes(int width, int height);
+int b200gs_gauss_forward_stage1(const b200gs_gauss_fwd* a, int* num_rendered, void* stream);
+int b200gs_gauss_forward_stage2(const b200gs_gauss_fwd* a, int num_rendered, void* stream);
+
+/* All dL_d* outputs must be zero-filled by the caller (G/rasterize_points.cu:196-226). */
+typedef struct b200gs_gauss_bwd {
+  int P, sh_degree, sh_coeffs, num_rendered, width, height;
+  float tan_fovx, tan_fovy, scale_modifier;
+  int antialiasing, debug;
+  const float* background;
+  const float* means3D;
+  const float* shs;               /* or NULL */
+  const float* colors_precomp;    /* or NULL */
+  const float* opacities;
+  const float* scales;            /* or NULL */
+  const float* rotations;         /* or NULL */
+  const float* cov3D_precomp;     /* or NULL */
+  const float* viewmatrix;
+  const float* projmatrix;
+  const float* campos;
+  const int* radii;
+  const void* geom; const void* binning; const void* img;
+  const float* dL_dout_color;     /* [3,H,W] */
+  const float* dL_dout_invdepth;  /* [1,H,W] or NULL */
+  const float* dL_dout_normal;    /* [3,H,W] */
+  const float* dL_dout_refl;      /* [1,H,W] or NULL (=0) */
+  void* accum; size_t accum_bytes;   /* >= b200gs_gauss_accum_bytes(P) */
+  float* dL_dmeans2D;     /* [P,3] "pixels" variant handed to Python (G/backward.cu:614, rasterize_points.cu:263) */
+  float* dL_dconic;       /* [P,4] (x, y, -, w) or NULL */
+  float* dL_dopacity;     /* [P]   */
+  float* dL_dcolors;      /* [P,3] */
+  float* dL_dnormals;     /* [P,3] */
+  float* dL_drefl;        /* [P] or NULL */
+  float* dL_dinvdepths;   /* [P] or NULL */
+  float* dL_dmeans3D;     /* [P,3] */
+  float* dL_dcov3D;       /* [P,6] */
+  float* dL_dsh;          /* [P,M,3] or NULL */
+  float* dL_dscales;      /* [P,3] */
+  float* dL_drotations;   /* [P,4] */
+} b200gs_gauss_bwd;
+
+size_t b200gs_gauss_accum_bytes(int P);
+int b200gs_gauss_backward(const b200gs_gauss_bwd* a, void* stream);
+
+/* Parity helpers: GeometryState / ImageState of the 3DGS path (G/cuda_rasterizer/rasterizer_impl.h). */
+int b200gs_gauss_inspect_geom(const void* geom, int P, float* depths, float* means2D /*[P,2]*/, float* cov3D /*[P,6]*/,
+                              float* conic_opacity /*[P,4]*/, float* rgb /*[P,3]*/, uint32_t* tiles_touched,
+                              uint32_t* point_offsets, uint8_t* clamped /*[P,3]*/, void* stream);
+int b200gs_gauss_inspect_image(const void* img, int width, int height, float* accum_alpha /*[N]*/,
+                               uint32_t* n_contrib /*[N]*/, uint32_t* ranges /*[T,2]*/, void* stream);
+
+/* ------------------------------------------------------------------------ */
 /* Cubemap environment lookup (C/src/cubemapencoder.h:6-17, cubemapencoder.cu:430-488,
  * :713-779).  fp32.  inputs [B,3] directions; cubemap [6,C,L,L]; fail_value [C];
  * outputs / grad_outputs are CHANNEL-MAJOR [C,B] like the reference's.  interp 0 =

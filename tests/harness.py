@@ -166,3 +166,115 @@ def grad_close_fraction(a, b, rtol=1e-4, scale_floor=1e-4):
     tol = rtol * torch.maximum(a.abs(), b.abs()) + rtol * max(float(rms), 1e-30)
     ok = (a - b).abs() <= tol
     return float(ok.double().mean()) if ok.numel() else 1.0
+
+
+# ================================================================ 3DGS (EWA) path
+def new_gauss_C():
+    import diff_gaussian_rasterization
+    return diff_gaussian_rasterization._C
+
+
+def gauss_scene(scene):
+    """3DGS inputs from a surfel test scene: a third scale, per-Gaussian unit normals."""
+    g = dict(scene)
+    s = scene["scales"]
+    g["scales3"] = torch.cat([s, 0.3 * s[:, :1]], 1).contiguous()
+    q = scene["rotations"]
+    n = torch.stack([2 * (q[:, 1] * q[:, 3] + q[:, 0] * q[:, 2]), 2 * (q[:, 2] * q[:, 3] - q[:, 0] * q[:, 1]),
+                     1 - 2 * (q[:, 1] ** 2 + q[:, 2] ** 2)], 1)
+    g["normals"] = n.contiguous()
+    return g
+
+
+def gauss_forward(Cmod, scene, cam, bg=(0.0, 0.0, 0.0), sh_degree=3, scale_modifier=1.0, antialiasing=False,
+                  colors_precomp=None, cov3D_precomp=None, debug=False):
+    dev = scene["means3D"].device
+    e = torch.empty((0,), dtype=torch.float32, device=dev)
+    bgt = torch.tensor(bg, dtype=torch.float32, device=dev)
+    use_sh = colors_precomp is None
+    out = Cmod.rasterize_gaussians(
+        bgt, scene["means3D"], e if use_sh else colors_precomp, scene["normals"], scene["refl"], scene["opacities"],
+        e if cov3D_precomp is not None else scene["scales3"], e if cov3D_precomp is not None else scene["rotations"],
+        scale_modifier, e if cov3D_precomp is None else cov3D_precomp, cam["viewmatrix"], cam["projmatrix"],
+        cam["tanfovx"], cam["tanfovy"], cam["height"], cam["width"], scene["shs"] if use_sh else e, sh_degree,
+        cam["campos"], False, antialiasing, debug)
+    keys = ("rendered", "color", "radii", "geom", "binning", "img", "invdepth", "normal_map", "refl_map")
+    r = dict(zip(keys, out))
+    r.update(bg=bgt, sh_degree=sh_degree, scale_modifier=scale_modifier, antialiasing=antialiasing,
+             colors_precomp=colors_precomp, cov3D_precomp=cov3D_precomp)
+    return r
+
+
+def gauss_backward(Cmod, scene, cam, fwd, grads):
+    """grads: color[3,H,W], invdepth[1,H,W], normal[3,H,W], refl[1,H,W]."""
+    dev = scene["means3D"].device
+    e = torch.empty((0,), dtype=torch.float32, device=dev)
+    use_sh = fwd["colors_precomp"] is None
+    cp = fwd["cov3D_precomp"]
+    out = Cmod.rasterize_gaussians_backward(
+        fwd["bg"], scene["means3D"], fwd["radii"], e if use_sh else fwd["colors_precomp"], scene["normals"],
+        scene["refl"], scene["opacities"], e if cp is not None else scene["scales3"],
+        e if cp is not None else scene["rotations"], fwd["scale_modifier"], e if cp is None else cp, cam["viewmatrix"],
+        cam["projmatrix"], cam["tanfovx"], cam["tanfovy"], grads["color"], grads["invdepth"], grads["normal"],
+        grads["refl"], scene["shs"] if use_sh else e, fwd["sh_degree"], cam["campos"], fwd["geom"], fwd["rendered"],
+        fwd["binning"], fwd["img"], fwd["antialiasing"], False)
+    keys = ("means2D", "colors", "normals", "refl", "opacity", "means3D", "cov3D", "sh", "scales", "rotations")
+    return dict(zip(keys, out))
+
+
+def gauss_grads(W, H, seed=0):
+    rng = np.random.default_rng(991 + seed)
+    return dict(color=rng.normal(0, 1, (3, H, W)).astype(np.float32), invdepth=rng.normal(0, 1, (1, H, W)).astype(np.float32),
+                normal=rng.normal(0, 1, (3, H, W)).astype(np.float32), refl=rng.normal(0, 1, (1, H, W)).astype(np.float32))
+
+
+def ref_gauss_state(fwd, P, W, H):
+    """Parse the reference's buffers of the 3DGS path (G/cuda_rasterizer/rasterizer_impl.cu:155-194)."""
+    def take(buf, off, nbytes, dtype, shape):
+        off = _al(off)
+        return buf[off:off + nbytes].view(dtype).reshape(shape), off + nbytes
+    g, off = fwd["geom"], 0
+    depths, off = take(g, off, 4 * P, torch.float32, (P,))
+    clamped, off = take(g, off, 3 * P, torch.uint8, (P, 3))
+    iradii, off = take(g, off, 4 * P, torch.int32, (P,))
+    means2D, off = take(g, off, 8 * P, torch.float32, (P, 2))
+    cov3D, off = take(g, off, 24 * P, torch.float32, (P, 6))
+    conic_opacity, off = take(g, off, 16 * P, torch.float32, (P, 4))
+    rgb, off = take(g, off, 12 * P, torch.float32, (P, 3))
+    tiles, off = take(g, off, 4 * P, torch.int32, (P,))
+    R, b, off = fwd["rendered"], fwd["binning"], 0
+    point_list, off = take(b, off, 4 * R, torch.int32, (R,))
+    _, off = take(b, off, 4 * R, torch.int32, (R,))
+    keys, off = take(b, off, 8 * R, torch.int64, (R,))
+    im, N, off = fwd["img"], W * H, 0
+    T = ((W + 15) // 16) * ((H + 15) // 16)
+    accum, off = take(im, off, 4 * N, torch.float32, (N,))
+    ncon, off = take(im, off, 4 * N, torch.int32, (N,))
+    ranges, off = take(im, off, 8 * N, torch.int32, (N, 2))
+    return dict(depths=depths, clamped=clamped, means2D=means2D, cov3D=cov3D, conic_opacity=conic_opacity, rgb=rgb,
+                tiles_touched=tiles, point_offsets=torch.cumsum(tiles, 0).to(torch.int32), point_list=point_list,
+                keys=keys, accum=accum, n_contrib=ncon, ranges=ranges[:T])
+
+
+def new_gauss_state(fwd, P, W, H):
+    import ctypes as C
+    import b200gs as _b
+    dev = fwd["geom"].device
+    f = lambda *s: torch.zeros(s, dtype=torch.float32, device=dev)  # noqa: E731
+    i = lambda *s: torch.zeros(s, dtype=torch.int32, device=dev)  # noqa: E731
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    depths, means2D, cov3D, co, rgb = f(P), f(P, 2), f(P, 6), f(P, 4), f(P, 3)
+    tiles, offs = i(P), i(P)
+    clamped = torch.zeros((P, 3), dtype=torch.uint8, device=dev)
+    _b.check(_b.gauss_inspect_geom(fwd["geom"].data_ptr(), P, depths.data_ptr(), means2D.data_ptr(), cov3D.data_ptr(),
+                                   co.data_ptr(), rgb.data_ptr(), tiles.data_ptr(), offs.data_ptr(), clamped.data_ptr(), st))
+    R = fwd["rendered"]
+    keys, pl = torch.zeros((R,), dtype=torch.int64, device=dev), i(R)
+    if R:
+        _b.check(_b.inspect_binning(fwd["binning"].data_ptr(), R, keys.data_ptr(), pl.data_ptr(), st))
+    N, T = W * H, ((W + 15) // 16) * ((H + 15) // 16)
+    accum, ncon, ranges = f(N), i(N), i(T, 2)
+    _b.check(_b.gauss_inspect_image(fwd["img"].data_ptr(), W, H, accum.data_ptr(), ncon.data_ptr(), ranges.data_ptr(), st))
+    return dict(depths=depths, clamped=clamped, means2D=means2D, cov3D=cov3D, conic_opacity=co, rgb=rgb,
+                tiles_touched=tiles, point_offsets=offs, point_list=pl, keys=keys, accum=accum, n_contrib=ncon,
+                ranges=ranges)

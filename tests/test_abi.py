@@ -67,3 +67,23 @@ def test_python_surface_matches_reference(lib_path):
         r(z, z, z[:, :1])
     with pytest.raises(Exception, match="scale/rotation pair"):
         r(z, z, z[:, :1], shs=torch.zeros(4, 16, 3))
+
+
+def test_gauss_and_cubemap_python_surface(lib_path):
+    import diff_gaussian_rasterization as d
+    assert d.GaussianRasterizationSettings._fields[-1] == "antialiasing" and len(d.GaussianRasterizationSettings._fields) == 13
+    for name in ("rasterize_gaussians", "rasterize_gaussians_backward", "mark_visible"):
+        assert callable(getattr(d._C, name))
+    assert not hasattr(d._C, "fusedssim")      # utils/loss_utils.py:16-19 of the reference probes for it under try/except
+    import pytest
+    import torch
+    z = torch.zeros(4, 3)
+    with pytest.raises(Exception, match="excatly one of either SHs"):
+        d.GaussianRasterizer(None)(z, z, z[:, :1])
+    import _cubemapencoder
+    import cubemapencoder
+    assert callable(_cubemapencoder.cubemap_encode_forward) and callable(_cubemapencoder.cubemap_encode_backward)
+    enc = cubemapencoder.CubemapEncoder(output_dim=3, resolution=8)
+    assert set(enc.state_dict().keys()) == {"params.Cubemap_texture", "params.Cubemap_failv"}
+    with pytest.raises(RuntimeError, match="CUDA tensor"):
+        _cubemapencoder.cubemap_encode_forward(z, torch.zeros(6, 3, 8, 8), torch.zeros(3), torch.zeros(3, 4), 1, 1, 4, 3, 8)
