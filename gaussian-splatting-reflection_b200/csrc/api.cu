@@ -64,7 +64,7 @@ SurfelGeom SurfelGeom::carve(void* base, size_t P, size_t* bytes) {
   g.clamped = c.take<uint8_t>(P);
   g.rects = c.take<uint2>(P);
   g.rec = c.take<SurfelRec>(P);
-  g.cull = c.take<uint2>(P);
+  g.cull = c.take<CullRec>(P);
   g.scan_state = c.take<uint32_t>(scan_state_words((int)P));
   g.flags = c.take<int>(4);
   if (bytes) *bytes = c.used + 128;
@@ -124,7 +124,7 @@ void b200gs_timing_enable(int on) { g_timing.store(on ? 1 : 0); }
 int b200gs_timing_stages(void) { return ST_COUNT; }
 const char* b200gs_timing_stage_name(int stage) {
   static const char* names[ST_COUNT] = {"preprocess", "scan", "duplicate", "sort", "tile_ranges", "composite_fwd",
-                                        "composite_bwd", "preprocess_bwd", "cubemap_fwd", "cubemap_bwd"};
+                                        "composite_bwd", "preprocess_bwd", "cubemap_fwd", "cubemap_bwd", "tile_hits", "depth_sort"};
   return (stage >= 0 && stage < ST_COUNT) ? names[stage] : "";
 }
 int b200gs_timing_read(float* ms, unsigned long long* counts, int n) {
@@ -195,6 +195,10 @@ int b200gs_surfel_forward_stage2(const b200gs_surfel_fwd* a, int R, void* stream
   Binning b = Binning::carve(R > 0 ? align128(a->binning) : nullptr, R, nullptr);
   rc = bin_and_sort(g.depths, g.rects, g.point_offsets, a->P, R, a->width, a->height, b, im.ranges, s, a->debug != 0);
   if (rc) return rc;
+  if (R > 0) {
+    rc = surfel_tile_hits(g.cull, b, R, a->width, s, a->debug != 0);
+    if (rc) return rc;
+  }
   return surfel_composite_forward(*a, g, im, b, s);
 }
 

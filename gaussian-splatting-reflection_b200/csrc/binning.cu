@@ -178,6 +178,75 @@ __global__ void __launch_bounds__(256) tile_ranges_kernel(int L, const uint64_t*
   if (idx == L - 1) ranges[cur].y = L;
 }
 
+// ------------------------------------------------------------------ tile hits
+// For every sorted (tile, Gaussian) instance: which of the tile's eight 8x4 warp blocks (bit w:
+// column w&1, row w>>1, the layout of tile_pixel()) can the Gaussian reach alpha >= 1/255 in?
+// Block = pixel centres [8c, 8c+7] x [4r, 4r+3] relative to the tile origin, tested as the
+// rectangle dilated by half a pixel against the CullRec ellipse (exact convex test: the x-extent
+// of ellipse /\ row band is attained at the ellipse's extreme point if that lies in the band, else
+// on one of the band's two boundary lines) and against the low-pass disk.  One byte per instance;
+// the list itself is untouched (the reference's list order and positions are what n_contrib counts).
+__global__ void __launch_bounds__(256) tile_hits_kernel(int R, const uint64_t* __restrict__ keys,
+                                                        const uint32_t* __restrict__ point_list,
+                                                        const CullRec* __restrict__ cull, int gx,
+                                                        uint8_t* __restrict__ hit) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= R) return;
+  const uint32_t tile = (uint32_t)(keys[i] >> 32);
+  const uint32_t id = point_list[i];
+  const float4 ca = __ldg(&cull[id].a), cb = __ldg(&cull[id].b);
+  unsigned mask;
+  if (ca.w < 0.0f) {
+    mask = (ca.w == CULL_NOTHING) ? 0u : 0xFFu;
+  } else {
+    const float ox = (float)((tile % (uint32_t)gx) * TILE_X) - 0.5f - ca.x;  // left edge of column 0, relative to e
+    const float oy = (float)((tile / (uint32_t)gx) * TILE_Y) - 0.5f - ca.y;  // top edge of row band 0
+    const float hx = ca.z, hy2 = ca.w, sl = cb.x, k = cb.y, dyR = cb.z, r2 = cb.w;
+    const float INF = __int_as_float(0x7f800000);
+    float lo[5], hi[5];
+#pragma unroll
+    for (int j = 0; j < 5; ++j) {
+      const float dy = oy + 4.0f * j;
+      const float rem = hy2 - dy * dy;
+      const float h = k * sqrtf(fmaxf(rem, 0.0f));
+      lo[j] = rem >= 0.0f ? sl * dy - h : INF;
+      hi[j] = rem >= 0.0f ? sl * dy + h : -INF;
+    }
+    // disk: squared distance from e to the column / row intervals
+    float ddx2[2], ddy2[4];
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      const float d = fmaxf(fmaxf(ox + 8.0f * c, -(ox + 8.0f * (c + 1))), 0.0f);
+      ddx2[c] = d * d;
+    }
+    mask = 0u;
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const float ya = oy + 4.0f * r, yb = oy + 4.0f * (r + 1);
+      const float d = fmaxf(fmaxf(ya, -yb), 0.0f);
+      ddy2[r] = d * d;
+      const float xmax = (dyR >= ya && dyR <= yb) ? hx : fmaxf(hi[r], hi[r + 1]);
+      const float xmin = (-dyR >= ya && -dyR <= yb) ? -hx : fminf(lo[r], lo[r + 1]);
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        const float xa = ox + 8.0f * c, xb = ox + 8.0f * (c + 1);
+        const bool ell = xmin <= xb && xmax >= xa;
+        const bool disk = ddx2[c] + ddy2[r] <= r2;
+        if (ell || disk) mask |= 1u << (r * 2 + c);
+      }
+    }
+  }
+  hit[i] = (uint8_t)mask;
+}
+
+int surfel_tile_hits(const CullRec* cull, const Binning& b, int R, int W, cudaStream_t s, bool debug) {
+  const int gx = (W + TILE_X - 1) / TILE_X;
+  StageScope _t(ST_TILE_HITS, s);
+  tile_hits_kernel<<<(R + 255) / 256, 256, 0, s>>>(R, b.keys, b.point_list, cull, gx, b.hit);
+  B200GS_LAUNCHED("tile_hits_kernel", debug, s);
+  return B200GS_OK;
+}
+
 // getHigherMsb (rasterizer_impl.cu:35-50)
 static uint32_t higher_msb(uint32_t n) {
   uint32_t msb = sizeof(n) * 4, step = msb;
@@ -196,6 +265,7 @@ Binning Binning::carve(void* base, size_t R, size_t* bytes) {
   b.point_list_unsorted = c.take<uint32_t>(R);
   b.keys = c.take<uint64_t>(R);
   b.keys_unsorted = c.take<uint64_t>(R);
+  b.hit = c.take<uint8_t>(R);
   b.sort_temp_bytes = radix_sort_temp_bytes(R);
   b.sort_temp = c.take<char>(b.sort_temp_bytes);
   if (bytes) *bytes = c.used + 128;

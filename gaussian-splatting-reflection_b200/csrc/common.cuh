@@ -46,7 +46,7 @@ extern std::atomic<unsigned long long> g_launches;
 // bench.py can attribute the step time to kernels without a profiler attached.
 enum Stage {
   ST_PREPROCESS = 0, ST_SCAN, ST_DUPLICATE, ST_SORT, ST_RANGES, ST_COMPOSITE_FWD,
-  ST_COMPOSITE_BWD, ST_PREPROCESS_BWD, ST_CUBEMAP_FWD, ST_CUBEMAP_BWD, ST_COUNT
+  ST_COMPOSITE_BWD, ST_PREPROCESS_BWD, ST_CUBEMAP_FWD, ST_CUBEMAP_BWD, ST_TILE_HITS, ST_DEPTH_SORT, ST_COUNT
 };
 extern std::atomic<int> g_timing;
 void stage_mark(int stage, bool begin, cudaStream_t s);
@@ -84,6 +84,17 @@ struct __align__(16) SurfelRec {
 };
 static_assert(sizeof(SurfelRec) == 80, "record must be 80 B");
 
+// Per-Gaussian cull record (32 B) written by the surfel preprocess: the ellipse {rho3d <= c2}
+// as centre + shape, and the low-pass disk re-centred on it (see cull_record()).
+//   a = ex ey hx hy2      ellipse centre (px), half width, squared half height; hy2 < 0 = flag
+//   b = s  k  dyR r2      chord on the line y = ey + dy: x = ex + s*dy -+ k*sqrt(hy2 - dy^2);
+//                         dyR = y offset of the right-most point; r2 = squared disk radius
+struct __align__(16) CullRec {
+  float4 a, b;
+};
+constexpr float CULL_EVERYTHING = -1.0f;
+constexpr float CULL_NOTHING = -2.0f;
+
 struct SurfelGeom {
   float* depths;            // [P]
   uint32_t* tiles_touched;  // [P]
@@ -91,7 +102,7 @@ struct SurfelGeom {
   uint8_t* clamped;         // [P] bit c = colour channel c clamped at 0
   uint2* rects;             // [P] tile rect: x = x0 | x1<<16, y = y0 | y1<<16 (only valid if tiles_touched>0)
   SurfelRec* rec;           // [P]
-  uint2* cull;              // [P] conservative pixel bbox of {alpha >= 1/255}: x = xmin | xmax<<16, y = ymin | ymax<<16
+  CullRec* cull;            // [P] region where alpha >= 1/255 is reachable
   uint32_t* scan_state;     // decoupled look-back tile states
   int* flags;               // [4] error flags (prefiltered violation, ...)
   static SurfelGeom carve(void* base, size_t P, size_t* bytes);
@@ -109,6 +120,7 @@ struct Binning {
   uint32_t* point_list_unsorted;  // [R]
   uint64_t* keys;                 // [R] sorted keys
   uint64_t* keys_unsorted;        // [R]
+  uint8_t* hit;                   // [R] per sorted instance: bit w = warp block w of the tile can reach alpha >= 1/255
   void* sort_temp;
   size_t sort_temp_bytes;
   static Binning carve(void* base, size_t R, size_t* bytes);
@@ -205,6 +217,7 @@ int surfel_preprocess(const b200gs_surfel_fwd& a, const SurfelGeom& g, cudaStrea
 int inclusive_scan_u32(const uint32_t* in, uint32_t* out, int n, uint32_t* state, cudaStream_t s, bool debug);
 int bin_and_sort(const float* depths, const uint2* rects, const uint32_t* offsets,
                  int P, int R, int W, int H, const Binning& b, uint2* ranges, cudaStream_t s, bool debug);
+int surfel_tile_hits(const CullRec* cull, const Binning& b, int R, int W, cudaStream_t s, bool debug);
 int surfel_composite_forward(const b200gs_surfel_fwd& a, const SurfelGeom& g, const SurfelImage& im,
                              const Binning& b, cudaStream_t s);
 int surfel_composite_backward(const b200gs_surfel_bwd& a, const SurfelGeom& g, const SurfelImage& im,

@@ -19,7 +19,7 @@ struct CompBwdArgs {
   const uint2* ranges;
   const uint32_t* point_list;
   const SurfelRec* rec;
-  const uint2* cull;
+  const uint8_t* hit;   // [R]
   const float* bg;
   const float* accum;         // [3,N] final T, M1, M2
   const uint32_t* n_contrib;  // [2,N]
@@ -93,11 +93,11 @@ __global__ void __launch_bounds__(BATCH, 2) surfel_composite_bwd_kernel(const Co
   const bool live = inside;
 
   const uint32_t* pl = a.point_list + range.x;
-  uint2 cull_cur = make_uint2(1u, 1u);
+  const uint8_t* ph = a.hit + range.x;
+  unsigned hit_cur = 0u, hit_next = 0u;
   auto stage = [&](int buf, int id) {
-    cull_cur = make_uint2(1u, 1u);
+    hit_cur = hit_next;
     if (id >= 0) {
-      cull_cur = __ldg(a.cull + id);
       const SurfelRec* g = a.rec + id;
       SurfelRec* d = &s_rec[buf][t];
 #pragma unroll
@@ -106,31 +106,25 @@ __global__ void __launch_bounds__(BATCH, 2) surfel_composite_bwd_kernel(const Co
     }
     cp_async_commit();
   };
-  int id_next = (t < n) ? (int)pl[n - 1 - t] : -1;
+  int id_next = -1;
+  if (t < n) { id_next = (int)pl[n - 1 - t]; hit_next = ph[n - 1 - t]; }
   stage(0, id_next);
-  id_next = (BATCH + t < n) ? (int)pl[n - 1 - (BATCH + t)] : -1;
+  id_next = -1; hit_next = 0u;
+  if (BATCH + t < n) { id_next = (int)pl[n - 1 - (BATCH + t)]; hit_next = ph[n - 1 - (BATCH + t)]; }
 
   // Warps whose pixels all have last_contributor == 0 have nothing to do, but they
   // still take part in the staging and barriers.
   const uint32_t warp_last = __reduce_max_sync(0xffffffffu, live ? last_contributor : 0u);
 
-  const int tx0 = tile_x * TILE_X, ty0 = tile_y * TILE_Y;
   for (int i = 0; i < rounds; ++i) {
     cp_async_wait_all();
-    {
-      const uint2 cb = cull_cur;
-      const int bx0 = (int)(cb.x & 0xffffu) - tx0, bx1 = (int)(cb.x >> 16) - tx0;
-      const int by0 = (int)(cb.y & 0xffffu) - ty0, by1 = (int)(cb.y >> 16) - ty0;
-      const unsigned col = ((bx0 <= 7 && bx1 >= 0) ? 0x55u : 0u) | ((bx0 <= 15 && bx1 >= 8) ? 0xAAu : 0u);
-      const unsigned row = ((by0 <= 3 && by1 >= 0) ? 0x03u : 0u) | ((by0 <= 7 && by1 >= 4) ? 0x0Cu : 0u) |
-                           ((by0 <= 11 && by1 >= 8) ? 0x30u : 0u) | ((by0 <= 15 && by1 >= 12) ? 0xC0u : 0u);
-      s_hit[i & 1][t] = (uint8_t)(col & row);
-    }
+    s_hit[i & 1][t] = (uint8_t)hit_cur;
     __syncthreads();
     if (i + 1 < rounds) {
       stage((i + 1) & 1, id_next);
       const int nx = (i + 2) * BATCH + t;
-      id_next = (nx < n) ? (int)pl[n - 1 - nx] : -1;
+      id_next = -1; hit_next = 0u;
+      if (nx < n) { id_next = (int)pl[n - 1 - nx]; hit_next = ph[n - 1 - nx]; }
     }
     const int buf = i & 1;
     const int count = min(BATCH, n - i * BATCH);
@@ -240,7 +234,7 @@ int surfel_composite_backward(const b200gs_surfel_bwd& f, const SurfelGeom& g, c
   a.W = f.width; a.H = f.height;
   a.gx = (f.width + TILE_X - 1) / TILE_X;
   const int gy = (f.height + TILE_Y - 1) / TILE_Y;
-  a.ranges = im.ranges; a.point_list = b.point_list; a.rec = g.rec; a.cull = g.cull; a.bg = f.background;
+  a.ranges = im.ranges; a.point_list = b.point_list; a.rec = g.rec; a.hit = b.hit; a.bg = f.background;
   a.accum = im.accum; a.n_contrib = im.n_contrib;
   a.dL_dpix = f.dL_dout_color; a.dL_dothers = f.dL_dout_others; a.dL_drefl = f.dL_dout_refl;
   a.acc = acc;

@@ -18,7 +18,7 @@ struct CompFwdArgs {
   const uint2* ranges;
   const uint32_t* point_list;
   const SurfelRec* rec;
-  const uint2* cull;
+  const uint8_t* hit;   // [R] per list entry: warp blocks that can reach alpha >= 1/255 (tile_hits_kernel)
   const float* bg;
   float* accum;         // [3,N]
   uint32_t* n_contrib;  // [2,N]
@@ -30,6 +30,18 @@ struct CompFwdArgs {
 
 constexpr int BATCH = 256;
 
+// Cull audit (b200gs_debug_cull_audit): the AUDIT instantiation ignores the hit masks, evaluates
+// every (warp, entry) pair like the reference does and counts the pairs that pass the
+// reference's alpha cut although their mask bit is clear -- [0] with the forward's
+// `unstable` threshold, [1] with the backward's.  Both must stay 0.
+__device__ unsigned long long g_cull_violations[2];
+// Workload statistics gathered by the AUDIT instantiation only: [0] (warp, entry) pairs visited with
+// the hit bit set, [1] those with >= 1 contributing lane, [2] lane contributions, [3] sum over
+// (warp, batch) of the busiest lane's contributions, [4] (warp, batch) count.
+__device__ unsigned long long g_cull_stats[8];
+std::atomic<int> g_cull_audit{0};
+
+template <bool AUDIT>
 __global__ void __launch_bounds__(BATCH) surfel_composite_fwd_kernel(const CompFwdArgs a) {
   __shared__ SurfelRec s_rec[2][BATCH];
   __shared__ int s_id[2][BATCH];
@@ -62,11 +74,12 @@ __global__ void __launch_bounds__(BATCH) surfel_composite_fwd_kernel(const CompF
   s_wmax[1][t] = 0;
 
   const uint32_t* pl = a.point_list + range.x;
-  uint2 cull_cur = make_uint2(1u, 1u);   // cull box of the entry this thread staged for the batch about to run
+  const uint8_t* ph = a.hit + range.x;
+  unsigned hit_cur = 0u;                 // hit mask of the entry this thread staged for the batch about to run
+  unsigned hit_next = 0u;
   auto stage = [&](int buf, int id) {
-    cull_cur = make_uint2(1u, 1u);       // "nothing": padding entries are never visited
+    hit_cur = hit_next;                  // 0 for padding entries: never visited
     if (id >= 0) {
-      cull_cur = __ldg(a.cull + id);
       const SurfelRec* g = a.rec + id;
       SurfelRec* d = &s_rec[buf][t];
 #pragma unroll
@@ -75,25 +88,18 @@ __global__ void __launch_bounds__(BATCH) surfel_composite_fwd_kernel(const CompF
     }
     cp_async_commit();
   };
-  int id_next = (t < n) ? (int)pl[t] : -1;
+  int id_next = -1;
+  if (t < n) { id_next = (int)pl[t]; hit_next = ph[t]; }
   stage(0, id_next);
-  id_next = (BATCH + t < n) ? (int)pl[BATCH + t] : -1;
+  id_next = -1; hit_next = 0u;
+  if (BATCH + t < n) { id_next = (int)pl[BATCH + t]; hit_next = ph[BATCH + t]; }
 
   const int warp = t >> 5;
-  const int tx0 = tile_x * TILE_X, ty0 = tile_y * TILE_Y;
   int last_batch = -1;
   for (int i = 0; i < rounds; ++i) {
     cp_async_wait_all();
-    {  // which of the 8 warp blocks can this thread's entry reach alpha >= 1/255 in?
-      const uint2 cb = cull_cur;
-      const int bx0 = (int)(cb.x & 0xffffu) - tx0, bx1 = (int)(cb.x >> 16) - tx0;
-      const int by0 = (int)(cb.y & 0xffffu) - ty0, by1 = (int)(cb.y >> 16) - ty0;
-      const unsigned col = ((bx0 <= 7 && bx1 >= 0) ? 0x55u : 0u) | ((bx0 <= 15 && bx1 >= 8) ? 0xAAu : 0u);
-      const unsigned row = ((by0 <= 3 && by1 >= 0) ? 0x03u : 0u) | ((by0 <= 7 && by1 >= 4) ? 0x0Cu : 0u) |
-                           ((by0 <= 11 && by1 >= 8) ? 0x30u : 0u) | ((by0 <= 15 && by1 >= 12) ? 0xC0u : 0u);
-      // s_hit[i&1] was last read while blending batch i-2; everyone left that before the barrier of i-1
-      s_hit[i & 1][t] = (uint8_t)(col & row);
-    }
+    // s_hit[i&1] was last read while blending batch i-2; everyone left that before the barrier of i-1
+    s_hit[i & 1][t] = (uint8_t)hit_cur;
     // batch i has landed for everyone, and everyone is past batch i-1
     if (__syncthreads_count(done) == BATCH) break;
     if (i > 0) {  // publish and clear the per-Gaussian weight maxima of batch i-1
@@ -104,15 +110,18 @@ __global__ void __launch_bounds__(BATCH) surfel_composite_fwd_kernel(const CompF
     if (i + 1 < rounds) {
       stage((i + 1) & 1, id_next);
       const int nx = (i + 2) * BATCH + t;
-      id_next = (nx < n) ? (int)pl[nx] : -1;
+      id_next = -1; hit_next = 0u;
+      if (nx < n) { id_next = (int)pl[nx]; hit_next = ph[nx]; }
     }
     last_batch = i;
     const int buf = i & 1;
     const SurfelRec* rb = s_rec[buf];
     bool warp_done = false;
+    int lane_cnt = 0;
 #pragma unroll 1
     for (int r = 0; r < BATCH / 32 && !warp_done; ++r) {
-      unsigned m = __ballot_sync(0xffffffffu, (s_hit[buf][r * 32 + lane] >> warp) & 1u);
+      unsigned m = __ballot_sync(0xffffffffu, AUDIT ? (i * BATCH + r * 32 + lane < n)
+                                                          : (bool)((s_hit[buf][r * 32 + lane] >> warp) & 1u));
       while (m) {
         if (__all_sync(0xffffffffu, done)) { warp_done = true; break; }
         const int j = r * 32 + __ffs(m) - 1;
@@ -120,7 +129,13 @@ __global__ void __launch_bounds__(BATCH) surfel_composite_fwd_kernel(const CompF
         const uint32_t contributor = (uint32_t)(i * BATCH + j + 1);  // 1-based position in the tile's list
         const float4 q0 = rb[j].q[0], q1 = rb[j].q[1], q2 = rb[j].q[2];
         SurfelHit h;
-        bool c = surfel_eval<false>(q0, q1, q2, fx, fy, h) && !done;
+        bool c = surfel_eval<false>(q0, q1, q2, fx, fy, h);
+        if (AUDIT && inside && !((s_hit[buf][j] >> warp) & 1u)) {
+          SurfelHit hb;
+          if (c) atomicAdd(&g_cull_violations[0], 1ull);
+          if (surfel_eval<true>(q0, q1, q2, fx, fy, hb)) atomicAdd(&g_cull_violations[1], 1ull);
+        }
+        c = c && !done;
         float w = 0.0f;
         if (c) {
           const float test_T = __fmul_rn(T, __fsub_rn(1.0f, h.alpha));
@@ -148,12 +163,25 @@ __global__ void __launch_bounds__(BATCH) surfel_composite_fwd_kernel(const CompF
             last_contributor = contributor;
           }
         }
+        if (AUDIT) {
+          const unsigned cm = __ballot_sync(0xffffffffu, c);
+          lane_cnt += c ? 1 : 0;
+          if (lane == 0 && ((s_hit[buf][j] >> warp) & 1u)) {
+            atomicAdd(&g_cull_stats[0], 1ull);
+            if (cm) atomicAdd(&g_cull_stats[1], 1ull);
+            atomicAdd(&g_cull_stats[2], (unsigned long long)__popc(cm));
+          }
+        }
         // gaussian_weights[id] = max over pixels of w  (forward.cu:457-459, made exact)
         if (__any_sync(0xffffffffu, c)) {
           const int wm = __reduce_max_sync(0xffffffffu, __float_as_int(w));
           if (lane == 0) atomicMax(&s_wmax[buf][j], wm);
         }
       }
+    }
+    if (AUDIT) {
+      const int mx = __reduce_max_sync(0xffffffffu, lane_cnt);
+      if (lane == 0) { atomicAdd(&g_cull_stats[3], (unsigned long long)mx); atomicAdd(&g_cull_stats[4], 1ull); }
     }
   }
   __syncthreads();
@@ -191,14 +219,41 @@ int surfel_composite_forward(const b200gs_surfel_fwd& f, const SurfelGeom& g, co
   a.W = f.width; a.H = f.height;
   a.gx = (f.width + TILE_X - 1) / TILE_X;
   const int gy = (f.height + TILE_Y - 1) / TILE_Y;
-  a.ranges = im.ranges; a.point_list = b.point_list; a.rec = g.rec; a.cull = g.cull; a.bg = f.background;
+  a.ranges = im.ranges; a.point_list = b.point_list; a.rec = g.rec; a.hit = b.hit; a.bg = f.background;
   a.accum = im.accum; a.n_contrib = im.n_contrib;
   a.out_color = f.out_color; a.out_others = f.out_others; a.out_refl = f.out_refl;
   a.gaussian_weights = f.gaussian_weights;
   StageScope _t(ST_COMPOSITE_FWD, s);
-  surfel_composite_fwd_kernel<<<a.gx * gy, BATCH, 0, s>>>(a);
+  if (g_cull_audit.load(std::memory_order_relaxed))
+    surfel_composite_fwd_kernel<true><<<a.gx * gy, BATCH, 0, s>>>(a);
+  else
+    surfel_composite_fwd_kernel<false><<<a.gx * gy, BATCH, 0, s>>>(a);
   B200GS_LAUNCHED("surfel_composite_fwd_kernel", f.debug, s);
   return B200GS_OK;
 }
 
 }  // namespace b200gs
+
+extern "C" {
+void b200gs_debug_cull_audit(int on) { b200gs::g_cull_audit.store(on ? 1 : 0); }
+int b200gs_debug_cull_stats(unsigned long long* out8, int reset) {
+  using namespace b200gs;
+  B200GS_CUDA(cudaDeviceSynchronize());
+  if (out8) B200GS_CUDA(cudaMemcpyFromSymbol(out8, g_cull_stats, 8 * sizeof(unsigned long long)));
+  if (reset) {
+    const unsigned long long z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    B200GS_CUDA(cudaMemcpyToSymbol(g_cull_stats, z, sizeof(z)));
+  }
+  return B200GS_OK;
+}
+int b200gs_debug_cull_violations(unsigned long long* out2, int reset) {
+  using namespace b200gs;
+  B200GS_CUDA(cudaDeviceSynchronize());
+  if (out2) B200GS_CUDA(cudaMemcpyFromSymbol(out2, g_cull_violations, 2 * sizeof(unsigned long long)));
+  if (reset) {
+    const unsigned long long z[2] = {0ull, 0ull};
+    B200GS_CUDA(cudaMemcpyToSymbol(g_cull_violations, z, sizeof(z)));
+  }
+  return B200GS_OK;
+}
+}

@@ -44,44 +44,52 @@ struct SurfelPreArgs {
   uint8_t* clamped;
   uint2* rects;
   SurfelRec* rec;
-  uint2* cull;
+  CullRec* cull;
   int* flags;
 };
 
-// Conservative pixel bounding box of the region where this Gaussian can reach
-// alpha = min(0.99, opa*exp(-rho/2)) >= 1/255, i.e. rho = min(rho3d, rho2d) <= 2 ln(255 opa):
-// the union of (a) the AABB of the projected ellipse {rho3d <= c2} -- the same closed form as
-// compute_aabb (forward.cu:119-145) with cutoff^2 = c2 -- and (b) the low-pass disk
-// {2 |xy - pix|^2 <= c2}.  The compositing kernels use it only to skip (warp, Gaussian) pairs
-// none of whose 32 pixels can pass the reference's `alpha < 1/255` cut, so results stay
-// bit-identical; when the ellipse is unbounded or the arithmetic is doubtful the box is "everything".
-__device__ __forceinline__ uint2 cull_bbox(const float* Tu, const float* Tv, const float* Tw, float cx, float cy,
-                                           float opa) {
-  const uint2 everything = make_uint2(0xffff0000u, 0xffff0000u);
-  const uint2 nothing = make_uint2(0x00000001u, 0x00000001u);  // min 1 > max 0
+// Conservative description of the pixel region where this Gaussian can reach
+// alpha = min(0.99, opa*exp(-rho/2)) >= 1/255, i.e. rho = min(rho3d, rho2d) <= c2 = 2 ln(255 opa):
+// the union of (a) the projected ellipse {rho3d <= c2} and (b) the low-pass disk {2 |xy - pix|^2 <= c2}.
+// The ellipse comes from the dual conic Q* = M diag(c2, c2, -1) M^T / d (the closed form behind
+// compute_aabb, forward.cu:119-145, which only keeps its axis-aligned extent): centre e = Q*[:2,2],
+// shape Sigma = e e^T - Q*[:2,:2], {p : (p-e)^T Sigma^-1 (p-e) <= 1}.  Evaluated in fp64 (the
+// differences cancel badly in fp32 for small far-off-origin ellipses), inflated by c2*1.002+0.02
+// and Sigma += (0.05 px)^2 I, and the disk is re-centred on e with its radius grown by |xy - e|.
+// tile_hits_kernel (binning.cu) intersects this with every 8x4 warp block of a tile, dilated by
+// half a pixel; the compositing kernels skip (warp, Gaussian) pairs that miss, which the
+// reference would have rejected pixel by pixel with `alpha < 1/255` -- results stay bit-identical.
+// When the ellipse is unbounded or the arithmetic is doubtful the record says "everything".
+__device__ __forceinline__ CullRec cull_record(const float* Tu, const float* Tv, const float* Tw, float cx, float cy,
+                                               float opa) {
+  CullRec everything, nothing;
+  everything.a = make_float4(0.f, 0.f, 0.f, CULL_EVERYTHING); everything.b = make_float4(0.f, 0.f, 0.f, 0.f);
+  nothing.a = make_float4(0.f, 0.f, 0.f, CULL_NOTHING); nothing.b = make_float4(0.f, 0.f, 0.f, 0.f);
   if (!(opa >= 0.0f)) return everything;                        // NaN / negative: leave it to the exact test
   if (opa < 0.0039f) return nothing;                            // opa*G <= opa < 1/255 always
-  float c2 = 2.0f * logf(255.0f * opa);
-  c2 = c2 * 1.001f + 0.01f;                                     // slack >> fp32 error of rho and expf
-  const float d = c2 * (Tw[0] * Tw[0] + Tw[1] * Tw[1]) - Tw[2] * Tw[2];
-  if (!(d < -1e-6f * Tw[2] * Tw[2])) return everything;         // ellipse not bounded (or nearly so)
-  const float f0 = c2 / d, f2 = -1.0f / d;
-  const float ex = f0 * (Tu[0] * Tw[0] + Tu[1] * Tw[1]) + f2 * Tu[2] * Tw[2];
-  const float ey = f0 * (Tv[0] * Tw[0] + Tv[1] * Tw[1]) + f2 * Tv[2] * Tw[2];
-  const float hx2 = ex * ex - (f0 * (Tu[0] * Tu[0] + Tu[1] * Tu[1]) + f2 * Tu[2] * Tu[2]);
-  const float hy2 = ey * ey - (f0 * (Tv[0] * Tv[0] + Tv[1] * Tv[1]) + f2 * Tv[2] * Tv[2]);
-  if (!(hx2 == hx2) || !(hy2 == hy2) || !(fabsf(ex) < 1e7f) || !(fabsf(ey) < 1e7f)) return everything;
-  const float hx = sqrtf(fmaxf(hx2, 0.0f)), hy = sqrtf(fmaxf(hy2, 0.0f));
-  const float r2 = sqrtf(0.5f * c2);
-  // 1-pixel geometric margin plus a relative one for large coordinates
-  const float mx = 1.0f + 1e-4f * (fabsf(ex) + hx + fabsf(cx)), my = 1.0f + 1e-4f * (fabsf(ey) + hy + fabsf(cy));
-  const float x0 = fminf(ex - hx, cx - r2) - mx, x1 = fmaxf(ex + hx, cx + r2) + mx;
-  const float y0 = fminf(ey - hy, cy - r2) - my, y1 = fmaxf(ey + hy, cy + r2) + my;
-  if (!(x0 == x0) || !(x1 == x1) || !(y0 == y0) || !(y1 == y1)) return everything;
-  if (x1 < 0.0f || y1 < 0.0f || x0 > 65535.0f || y0 > 65535.0f) return nothing;
-  const unsigned ix0 = (unsigned)fmaxf(floorf(x0), 0.0f), ix1 = (unsigned)fminf(ceilf(x1), 65535.0f);
-  const unsigned iy0 = (unsigned)fmaxf(floorf(y0), 0.0f), iy1 = (unsigned)fminf(ceilf(y1), 65535.0f);
-  return make_uint2(ix0 | (ix1 << 16), iy0 | (iy1 << 16));
+  const double c2 = 2.0 * (double)logf(255.0f * opa) * 1.002 + 0.02;   // slack >> fp32 error of rho and expf
+  const double u0 = Tu[0], u1 = Tu[1], u2 = Tu[2], v0 = Tv[0], v1 = Tv[1], v2 = Tv[2], w0 = Tw[0], w1 = Tw[1], w2 = Tw[2];
+  const double d = c2 * (w0 * w0 + w1 * w1) - w2 * w2;
+  if (!(d < -1e-6 * w2 * w2)) return everything;                // ellipse not bounded (or nearly so)
+  const double f0 = c2 / d, f2 = -1.0 / d;
+  const double ex = f0 * (u0 * w0 + u1 * w1) + f2 * u2 * w2;
+  const double ey = f0 * (v0 * w0 + v1 * w1) + f2 * v2 * w2;
+  const double delta2 = 0.05 * 0.05;
+  const double S00 = ex * ex - (f0 * (u0 * u0 + u1 * u1) + f2 * u2 * u2) + delta2;
+  const double S11 = ey * ey - (f0 * (v0 * v0 + v1 * v1) + f2 * v2 * v2) + delta2;
+  const double S01 = ex * ey - (f0 * (u0 * v0 + u1 * v1) + f2 * u2 * v2);
+  const double det = S00 * S11 - S01 * S01;
+  if (!(S00 > 0.0) || !(S11 > 0.0) || !(det > 0.0)) return everything;
+  if (!(fabs(ex) < 1e6) || !(fabs(ey) < 1e6) || !(S00 < 1e10) || !(S11 < 1e10)) return everything;
+  const double hx = sqrt(S00);
+  const double dcx = (double)cx - ex, dcy = (double)cy - ey;
+  const double rr = sqrt(0.5 * c2) + sqrt(dcx * dcx + dcy * dcy);
+  if (!(rr < 1e6)) return everything;
+  CullRec r;
+  r.a = make_float4((float)ex, (float)ey, (float)(hx * (1.0 + 1e-6)), (float)(S11 * (1.0 + 1e-6)));
+  r.b = make_float4((float)(S01 / S11), (float)(sqrt(det) / S11 * (1.0 + 1e-6)), (float)(S01 / hx),
+                    (float)(rr * rr * (1.0 + 1e-6)));
+  return r;
 }
 
 __global__ void __launch_bounds__(256) surfel_preprocess_kernel(const SurfelPreArgs a) {
@@ -220,7 +228,7 @@ __global__ void __launch_bounds__(256) surfel_preprocess_kernel(const SurfelPreA
   const float opa = a.opacities[idx];
   const float refl = a.refl ? a.refl[idx] : 0.0f;
   const float mk = (a.mask && a.mask[idx]) ? 1.0f : 0.0f;
-  a.cull[idx] = cull_bbox(Tu, Tv, Tw, cx, cy, opa);
+  a.cull[idx] = cull_record(Tu, Tv, Tw, cx, cy, opa);
   SurfelRec* r = a.rec + idx;
   r->q[0] = make_float4(Tu[0], Tu[1], Tu[2], Tv[0]);
   r->q[1] = make_float4(Tv[1], Tv[2], Tw[0], Tw[1]);

@@ -119,6 +119,26 @@ def timing_read():
     return {timing_stage_name(i).decode(): (float(ms[i]), int(cnt[i])) for i in range(n)}
 
 
+debug_cull_audit = _sig("b200gs_debug_cull_audit", None, _i)
+_cull_violations = _sig("b200gs_debug_cull_violations", _i, _p, _i)
+
+
+_cull_stats = _sig("b200gs_debug_cull_stats", _i, _p, _i)
+
+
+def cull_stats(reset=True):
+    out = (C.c_ulonglong * 8)()
+    check(_cull_stats(C.cast(out, _p), 1 if reset else 0))
+    return [int(x) for x in out]
+
+
+def cull_violations(reset=True):
+    """-> (forward-threshold, backward-threshold) violation counts of the cull audit."""
+    out = (C.c_ulonglong * 2)()
+    check(_cull_violations(C.cast(out, _p), 1 if reset else 0))
+    return int(out[0]), int(out[1])
+
+
 mark_visible = _sig("b200gs_mark_visible", _i, _i, _p, _p, _p, _p, _p)
 surfel_geom_bytes = _sig("b200gs_surfel_geom_bytes", _sz, _i)
 surfel_image_bytes = _sig("b200gs_surfel_image_bytes", _sz, _i, _i)

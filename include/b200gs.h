@@ -53,6 +53,19 @@ int b200gs_timing_stages(void);
 const char* b200gs_timing_stage_name(int stage);
 int b200gs_timing_read(float* ms, unsigned long long* counts, int n);
 
+/* Cull audit (test infrastructure for the sub-tile culling of the surfel compositing):
+ * while on, the forward compositing ignores the per-instance hit masks, evaluates every
+ * (warp block, Gaussian) pair the way the reference does and counts the pairs that pass the
+ * reference's alpha >= 1/255 cut although their mask bit is clear -- out2[0] with the forward's
+ * `unstable` threshold (S/cuda_rasterizer/forward.cu:373), out2[1] with the backward's
+ * (backward.cu:302).  Both must read 0: the masks may only drop pairs the reference drops.  */
+void b200gs_debug_cull_audit(int on);
+int b200gs_debug_cull_violations(unsigned long long* out2, int reset);
+/* Workload counters of the audit pass: out8[0] (warp block, entry) pairs visited with the hit
+ * bit set, [1] those with >= 1 contributing pixel, [2] contributing (pixel, entry) pairs,
+ * [3] sum over (warp, batch) of the busiest pixel's contributions, [4] (warp, batch) count.   */
+int b200gs_debug_cull_stats(unsigned long long* out8, int reset);
+
 /* ------------------------------------------------------------------------ */
 /* markVisible  (S/rasterize_points.cu:269-288, rasterizer_impl.cu:54-66)     */
 int b200gs_mark_visible(int P, const float* means3D, const float* viewmatrix,
