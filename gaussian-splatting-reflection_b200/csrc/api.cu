@@ -79,6 +79,7 @@ SurfelImage SurfelImage::carve(void* base, int W, int H, size_t* bytes) {
   im.accum = c.take<float>(3 * N);
   im.n_contrib = c.take<uint32_t>(2 * N);
   im.ranges = c.take<uint2>(tiles);
+  im.cranges = c.take<uint2>(tiles);
   if (bytes) *bytes = c.used + 128;
   return im;
 }
@@ -195,8 +196,12 @@ int b200gs_surfel_forward_stage2(const b200gs_surfel_fwd* a, int R, void* stream
   Binning b = Binning::carve(R > 0 ? align128(a->binning) : nullptr, R, nullptr);
   rc = bin_and_sort(g.depths, g.rects, g.point_offsets, a->P, R, a->width, a->height, b, im.ranges, s, a->debug != 0);
   if (rc) return rc;
+  {
+    const size_t tiles = (size_t)((a->width + TILE_X - 1) / TILE_X) * ((a->height + TILE_Y - 1) / TILE_Y);
+    B200GS_CUDA(cudaMemsetAsync(im.cranges, 0, tiles * sizeof(uint2), s));
+  }
   if (R > 0) {
-    rc = surfel_tile_hits(g.cull, b, R, a->width, s, a->debug != 0);
+    rc = surfel_tile_hits(g.cull, b, R, a->width, a->height, im.ranges, im.cranges, s, a->debug != 0);
     if (rc) return rc;
   }
   return surfel_composite_forward(*a, g, im, b, s);

@@ -182,67 +182,207 @@ __global__ void __launch_bounds__(256) tile_ranges_kernel(int L, const uint64_t*
 // For every sorted (tile, Gaussian) instance: which of the tile's eight 8x4 warp blocks (bit w:
 // column w&1, row w>>1, the layout of tile_pixel()) can the Gaussian reach alpha >= 1/255 in?
 // Block = pixel centres [8c, 8c+7] x [4r, 4r+3] relative to the tile origin, tested as the
-// rectangle dilated by half a pixel against the CullRec ellipse (exact convex test: the x-extent
-// of ellipse /\ row band is attained at the ellipse's extreme point if that lies in the band, else
-// on one of the band's two boundary lines) and against the low-pass disk.  One byte per instance;
-// the list itself is untouched (the reference's list order and positions are what n_contrib counts).
-__global__ void __launch_bounds__(256) tile_hits_kernel(int R, const uint64_t* __restrict__ keys,
-                                                        const uint32_t* __restrict__ point_list,
-                                                        const CullRec* __restrict__ cull, int gx,
-                                                        uint8_t* __restrict__ hit) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= R) return;
-  const uint32_t tile = (uint32_t)(keys[i] >> 32);
-  const uint32_t id = point_list[i];
-  const float4 ca = __ldg(&cull[id].a), cb = __ldg(&cull[id].b);
-  unsigned mask;
-  if (ca.w < 0.0f) {
-    mask = (ca.w == CULL_NOTHING) ? 0u : 0xFFu;
-  } else {
-    const float ox = (float)((tile % (uint32_t)gx) * TILE_X) - 0.5f - ca.x;  // left edge of column 0, relative to e
-    const float oy = (float)((tile / (uint32_t)gx) * TILE_Y) - 0.5f - ca.y;  // top edge of row band 0
-    const float hx = ca.z, hy2 = ca.w, sl = cb.x, k = cb.y, dyR = cb.z, r2 = cb.w;
-    const float INF = __int_as_float(0x7f800000);
-    float lo[5], hi[5];
+// rectangle dilated by half a pixel: (a) the exact minimum of the CullRec quadratic form f over
+// the rectangle -- for ANY quadratic it is attained at a corner, at the vertex of f along an edge
+// (if f is convex along it and the vertex lies on the edge) or at the interior critical point (if
+// f is convex and the point lies inside) -- compared with a tolerance 100x the fp32 evaluation
+// error; (b) the distance of the low-pass disk centre to the rectangle.
+// Instances with an empty mask are dropped from the COMPACTED list the compositing kernels walk
+// (single-pass stream compaction, chained-scan look-back); the reference's list itself is
+// untouched and every survivor carries its position in it (that is what n_contrib counts).
+constexpr int TH_THREADS = 256;
+constexpr int TH_ITEMS = 4;
+constexpr int TH_TILE = TH_THREADS * TH_ITEMS;
+
+__device__ __forceinline__ unsigned block_hit_mask(const CullRec* __restrict__ cull, uint32_t id, int tx0, int ty0) {
+  const double4 c0 = *reinterpret_cast<const double4*>(&cull[id].A);   // A B C D
+  const double2 c1 = *reinterpret_cast<const double2*>(&cull[id].E);   // E F
+  const float4 c2 = *reinterpret_cast<const float4*>(&cull[id].cx);    // cx cy r2 flag
+  if (c2.w != 0.0f) return (c2.w == CULL_NOTHING) ? 0u : 0xFFu;
+  // translate the form to the corner (-0.5, -0.5) of the dilated tile, in fp64
+  const double ox = (double)tx0 - 0.5, oy = (double)ty0 - 0.5;
+  const double Dd = c0.x * ox + c0.y * oy + c0.w;
+  const double Ed = c0.y * ox + c0.z * oy + c1.x;
+  const double Fd = (c0.x * ox + 2.0 * c0.y * oy + 2.0 * c0.w) * ox + (c0.z * oy + 2.0 * c1.x) * oy + c1.y;
+  const float A = (float)c0.x, B = (float)c0.y, C = (float)c0.z, D = (float)Dd, E = (float)Ed, F = (float)Fd;
+  if (!(fabsf(D) < 1e30f) || !(fabsf(E) < 1e30f) || !(fabsf(F) < 1e30f)) return 0xFFu;
+  const float tol = 1e-5f * (256.0f * (fabsf(A) + 2.0f * fabsf(B) + fabsf(C)) + 32.0f * (fabsf(D) + fabsf(E)) + fabsf(F));
+  const float INF = __int_as_float(0x7f800000);
+  // f(x,y) = A x^2 + 2 B x y + C y^2 + 2 D x + 2 E y + F on the grid lines x in {0,8,16}, y in {0,4,..,16}
+  float mn[4][2];
 #pragma unroll
-    for (int j = 0; j < 5; ++j) {
-      const float dy = oy + 4.0f * j;
-      const float rem = hy2 - dy * dy;
-      const float h = k * sqrtf(fmaxf(rem, 0.0f));
-      lo[j] = rem >= 0.0f ? sl * dy - h : INF;
-      hi[j] = rem >= 0.0f ? sl * dy + h : -INF;
+  for (int r = 0; r < 4; ++r) { mn[r][0] = INF; mn[r][1] = INF; }
+  float corner[5][3];
+#pragma unroll
+  for (int j = 0; j < 5; ++j) {
+    const float y = 4.0f * j;
+    const float gy = (C * y + 2.0f * E) * y + F;      // terms without x
+    const float bx = B * y + D;                         // f = A x^2 + 2 bx x + gy
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      const float x = 8.0f * i;
+      corner[j][i] = (A * x + 2.0f * bx) * x + gy;
     }
-    // disk: squared distance from e to the column / row intervals
-    float ddx2[2], ddy2[4];
-#pragma unroll
-    for (int c = 0; c < 2; ++c) {
-      const float d = fmaxf(fmaxf(ox + 8.0f * c, -(ox + 8.0f * (c + 1))), 0.0f);
-      ddx2[c] = d * d;
+    // vertex of f along the horizontal line
+    float hv0 = INF, hv1 = INF;
+    if (A > 0.0f) {
+      const float xs = -bx / A;
+      const float val = gy - bx * bx / A;
+      if (xs > 0.0f && xs < 16.0f) { if (xs <= 8.0f) hv0 = val; if (xs >= 8.0f) hv1 = val; }
     }
-    mask = 0u;
+    if (j < 4) { mn[j][0] = fminf(mn[j][0], hv0); mn[j][1] = fminf(mn[j][1], hv1); }
+    if (j > 0) { mn[j - 1][0] = fminf(mn[j - 1][0], hv0); mn[j - 1][1] = fminf(mn[j - 1][1], hv1); }
+  }
 #pragma unroll
-    for (int r = 0; r < 4; ++r) {
-      const float ya = oy + 4.0f * r, yb = oy + 4.0f * (r + 1);
-      const float d = fmaxf(fmaxf(ya, -yb), 0.0f);
-      ddy2[r] = d * d;
-      const float xmax = (dyR >= ya && dyR <= yb) ? hx : fmaxf(hi[r], hi[r + 1]);
-      const float xmin = (-dyR >= ya && -dyR <= yb) ? -hx : fminf(lo[r], lo[r + 1]);
+  for (int r = 0; r < 4; ++r)
 #pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        const float xa = ox + 8.0f * c, xb = ox + 8.0f * (c + 1);
-        const bool ell = xmin <= xb && xmax >= xa;
-        const bool disk = ddx2[c] + ddy2[r] <= r2;
-        if (ell || disk) mask |= 1u << (r * 2 + c);
+    for (int c = 0; c < 2; ++c)
+      mn[r][c] = fminf(mn[r][c], fminf(fminf(corner[r][c], corner[r][c + 1]), fminf(corner[r + 1][c], corner[r + 1][c + 1])));
+  // vertices along the three vertical lines
+  if (C > 0.0f) {
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      const float x = 8.0f * i;
+      const float by = B * x + E;                        // f = C y^2 + 2 by y + gx
+      const float gx = (A * x + 2.0f * D) * x + F;
+      const float ys = -by / C;
+      const float val = gx - by * by / C;
+      if (ys > 0.0f && ys < 16.0f) {
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+          if (ys >= 4.0f * r && ys <= 4.0f * (r + 1)) {
+            if (i < 2) mn[r][i] = fminf(mn[r][i], val);
+            if (i > 0) mn[r][i - 1] = fminf(mn[r][i - 1], val);
+          }
       }
     }
   }
-  hit[i] = (uint8_t)mask;
+  // interior critical point
+  const float det = A * C - B * B;
+  if (A > 0.0f && det > 0.0f) {
+    const float xs = (B * E - C * D) / det, ys = (B * D - A * E) / det;
+    if (xs > 0.0f && xs < 16.0f && ys > 0.0f && ys < 16.0f) {
+      const float val = D * xs + E * ys + F;             // f at the critical point
+#pragma unroll
+      for (int r = 0; r < 4; ++r)
+#pragma unroll
+        for (int c = 0; c < 2; ++c)
+          if (xs >= 8.0f * c && xs <= 8.0f * (c + 1) && ys >= 4.0f * r && ys <= 4.0f * (r + 1)) mn[r][c] = fminf(mn[r][c], val);
+    }
+  }
+  // low-pass disk
+  const float dxc = c2.x - ((float)tx0 - 0.5f), dyc = c2.y - ((float)ty0 - 0.5f);   // centre relative to the dilated corner
+  unsigned mask = 0u;
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const float ddy = fmaxf(fmaxf(4.0f * r - dyc, dyc - 4.0f * (r + 1)), 0.0f);
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      const float ddx = fmaxf(fmaxf(8.0f * c - dxc, dxc - 8.0f * (c + 1)), 0.0f);
+      const bool disk = ddx * ddx + ddy * ddy <= c2.z;
+      if (mn[r][c] <= tol || disk) mask |= 1u << (r * 2 + c);
+    }
+  }
+  return mask;
 }
 
-int surfel_tile_hits(const CullRec* cull, const Binning& b, int R, int W, cudaStream_t s, bool debug) {
+// state[0] = ticket; look-back words (flag << 32 | count) start at state + 2.
+__global__ void __launch_bounds__(TH_THREADS) tile_hits_kernel(int R, const uint64_t* __restrict__ keys,
+                                                               const uint32_t* __restrict__ point_list,
+                                                               const CullRec* __restrict__ cull, int gx,
+                                                               const uint2* __restrict__ ranges, uint2* __restrict__ cranges,
+                                                               uint32_t* __restrict__ comp_id, uint32_t* __restrict__ comp_pos,
+                                                               uint8_t* __restrict__ comp_hit, uint32_t* state,
+                                                               int keep_all) {
+  __shared__ uint32_t s_tile;
+  __shared__ uint32_t s_cnt[TH_ITEMS][TH_THREADS / 32];
+  __shared__ uint32_t s_base;
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  if (t == 0) s_tile = atomicAdd(state, 1u);
+  __syncthreads();
+  const uint32_t blk = s_tile;
+  const int base = (int)blk * TH_TILE;
+
+  unsigned mask[TH_ITEMS];
+  uint32_t id[TH_ITEMS], tile[TH_ITEMS], wexcl[TH_ITEMS];
+  bool keep[TH_ITEMS];
+#pragma unroll
+  for (int k = 0; k < TH_ITEMS; ++k) {
+    const int i = base + k * TH_THREADS + t;
+    mask[k] = 0u; id[k] = 0u; tile[k] = 0u;
+    if (i < R) {
+      tile[k] = (uint32_t)(keys[i] >> 32);
+      id[k] = point_list[i];
+      mask[k] = block_hit_mask(cull, id[k], (int)(tile[k] % (uint32_t)gx) * TILE_X, (int)(tile[k] / (uint32_t)gx) * TILE_Y);
+    }
+    keep[k] = i < R && (mask[k] != 0u || keep_all);   // keep_all: cull audit walks the full lists
+    const unsigned bal = __ballot_sync(0xffffffffu, keep[k]);
+    wexcl[k] = __popc(bal & ((1u << lane) - 1u));
+    if (lane == 0) s_cnt[k][warp] = __popc(bal);
+  }
+  __syncthreads();
+  // exclusive offsets of every (round, warp) group and the block total
+  uint32_t total = 0, mine[TH_ITEMS] = {0u, 0u, 0u, 0u};
+#pragma unroll
+  for (int k = 0; k < TH_ITEMS; ++k)
+#pragma unroll
+    for (int w = 0; w < TH_THREADS / 32; ++w) {
+      if (w == warp) mine[k] = total;
+      total += s_cnt[k][w];
+    }
+  if (warp == 0) {
+    volatile unsigned long long* st = reinterpret_cast<volatile unsigned long long*>(state + 2);
+    if (lane == 0) st[blk] = ((blk == 0 ? 2ull : 1ull) << 32) | total;
+    uint32_t excl = 0;
+    if (blk > 0) {
+      int look = (int)blk - 1;
+      while (true) {
+        const int q = look - lane;
+        unsigned long long w = 2ull << 32;
+        if (q >= 0) { do { w = st[q]; } while ((w >> 32) == 0ull); }
+        const bool full = (w >> 32) == 2ull;
+        const unsigned ballot = __ballot_sync(0xffffffffu, full);
+        const int first = __ffs(ballot) - 1;
+        uint32_t val = (first < 0 || lane <= first) ? (uint32_t)w : 0u;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) val += __shfl_xor_sync(0xffffffffu, val, d);
+        excl += val;
+        if (first >= 0) break;
+        look -= 32;
+      }
+      if (lane == 0) st[blk] = (2ull << 32) | (unsigned long long)(excl + total);
+    }
+    if (lane == 0) s_base = excl;
+  }
+  __syncthreads();
+  const uint32_t gbase = s_base;
+#pragma unroll
+  for (int k = 0; k < TH_ITEMS; ++k) {
+    const int i = base + k * TH_THREADS + t;
+    if (i >= R) continue;
+    const uint32_t off = gbase + mine[k] + wexcl[k];
+    const uint2 rg = ranges[tile[k]];
+    if (keep[k]) {
+      comp_id[off] = id[k];
+      comp_pos[off] = (uint32_t)i - rg.x;
+      comp_hit[off] = (uint8_t)mask[k];
+    }
+    if ((uint32_t)i == rg.x) cranges[tile[k]].x = off;
+    if ((uint32_t)i + 1u == rg.y) cranges[tile[k]].y = off + (keep[k] ? 1u : 0u);
+  }
+}
+
+size_t tile_hits_state_words(size_t R) { return 2 * ((R + TH_TILE - 1) / TH_TILE + 2); }
+
+int surfel_tile_hits(const CullRec* cull, const Binning& b, int R, int W, int H, const uint2* ranges, uint2* cranges,
+                     cudaStream_t s, bool debug) {
+  (void)H;
   const int gx = (W + TILE_X - 1) / TILE_X;
   StageScope _t(ST_TILE_HITS, s);
-  tile_hits_kernel<<<(R + 255) / 256, 256, 0, s>>>(R, b.keys, b.point_list, cull, gx, b.hit);
+  B200GS_CUDA(cudaMemsetAsync(b.hit_state, 0, tile_hits_state_words(R) * sizeof(uint32_t), s));
+  tile_hits_kernel<<<(R + TH_TILE - 1) / TH_TILE, TH_THREADS, 0, s>>>(R, b.keys, b.point_list, cull, gx, ranges, cranges,
+                                                                       b.comp_id, b.comp_pos, b.comp_hit, b.hit_state,
+                                                                       g_cull_audit.load(std::memory_order_relaxed));
   B200GS_LAUNCHED("tile_hits_kernel", debug, s);
   return B200GS_OK;
 }
@@ -265,7 +405,10 @@ Binning Binning::carve(void* base, size_t R, size_t* bytes) {
   b.point_list_unsorted = c.take<uint32_t>(R);
   b.keys = c.take<uint64_t>(R);
   b.keys_unsorted = c.take<uint64_t>(R);
-  b.hit = c.take<uint8_t>(R);
+  b.comp_id = c.take<uint32_t>(R);
+  b.comp_pos = c.take<uint32_t>(R);
+  b.comp_hit = c.take<uint8_t>(R);
+  b.hit_state = c.take<uint32_t>(tile_hits_state_words(R));
   b.sort_temp_bytes = radix_sort_temp_bytes(R);
   b.sort_temp = c.take<char>(b.sort_temp_bytes);
   if (bytes) *bytes = c.used + 128;

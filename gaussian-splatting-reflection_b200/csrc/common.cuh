@@ -49,6 +49,7 @@ enum Stage {
   ST_COMPOSITE_BWD, ST_PREPROCESS_BWD, ST_CUBEMAP_FWD, ST_CUBEMAP_BWD, ST_TILE_HITS, ST_DEPTH_SORT, ST_COUNT
 };
 extern std::atomic<int> g_timing;
+extern std::atomic<int> g_cull_audit;   // surfel_composite_fwd.cu: b200gs_debug_cull_audit
 void stage_mark(int stage, bool begin, cudaStream_t s);
 struct StageScope {
   int st; cudaStream_t s; bool on;
@@ -84,14 +85,16 @@ struct __align__(16) SurfelRec {
 };
 static_assert(sizeof(SurfelRec) == 80, "record must be 80 B");
 
-// Per-Gaussian cull record (32 B) written by the surfel preprocess: the ellipse {rho3d <= c2}
-// as centre + shape, and the low-pass disk re-centred on it (see cull_record()).
-//   a = ex ey hx hy2      ellipse centre (px), half width, squared half height; hy2 < 0 = flag
-//   b = s  k  dyR r2      chord on the line y = ey + dy: x = ex + s*dy -+ k*sqrt(hy2 - dy^2);
-//                         dyR = y offset of the right-most point; r2 = squared disk radius
+// Per-Gaussian cull record (64 B) written by the surfel preprocess: the point conic of
+// {rho3d <= c2} in pixel coordinates, f(x,y) = A x^2 + 2B xy + C y^2 + 2D x + 2E y + F <= 0
+// (valid for ellipses AND for the hyperbolas of splats that cross the camera plane), in fp64
+// and normalised to max(|A|,|B|,|C|) = 1, plus the low-pass disk {|p - (cx,cy)|^2 <= r2}.
+// flag: 0 = use the test, CULL_EVERYTHING / CULL_NOTHING = fixed answer.  See cull_record().
 struct __align__(16) CullRec {
-  float4 a, b;
+  double A, B, C, D, E, F;
+  float cx, cy, r2, flag;
 };
+static_assert(sizeof(CullRec) == 64, "cull record must be 64 B");
 constexpr float CULL_EVERYTHING = -1.0f;
 constexpr float CULL_NOTHING = -2.0f;
 
@@ -112,6 +115,7 @@ struct SurfelImage {
   float* accum;        // [3,N]: final T, M1, M2
   uint32_t* n_contrib; // [2,N]: last contributor, median contributor
   uint2* ranges;       // [tiles]
+  uint2* cranges;      // [tiles] ranges into the compacted instance list (Binning::comp_*)
   static SurfelImage carve(void* base, int W, int H, size_t* bytes);
 };
 
@@ -120,7 +124,12 @@ struct Binning {
   uint32_t* point_list_unsorted;  // [R]
   uint64_t* keys;                 // [R] sorted keys
   uint64_t* keys_unsorted;        // [R]
-  uint8_t* hit;                   // [R] per sorted instance: bit w = warp block w of the tile can reach alpha >= 1/255
+  // Compacted instance list: the sorted instances that can reach alpha >= 1/255 in at least one
+  // 8x4 warp block of their tile (tile_hits_kernel), in list order, with their list position.
+  uint32_t* comp_id;              // [<=R] Gaussian id
+  uint32_t* comp_pos;             // [<=R] 0-based position in the tile's (uncompacted) list
+  uint8_t* comp_hit;              // [<=R] bit w = warp block w of the tile can be reached
+  uint32_t* hit_state;            // look-back words + ticket of the compaction
   void* sort_temp;
   size_t sort_temp_bytes;
   static Binning carve(void* base, size_t R, size_t* bytes);
@@ -217,7 +226,9 @@ int surfel_preprocess(const b200gs_surfel_fwd& a, const SurfelGeom& g, cudaStrea
 int inclusive_scan_u32(const uint32_t* in, uint32_t* out, int n, uint32_t* state, cudaStream_t s, bool debug);
 int bin_and_sort(const float* depths, const uint2* rects, const uint32_t* offsets,
                  int P, int R, int W, int H, const Binning& b, uint2* ranges, cudaStream_t s, bool debug);
-int surfel_tile_hits(const CullRec* cull, const Binning& b, int R, int W, cudaStream_t s, bool debug);
+int surfel_tile_hits(const CullRec* cull, const Binning& b, int R, int W, int H, const uint2* ranges, uint2* cranges,
+                     cudaStream_t s, bool debug);
+size_t tile_hits_state_words(size_t R);
 int surfel_composite_forward(const b200gs_surfel_fwd& a, const SurfelGeom& g, const SurfelImage& im,
                              const Binning& b, cudaStream_t s);
 int surfel_composite_backward(const b200gs_surfel_bwd& a, const SurfelGeom& g, const SurfelImage& im,

@@ -16,10 +16,11 @@ namespace b200gs {
 
 struct CompBwdArgs {
   int W, H, gx;
-  const uint2* ranges;
-  const uint32_t* point_list;
+  const uint2* ranges;        // ranges into the COMPACTED instance list
+  const uint32_t* point_list; // compacted ids
+  const uint32_t* list_pos;   // position of every compacted entry in the tile's full list (ascending)
   const SurfelRec* rec;
-  const uint8_t* hit;   // [R]
+  const uint8_t* hit;         // per compacted entry
   const float* bg;
   const float* accum;         // [3,N] final T, M1, M2
   const uint32_t* n_contrib;  // [2,N]
@@ -34,7 +35,9 @@ constexpr int BATCH = 256;
 __global__ void __launch_bounds__(BATCH, 2) surfel_composite_bwd_kernel(const CompBwdArgs a) {
   __shared__ SurfelRec s_rec[2][BATCH];
   __shared__ int s_id[2][BATCH];
-  __shared__ uint8_t s_hit[2][BATCH];   // bit w: the entry's cull box overlaps warp w's 8x4 pixel block
+  __shared__ uint32_t s_pos[2][BATCH];
+  __shared__ uint8_t s_hit[2][BATCH];   // bit w: the entry can reach alpha >= 1/255 in warp w's 8x4 pixel block
+  __shared__ int s_n;                   // live prefix of the tile's compacted list
 
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const int tile = blockIdx.x;
@@ -48,9 +51,7 @@ __global__ void __launch_bounds__(BATCH, 2) surfel_composite_bwd_kernel(const Co
   const size_t pix_id = (size_t)a.W * pyi + pxi;
 
   const uint2 range = a.ranges[tile];
-  const int n = (int)(range.y - range.x);
-  const int rounds = (n + BATCH - 1) / BATCH;
-  if (n == 0) return;
+  if (range.y == range.x) return;
 
   // lane -> accumulator component owned after the reduce-scatter
   const int b16 = (lane >> 4) & 1, b8 = (lane >> 3) & 1, b4 = (lane >> 2) & 1, b2 = (lane >> 1) & 1, b1 = lane & 1;
@@ -94,10 +95,39 @@ __global__ void __launch_bounds__(BATCH, 2) surfel_composite_bwd_kernel(const Co
 
   const uint32_t* pl = a.point_list + range.x;
   const uint8_t* ph = a.hit + range.x;
+  const uint32_t* pp = a.list_pos + range.x;
+
+  // Entries at or behind the last contributor of every pixel of the tile are never used
+  // (backward.cu:290: `contributor >= last_contributor` -> continue): list positions ascend, so
+  // the live part is a prefix of the compacted list; find its length by bisection.
+  const uint32_t warp_last = __reduce_max_sync(0xffffffffu, inside ? last_contributor : 0u);
+  {
+    __shared__ uint32_t s_last[BATCH / 32];
+    if (lane == 0) s_last[warp] = warp_last;
+    __syncthreads();
+    if (t == 0) {
+      uint32_t tile_last = 0;
+#pragma unroll
+      for (int w = 0; w < BATCH / 32; ++w) tile_last = max(tile_last, s_last[w]);
+      int lo = 0, hi = (int)(range.y - range.x);     // first index with pos >= tile_last
+      while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (pp[mid] < tile_last) lo = mid + 1; else hi = mid;
+      }
+      s_n = lo;
+    }
+    __syncthreads();
+  }
+  const int n = s_n;
+  const int rounds = (n + BATCH - 1) / BATCH;
+  if (n == 0) return;
+
   unsigned hit_cur = 0u, hit_next = 0u;
+  uint32_t pos_next = 0u;
   auto stage = [&](int buf, int id) {
     hit_cur = hit_next;
     if (id >= 0) {
+      s_pos[buf][t] = pos_next;
       const SurfelRec* g = a.rec + id;
       SurfelRec* d = &s_rec[buf][t];
 #pragma unroll
@@ -107,14 +137,13 @@ __global__ void __launch_bounds__(BATCH, 2) surfel_composite_bwd_kernel(const Co
     cp_async_commit();
   };
   int id_next = -1;
-  if (t < n) { id_next = (int)pl[n - 1 - t]; hit_next = ph[n - 1 - t]; }
+  if (t < n) { id_next = (int)pl[n - 1 - t]; hit_next = ph[n - 1 - t]; pos_next = pp[n - 1 - t]; }
   stage(0, id_next);
   id_next = -1; hit_next = 0u;
-  if (BATCH + t < n) { id_next = (int)pl[n - 1 - (BATCH + t)]; hit_next = ph[n - 1 - (BATCH + t)]; }
+  if (BATCH + t < n) { const int q = n - 1 - (BATCH + t); id_next = (int)pl[q]; hit_next = ph[q]; pos_next = pp[q]; }
 
   // Warps whose pixels all have last_contributor == 0 have nothing to do, but they
   // still take part in the staging and barriers.
-  const uint32_t warp_last = __reduce_max_sync(0xffffffffu, live ? last_contributor : 0u);
 
   for (int i = 0; i < rounds; ++i) {
     cp_async_wait_all();
@@ -124,25 +153,20 @@ __global__ void __launch_bounds__(BATCH, 2) surfel_composite_bwd_kernel(const Co
       stage((i + 1) & 1, id_next);
       const int nx = (i + 2) * BATCH + t;
       id_next = -1; hit_next = 0u;
-      if (nx < n) { id_next = (int)pl[n - 1 - nx]; hit_next = ph[n - 1 - nx]; }
+      if (nx < n) { const int q = n - 1 - nx; id_next = (int)pl[q]; hit_next = ph[q]; pos_next = pp[q]; }
     }
     const int buf = i & 1;
     const int count = min(BATCH, n - i * BATCH);
     const SurfelRec* rb = s_rec[buf];
-    // entries behind every pixel's last contributor: skip the whole prefix at once
-    int j0 = 0;
-    {
-      const int first_pos = n - i * BATCH;  // `contributor` value before this batch
-      if ((uint32_t)first_pos > warp_last) j0 = min(count, first_pos - (int)warp_last);
-    }
 #pragma unroll 1
-    for (int r = j0 >> 5; r < (count + 31) >> 5; ++r) {
-      unsigned m = __ballot_sync(0xffffffffu, (s_hit[buf][r * 32 + lane] >> warp) & 1u);
-      if (r == (j0 >> 5)) m &= 0xffffffffu << (j0 & 31);   // entries behind every pixel's last contributor
+    for (int r = 0; r < (count + 31) >> 5; ++r) {
+      // entries of other warp blocks, and entries behind every pixel's last contributor, are skipped
+      const int e = r * 32 + lane;
+      unsigned m = __ballot_sync(0xffffffffu, e < count && ((s_hit[buf][e] >> warp) & 1u) && s_pos[buf][e] < warp_last);
       while (m) {
       const int j = r * 32 + __ffs(m) - 1;
       m &= m - 1;
-      const uint32_t contributor = (uint32_t)(n - 1 - (i * BATCH + j));   // 0-based list position
+      const uint32_t contributor = s_pos[buf][j];   // 0-based position in the tile's full list
       const float4 q0 = rb[j].q[0], q1 = rb[j].q[1], q2 = rb[j].q[2];
       SurfelHit h;
       bool c = live && contributor < last_contributor;
@@ -234,7 +258,7 @@ int surfel_composite_backward(const b200gs_surfel_bwd& f, const SurfelGeom& g, c
   a.W = f.width; a.H = f.height;
   a.gx = (f.width + TILE_X - 1) / TILE_X;
   const int gy = (f.height + TILE_Y - 1) / TILE_Y;
-  a.ranges = im.ranges; a.point_list = b.point_list; a.rec = g.rec; a.hit = b.hit; a.bg = f.background;
+  a.ranges = im.cranges; a.point_list = b.comp_id; a.list_pos = b.comp_pos; a.rec = g.rec; a.hit = b.comp_hit; a.bg = f.background;
   a.accum = im.accum; a.n_contrib = im.n_contrib;
   a.dL_dpix = f.dL_dout_color; a.dL_dothers = f.dL_dout_others; a.dL_drefl = f.dL_dout_refl;
   a.acc = acc;

@@ -15,10 +15,11 @@ namespace b200gs {
 
 struct CompFwdArgs {
   int W, H, gx;
-  const uint2* ranges;
-  const uint32_t* point_list;
+  const uint2* ranges;        // ranges into the COMPACTED instance list
+  const uint32_t* point_list; // compacted ids
+  const uint32_t* list_pos;   // position of every compacted entry in the tile's full list
   const SurfelRec* rec;
-  const uint8_t* hit;   // [R] per list entry: warp blocks that can reach alpha >= 1/255 (tile_hits_kernel)
+  const uint8_t* hit;         // per compacted entry: warp blocks that can reach alpha >= 1/255 (tile_hits_kernel)
   const float* bg;
   float* accum;         // [3,N]
   uint32_t* n_contrib;  // [2,N]
@@ -45,6 +46,7 @@ template <bool AUDIT>
 __global__ void __launch_bounds__(BATCH) surfel_composite_fwd_kernel(const CompFwdArgs a) {
   __shared__ SurfelRec s_rec[2][BATCH];
   __shared__ int s_id[2][BATCH];
+  __shared__ uint32_t s_pos[2][BATCH];
   __shared__ int s_wmax[2][BATCH];
   __shared__ uint8_t s_hit[2][BATCH];   // bit w: the entry's cull box overlaps warp w's 8x4 pixel block
 
@@ -75,11 +77,14 @@ __global__ void __launch_bounds__(BATCH) surfel_composite_fwd_kernel(const CompF
 
   const uint32_t* pl = a.point_list + range.x;
   const uint8_t* ph = a.hit + range.x;
+  const uint32_t* pp = a.list_pos + range.x;
   unsigned hit_cur = 0u;                 // hit mask of the entry this thread staged for the batch about to run
   unsigned hit_next = 0u;
+  uint32_t pos_next = 0u;
   auto stage = [&](int buf, int id) {
     hit_cur = hit_next;                  // 0 for padding entries: never visited
     if (id >= 0) {
+      s_pos[buf][t] = pos_next;
       const SurfelRec* g = a.rec + id;
       SurfelRec* d = &s_rec[buf][t];
 #pragma unroll
@@ -89,10 +94,10 @@ __global__ void __launch_bounds__(BATCH) surfel_composite_fwd_kernel(const CompF
     cp_async_commit();
   };
   int id_next = -1;
-  if (t < n) { id_next = (int)pl[t]; hit_next = ph[t]; }
+  if (t < n) { id_next = (int)pl[t]; hit_next = ph[t]; pos_next = pp[t]; }
   stage(0, id_next);
   id_next = -1; hit_next = 0u;
-  if (BATCH + t < n) { id_next = (int)pl[BATCH + t]; hit_next = ph[BATCH + t]; }
+  if (BATCH + t < n) { id_next = (int)pl[BATCH + t]; hit_next = ph[BATCH + t]; pos_next = pp[BATCH + t]; }
 
   const int warp = t >> 5;
   int last_batch = -1;
@@ -111,7 +116,7 @@ __global__ void __launch_bounds__(BATCH) surfel_composite_fwd_kernel(const CompF
       stage((i + 1) & 1, id_next);
       const int nx = (i + 2) * BATCH + t;
       id_next = -1; hit_next = 0u;
-      if (nx < n) { id_next = (int)pl[nx]; hit_next = ph[nx]; }
+      if (nx < n) { id_next = (int)pl[nx]; hit_next = ph[nx]; pos_next = pp[nx]; }
     }
     last_batch = i;
     const int buf = i & 1;
@@ -126,7 +131,7 @@ __global__ void __launch_bounds__(BATCH) surfel_composite_fwd_kernel(const CompF
         if (__all_sync(0xffffffffu, done)) { warp_done = true; break; }
         const int j = r * 32 + __ffs(m) - 1;
         m &= m - 1;
-        const uint32_t contributor = (uint32_t)(i * BATCH + j + 1);  // 1-based position in the tile's list
+        const uint32_t contributor = s_pos[buf][j] + 1u;  // 1-based position in the tile's (full) list
         const float4 q0 = rb[j].q[0], q1 = rb[j].q[1], q2 = rb[j].q[2];
         SurfelHit h;
         bool c = surfel_eval<false>(q0, q1, q2, fx, fy, h);
@@ -219,7 +224,7 @@ int surfel_composite_forward(const b200gs_surfel_fwd& f, const SurfelGeom& g, co
   a.W = f.width; a.H = f.height;
   a.gx = (f.width + TILE_X - 1) / TILE_X;
   const int gy = (f.height + TILE_Y - 1) / TILE_Y;
-  a.ranges = im.ranges; a.point_list = b.point_list; a.rec = g.rec; a.hit = b.hit; a.bg = f.background;
+  a.ranges = im.cranges; a.point_list = b.comp_id; a.list_pos = b.comp_pos; a.rec = g.rec; a.hit = b.comp_hit; a.bg = f.background;
   a.accum = im.accum; a.n_contrib = im.n_contrib;
   a.out_color = f.out_color; a.out_others = f.out_others; a.out_refl = f.out_refl;
   a.gaussian_weights = f.gaussian_weights;

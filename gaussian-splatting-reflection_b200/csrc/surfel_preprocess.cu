@@ -50,45 +50,49 @@ struct SurfelPreArgs {
 
 // Conservative description of the pixel region where this Gaussian can reach
 // alpha = min(0.99, opa*exp(-rho/2)) >= 1/255, i.e. rho = min(rho3d, rho2d) <= c2 = 2 ln(255 opa):
-// the union of (a) the projected ellipse {rho3d <= c2} and (b) the low-pass disk {2 |xy - pix|^2 <= c2}.
-// The ellipse comes from the dual conic Q* = M diag(c2, c2, -1) M^T / d (the closed form behind
-// compute_aabb, forward.cu:119-145, which only keeps its axis-aligned extent): centre e = Q*[:2,2],
-// shape Sigma = e e^T - Q*[:2,:2], {p : (p-e)^T Sigma^-1 (p-e) <= 1}.  Evaluated in fp64 (the
-// differences cancel badly in fp32 for small far-off-origin ellipses), inflated by c2*1.002+0.02
-// and Sigma += (0.05 px)^2 I, and the disk is re-centred on e with its radius grown by |xy - e|.
-// tile_hits_kernel (binning.cu) intersects this with every 8x4 warp block of a tile, dilated by
-// half a pixel; the compositing kernels skip (warp, Gaussian) pairs that miss, which the
-// reference would have rejected pixel by pixel with `alpha < 1/255` -- results stay bit-identical.
-// When the ellipse is unbounded or the arithmetic is doubtful the record says "everything".
+// the union of (a) {rho3d <= c2} and (b) the low-pass disk {2 |xy - pix|^2 <= c2}.
+// (a): the ray-splat intersection of pixel p = (x, y, 1) is (u, v, 1) ~ cross(x Tw - Tu, y Tw - Tv)
+//      = x (Tv x Tw) + y (Tw x Tu) + (Tu x Tv)   (forward.cu:362-376; the x*y term cancels), a
+//      LINEAR map of p, so rho3d = u^2 + v^2 <= c2 is the quadratic form
+//      f(p) = (a1.p)^2 + (a2.p)^2 - c2 (a3.p)^2 <= 0 with a_i = i-th components of the three cross
+//      products.  Unlike the bounding-box closed form of compute_aabb (forward.cu:119-145) this
+//      stays valid when the splat crosses the camera plane and the conic is a hyperbola -- the case
+//      where the reference's rect degenerates to "the whole screen" and the Gaussian sits in every
+//      tile's list without ever contributing.
+// Evaluated in fp64 from the fp32 T rows, c2 inflated to 1.002 c2 + 0.02 (>> fp32 error of rho and
+// expf), coefficients normalised.  tile_hits_kernel (binning.cu) minimises f over every 8x4 warp
+// block of a tile (dilated by half a pixel); the compositing kernels skip (warp, Gaussian) pairs
+// that miss, which the reference would have rejected pixel by pixel with `alpha < 1/255` --
+// results stay bit-identical.  Doubtful arithmetic -> "everything".
 __device__ __forceinline__ CullRec cull_record(const float* Tu, const float* Tv, const float* Tw, float cx, float cy,
                                                float opa) {
-  CullRec everything, nothing;
-  everything.a = make_float4(0.f, 0.f, 0.f, CULL_EVERYTHING); everything.b = make_float4(0.f, 0.f, 0.f, 0.f);
-  nothing.a = make_float4(0.f, 0.f, 0.f, CULL_NOTHING); nothing.b = make_float4(0.f, 0.f, 0.f, 0.f);
-  if (!(opa >= 0.0f)) return everything;                        // NaN / negative: leave it to the exact test
-  if (opa < 0.0039f) return nothing;                            // opa*G <= opa < 1/255 always
-  const double c2 = 2.0 * (double)logf(255.0f * opa) * 1.002 + 0.02;   // slack >> fp32 error of rho and expf
-  const double u0 = Tu[0], u1 = Tu[1], u2 = Tu[2], v0 = Tv[0], v1 = Tv[1], v2 = Tv[2], w0 = Tw[0], w1 = Tw[1], w2 = Tw[2];
-  const double d = c2 * (w0 * w0 + w1 * w1) - w2 * w2;
-  if (!(d < -1e-6 * w2 * w2)) return everything;                // ellipse not bounded (or nearly so)
-  const double f0 = c2 / d, f2 = -1.0 / d;
-  const double ex = f0 * (u0 * w0 + u1 * w1) + f2 * u2 * w2;
-  const double ey = f0 * (v0 * w0 + v1 * w1) + f2 * v2 * w2;
-  const double delta2 = 0.05 * 0.05;
-  const double S00 = ex * ex - (f0 * (u0 * u0 + u1 * u1) + f2 * u2 * u2) + delta2;
-  const double S11 = ey * ey - (f0 * (v0 * v0 + v1 * v1) + f2 * v2 * v2) + delta2;
-  const double S01 = ex * ey - (f0 * (u0 * v0 + u1 * v1) + f2 * u2 * v2);
-  const double det = S00 * S11 - S01 * S01;
-  if (!(S00 > 0.0) || !(S11 > 0.0) || !(det > 0.0)) return everything;
-  if (!(fabs(ex) < 1e6) || !(fabs(ey) < 1e6) || !(S00 < 1e10) || !(S11 < 1e10)) return everything;
-  const double hx = sqrt(S00);
-  const double dcx = (double)cx - ex, dcy = (double)cy - ey;
-  const double rr = sqrt(0.5 * c2) + sqrt(dcx * dcx + dcy * dcy);
-  if (!(rr < 1e6)) return everything;
   CullRec r;
-  r.a = make_float4((float)ex, (float)ey, (float)(hx * (1.0 + 1e-6)), (float)(S11 * (1.0 + 1e-6)));
-  r.b = make_float4((float)(S01 / S11), (float)(sqrt(det) / S11 * (1.0 + 1e-6)), (float)(S01 / hx),
-                    (float)(rr * rr * (1.0 + 1e-6)));
+  r.A = r.B = r.C = r.D = r.E = r.F = 0.0;
+  r.cx = cx; r.cy = cy; r.r2 = 0.0f; r.flag = CULL_EVERYTHING;
+  if (!(opa >= 0.0f)) return r;                                  // NaN / negative: leave it to the exact test
+  if (opa < 0.0039f) { r.flag = CULL_NOTHING; return r; }        // opa*G <= opa < 1/255 always
+  const double c2 = 2.0 * (double)logf(255.0f * opa) * 1.002 + 0.02;
+  const double u0 = Tu[0], u1 = Tu[1], u2 = Tu[2], v0 = Tv[0], v1 = Tv[1], v2 = Tv[2], w0 = Tw[0], w1 = Tw[1], w2 = Tw[2];
+  // N0 = Tv x Tw, N1 = Tw x Tu, N2 = Tu x Tv
+  const double n0x = v1 * w2 - v2 * w1, n0y = v2 * w0 - v0 * w2, n0z = v0 * w1 - v1 * w0;
+  const double n1x = w1 * u2 - w2 * u1, n1y = w2 * u0 - w0 * u2, n1z = w0 * u1 - w1 * u0;
+  const double n2x = u1 * v2 - u2 * v1, n2y = u2 * v0 - u0 * v2, n2z = u0 * v1 - u1 * v0;
+  double A = n0x * n0x + n0y * n0y - c2 * n0z * n0z;
+  double B = n0x * n1x + n0y * n1y - c2 * n0z * n1z;
+  double C = n1x * n1x + n1y * n1y - c2 * n1z * n1z;
+  double D = n0x * n2x + n0y * n2y - c2 * n0z * n2z;
+  double E = n1x * n2x + n1y * n2y - c2 * n1z * n2z;
+  double F = n2x * n2x + n2y * n2y - c2 * n2z * n2z;
+  const double m = fmax(fmax(fabs(A), fabs(C)), fabs(B));
+  if (!(m > 0.0) || !(m < 1e300)) return r;
+  const double im = 1.0 / m;
+  A *= im; B *= im; C *= im; D *= im; E *= im; F *= im;
+  if (!(fabs(A) <= 1.0) || !(fabs(B) <= 1.0) || !(fabs(C) <= 1.0)) return r;   // also catches NaN
+  if (!(fabs(D) < 1e30) || !(fabs(E) < 1e30) || !(fabs(F) < 1e30)) return r;
+  if (!(fabsf(cx) < 1e30f) || !(fabsf(cy) < 1e30f)) return r;
+  r.A = A; r.B = B; r.C = C; r.D = D; r.E = E; r.F = F;
+  r.r2 = (float)(0.5 * c2 * (1.0 + 1e-6));
+  r.flag = 0.0f;
   return r;
 }
 
