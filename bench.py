@@ -117,10 +117,12 @@ def algorithmic_bytes(P, V, R, N):
     instances, N pixels."""
     return {
         "preprocess": 237 * P + 87 * V + 8 * P,        # inputs; state of visible ones; radii + tiles_touched
+        "depth_sort": 16 * P,                           # (depth bits, id) pairs read once, written once
         "scan": 8 * P,
-        "duplicate": 12 * V + 12 * R,                   # depth + rect in, (key,value) out
-        "sort": 24 * R,                                 # read pairs once, write them once
-        "tile_ranges": 8 * R,
+        "duplicate": 16 * V + 8 * R,                    # id + offset + rect in, (tile, id) out
+        "sort": 16 * R,                                 # read the 8-B pairs once, write them once
+        "tile_ranges": 4 * R,
+        "tile_hits": 8 * R + 64 * V + 9 * R // 16,      # (tile, id) in, cull record per Gaussian, survivors out (~1/16)
         "composite_fwd": 64 * R + 68 * N,               # staged record per tile entry; 12 planes + 5 state words out
         "composite_bwd": 80 * R + 68 * N + 60 * V,      # record + colour/refl; pixel state + 12 grad planes; partial sums
         "preprocess_bwd": 237 * P + 60 * V + 248 * V,   # inputs again, partial sums in, final gradients out

@@ -61,6 +61,7 @@ SurfelGeom SurfelGeom::carve(void* base, size_t P, size_t* bytes) {
   g.depths = c.take<float>(P);
   g.tiles_touched = c.take<uint32_t>(P);
   g.point_offsets = c.take<uint32_t>(P);
+  g.order = DepthOrder::carve(c, P);
   g.clamped = c.take<uint8_t>(P);
   g.rects = c.take<uint2>(P);
   g.rec = c.take<SurfelRec>(P);
@@ -173,7 +174,7 @@ int b200gs_surfel_forward_stage1(const b200gs_surfel_fwd* a, int* num_rendered, 
   SurfelGeom g = SurfelGeom::carve(align128(a->geom), a->P, nullptr);
   rc = surfel_preprocess(*a, g, s);
   if (rc) return rc;
-  rc = inclusive_scan_u32(g.tiles_touched, g.point_offsets, a->P, g.scan_state, s, a->debug != 0);
+  rc = depth_order_and_scan(g.depths, g.tiles_touched, a->P, g.order, g.point_offsets, g.scan_state, s, a->debug != 0);
   if (rc) return rc;
   int host[2] = {0, 0};
   B200GS_CUDA(cudaMemcpyAsync(&host[0], g.point_offsets + a->P - 1, sizeof(int), cudaMemcpyDeviceToHost, s));
@@ -194,7 +195,7 @@ int b200gs_surfel_forward_stage2(const b200gs_surfel_fwd* a, int R, void* stream
   SurfelGeom g = SurfelGeom::carve(align128(a->geom), a->P, nullptr);
   SurfelImage im = SurfelImage::carve(align128(a->img), a->width, a->height, nullptr);
   Binning b = Binning::carve(R > 0 ? align128(a->binning) : nullptr, R, nullptr);
-  rc = bin_and_sort(g.depths, g.rects, g.point_offsets, a->P, R, a->width, a->height, b, im.ranges, s, a->debug != 0);
+  rc = bin_and_sort(g.order.vals_a, g.rects, g.point_offsets, a->P, R, a->width, a->height, b, im.ranges, s, a->debug != 0);
   if (rc) return rc;
   {
     const size_t tiles = (size_t)((a->width + TILE_X - 1) / TILE_X) * ((a->height + TILE_Y - 1) / TILE_Y);

@@ -1,11 +1,15 @@
-// binning.cu -- K2: prefix sum of tiles_touched, (tile|depth, id) instance
-// emission, 64-bit stable sort and per-tile ranges.
+// binning.cu -- K2: depth order of the Gaussians, prefix sum of tiles_touched, (tile, id)
+// instance emission, stable sort by tile, per-tile ranges, sub-tile hit masks + compaction.
 //
 // Restates rasterizer_impl.cu:70-111 (duplicateWithKeys), :116-138
 // (identifyTileRanges), :35-50 (getHigherMsb) and the two CUB calls at :282 and
 // :308-313 of S/cuda_rasterizer/ (the same lines +-2 in G/).  Results are
-// integer and must be bit-identical to the reference: keys are
-// (tile_id << 32) | float_bits(depth), sorted stably on bits [0, 32+bit).
+// integer and must be bit-identical to the reference, whose keys are
+// (tile_id << 32) | float_bits(depth), sorted stably on bits [0, 32+bit) from an emission in
+// (Gaussian id, rect row, rect column) order.  Here the same order is produced as: stable sort
+// of the Gaussians by depth bits (ties keep id order) -> emission in that order -> stable sort
+// of the instances by tile id (radix_sort.cuh).  The 64-bit keys are only materialised by
+// b200gs_inspect_binning for the parity tests.
 #include "common.cuh"
 #include "radix_sort.cuh"
 
@@ -19,8 +23,10 @@ constexpr int SCAN_THREADS = 256;
 constexpr int SCAN_ITEMS = 16;
 constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
 
+// `gather` (optional): the scan runs over in[gather[i]].
 __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out,
-                                                            int n, unsigned long long* state, uint32_t* ticket) {
+                                                            int n, unsigned long long* state, uint32_t* ticket,
+                                                            const uint32_t* __restrict__ gather) {
   __shared__ uint32_t s_tile;
   __shared__ uint32_t s_warp[SCAN_THREADS / 32];
   __shared__ uint32_t s_prefix;
@@ -30,7 +36,10 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(const uint32_t* __re
   const int base = tile * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
 
   uint32_t v[SCAN_ITEMS];
-  if (base + SCAN_ITEMS <= n) {
+  if (gather != nullptr) {
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; ++k) v[k] = (base + k < n) ? in[gather[base + k]] : 0u;
+  } else if (base + SCAN_ITEMS <= n) {
     const uint4* p = reinterpret_cast<const uint4*>(in + base);
 #pragma unroll
     for (int k = 0; k < SCAN_ITEMS / 4; ++k) {
@@ -107,42 +116,86 @@ size_t scan_state_words(int n) {
   return 2 * (tiles + 2);
 }
 
-int inclusive_scan_u32(const uint32_t* in, uint32_t* out, int n, uint32_t* state, cudaStream_t s, bool debug) {
+int inclusive_scan_u32(const uint32_t* in, uint32_t* out, int n, uint32_t* state, cudaStream_t s, bool debug,
+                       const uint32_t* gather) {
   if (n <= 0) return B200GS_OK;
   const int tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
   StageScope _t(ST_SCAN, s);
   B200GS_CUDA(cudaMemsetAsync(state, 0, scan_state_words(n) * sizeof(uint32_t), s));
   unsigned long long* st = reinterpret_cast<unsigned long long*>(state);
-  scan_kernel<<<tiles, SCAN_THREADS, 0, s>>>(in, out, n, st + 1, state);  // word 0 = ticket
+  scan_kernel<<<tiles, SCAN_THREADS, 0, s>>>(in, out, n, st + 1, state, gather);  // word 0 = ticket
   B200GS_LAUNCHED("scan_kernel", debug, s);
   return B200GS_OK;
 }
 
-// ------------------------------------------------------------------ emission
-// duplicateWithKeys (rasterizer_impl.cu:70-111): rect rows outer, columns inner,
-// key = tile << 32 | depth bits, value = Gaussian id.  One thread per Gaussian
-// for small rects; rects of >= 32 tiles are handed to the whole warp.
-__global__ void __launch_bounds__(256) duplicate_kernel(int P, const float* __restrict__ depths,
-                                                        const uint2* __restrict__ rects,
-                                                        const uint32_t* __restrict__ offsets, uint64_t* __restrict__ keys,
-                                                        uint32_t* __restrict__ vals, int gx) {
+// ------------------------------------------------------------------ depth order
+// Sort key of a Gaussian: the bits of its view depth (what the reference puts in the low key
+// word); culled Gaussians get the largest key -- they emit nothing, so where they land is moot.
+__global__ void __launch_bounds__(256) depth_keys_kernel(int P, const float* __restrict__ depths,
+                                                         const uint32_t* __restrict__ tiles_touched,
+                                                         uint32_t* __restrict__ keys, uint32_t* __restrict__ vals) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= P) return;
+  keys[idx] = tiles_touched[idx] > 0u ? __float_as_uint(depths[idx]) : 0xffffffffu;
+  vals[idx] = (uint32_t)idx;
+}
+
+DepthOrder DepthOrder::carve(Carver& c, size_t P) {
+  DepthOrder o;
+  o.keys_a = c.take<uint32_t>(P);
+  o.vals_a = c.take<uint32_t>(P);
+  o.keys_b = c.take<uint32_t>(P);
+  o.vals_b = c.take<uint32_t>(P);
+  o.ws_bytes = radix_workspace_bytes(P);
+  o.ws = c.take<char>(o.ws_bytes);
+  return o;
+}
+
+// -> o.vals_a = Gaussian ids in (depth bits, id) order; point_offsets = inclusive prefix sum of
+// tiles_touched in that order (the last entry is the instance count R).
+int depth_order_and_scan(const float* depths, const uint32_t* tiles_touched, int P, const DepthOrder& o,
+                         uint32_t* point_offsets, uint32_t* scan_state, cudaStream_t s, bool debug) {
+  if (P <= 0) return B200GS_OK;
+  {
+    StageScope _t(ST_DEPTH_SORT, s);
+    int rc = radix_workspace_clear(o.ws, s);
+    if (rc) return rc;
+    depth_keys_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, depths, tiles_touched, o.keys_a, o.vals_a);
+    B200GS_LAUNCHED("depth_keys_kernel", debug, s);
+    const RadixPlan plan = radix_plan(32);   // 4 passes: result back in (keys_a, vals_a)
+    rc = radix_histogram(o.keys_a, P, plan, o.ws, s, debug);
+    if (rc) return rc;
+    rc = radix_sort_pairs_u32(o.keys_a, o.vals_a, o.keys_b, o.vals_b, P, plan, o.ws, s, debug);
+    if (rc) return rc;
+  }
+  return inclusive_scan_u32(tiles_touched, point_offsets, P, scan_state, s, debug, o.vals_a);
+}
+
+// ------------------------------------------------------------------ emission
+// duplicateWithKeys (rasterizer_impl.cu:70-111): rect rows outer, columns inner, value =
+// Gaussian id; the key is the tile id only (the depth order is already in the emission order).
+// Thread i handles the i-th Gaussian in depth order; one thread per Gaussian for small rects,
+// rects of >= 32 tiles are handed to the whole warp.
+__global__ void __launch_bounds__(256) duplicate_kernel(int P, const uint32_t* __restrict__ order,
+                                                        const uint2* __restrict__ rects,
+                                                        const uint32_t* __restrict__ offsets, uint32_t* __restrict__ keys,
+                                                        uint32_t* __restrict__ vals, int gx) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int lane = threadIdx.x & 31;
-  uint32_t off = 0, cnt = 0;
-  if (idx < P) {
-    off = idx == 0 ? 0u : offsets[idx - 1];
-    cnt = offsets[idx] - off;
+  uint32_t off = 0, cnt = 0, id = 0;
+  if (i < P) {
+    off = i == 0 ? 0u : offsets[i - 1];
+    cnt = offsets[i] - off;
   }
   uint2 rc = make_uint2(0, 0);
-  uint32_t dbits = 0;
-  if (cnt > 0) { rc = rects[idx]; dbits = __float_as_uint(depths[idx]); }
+  if (cnt > 0) { id = order[i]; rc = rects[id]; }
   const bool big = cnt >= 32;
   if (cnt > 0 && !big) {
     const int x0 = rc.x & 0xffff, x1 = rc.x >> 16, y0 = rc.y & 0xffff, y1 = rc.y >> 16;
     for (int y = y0; y < y1; ++y)
       for (int x = x0; x < x1; ++x) {
-        keys[off] = ((uint64_t)(uint32_t)(y * gx + x) << 32) | dbits;
-        vals[off] = (uint32_t)idx;
+        keys[off] = (uint32_t)(y * gx + x);
+        vals[off] = id;
         ++off;
       }
   }
@@ -152,27 +205,26 @@ __global__ void __launch_bounds__(256) duplicate_kernel(int P, const float* __re
     todo &= todo - 1;
     const uint32_t rx = __shfl_sync(0xffffffffu, rc.x, src), ry = __shfl_sync(0xffffffffu, rc.y, src);
     const uint32_t o = __shfl_sync(0xffffffffu, off, src), c = __shfl_sync(0xffffffffu, cnt, src);
-    const uint32_t db = __shfl_sync(0xffffffffu, dbits, src);
+    const uint32_t gid = __shfl_sync(0xffffffffu, id, src);
     const int x0 = rx & 0xffff, x1 = rx >> 16, y0 = ry & 0xffff;
     const int w = x1 - x0;
-    const uint32_t id = (uint32_t)(idx - lane + src);
-    for (uint32_t i = lane; i < c; i += 32) {
-      const int y = y0 + (int)(i / w), x = x0 + (int)(i % w);
-      keys[o + i] = ((uint64_t)(uint32_t)(y * gx + x) << 32) | db;
-      vals[o + i] = id;
+    for (uint32_t k = lane; k < c; k += 32) {
+      const int y = y0 + (int)(k / w), x = x0 + (int)(k % w);
+      keys[o + k] = (uint32_t)(y * gx + x);
+      vals[o + k] = gid;
     }
   }
 }
 
 // identifyTileRanges (rasterizer_impl.cu:116-138)
-__global__ void __launch_bounds__(256) tile_ranges_kernel(int L, const uint64_t* __restrict__ keys, uint2* ranges) {
+__global__ void __launch_bounds__(256) tile_ranges_kernel(int L, const uint32_t* __restrict__ keys, uint2* ranges) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= L) return;
-  const uint32_t cur = (uint32_t)(keys[idx] >> 32);
+  const uint32_t cur = keys[idx];
   if (idx == 0) {
     ranges[cur].x = 0;
   } else {
-    const uint32_t prev = (uint32_t)(keys[idx - 1] >> 32);
+    const uint32_t prev = keys[idx - 1];
     if (cur != prev) { ranges[prev].y = idx; ranges[cur].x = idx; }
   }
   if (idx == L - 1) ranges[cur].y = L;
@@ -287,7 +339,7 @@ __device__ __forceinline__ unsigned block_hit_mask(const CullRec* __restrict__ c
 }
 
 // state[0] = ticket; look-back words (flag << 32 | count) start at state + 2.
-__global__ void __launch_bounds__(TH_THREADS) tile_hits_kernel(int R, const uint64_t* __restrict__ keys,
+__global__ void __launch_bounds__(TH_THREADS) tile_hits_kernel(int R, const uint32_t* __restrict__ keys,
                                                                const uint32_t* __restrict__ point_list,
                                                                const CullRec* __restrict__ cull, int gx,
                                                                const uint2* __restrict__ ranges, uint2* __restrict__ cranges,
@@ -311,7 +363,7 @@ __global__ void __launch_bounds__(TH_THREADS) tile_hits_kernel(int R, const uint
     const int i = base + k * TH_THREADS + t;
     mask[k] = 0u; id[k] = 0u; tile[k] = 0u;
     if (i < R) {
-      tile[k] = (uint32_t)(keys[i] >> 32);
+      tile[k] = keys[i];
       id[k] = point_list[i];
       mask[k] = block_hit_mask(cull, id[k], (int)(tile[k] % (uint32_t)gx) * TILE_X, (int)(tile[k] / (uint32_t)gx) * TILE_Y);
     }
@@ -380,7 +432,7 @@ int surfel_tile_hits(const CullRec* cull, const Binning& b, int R, int W, int H,
   const int gx = (W + TILE_X - 1) / TILE_X;
   StageScope _t(ST_TILE_HITS, s);
   B200GS_CUDA(cudaMemsetAsync(b.hit_state, 0, tile_hits_state_words(R) * sizeof(uint32_t), s));
-  tile_hits_kernel<<<(R + TH_TILE - 1) / TH_TILE, TH_THREADS, 0, s>>>(R, b.keys, b.point_list, cull, gx, ranges, cranges,
+  tile_hits_kernel<<<(R + TH_TILE - 1) / TH_TILE, TH_THREADS, 0, s>>>(R, b.tile_ids, b.point_list, cull, gx, ranges, cranges,
                                                                        b.comp_id, b.comp_pos, b.comp_hit, b.hit_state,
                                                                        g_cull_audit.load(std::memory_order_relaxed));
   B200GS_LAUNCHED("tile_hits_kernel", debug, s);
@@ -402,39 +454,50 @@ Binning Binning::carve(void* base, size_t R, size_t* bytes) {
   Carver c(base);
   Binning b;
   b.point_list = c.take<uint32_t>(R);
-  b.point_list_unsorted = c.take<uint32_t>(R);
-  b.keys = c.take<uint64_t>(R);
-  b.keys_unsorted = c.take<uint64_t>(R);
+  b.tile_ids = c.take<uint32_t>(R);
+  b.tmp_vals = c.take<uint32_t>(R);
+  b.tmp_keys = c.take<uint32_t>(R);
   b.comp_id = c.take<uint32_t>(R);
   b.comp_pos = c.take<uint32_t>(R);
   b.comp_hit = c.take<uint8_t>(R);
   b.hit_state = c.take<uint32_t>(tile_hits_state_words(R));
-  b.sort_temp_bytes = radix_sort_temp_bytes(R);
-  b.sort_temp = c.take<char>(b.sort_temp_bytes);
+  b.sort_ws_bytes = radix_workspace_bytes(R);
+  b.sort_ws = c.take<char>(b.sort_ws_bytes);
   if (bytes) *bytes = c.used + 128;
   return b;
 }
 
-int bin_and_sort(const float* depths, const uint2* rects, const uint32_t* offsets, int P, int R, int W, int H,
+// order: Gaussian ids in depth order; offsets: inclusive prefix of tiles_touched in that order.
+int bin_and_sort(const uint32_t* order, const uint2* rects, const uint32_t* offsets, int P, int R, int W, int H,
                  const Binning& b, uint2* ranges, cudaStream_t s, bool debug) {
   const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
   B200GS_CUDA(cudaMemsetAsync(ranges, 0, (size_t)gx * gy * sizeof(uint2), s));
   if (R <= 0) return B200GS_OK;
-  {
-  StageScope _t(ST_DUPLICATE, s);
-  duplicate_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, depths, rects, offsets, b.keys_unsorted, b.point_list_unsorted, gx);
-  B200GS_LAUNCHED("duplicate_kernel", debug, s);
-  }
-  const int end_bit = 32 + (int)higher_msb((uint32_t)(gx * gy));
+  // same bit count as the reference's sort range above the depth word (rasterizer_impl.cu:306)
+  const RadixPlan plan = radix_plan((int)higher_msb((uint32_t)(gx * gy)));
+  // the sorted pairs must end up in (tile_ids, point_list): start there for an even pass count
+  const bool odd = (plan.passes & 1) != 0;
+  uint32_t* ka = odd ? b.tmp_keys : b.tile_ids;
+  uint32_t* va = odd ? b.tmp_vals : b.point_list;
+  uint32_t* kb = odd ? b.tile_ids : b.tmp_keys;
+  uint32_t* vb = odd ? b.point_list : b.tmp_vals;
   int rc;
   {
-  StageScope _t(ST_SORT, s);
-  rc = radix_sort_pairs(b.keys_unsorted, b.keys, b.point_list_unsorted, b.point_list, R, end_bit, b.sort_temp,
-                            b.sort_temp_bytes, s, debug);
+    StageScope _t(ST_DUPLICATE, s);
+    duplicate_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, order, rects, offsets, ka, va, gx);
+    B200GS_LAUNCHED("duplicate_kernel", debug, s);
   }
-  if (rc) return rc;
+  {
+    StageScope _t(ST_SORT, s);
+    rc = radix_workspace_clear(b.sort_ws, s);
+    if (rc) return rc;
+    rc = radix_histogram(ka, R, plan, b.sort_ws, s, debug);
+    if (rc) return rc;
+    rc = radix_sort_pairs_u32(ka, va, kb, vb, R, plan, b.sort_ws, s, debug);
+    if (rc) return rc;
+  }
   StageScope _t(ST_RANGES, s);
-  tile_ranges_kernel<<<(R + 255) / 256, 256, 0, s>>>(R, b.keys, ranges);
+  tile_ranges_kernel<<<(R + 255) / 256, 256, 0, s>>>(R, b.tile_ids, ranges);
   B200GS_LAUNCHED("tile_ranges_kernel", debug, s);
   return B200GS_OK;
 }

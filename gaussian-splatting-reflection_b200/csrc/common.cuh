@@ -98,10 +98,19 @@ static_assert(sizeof(CullRec) == 64, "cull record must be 64 B");
 constexpr float CULL_EVERYTHING = -1.0f;
 constexpr float CULL_NOTHING = -2.0f;
 
+// Depth order of the Gaussians: ping-pong (depth bits, id) pairs of the P-sized radix sort.
+struct DepthOrder {
+  uint32_t *keys_a, *vals_a, *keys_b, *vals_b;   // result: vals_a = ids in (depth bits, id) order
+  void* ws;
+  size_t ws_bytes;
+  static DepthOrder carve(Carver& c, size_t P);
+};
+
 struct SurfelGeom {
   float* depths;            // [P]
   uint32_t* tiles_touched;  // [P]
-  uint32_t* point_offsets;  // [P] inclusive prefix sum
+  uint32_t* point_offsets;  // [P] inclusive prefix sum of tiles_touched IN DEPTH ORDER (order.vals_a)
+  DepthOrder order;
   uint8_t* clamped;         // [P] bit c = colour channel c clamped at 0
   uint2* rects;             // [P] tile rect: x = x0 | x1<<16, y = y0 | y1<<16 (only valid if tiles_touched>0)
   SurfelRec* rec;           // [P]
@@ -120,18 +129,18 @@ struct SurfelImage {
 };
 
 struct Binning {
-  uint32_t* point_list;           // [R] sorted Gaussian ids
-  uint32_t* point_list_unsorted;  // [R]
-  uint64_t* keys;                 // [R] sorted keys
-  uint64_t* keys_unsorted;        // [R]
+  uint32_t* point_list;           // [R] Gaussian ids sorted by (tile, depth bits, id)
+  uint32_t* tile_ids;             // [R] tile id of every sorted instance
+  uint32_t* tmp_vals;             // [R] ping-pong partners of the two above
+  uint32_t* tmp_keys;             // [R]
   // Compacted instance list: the sorted instances that can reach alpha >= 1/255 in at least one
   // 8x4 warp block of their tile (tile_hits_kernel), in list order, with their list position.
   uint32_t* comp_id;              // [<=R] Gaussian id
   uint32_t* comp_pos;             // [<=R] 0-based position in the tile's (uncompacted) list
   uint8_t* comp_hit;              // [<=R] bit w = warp block w of the tile can be reached
   uint32_t* hit_state;            // look-back words + ticket of the compaction
-  void* sort_temp;
-  size_t sort_temp_bytes;
+  void* sort_ws;                  // radix workspace (radix_sort.cuh)
+  size_t sort_ws_bytes;
   static Binning carve(void* base, size_t R, size_t* bytes);
 };
 
@@ -153,7 +162,8 @@ static_assert(sizeof(GaussRec) == 64, "record must be 64 B");
 struct GaussGeom {
   float* depths;            // [P]
   uint32_t* tiles_touched;  // [P]
-  uint32_t* point_offsets;  // [P]
+  uint32_t* point_offsets;  // [P] in depth order
+  DepthOrder order;
   uint8_t* clamped;         // [P] bit c
   uint2* rects;             // [P]
   GaussRec* rec;            // [P]
@@ -223,8 +233,11 @@ __device__ constexpr float SH_C3_6 = -0.5900435899266435f;
 
 // ---------------------------------------------------------------- stage launchers (internal)
 int surfel_preprocess(const b200gs_surfel_fwd& a, const SurfelGeom& g, cudaStream_t s);
-int inclusive_scan_u32(const uint32_t* in, uint32_t* out, int n, uint32_t* state, cudaStream_t s, bool debug);
-int bin_and_sort(const float* depths, const uint2* rects, const uint32_t* offsets,
+int inclusive_scan_u32(const uint32_t* in, uint32_t* out, int n, uint32_t* state, cudaStream_t s, bool debug,
+                       const uint32_t* gather = nullptr);
+int depth_order_and_scan(const float* depths, const uint32_t* tiles_touched, int P, const DepthOrder& o,
+                         uint32_t* point_offsets, uint32_t* scan_state, cudaStream_t s, bool debug);
+int bin_and_sort(const uint32_t* order, const uint2* rects, const uint32_t* offsets,
                  int P, int R, int W, int H, const Binning& b, uint2* ranges, cudaStream_t s, bool debug);
 int surfel_tile_hits(const CullRec* cull, const Binning& b, int R, int W, int H, const uint2* ranges, uint2* cranges,
                      cudaStream_t s, bool debug);

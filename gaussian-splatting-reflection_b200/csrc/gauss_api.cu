@@ -12,6 +12,7 @@ GaussGeom GaussGeom::carve(void* base, size_t P, size_t* bytes) {
   g.depths = c.take<float>(P);
   g.tiles_touched = c.take<uint32_t>(P);
   g.point_offsets = c.take<uint32_t>(P);
+  g.order = DepthOrder::carve(c, P);
   g.clamped = c.take<uint8_t>(P);
   g.rects = c.take<uint2>(P);
   g.rec = c.take<GaussRec>(P);
@@ -111,7 +112,7 @@ int b200gs_gauss_forward_stage1(const b200gs_gauss_fwd* a, int* num_rendered, vo
   GaussGeom g = GaussGeom::carve(align128(a->geom), a->P, nullptr);
   rc = gauss_preprocess(*a, g, s);
   if (rc) return rc;
-  rc = inclusive_scan_u32(g.tiles_touched, g.point_offsets, a->P, g.scan_state, s, a->debug != 0);
+  rc = depth_order_and_scan(g.depths, g.tiles_touched, a->P, g.order, g.point_offsets, g.scan_state, s, a->debug != 0);
   if (rc) return rc;
   int host[2] = {0, 0};
   B200GS_CUDA(cudaMemcpyAsync(&host[0], g.point_offsets + a->P - 1, sizeof(int), cudaMemcpyDeviceToHost, s));
@@ -132,7 +133,7 @@ int b200gs_gauss_forward_stage2(const b200gs_gauss_fwd* a, int R, void* stream) 
   GaussGeom g = GaussGeom::carve(align128(a->geom), a->P, nullptr);
   GaussImage im = GaussImage::carve(align128(a->img), a->width, a->height, nullptr);
   Binning b = Binning::carve(R > 0 ? align128(a->binning) : nullptr, R, nullptr);
-  rc = bin_and_sort(g.depths, g.rects, g.point_offsets, a->P, R, a->width, a->height, b, im.ranges, s, a->debug != 0);
+  rc = bin_and_sort(g.order.vals_a, g.rects, g.point_offsets, a->P, R, a->width, a->height, b, im.ranges, s, a->debug != 0);
   if (rc) return rc;
   return gauss_composite_forward(*a, g, im, b, s);
 }
@@ -164,7 +165,8 @@ int b200gs_gauss_inspect_geom(const void* geom, int P, float* depths, float* mea
                                                       cov3D, conic_opacity, rgb, clamped);
   B200GS_LAUNCHED("unpack_gauss_kernel", false, s);
   if (tiles_touched) B200GS_CUDA(cudaMemcpyAsync(tiles_touched, g.tiles_touched, (size_t)P * 4, cudaMemcpyDeviceToDevice, s));
-  if (point_offsets) B200GS_CUDA(cudaMemcpyAsync(point_offsets, g.point_offsets, (size_t)P * 4, cudaMemcpyDeviceToDevice, s));
+  // the reference's point_offsets: inclusive prefix of tiles_touched in id order (ours is in depth order)
+  if (point_offsets) return inclusive_scan_u32(g.tiles_touched, point_offsets, P, g.scan_state, s, false);
   return B200GS_OK;
 }
 

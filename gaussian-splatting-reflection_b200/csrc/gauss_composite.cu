@@ -83,9 +83,9 @@ __global__ void __launch_bounds__(GBATCH) gauss_composite_fwd_kernel(const GComp
   float C0 = 0.f, C1 = 0.f, C2 = 0.f, N0 = 0.f, N1 = 0.f, N2 = 0.f, refl = 0.f, invd = 0.f;
 
   const uint32_t* pl = a.point_list + range.x;
-  uint2 cull_cur = make_uint2(1u, 1u);
+  uint2 cull_cur = make_uint2(0x0000ffffu, 0x0000ffffu);
   auto stage = [&](int buf, int id) {
-    cull_cur = make_uint2(1u, 1u);
+    cull_cur = make_uint2(0x0000ffffu, 0x0000ffffu);
     if (id >= 0) {
       cull_cur = __ldg(a.cull + id);
       const GaussRec* g = a.rec + id;
@@ -232,9 +232,9 @@ __global__ void __launch_bounds__(GBATCH, 2) gauss_composite_bwd_kernel(const GC
   float acc_r = 0.f, last_r = 0.f, acc_i = 0.f, last_i = 0.f, last_alpha = 0.f;
 
   const uint32_t* pl = a.point_list + range.x;
-  uint2 cull_cur = make_uint2(1u, 1u);
+  uint2 cull_cur = make_uint2(0x0000ffffu, 0x0000ffffu);
   auto stage = [&](int buf, int id) {
-    cull_cur = make_uint2(1u, 1u);
+    cull_cur = make_uint2(0x0000ffffu, 0x0000ffffu);
     if (id >= 0) {
       cull_cur = __ldg(a.cull + id);
       const GaussRec* g = a.rec + id;

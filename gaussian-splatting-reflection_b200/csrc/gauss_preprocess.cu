@@ -85,7 +85,7 @@ __device__ __forceinline__ float ndc2pix(float v, int S) { return (float)((((dou
 // sqrt(c2 * cov_xx), sqrt(c2 * cov_yy) of the (low-pass filtered) 2D covariance.
 __device__ __forceinline__ uint2 gauss_cull_bbox(float cx, float cy, float cov_xx, float cov_yy, float opa) {
   const uint2 everything = make_uint2(0xffff0000u, 0xffff0000u);
-  const uint2 nothing = make_uint2(1u, 1u);
+  const uint2 nothing = make_uint2(0x0000ffffu, 0x0000ffffu);  // min 65535 > max 0: misses every block, also at tile 0
   if (!(opa >= 0.0f)) return everything;
   if (opa < 0.0039f) return nothing;
   const float c2 = 2.0f * logf(255.0f * opa) * 1.001f + 0.01f;

@@ -38,6 +38,13 @@ __global__ void unpack_geom_kernel(int P, const SurfelRec* rec, const uint32_t* 
   }
 }
 
+// The reference's 64-bit sort keys (rasterizer_impl.cu:100-104): tile << 32 | depth bits.
+__global__ void rebuild_keys_kernel(int R, const uint32_t* tile_ids, const uint32_t* point_list, const float* depths,
+                                    uint64_t* keys) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < R) keys[i] = ((uint64_t)tile_ids[i] << 32) | __float_as_uint(depths[point_list[i]]);
+}
+
 __global__ void mask_depth_kernel(int P, const float* depths, const uint32_t* tiles, float* out) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx < P) out[idx] = tiles[idx] > 0 ? depths[idx] : 0.0f;
@@ -72,16 +79,22 @@ int b200gs_surfel_inspect_geom(const void* geom, int P, float* depths, float* me
   unpack_geom_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, g.rec, g.tiles_touched, g.clamped, means2D, transMat, normal_opacity, rgb, clamped);
   B200GS_LAUNCHED("unpack_geom_kernel", false, s);
   if (tiles_touched) B200GS_CUDA(cudaMemcpyAsync(tiles_touched, g.tiles_touched, (size_t)P * 4, cudaMemcpyDeviceToDevice, s));
-  if (point_offsets) B200GS_CUDA(cudaMemcpyAsync(point_offsets, g.point_offsets, (size_t)P * 4, cudaMemcpyDeviceToDevice, s));
+  // the reference's point_offsets: inclusive prefix of tiles_touched in id order (ours is in depth order)
+  if (point_offsets) return inclusive_scan_u32(g.tiles_touched, point_offsets, P, g.scan_state, s, false);
   return B200GS_OK;
 }
 
-int b200gs_inspect_binning(const void* binning, int R, uint64_t* keys, uint32_t* point_list, void* stream) {
+int b200gs_inspect_binning(const void* binning, int R, const float* depths, uint64_t* keys, uint32_t* point_list,
+                           void* stream) {
   if (R <= 0) return B200GS_OK;
   cudaStream_t s = (cudaStream_t)stream;
   void* base = reinterpret_cast<void*>((reinterpret_cast<uintptr_t>(binning) + 127) & ~uintptr_t(127));
   Binning b = Binning::carve(base, R, nullptr);
-  if (keys) B200GS_CUDA(cudaMemcpyAsync(keys, b.keys, (size_t)R * 8, cudaMemcpyDeviceToDevice, s));
+  if (keys) {
+    if (!depths) { set_error("inspect_binning: keys need the per-Gaussian depths (from *_inspect_geom)"); return B200GS_EINVAL; }
+    rebuild_keys_kernel<<<(R + 255) / 256, 256, 0, s>>>(R, b.tile_ids, b.point_list, depths, keys);
+    B200GS_LAUNCHED("rebuild_keys_kernel", false, s);
+  }
   if (point_list) B200GS_CUDA(cudaMemcpyAsync(point_list, b.point_list, (size_t)R * 4, cudaMemcpyDeviceToDevice, s));
   return B200GS_OK;
 }

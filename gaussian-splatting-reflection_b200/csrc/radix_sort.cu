@@ -1,24 +1,262 @@
-// radix_sort.cu -- bring-up implementation: CUB's onesweep sort (header-only, from
-// the CUDA toolkit), i.e. exactly the call the reference makes.  To be replaced by
-// the hand-written sm_100a sort; the interface in radix_sort.cuh stays.
+// radix_sort.cu -- hand-written onesweep LSD radix sort of (u32 key, u32 value) pairs (sm_100a).
+// See radix_sort.cuh for what it replaces and why 32-bit keys suffice.
+//
+// One pass = one kernel, one read and one write of every pair:
+//   * blocks take their tile of RS_TILE pairs in ticket order (so a block only ever waits for
+//     blocks that already run);
+//   * every warp ranks its 512 keys with match.any: lanes holding the same digit find each other,
+//     the lowest one bumps the warp's private digit counter in shared memory, and every lane's
+//     rank is the old counter value plus the number of equal-digit lanes below it -- stable in
+//     (iteration, lane) order, which is memory order;
+//   * thread d owns digit d: it turns the per-warp counters into warp offsets, publishes the
+//     block's count of digit d as a 64-bit (flag | count) word and walks back over the preceding
+//     blocks' words (aggregate -> keep walking, inclusive prefix -> stop) -- the chained scan that
+//     makes a single pass possible;
+//   * pairs are reordered through shared memory so that each digit leaves the block as one
+//     contiguous, coalesced run.
+// The digit histograms that give every digit's global base come from radix_histogram (all passes
+// in one read of the keys, match.any-aggregated shared-memory atomics).
 #include "common.cuh"
 #include "radix_sort.cuh"
-#include <cub/device/device_radix_sort.cuh>
 
 namespace b200gs {
 
-size_t radix_sort_temp_bytes(size_t n) {
-  size_t bytes = 0;
-  cub::DeviceRadixSort::SortPairs(nullptr, bytes, (const uint64_t*)nullptr, (uint64_t*)nullptr,
-                                  (const uint32_t*)nullptr, (uint32_t*)nullptr, (int)n);
-  return bytes + 256;
+RadixPlan radix_plan(int total_bits) {
+  RadixPlan p;
+  if (total_bits < 1) total_bits = 1;
+  if (total_bits > 32) total_bits = 32;
+  p.passes = (total_bits + 7) / 8;
+  int shift = 0;
+  for (int i = 0; i < RS_MAX_PASSES; ++i) { p.shift[i] = 0; p.bits[i] = 0; }
+  for (int i = 0; i < p.passes; ++i) {
+    const int left = total_bits - shift, todo = p.passes - i;
+    p.bits[i] = (left + todo - 1) / todo;
+    p.shift[i] = shift;
+    shift += p.bits[i];
+  }
+  return p;
 }
 
-int radix_sort_pairs(const uint64_t* keys_in, uint64_t* keys_out, const uint32_t* vals_in, uint32_t* vals_out, int n,
-                     int end_bit, void* temp, size_t temp_bytes, cudaStream_t s, bool debug) {
-  B200GS_CUDA(cub::DeviceRadixSort::SortPairs(temp, temp_bytes, keys_in, keys_out, vals_in, vals_out, n, 0, end_bit, s));
-  g_launches.fetch_add(7, std::memory_order_relaxed);
-  if (debug) B200GS_CUDA(cudaStreamSynchronize(s));
+// workspace layout (u32 words): hist[RS_MAX_PASSES][256] | tickets[RS_MAX_PASSES] | pad | u64 state[blocks][256]
+static constexpr size_t WS_HIST_WORDS = (size_t)RS_MAX_PASSES * RS_RADIX;
+static constexpr size_t WS_HEAD_WORDS = WS_HIST_WORDS + 32;
+static inline size_t ws_blocks(size_t n) { return (n + RS_TILE - 1) / RS_TILE; }
+
+size_t radix_workspace_bytes(size_t n) {
+  return WS_HEAD_WORDS * sizeof(uint32_t) + ws_blocks(n) * RS_RADIX * sizeof(unsigned long long) + 256;
+}
+static inline uint32_t* ws_hist(void* ws) { return reinterpret_cast<uint32_t*>(ws); }
+static inline uint32_t* ws_tickets(void* ws) { return reinterpret_cast<uint32_t*>(ws) + WS_HIST_WORDS; }
+static inline unsigned long long* ws_state(void* ws) {
+  return reinterpret_cast<unsigned long long*>(reinterpret_cast<uint32_t*>(ws) + WS_HEAD_WORDS);
+}
+
+int radix_workspace_clear(void* workspace, cudaStream_t s) {
+  B200GS_CUDA(cudaMemsetAsync(workspace, 0, WS_HEAD_WORDS * sizeof(uint32_t), s));
+  return B200GS_OK;
+}
+
+// ------------------------------------------------------------------ histogram
+struct HistArgs {
+  const uint32_t* keys;
+  int n, passes;
+  int shift[RS_MAX_PASSES];
+  uint32_t mask[RS_MAX_PASSES];
+  uint32_t* hist;  // [RS_MAX_PASSES][256]
+};
+
+__global__ void __launch_bounds__(256) radix_hist_kernel(const HistArgs a) {
+  __shared__ uint32_t s_h[RS_MAX_PASSES][RS_RADIX];
+  const int t = threadIdx.x, lane = t & 31;
+#pragma unroll
+  for (int p = 0; p < RS_MAX_PASSES; ++p) s_h[p][t] = 0u;
+  __syncthreads();
+  // whole warps iterate together (match.any needs the full warp): round n up to a warp multiple
+  const int n32 = (a.n + 31) & ~31;
+  for (int i = blockIdx.x * blockDim.x + t; i < n32; i += gridDim.x * blockDim.x) {
+    const bool valid = i < a.n;
+    const uint32_t key = valid ? a.keys[i] : 0u;
+    for (int p = 0; p < a.passes; ++p) {
+      const uint32_t d = valid ? ((key >> a.shift[p]) & a.mask[p]) : (uint32_t)RS_RADIX;
+      const unsigned peers = __match_any_sync(0xffffffffu, d);
+      if (valid && lane == __ffs(peers) - 1) atomicAdd(&s_h[p][d], (uint32_t)__popc(peers));
+    }
+  }
+  __syncthreads();
+  for (int p = 0; p < a.passes; ++p) {
+    const uint32_t v = s_h[p][t];
+    if (v) atomicAdd(&a.hist[p * RS_RADIX + t], v);
+  }
+}
+
+// in place: digit counts -> exclusive bucket bases, one block per pass
+__global__ void __launch_bounds__(RS_RADIX) radix_bases_kernel(uint32_t* hist) {
+  __shared__ uint32_t s_w[RS_RADIX / 32];
+  uint32_t* h = hist + blockIdx.x * RS_RADIX;
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const uint32_t v = h[t];
+  uint32_t inc = v;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
+    if (lane >= d) inc += o;
+  }
+  if (lane == 31) s_w[warp] = inc;
+  __syncthreads();
+  uint32_t off = 0;
+#pragma unroll
+  for (int w = 0; w < RS_RADIX / 32; ++w) if (w < warp) off += s_w[w];
+  h[t] = off + inc - v;
+}
+
+int radix_histogram(const uint32_t* keys, int n, const RadixPlan& plan, void* workspace, cudaStream_t s, bool debug) {
+  if (n <= 0) return B200GS_OK;
+  HistArgs a;
+  a.keys = keys; a.n = n; a.passes = plan.passes; a.hist = ws_hist(workspace);
+  for (int p = 0; p < RS_MAX_PASSES; ++p) { a.shift[p] = plan.shift[p]; a.mask[p] = (1u << plan.bits[p]) - 1u; }
+  const int blocks = (int)((((size_t)n + 255) / 256) < 148 * 8 ? (((size_t)n + 255) / 256) : 148 * 8);
+  radix_hist_kernel<<<blocks, 256, 0, s>>>(a);
+  B200GS_LAUNCHED("radix_hist_kernel", debug, s);
+  return B200GS_OK;
+}
+
+// ------------------------------------------------------------------ one pass
+struct PassArgs {
+  const uint32_t* keys_in;
+  const uint32_t* vals_in;
+  uint32_t* keys_out;
+  uint32_t* vals_out;
+  int n, shift, nbits;
+  const uint32_t* bases;        // [256] exclusive bucket bases of this pass
+  unsigned long long* state;    // [blocks][1 << nbits], zeroed: flag << 62 | count  (1 = aggregate, 2 = inclusive)
+  uint32_t* ticket;
+};
+
+__global__ void __launch_bounds__(RS_THREADS) radix_pass_kernel(const PassArgs a) {
+  __shared__ uint32_t s_keys[RS_TILE];
+  __shared__ uint32_t s_vals[RS_TILE];
+  __shared__ uint32_t s_cnt[RS_THREADS / 32][RS_RADIX];
+  __shared__ uint32_t s_excl[RS_RADIX];    // exclusive prefix of the block's digit counts
+  __shared__ uint32_t s_gbase[RS_RADIX];   // global position of local position 0 of each digit's run (mod 2^32)
+  __shared__ uint32_t s_wsum[RS_THREADS / 32];
+  __shared__ uint32_t s_blk;
+
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const uint32_t dmask = (1u << a.nbits) - 1u;
+  if (t == 0) s_blk = atomicAdd(a.ticket, 1u);
+#pragma unroll
+  for (int w = 0; w < RS_THREADS / 32; ++w) s_cnt[w][t] = 0u;
+  __syncthreads();
+  const uint32_t blk = s_blk;
+  const int blk_base = (int)blk * RS_TILE;
+  const int wbase = blk_base + warp * (32 * RS_ITEMS);
+
+  uint32_t key[RS_ITEMS], rank[RS_ITEMS];
+#pragma unroll
+  for (int k = 0; k < RS_ITEMS; ++k) {
+    const int i = wbase + k * 32 + lane;
+    key[k] = i < a.n ? a.keys_in[i] : 0xffffffffu;
+  }
+  uint32_t* cnt = s_cnt[warp];
+#pragma unroll
+  for (int k = 0; k < RS_ITEMS; ++k) {
+    const bool valid = wbase + k * 32 + lane < a.n;
+    const uint32_t d = valid ? ((key[k] >> a.shift) & dmask) : (uint32_t)RS_RADIX;
+    const unsigned peers = __match_any_sync(0xffffffffu, d);
+    const int leader = __ffs(peers) - 1;
+    uint32_t old = 0u;
+    if (lane == leader && valid) { old = cnt[d]; cnt[d] = old + (uint32_t)__popc(peers); }
+    old = __shfl_sync(0xffffffffu, old, leader);
+    rank[k] = old + (uint32_t)__popc(peers & ((1u << lane) - 1u));
+    __syncwarp();
+  }
+  __syncthreads();
+
+  // thread t owns digit t
+  uint32_t total = 0u;
+#pragma unroll
+  for (int w = 0; w < RS_THREADS / 32; ++w) {
+    const uint32_t c = s_cnt[w][t];
+    s_cnt[w][t] = total;          // offset of warp w's keys inside the digit's run
+    total += c;
+  }
+  const int nb = 1 << a.nbits;
+  volatile unsigned long long* st = a.state;
+  if (t < nb) st[(size_t)blk * nb + t] = ((blk == 0 ? 2ull : 1ull) << 62) | total;
+
+  uint32_t inc = total;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
+    if (lane >= d) inc += o;
+  }
+  if (lane == 31) s_wsum[warp] = inc;
+  __syncthreads();
+  uint32_t woff = 0u;
+#pragma unroll
+  for (int w = 0; w < RS_THREADS / 32; ++w) if (w < warp) woff += s_wsum[w];
+  const uint32_t excl = woff + inc - total;
+  s_excl[t] = excl;
+
+  if (t < nb) {
+    uint32_t prev = 0u;
+    if (blk > 0) {
+      long long look = (long long)blk - 1;
+      while (true) {
+        unsigned long long w;
+        do { w = st[(size_t)look * nb + t]; } while ((w >> 62) == 0ull);
+        prev += (uint32_t)w;
+        if ((w >> 62) == 2ull) break;
+        --look;
+      }
+      st[(size_t)blk * nb + t] = (2ull << 62) | (unsigned long long)(prev + total);
+    }
+    s_gbase[t] = a.bases[t] + prev - excl;
+  }
+  __syncthreads();
+
+  // reorder through shared memory
+#pragma unroll
+  for (int k = 0; k < RS_ITEMS; ++k) {
+    const int i = wbase + k * 32 + lane;
+    if (i < a.n) {
+      const uint32_t d = (key[k] >> a.shift) & dmask;
+      const uint32_t pos = s_excl[d] + cnt[d] + rank[k];
+      s_keys[pos] = key[k];
+      s_vals[pos] = a.vals_in[i];
+    }
+  }
+  __syncthreads();
+  const int nvalid = min(RS_TILE, a.n - blk_base);
+  for (int p = t; p < nvalid; p += RS_THREADS) {
+    const uint32_t k = s_keys[p];
+    const uint32_t g = s_gbase[(k >> a.shift) & dmask] + (uint32_t)p;
+    a.keys_out[g] = k;
+    a.vals_out[g] = s_vals[p];
+  }
+}
+
+int radix_sort_pairs_u32(uint32_t* keys_a, uint32_t* vals_a, uint32_t* keys_b, uint32_t* vals_b, int n,
+                         const RadixPlan& plan, void* workspace, cudaStream_t s, bool debug) {
+  if (n <= 0) return B200GS_OK;
+  radix_bases_kernel<<<plan.passes, RS_RADIX, 0, s>>>(ws_hist(workspace));
+  B200GS_LAUNCHED("radix_bases_kernel", debug, s);
+  const int blocks = (int)ws_blocks((size_t)n);
+  uint32_t *ki = keys_a, *vi = vals_a, *ko = keys_b, *vo = vals_b;
+  for (int p = 0; p < plan.passes; ++p) {
+    PassArgs a;
+    a.keys_in = ki; a.vals_in = vi; a.keys_out = ko; a.vals_out = vo;
+    a.n = n; a.shift = plan.shift[p]; a.nbits = plan.bits[p];
+    a.bases = ws_hist(workspace) + p * RS_RADIX;
+    a.state = ws_state(workspace);
+    a.ticket = ws_tickets(workspace) + p;
+    B200GS_CUDA(cudaMemsetAsync(a.state, 0, (size_t)blocks * ((size_t)1 << a.nbits) * sizeof(unsigned long long), s));
+    radix_pass_kernel<<<blocks, RS_THREADS, 0, s>>>(a);
+    B200GS_LAUNCHED("radix_pass_kernel", debug, s);
+    uint32_t* x;
+    x = ki; ki = ko; ko = x;
+    x = vi; vi = vo; vo = x;
+  }
   return B200GS_OK;
 }
 

@@ -148,7 +148,7 @@ surfel_forward_stage1 = _sig("b200gs_surfel_forward_stage1", _i, C.POINTER(Surfe
 surfel_forward_stage2 = _sig("b200gs_surfel_forward_stage2", _i, C.POINTER(SurfelFwd), _i, _p)
 surfel_backward = _sig("b200gs_surfel_backward", _i, C.POINTER(SurfelBwd), _p)
 surfel_inspect_geom = _sig("b200gs_surfel_inspect_geom", _i, _p, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p)
-inspect_binning = _sig("b200gs_inspect_binning", _i, _p, _i, _p, _p, _p)
+inspect_binning = _sig("b200gs_inspect_binning", _i, _p, _i, _p, _p, _p, _p)
 surfel_inspect_image = _sig("b200gs_surfel_inspect_image", _i, _p, _i, _i, _p, _p, _p, _p)
 
 

@@ -171,7 +171,10 @@ int b200gs_surfel_inspect_geom(const void* geom, int P,
                                float* normal_opacity /*[P,4]*/, float* rgb /*[P,3]*/,
                                uint32_t* tiles_touched, uint32_t* point_offsets,
                                uint8_t* clamped /*[P,3]*/, void* stream);
-int b200gs_inspect_binning(const void* binning, int num_rendered,
+/* The library sorts 32-bit (tile, id) pairs emitted in depth order; the reference's 64-bit keys
+ * (tile << 32 | depth bits) are rebuilt here from `depths` (float[P] as returned by
+ * *_inspect_geom; needed only when point_list_keys != NULL).                              */
+int b200gs_inspect_binning(const void* binning, int num_rendered, const float* depths,
                            uint64_t* point_list_keys, uint32_t* point_list, void* stream);
 int b200gs_surfel_inspect_image(const void* img, int width, int height,
                                 float* accum_alpha /*[3,N]*/, uint32_t* n_contrib /*[2,N]*/,

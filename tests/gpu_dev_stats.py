@@ -35,33 +35,6 @@ def main(name="bench"):
     print(f"  sum over tiles of max last_contributor = {int(tile_max.sum())}  ({tile_max.sum().item()/max(n.sum().item(),1):.3f} of lists)")
     print(f"  (warp,entry) pairs up to warp's last   = {int(warp_max.sum())}  ({warp_max.sum().item()/max(8*n.sum().item(),1):.3f} of 8*lists)")
     print(f"  mean last_contributor per pixel        = {last.float().mean():.1f}")
-    # hit masks
-    b = f["binning"]
-    base = (-b.data_ptr()) % 128
-    off = base
-    off = al(off) + 4 * R
-    off = al(off) + 4 * R
-    off = al(off) + 8 * R
-    off = al(off) + 8 * R
-    off = al(off)
-    hit = b[off:off + R]
-    bits = torch.zeros((), dtype=torch.long, device="cuda")
-    for w in range(8):
-        bits += ((hit >> w) & 1).sum()
-    print(f"  hit bits set = {int(bits)} of {8*R} ({bits.item()/(8*R):.3f}); zero masks: {(hit == 0).float().mean():.3f}")
-    # hit bits among entries a warp actually walks (position < warp_max)
-    pos = torch.arange(R, device="cuda")
-    tile_of = torch.repeat_interleave(torch.arange(gx * gy, device="cuda"), n)
-    rel = pos - ranges[tile_of, 0]
-    walked = torch.zeros((), dtype=torch.long, device="cuda")
-    walked_hit = torch.zeros((), dtype=torch.long, device="cuda")
-    for w in range(8):
-        m = rel < warp_max[tile_of, w]
-        walked += m.sum()
-        walked_hit += (m & (((hit >> w) & 1) > 0)).sum()
-    print(f"  walked (warp,entry) pairs = {int(walked)}, with hit bit = {int(walked_hit)} ({walked_hit.item()/max(walked.item(),1):.3f})")
-
-
     import b200gs
     b200gs.cull_stats(reset=True)
     b200gs.debug_cull_audit(1)

@@ -137,7 +137,7 @@ def new_surfel_state(fwd, P, W, H):
     keys = torch.zeros((R,), dtype=torch.int64, device=dev)
     pl = i(R)
     if R:
-        _b.check(_b.inspect_binning(fwd["binning"].data_ptr(), R, keys.data_ptr(), pl.data_ptr(), st))
+        _b.check(_b.inspect_binning(fwd["binning"].data_ptr(), R, depths.data_ptr(), keys.data_ptr(), pl.data_ptr(), st))
     N = W * H
     T = ((W + 15) // 16) * ((H + 15) // 16)
     accum, ncon, ranges = f(3, N), i(2, N), i(T, 2)
@@ -271,7 +271,7 @@ def new_gauss_state(fwd, P, W, H):
     R = fwd["rendered"]
     keys, pl = torch.zeros((R,), dtype=torch.int64, device=dev), i(R)
     if R:
-        _b.check(_b.inspect_binning(fwd["binning"].data_ptr(), R, keys.data_ptr(), pl.data_ptr(), st))
+        _b.check(_b.inspect_binning(fwd["binning"].data_ptr(), R, depths.data_ptr(), keys.data_ptr(), pl.data_ptr(), st))
     N, T = W * H, ((W + 15) // 16) * ((H + 15) // 16)
     accum, ncon, ranges = f(N), i(N), i(T, 2)
     _b.check(_b.gauss_inspect_image(fwd["img"].data_ptr(), W, H, accum.data_ptr(), ncon.data_ptr(), ranges.data_ptr(), st))
