@@ -246,21 +246,70 @@ constexpr int TH_THREADS = 256;
 constexpr int TH_ITEMS = 4;
 constexpr int TH_TILE = TH_THREADS * TH_ITEMS;
 
-__device__ __forceinline__ unsigned block_hit_mask(const CullRec* __restrict__ cull, uint32_t id, int tx0, int ty0) {
-  const double4 c0 = *reinterpret_cast<const double4*>(&cull[id].A);   // A B C D
-  const double2 c1 = *reinterpret_cast<const double2*>(&cull[id].E);   // E F
-  const float4 c2 = *reinterpret_cast<const float4*>(&cull[id].cx);    // cx cy r2 flag
-  if (c2.w != 0.0f) return (c2.w == CULL_NOTHING) ? 0u : 0xFFu;
-  // translate the form to the corner (-0.5, -0.5) of the dilated tile, in fp64
+// The CullRec form translated to the corner (-0.5, -0.5) of the dilated tile: the tile is [0,16]^2
+// and block (r, c) is [8c, 8c+8] x [4r, 4r+4] in this frame.
+struct TileForm {
+  float A, B, C, D, E, F, tol;   // f(x,y) = A x^2 + 2 B x y + C y^2 + 2 D x + 2 E y + F; hit if min f <= tol
+  float dxc, dyc, r2;            // low-pass disk: centre in this frame, squared radius
+};
+
+// -> 0: fixed answer "nothing", 1: fixed answer "everything", 2: use the form
+__device__ __forceinline__ int load_tile_form(const CullRec* __restrict__ cull, uint32_t id, int tx0, int ty0, TileForm& f) {
+  const float4 c2 = __ldg(reinterpret_cast<const float4*>(&cull[id].cx));    // cx cy r2 flag
+  if (c2.w != 0.0f) return (c2.w == CULL_NOTHING) ? 0 : 1;
+  const double4 c0 = *reinterpret_cast<const double4*>(&cull[id].A);         // A B C D
+  const double2 c1 = *reinterpret_cast<const double2*>(&cull[id].E);         // E F
+  // translation in fp64: the pixel coordinates are large against the extent of small far-off ellipses
   const double ox = (double)tx0 - 0.5, oy = (double)ty0 - 0.5;
   const double Dd = c0.x * ox + c0.y * oy + c0.w;
   const double Ed = c0.y * ox + c0.z * oy + c1.x;
   const double Fd = (c0.x * ox + 2.0 * c0.y * oy + 2.0 * c0.w) * ox + (c0.z * oy + 2.0 * c1.x) * oy + c1.y;
-  const float A = (float)c0.x, B = (float)c0.y, C = (float)c0.z, D = (float)Dd, E = (float)Ed, F = (float)Fd;
-  if (!(fabsf(D) < 1e30f) || !(fabsf(E) < 1e30f) || !(fabsf(F) < 1e30f)) return 0xFFu;
-  const float tol = 1e-5f * (256.0f * (fabsf(A) + 2.0f * fabsf(B) + fabsf(C)) + 32.0f * (fabsf(D) + fabsf(E)) + fabsf(F));
+  f.A = (float)c0.x; f.B = (float)c0.y; f.C = (float)c0.z; f.D = (float)Dd; f.E = (float)Ed; f.F = (float)Fd;
+  if (!(fabsf(f.D) < 1e30f) || !(fabsf(f.E) < 1e30f) || !(fabsf(f.F) < 1e30f)) return 1;
+  f.tol = 1e-5f * (256.0f * (fabsf(f.A) + 2.0f * fabsf(f.B) + fabsf(f.C)) + 32.0f * (fabsf(f.D) + fabsf(f.E)) + fabsf(f.F));
+  f.dxc = c2.x - ((float)tx0 - 0.5f);
+  f.dyc = c2.y - ((float)ty0 - 0.5f);
+  f.r2 = c2.z;
+  return 2;
+}
+
+// Can the Gaussian reach the tile at all?  Same test as block_masks() on the whole tile rectangle
+// (a superset of the union of its blocks): most instances of a scene with near-camera splats fail
+// it, so only the survivors pay for the per-block refinement.
+__device__ __forceinline__ bool tile_reachable(const TileForm& f) {
+  const float A = f.A, B = f.B, C = f.C, D = f.D, E = f.E, F = f.F;
+  const float S = 16.0f;
+  float mn = fminf(fminf(F, (A * S + 2.0f * D) * S + F),
+                   fminf((C * S + 2.0f * E) * S + F, (A * S + 2.0f * (B * S + D)) * S + (C * S + 2.0f * E) * S + F));
+  if (A > 0.0f) {   // horizontal edges y = 0, 16
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const float y = S * j, bx = B * y + D, gy = (C * y + 2.0f * E) * y + F;
+      const float xs = -bx / A;
+      if (xs > 0.0f && xs < S) mn = fminf(mn, gy - bx * bx / A);
+    }
+  }
+  if (C > 0.0f) {   // vertical edges x = 0, 16
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      const float x = S * i, by = B * x + E, gx = (A * x + 2.0f * D) * x + F;
+      const float ys = -by / C;
+      if (ys > 0.0f && ys < S) mn = fminf(mn, gx - by * by / C);
+    }
+  }
+  const float det = A * C - B * B;
+  if (A > 0.0f && det > 0.0f) {
+    const float xs = (B * E - C * D) / det, ys = (B * D - A * E) / det;
+    if (xs > 0.0f && xs < S && ys > 0.0f && ys < S) mn = fminf(mn, D * xs + E * ys + F);
+  }
+  const float ddx = fmaxf(fmaxf(-f.dxc, f.dxc - S), 0.0f), ddy = fmaxf(fmaxf(-f.dyc, f.dyc - S), 0.0f);
+  return mn <= f.tol || ddx * ddx + ddy * ddy <= f.r2;
+}
+
+__device__ __forceinline__ unsigned block_masks(const TileForm& f) {
+  const float A = f.A, B = f.B, C = f.C, D = f.D, E = f.E, F = f.F, tol = f.tol;
   const float INF = __int_as_float(0x7f800000);
-  // f(x,y) = A x^2 + 2 B x y + C y^2 + 2 D x + 2 E y + F on the grid lines x in {0,8,16}, y in {0,4,..,16}
+  // f on the grid lines x in {0,8,16}, y in {0,4,..,16}
   float mn[4][2];
 #pragma unroll
   for (int r = 0; r < 4; ++r) { mn[r][0] = INF; mn[r][1] = INF; }
@@ -323,15 +372,14 @@ __device__ __forceinline__ unsigned block_hit_mask(const CullRec* __restrict__ c
     }
   }
   // low-pass disk
-  const float dxc = c2.x - ((float)tx0 - 0.5f), dyc = c2.y - ((float)ty0 - 0.5f);   // centre relative to the dilated corner
   unsigned mask = 0u;
 #pragma unroll
   for (int r = 0; r < 4; ++r) {
-    const float ddy = fmaxf(fmaxf(4.0f * r - dyc, dyc - 4.0f * (r + 1)), 0.0f);
+    const float ddy = fmaxf(fmaxf(4.0f * r - f.dyc, f.dyc - 4.0f * (r + 1)), 0.0f);
 #pragma unroll
     for (int c = 0; c < 2; ++c) {
-      const float ddx = fmaxf(fmaxf(8.0f * c - dxc, dxc - 8.0f * (c + 1)), 0.0f);
-      const bool disk = ddx * ddx + ddy * ddy <= c2.z;
+      const float ddx = fmaxf(fmaxf(8.0f * c - f.dxc, f.dxc - 8.0f * (c + 1)), 0.0f);
+      const bool disk = ddx * ddx + ddy * ddy <= f.r2;
       if (mn[r][c] <= tol || disk) mask |= 1u << (r * 2 + c);
     }
   }
@@ -349,8 +397,11 @@ __global__ void __launch_bounds__(TH_THREADS) tile_hits_kernel(int R, const uint
   __shared__ uint32_t s_tile;
   __shared__ uint32_t s_cnt[TH_ITEMS][TH_THREADS / 32];
   __shared__ uint32_t s_base;
+  __shared__ uint8_t s_mask[TH_TILE];    // per item of the block: hit mask
+  __shared__ uint16_t s_queue[TH_TILE];  // items that reach their tile and need the per-block refinement
+  __shared__ uint32_t s_qn;
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-  if (t == 0) s_tile = atomicAdd(state, 1u);
+  if (t == 0) { s_tile = atomicAdd(state, 1u); s_qn = 0u; }
   __syncthreads();
   const uint32_t blk = s_tile;
   const int base = (int)blk * TH_TILE;
@@ -358,15 +409,45 @@ __global__ void __launch_bounds__(TH_THREADS) tile_hits_kernel(int R, const uint
   unsigned mask[TH_ITEMS];
   uint32_t id[TH_ITEMS], tile[TH_ITEMS], wexcl[TH_ITEMS];
   bool keep[TH_ITEMS];
+  // phase 1: whole-tile test for every item; survivors are queued
 #pragma unroll
   for (int k = 0; k < TH_ITEMS; ++k) {
     const int i = base + k * TH_THREADS + t;
-    mask[k] = 0u; id[k] = 0u; tile[k] = 0u;
+    id[k] = 0u; tile[k] = 0u;
+    unsigned m = 0u;
+    bool refine = false;
     if (i < R) {
       tile[k] = keys[i];
       id[k] = point_list[i];
-      mask[k] = block_hit_mask(cull, id[k], (int)(tile[k] % (uint32_t)gx) * TILE_X, (int)(tile[k] / (uint32_t)gx) * TILE_Y);
+      TileForm f;
+      const int kind = load_tile_form(cull, id[k], (int)(tile[k] % (uint32_t)gx) * TILE_X, (int)(tile[k] / (uint32_t)gx) * TILE_Y, f);
+      if (kind == 1) m = 0xFFu;
+      else if (kind == 2) refine = tile_reachable(f);
     }
+    s_mask[k * TH_THREADS + t] = (uint8_t)m;
+    const unsigned bal = __ballot_sync(0xffffffffu, refine);
+    if (bal) {
+      uint32_t qb = 0u;
+      if (lane == 0) qb = atomicAdd(&s_qn, (uint32_t)__popc(bal));
+      qb = __shfl_sync(0xffffffffu, qb, 0);
+      if (refine) s_queue[qb + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)(k * TH_THREADS + t);
+    }
+  }
+  __syncthreads();
+  // phase 2: per-block refinement of the queued items, densely packed over the threads
+  for (uint32_t q = t; q < s_qn; q += TH_THREADS) {
+    const int li = s_queue[q];
+    const int i = base + li;
+    const uint32_t tl = keys[i];
+    TileForm f;
+    load_tile_form(cull, point_list[i], (int)(tl % (uint32_t)gx) * TILE_X, (int)(tl / (uint32_t)gx) * TILE_Y, f);
+    s_mask[li] = (uint8_t)block_masks(f);
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < TH_ITEMS; ++k) {
+    const int i = base + k * TH_THREADS + t;
+    mask[k] = s_mask[k * TH_THREADS + t];
     keep[k] = i < R && (mask[k] != 0u || keep_all);   // keep_all: cull audit walks the full lists
     const unsigned bal = __ballot_sync(0xffffffffu, keep[k]);
     wexcl[k] = __popc(bal & ((1u << lane) - 1u));

@@ -71,9 +71,24 @@ __global__ void __launch_bounds__(256) radix_hist_kernel(const HistArgs a) {
 #pragma unroll
   for (int p = 0; p < RS_MAX_PASSES; ++p) s_h[p][t] = 0u;
   __syncthreads();
-  // whole warps iterate together (match.any needs the full warp): round n up to a warp multiple
-  const int n32 = (a.n + 31) & ~31;
-  for (int i = blockIdx.x * blockDim.x + t; i < n32; i += gridDim.x * blockDim.x) {
+  // 16-B loads, whole warps iterate together (match.any needs the full warp)
+  const int nv = a.n >> 2;                       // number of complete uint4
+  const int nv32 = (nv + 31) & ~31;
+  const uint4* k4 = reinterpret_cast<const uint4*>(a.keys);
+  for (int v = blockIdx.x * blockDim.x + t; v < nv32; v += gridDim.x * blockDim.x) {
+    const bool valid = v < nv;
+    const uint4 q = valid ? __ldg(k4 + v) : make_uint4(0u, 0u, 0u, 0u);
+    const uint32_t key[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+    for (int c = 0; c < 4; ++c)
+      for (int p = 0; p < a.passes; ++p) {
+        const uint32_t d = valid ? ((key[c] >> a.shift[p]) & a.mask[p]) : (uint32_t)RS_RADIX;
+        const unsigned peers = __match_any_sync(0xffffffffu, d);
+        if (valid && lane == __ffs(peers) - 1) atomicAdd(&s_h[p][d], (uint32_t)__popc(peers));
+      }
+  }
+  if (blockIdx.x == 0 && t < 32) {               // the last n % 4 keys
+    const int i = (nv << 2) + t;
     const bool valid = i < a.n;
     const uint32_t key = valid ? a.keys[i] : 0u;
     for (int p = 0; p < a.passes; ++p) {
