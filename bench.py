@@ -52,6 +52,9 @@ def parse():
     ap.add_argument("--points", type=int, default=0, help="override P (debug only; result is then not the headline)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--exact-lists", action="store_true",
+                    help="time the exact-lists mode (the reference's instance lists bit for bit) instead of the "
+                         "default culled emission")
     ap.add_argument("--cpu-sample-tiles", type=int, default=8)
     ap.add_argument("--cpu-sample-len", type=int, default=600, help="list positions walked per sampled tile")
     return ap.parse_args()
@@ -114,8 +117,10 @@ class ClockSampler:
 def algorithmic_bytes(P, V, R, N):
     """compulsory HBM bytes per launch of each stage (surfel path, SH
     degree 3, colours from SH), each datum moved once.  P Gaussians, V visible, R (Gaussian,tile)
-    instances, N pixels."""
+    instances the stage works on (the emitted ones: all of the reference's in exact-lists mode,
+    the reachable ones in the default culled-emission mode), N pixels."""
     return {
+        "count_kept": 4 * P + 72 * V + 4 * P,           # tiles_touched; rect + cull record of visible ones; count out
         "preprocess": 237 * P + 87 * V + 8 * P,        # inputs; state of visible ones; radii + tiles_touched
         "depth_sort": 16 * P,                           # (depth bits, id) pairs read once, written once
         "scan": 8 * P,
@@ -250,8 +255,17 @@ def main():
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item())
 
+    R_ref = None
+    if a.impl == "new":
+        b200gs.set_exact_lists(1)
+        f, _ = step()
+        R_ref = int(f["rendered"])           # the reference's instance count
+        del f
+        b200gs.set_exact_lists(1 if a.exact_lists else 0)
     f, _ = step()
     R, V = int(f["rendered"]), int((f["radii"] > 0).sum())
+    if R_ref is None:
+        R_ref = R
     del f
 
     # ---- device-resident timing (value) with per-stage events and clock sampling -------------
@@ -364,7 +378,9 @@ def main():
         "ms_per_step": round(ms_per_step, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{a.workload}: room scene, replicated Gaussians, ring camera {'0' if world == 1 else '0..%d' % (world - 1)} of 32",
-                   "gaussians": P, "width": W, "height": H, "sh_degree": 3, "visible": V, "instances": R,
+                   "gaussians": P, "width": W, "height": H, "sh_degree": 3, "visible": V, "instances": R_ref, "instances_emitted": R,
+                   "lists": ("exact (reference's lists bit for bit)" if (a.exact_lists or a.impl == "reference")
+                             else "culled emission (only instances that can reach alpha >= 1/255)"),
                    "views_per_step": world, "l2": "inputs (>= 0.7 GB of Gaussian data + 1.3 GB of sort keys per step) exceed the 126 MB L2; no flush",
                    "parallelism": f"view-parallel x{world}, replicated Gaussians" + (", NCCL all-reduce of [P,59] fp32 gradients" if world > 1 else "")},
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),

@@ -11,6 +11,7 @@ namespace b200gs {
 
 static thread_local char t_err[512] = "";
 std::atomic<unsigned long long> g_launches{0};
+std::atomic<int> g_exact_lists{0};
 
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -60,6 +61,7 @@ SurfelGeom SurfelGeom::carve(void* base, size_t P, size_t* bytes) {
   SurfelGeom g;
   g.depths = c.take<float>(P);
   g.tiles_touched = c.take<uint32_t>(P);
+  g.tiles_kept = c.take<uint32_t>(P);
   g.point_offsets = c.take<uint32_t>(P);
   g.order = DepthOrder::carve(c, P);
   g.clamped = c.take<uint8_t>(P);
@@ -122,11 +124,14 @@ int b200gs_version(void) { return 1; }
 int b200gs_sm_arch(void) { return 100; }
 unsigned long long b200gs_launch_count(void) { return g_launches.load(); }
 
+void b200gs_set_exact_lists(int on) { g_exact_lists.store(on ? 1 : 0); }
+int b200gs_get_exact_lists(void) { return g_exact_lists.load(); }
+
 void b200gs_timing_enable(int on) { g_timing.store(on ? 1 : 0); }
 int b200gs_timing_stages(void) { return ST_COUNT; }
 const char* b200gs_timing_stage_name(int stage) {
   static const char* names[ST_COUNT] = {"preprocess", "scan", "duplicate", "sort", "tile_ranges", "composite_fwd",
-                                        "composite_bwd", "preprocess_bwd", "cubemap_fwd", "cubemap_bwd", "tile_hits", "depth_sort"};
+                                        "composite_bwd", "preprocess_bwd", "cubemap_fwd", "cubemap_bwd", "tile_hits", "depth_sort", "count_kept"};
   return (stage >= 0 && stage < ST_COUNT) ? names[stage] : "";
 }
 int b200gs_timing_read(float* ms, unsigned long long* counts, int n) {
@@ -174,7 +179,14 @@ int b200gs_surfel_forward_stage1(const b200gs_surfel_fwd* a, int* num_rendered, 
   SurfelGeom g = SurfelGeom::carve(align128(a->geom), a->P, nullptr);
   rc = surfel_preprocess(*a, g, s);
   if (rc) return rc;
-  rc = depth_order_and_scan(g.depths, g.tiles_touched, a->P, g.order, g.point_offsets, g.scan_state, s, a->debug != 0);
+  const bool exact = g_exact_lists.load(std::memory_order_relaxed) != 0;
+  const uint32_t* counts = g.tiles_touched;
+  if (!exact) {
+    rc = surfel_count_kept(a->P, g.tiles_touched, g.rects, g.cull, g.tiles_kept, s, a->debug != 0);
+    if (rc) return rc;
+    counts = g.tiles_kept;
+  }
+  rc = depth_order_and_scan(g.depths, counts, a->P, g.order, g.point_offsets, g.scan_state, s, a->debug != 0);
   if (rc) return rc;
   int host[2] = {0, 0};
   B200GS_CUDA(cudaMemcpyAsync(&host[0], g.point_offsets + a->P - 1, sizeof(int), cudaMemcpyDeviceToHost, s));
@@ -195,7 +207,8 @@ int b200gs_surfel_forward_stage2(const b200gs_surfel_fwd* a, int R, void* stream
   SurfelGeom g = SurfelGeom::carve(align128(a->geom), a->P, nullptr);
   SurfelImage im = SurfelImage::carve(align128(a->img), a->width, a->height, nullptr);
   Binning b = Binning::carve(R > 0 ? align128(a->binning) : nullptr, R, nullptr);
-  rc = bin_and_sort(g.order.vals_a, g.rects, g.point_offsets, a->P, R, a->width, a->height, b, im.ranges, s, a->debug != 0);
+  rc = bin_and_sort(g.order.vals_a, g.rects, g.point_offsets, a->P, R, a->width, a->height, b, im.ranges, s, a->debug != 0,
+                    g_exact_lists.load(std::memory_order_relaxed) != 0 ? nullptr : g.cull);
   if (rc) return rc;
   {
     const size_t tiles = (size_t)((a->width + TILE_X - 1) / TILE_X) * ((a->height + TILE_Y - 1) / TILE_Y);

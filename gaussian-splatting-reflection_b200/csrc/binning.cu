@@ -12,6 +12,7 @@
 // b200gs_inspect_binning for the parity tests.
 #include "common.cuh"
 #include "radix_sort.cuh"
+#include "cull_rows.cuh"
 
 namespace b200gs {
 
@@ -216,6 +217,67 @@ __global__ void __launch_bounds__(256) duplicate_kernel(int P, const uint32_t* _
   }
 }
 
+// ------------------------------------------------------------------ culled emission
+// Default mode of the surfel path (b200gs_set_exact_lists(0)): instances whose tile the Gaussian
+// cannot reach with alpha >= 1/255 (cull_rows.cuh) are never emitted, so everything downstream --
+// sort, ranges, block masks, compositing -- works on the few per cent of the reference's list that
+// can contribute.  Images, radii, weights and gradients are unchanged (the reference rejects those
+// pairs pixel by pixel); the lists are a subsequence of the reference's.  The exact-lists mode
+// keeps duplicate_kernel above and reproduces the reference's lists bit for bit.
+__global__ void __launch_bounds__(256) count_kept_kernel(int P, const uint32_t* __restrict__ tiles_touched,
+                                                         const uint2* __restrict__ rects, const CullRec* __restrict__ cull,
+                                                         uint32_t* __restrict__ kept) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= P) return;
+  uint32_t n = 0;
+  if (tiles_touched[idx] > 0u) {
+    const uint2 rc = rects[idx];
+    const int x0 = rc.x & 0xffff, x1 = rc.x >> 16, y0 = rc.y & 0xffff, y1 = rc.y >> 16;
+    RowCull rw;
+    rowcull_init(cull[idx], rw);
+    for (int y = y0; y < y1; ++y) {
+      int a1, b1, a2, b2, d0, d1;
+      rowcull_ranges(rw, y, x0, x1, a1, b1, a2, b2, d0, d1);
+      n += (uint32_t)rowcull_count(a1, b1, a2, b2, d0, d1);
+    }
+  }
+  kept[idx] = n;
+}
+
+__global__ void __launch_bounds__(256) emit_kept_kernel(int P, const uint32_t* __restrict__ order,
+                                                        const uint2* __restrict__ rects, const CullRec* __restrict__ cull,
+                                                        const uint32_t* __restrict__ offsets, uint32_t* __restrict__ keys,
+                                                        uint32_t* __restrict__ vals, int gx) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= P) return;
+  uint32_t off = i == 0 ? 0u : offsets[i - 1];
+  const uint32_t end = offsets[i];
+  if (end == off) return;
+  const uint32_t id = order[i];
+  const uint2 rc = rects[id];
+  const int x0 = rc.x & 0xffff, x1 = rc.x >> 16, y0 = rc.y & 0xffff, y1 = rc.y >> 16;
+  RowCull rw;
+  rowcull_init(cull[id], rw);
+  for (int y = y0; y < y1; ++y) {
+    int a1, b1, a2, b2, d0, d1;
+    rowcull_ranges(rw, y, x0, x1, a1, b1, a2, b2, d0, d1);
+    const uint32_t row = (uint32_t)(y * gx);
+    for (int x = a1; x <= b1 && off < end; ++x) { keys[off] = row + (uint32_t)x; vals[off] = id; ++off; }
+    for (int x = a2; x <= b2 && off < end; ++x) { keys[off] = row + (uint32_t)x; vals[off] = id; ++off; }
+    for (int x = d0; x <= d1 && off < end; ++x)
+      if (!((x >= a1 && x <= b1) || (x >= a2 && x <= b2))) { keys[off] = row + (uint32_t)x; vals[off] = id; ++off; }
+  }
+}
+
+int surfel_count_kept(int P, const uint32_t* tiles_touched, const uint2* rects, const CullRec* cull, uint32_t* kept,
+                      cudaStream_t s, bool debug) {
+  if (P <= 0) return B200GS_OK;
+  StageScope _t(ST_COUNT_KEPT, s);
+  count_kept_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, tiles_touched, rects, cull, kept);
+  B200GS_LAUNCHED("count_kept_kernel", debug, s);
+  return B200GS_OK;
+}
+
 // identifyTileRanges (rasterizer_impl.cu:116-138)
 __global__ void __launch_bounds__(256) tile_ranges_kernel(int L, const uint32_t* __restrict__ keys, uint2* ranges) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -387,6 +449,10 @@ __device__ __forceinline__ unsigned block_masks(const TileForm& f) {
 }
 
 // state[0] = ticket; look-back words (flag << 32 | count) start at state + 2.
+// PREFILTER: whole-tile test first, per-block refinement only for the survivors (exact-lists mode,
+// where most instances miss their tile); without it every instance goes straight to the per-block
+// test (culled emission already dropped the instances that miss their tile).
+template <bool PREFILTER>
 __global__ void __launch_bounds__(TH_THREADS) tile_hits_kernel(int R, const uint32_t* __restrict__ keys,
                                                                const uint32_t* __restrict__ point_list,
                                                                const CullRec* __restrict__ cull, int gx,
@@ -422,10 +488,13 @@ __global__ void __launch_bounds__(TH_THREADS) tile_hits_kernel(int R, const uint
       TileForm f;
       const int kind = load_tile_form(cull, id[k], (int)(tile[k] % (uint32_t)gx) * TILE_X, (int)(tile[k] / (uint32_t)gx) * TILE_Y, f);
       if (kind == 1) m = 0xFFu;
-      else if (kind == 2) refine = tile_reachable(f);
+      else if (kind == 2) {
+        if (PREFILTER) refine = tile_reachable(f);
+        else m = block_masks(f);
+      }
     }
     s_mask[k * TH_THREADS + t] = (uint8_t)m;
-    const unsigned bal = __ballot_sync(0xffffffffu, refine);
+    const unsigned bal = PREFILTER ? __ballot_sync(0xffffffffu, refine) : 0u;
     if (bal) {
       uint32_t qb = 0u;
       if (lane == 0) qb = atomicAdd(&s_qn, (uint32_t)__popc(bal));
@@ -513,9 +582,13 @@ int surfel_tile_hits(const CullRec* cull, const Binning& b, int R, int W, int H,
   const int gx = (W + TILE_X - 1) / TILE_X;
   StageScope _t(ST_TILE_HITS, s);
   B200GS_CUDA(cudaMemsetAsync(b.hit_state, 0, tile_hits_state_words(R) * sizeof(uint32_t), s));
-  tile_hits_kernel<<<(R + TH_TILE - 1) / TH_TILE, TH_THREADS, 0, s>>>(R, b.tile_ids, b.point_list, cull, gx, ranges, cranges,
-                                                                       b.comp_id, b.comp_pos, b.comp_hit, b.hit_state,
-                                                                       g_cull_audit.load(std::memory_order_relaxed));
+  const int keep_all = g_cull_audit.load(std::memory_order_relaxed);
+  if (g_exact_lists.load(std::memory_order_relaxed))
+    tile_hits_kernel<true><<<(R + TH_TILE - 1) / TH_TILE, TH_THREADS, 0, s>>>(R, b.tile_ids, b.point_list, cull, gx, ranges, cranges,
+                                                                             b.comp_id, b.comp_pos, b.comp_hit, b.hit_state, keep_all);
+  else
+    tile_hits_kernel<false><<<(R + TH_TILE - 1) / TH_TILE, TH_THREADS, 0, s>>>(R, b.tile_ids, b.point_list, cull, gx, ranges, cranges,
+                                                                              b.comp_id, b.comp_pos, b.comp_hit, b.hit_state, keep_all);
   B200GS_LAUNCHED("tile_hits_kernel", debug, s);
   return B200GS_OK;
 }
@@ -549,8 +622,9 @@ Binning Binning::carve(void* base, size_t R, size_t* bytes) {
 }
 
 // order: Gaussian ids in depth order; offsets: inclusive prefix of tiles_touched in that order.
+// cull != nullptr: culled emission (offsets then count the kept tiles), else the reference's full lists.
 int bin_and_sort(const uint32_t* order, const uint2* rects, const uint32_t* offsets, int P, int R, int W, int H,
-                 const Binning& b, uint2* ranges, cudaStream_t s, bool debug) {
+                 const Binning& b, uint2* ranges, cudaStream_t s, bool debug, const CullRec* cull) {
   const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
   B200GS_CUDA(cudaMemsetAsync(ranges, 0, (size_t)gx * gy * sizeof(uint2), s));
   if (R <= 0) return B200GS_OK;
@@ -565,8 +639,13 @@ int bin_and_sort(const uint32_t* order, const uint2* rects, const uint32_t* offs
   int rc;
   {
     StageScope _t(ST_DUPLICATE, s);
-    duplicate_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, order, rects, offsets, ka, va, gx);
-    B200GS_LAUNCHED("duplicate_kernel", debug, s);
+    if (cull != nullptr) {
+      emit_kept_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, order, rects, cull, offsets, ka, va, gx);
+      B200GS_LAUNCHED("emit_kept_kernel", debug, s);
+    } else {
+      duplicate_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, order, rects, offsets, ka, va, gx);
+      B200GS_LAUNCHED("duplicate_kernel", debug, s);
+    }
   }
   {
     StageScope _t(ST_SORT, s);

@@ -46,7 +46,7 @@ extern std::atomic<unsigned long long> g_launches;
 // bench.py can attribute the step time to kernels without a profiler attached.
 enum Stage {
   ST_PREPROCESS = 0, ST_SCAN, ST_DUPLICATE, ST_SORT, ST_RANGES, ST_COMPOSITE_FWD,
-  ST_COMPOSITE_BWD, ST_PREPROCESS_BWD, ST_CUBEMAP_FWD, ST_CUBEMAP_BWD, ST_TILE_HITS, ST_DEPTH_SORT, ST_COUNT
+  ST_COMPOSITE_BWD, ST_PREPROCESS_BWD, ST_CUBEMAP_FWD, ST_CUBEMAP_BWD, ST_TILE_HITS, ST_DEPTH_SORT, ST_COUNT_KEPT, ST_COUNT
 };
 extern std::atomic<int> g_timing;
 extern std::atomic<int> g_cull_audit;   // surfel_composite_fwd.cu: b200gs_debug_cull_audit
@@ -108,8 +108,9 @@ struct DepthOrder {
 
 struct SurfelGeom {
   float* depths;            // [P]
-  uint32_t* tiles_touched;  // [P]
-  uint32_t* point_offsets;  // [P] inclusive prefix sum of tiles_touched IN DEPTH ORDER (order.vals_a)
+  uint32_t* tiles_touched;  // [P] the reference's count (rect area)
+  uint32_t* tiles_kept;     // [P] tiles of the rect the Gaussian can reach (culled emission)
+  uint32_t* point_offsets;  // [P] inclusive prefix sum of tiles_kept / tiles_touched IN DEPTH ORDER (order.vals_a)
   DepthOrder order;
   uint8_t* clamped;         // [P] bit c = colour channel c clamped at 0
   uint2* rects;             // [P] tile rect: x = x0 | x1<<16, y = y0 | y1<<16 (only valid if tiles_touched>0)
@@ -238,7 +239,11 @@ int inclusive_scan_u32(const uint32_t* in, uint32_t* out, int n, uint32_t* state
 int depth_order_and_scan(const float* depths, const uint32_t* tiles_touched, int P, const DepthOrder& o,
                          uint32_t* point_offsets, uint32_t* scan_state, cudaStream_t s, bool debug);
 int bin_and_sort(const uint32_t* order, const uint2* rects, const uint32_t* offsets,
-                 int P, int R, int W, int H, const Binning& b, uint2* ranges, cudaStream_t s, bool debug);
+                 int P, int R, int W, int H, const Binning& b, uint2* ranges, cudaStream_t s, bool debug,
+                 const CullRec* cull = nullptr);
+int surfel_count_kept(int P, const uint32_t* tiles_touched, const uint2* rects, const CullRec* cull, uint32_t* kept,
+                      cudaStream_t s, bool debug);
+extern std::atomic<int> g_exact_lists;  // api.cu: b200gs_set_exact_lists
 int surfel_tile_hits(const CullRec* cull, const Binning& b, int R, int W, int H, const uint2* ranges, uint2* cranges,
                      cudaStream_t s, bool debug);
 size_t tile_hits_state_words(size_t R);

@@ -119,6 +119,8 @@ def timing_read():
     return {timing_stage_name(i).decode(): (float(ms[i]), int(cnt[i])) for i in range(n)}
 
 
+set_exact_lists = _sig("b200gs_set_exact_lists", None, _i)
+get_exact_lists = _sig("b200gs_get_exact_lists", _i)
 debug_cull_audit = _sig("b200gs_debug_cull_audit", None, _i)
 _cull_violations = _sig("b200gs_debug_cull_violations", _i, _p, _i)
 

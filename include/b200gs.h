@@ -53,6 +53,17 @@ int b200gs_timing_stages(void);
 const char* b200gs_timing_stage_name(int stage);
 int b200gs_timing_read(float* ms, unsigned long long* counts, int n);
 
+/* Instance lists of the surfel path.  0 (default): culled emission -- a (Gaussian, tile) instance is
+ * only emitted if the Gaussian can reach alpha >= 1/255 somewhere in the tile, so num_rendered and
+ * the sorted lists are a subsequence of the reference's (typically a few per cent of it when splats
+ * cross the camera plane); colour/aux/reflection images, radii, weights and gradients are
+ * unchanged.  1: exact lists -- num_rendered, the sorted (key, value) lists, the tile ranges and
+ * n_contrib are the reference's, bit for bit (S/cuda_rasterizer/rasterizer_impl.cu:282-321); the
+ * compositing kernels then skip the unreachable instances through the compacted list instead.
+ * Process-wide; must not change between a forward's stage 1 and its backward.               */
+void b200gs_set_exact_lists(int on);
+int b200gs_get_exact_lists(void);
+
 /* Cull audit (test infrastructure for the sub-tile culling of the surfel compositing):
  * while on, the forward compositing ignores the per-instance hit masks, evaluates every
  * (warp block, Gaussian) pair the way the reference does and counts the pairs that pass the

@@ -18,6 +18,22 @@ for p in (ROOT, PKG_PY):
         sys.path.insert(0, p)
 
 
+import contextlib
+
+
+@contextlib.contextmanager
+def exact_lists(on=True):
+    """Run the surfel path in exact-lists mode (the reference's instance lists bit for bit) or in
+    the default culled-emission mode (include/b200gs.h: b200gs_set_exact_lists)."""
+    import b200gs
+    old = b200gs.get_exact_lists()
+    b200gs.set_exact_lists(1 if on else 0)
+    try:
+        yield
+    finally:
+        b200gs.set_exact_lists(old)
+
+
 def new_surfel_C():
     import diff_surfel_rasterization
     return diff_surfel_rasterization._C
