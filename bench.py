@@ -55,7 +55,7 @@ def parse():
     ap.add_argument("--exact-lists", action="store_true",
                     help="time the exact-lists mode (the reference's instance lists bit for bit) instead of the "
                          "default culled emission")
-    ap.add_argument("--cpu-sample-tiles", type=int, default=8)
+    ap.add_argument("--cpu-sample-tiles", type=int, default=4)
     ap.add_argument("--cpu-sample-len", type=int, default=600, help="list positions walked per sampled tile")
     return ap.parse_args()
 
@@ -367,7 +367,7 @@ def main():
 
     cpu = None
     if a.impl == "new" and world == 1 and not a.no_cpu_baseline:
-        cpu = cpu_baseline(sc_np, cam_np, a.cpu_sample_tiles, a.cpu_sample_len, R)
+        cpu = cpu_baseline(sc_np, cam_np, a.cpu_sample_tiles, a.cpu_sample_len, R_ref)   # the oracle walks the reference's full lists
     elif a.impl == "reference":
         cpu = {"value": value, "unit": UNIT, "cores": 0, "kind": "reference",
                "sample": "the reference has no CPU implementation of this path (CUDA only): this arm is its "

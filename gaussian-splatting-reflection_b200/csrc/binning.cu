@@ -224,24 +224,59 @@ __global__ void __launch_bounds__(256) duplicate_kernel(int P, const uint32_t* _
 // can contribute.  Images, radii, weights and gradients are unchanged (the reference rejects those
 // pairs pixel by pixel); the lists are a subsequence of the reference's.  The exact-lists mode
 // keeps duplicate_kernel above and reproduces the reference's lists bit for bit.
+// One thread per Gaussian for rects of < COOP_ROWS tile rows; taller rects are handed to the whole
+// warp, one tile row per lane (every lane rebuilds the RowCull from the same 64-B record).
+constexpr int COOP_ROWS = 20;          // counting
+constexpr int EMIT_COOP_ROWS = 1 << 30; // emission: measured slower than one thread per Gaussian at any threshold (B200, bench scene)
+
+__device__ __forceinline__ void emit_row(const RowCull& rw, int y, int x0, int x1, int gx, uint32_t id, uint32_t off, uint32_t end,
+                                         uint32_t* __restrict__ keys, uint32_t* __restrict__ vals) {
+  int a1, b1, a2, b2, d0, d1;
+  rowcull_ranges(rw, y, x0, x1, a1, b1, a2, b2, d0, d1);
+  const uint32_t row = (uint32_t)(y * gx);
+  for (int x = a1; x <= b1 && off < end; ++x) { keys[off] = row + (uint32_t)x; vals[off] = id; ++off; }
+  for (int x = a2; x <= b2 && off < end; ++x) { keys[off] = row + (uint32_t)x; vals[off] = id; ++off; }
+  for (int x = d0; x <= d1 && off < end; ++x)
+    if (!((x >= a1 && x <= b1) || (x >= a2 && x <= b2))) { keys[off] = row + (uint32_t)x; vals[off] = id; ++off; }
+}
+
+__device__ __forceinline__ uint32_t count_row(const RowCull& rw, int y, int x0, int x1) {
+  int a1, b1, a2, b2, d0, d1;
+  rowcull_ranges(rw, y, x0, x1, a1, b1, a2, b2, d0, d1);
+  return (uint32_t)rowcull_count(a1, b1, a2, b2, d0, d1);
+}
+
 __global__ void __launch_bounds__(256) count_kept_kernel(int P, const uint32_t* __restrict__ tiles_touched,
                                                          const uint2* __restrict__ rects, const CullRec* __restrict__ cull,
                                                          uint32_t* __restrict__ kept) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= P) return;
+  const int lane = threadIdx.x & 31;
   uint32_t n = 0;
-  if (tiles_touched[idx] > 0u) {
-    const uint2 rc = rects[idx];
+  uint2 rc = make_uint2(0u, 0u);
+  const bool vis = idx < P && tiles_touched[idx] > 0u;
+  if (vis) rc = rects[idx];
+  const int rows = (int)(rc.y >> 16) - (int)(rc.y & 0xffff);
+  const bool coop = vis && rows >= COOP_ROWS;
+  if (vis && !coop) {
     const int x0 = rc.x & 0xffff, x1 = rc.x >> 16, y0 = rc.y & 0xffff, y1 = rc.y >> 16;
     RowCull rw;
     rowcull_init(cull[idx], rw);
-    for (int y = y0; y < y1; ++y) {
-      int a1, b1, a2, b2, d0, d1;
-      rowcull_ranges(rw, y, x0, x1, a1, b1, a2, b2, d0, d1);
-      n += (uint32_t)rowcull_count(a1, b1, a2, b2, d0, d1);
-    }
+    for (int y = y0; y < y1; ++y) n += count_row(rw, y, x0, x1);
   }
-  kept[idx] = n;
+  unsigned todo = __ballot_sync(0xffffffffu, coop);
+  while (todo) {
+    const int src = __ffs(todo) - 1;
+    todo &= todo - 1;
+    const uint32_t rx = __shfl_sync(0xffffffffu, rc.x, src), ry = __shfl_sync(0xffffffffu, rc.y, src);
+    const int x0 = rx & 0xffff, x1 = rx >> 16, y0 = ry & 0xffff, y1 = ry >> 16;
+    RowCull rw;
+    rowcull_init(cull[idx - lane + src], rw);
+    uint32_t part = 0;
+    for (int y = y0 + lane; y < y1; y += 32) part += count_row(rw, y, x0, x1);
+    part = __reduce_add_sync(0xffffffffu, part);
+    if (lane == src) n = part;
+  }
+  if (idx < P) kept[idx] = n;
 }
 
 __global__ void __launch_bounds__(256) emit_kept_kernel(int P, const uint32_t* __restrict__ order,
@@ -249,23 +284,47 @@ __global__ void __launch_bounds__(256) emit_kept_kernel(int P, const uint32_t* _
                                                         const uint32_t* __restrict__ offsets, uint32_t* __restrict__ keys,
                                                         uint32_t* __restrict__ vals, int gx) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= P) return;
-  uint32_t off = i == 0 ? 0u : offsets[i - 1];
-  const uint32_t end = offsets[i];
-  if (end == off) return;
-  const uint32_t id = order[i];
-  const uint2 rc = rects[id];
-  const int x0 = rc.x & 0xffff, x1 = rc.x >> 16, y0 = rc.y & 0xffff, y1 = rc.y >> 16;
-  RowCull rw;
-  rowcull_init(cull[id], rw);
-  for (int y = y0; y < y1; ++y) {
-    int a1, b1, a2, b2, d0, d1;
-    rowcull_ranges(rw, y, x0, x1, a1, b1, a2, b2, d0, d1);
-    const uint32_t row = (uint32_t)(y * gx);
-    for (int x = a1; x <= b1 && off < end; ++x) { keys[off] = row + (uint32_t)x; vals[off] = id; ++off; }
-    for (int x = a2; x <= b2 && off < end; ++x) { keys[off] = row + (uint32_t)x; vals[off] = id; ++off; }
-    for (int x = d0; x <= d1 && off < end; ++x)
-      if (!((x >= a1 && x <= b1) || (x >= a2 && x <= b2))) { keys[off] = row + (uint32_t)x; vals[off] = id; ++off; }
+  const int lane = threadIdx.x & 31;
+  uint32_t off = 0, end = 0, id = 0;
+  if (i < P) { off = i == 0 ? 0u : offsets[i - 1]; end = offsets[i]; }
+  const bool any = end > off;
+  uint2 rc = make_uint2(0u, 0u);
+  if (any) { id = order[i]; rc = rects[id]; }
+  const int rows = (int)(rc.y >> 16) - (int)(rc.y & 0xffff);
+  const bool coop = any && rows >= EMIT_COOP_ROWS;
+  if (any && !coop) {
+    const int x0 = rc.x & 0xffff, x1 = rc.x >> 16, y0 = rc.y & 0xffff, y1 = rc.y >> 16;
+    RowCull rw;
+    rowcull_init(cull[id], rw);
+    for (int y = y0; y < y1; ++y) {
+      const uint32_t c = count_row(rw, y, x0, x1);
+      emit_row(rw, y, x0, x1, gx, id, off, end, keys, vals);
+      off += c;
+    }
+  }
+  unsigned todo = __ballot_sync(0xffffffffu, coop);
+  while (todo) {
+    const int src = __ffs(todo) - 1;
+    todo &= todo - 1;
+    const uint32_t rx = __shfl_sync(0xffffffffu, rc.x, src), ry = __shfl_sync(0xffffffffu, rc.y, src);
+    const uint32_t gid = __shfl_sync(0xffffffffu, id, src);
+    uint32_t o = __shfl_sync(0xffffffffu, off, src);
+    const uint32_t e = __shfl_sync(0xffffffffu, end, src);
+    const int x0 = rx & 0xffff, x1 = rx >> 16, y0 = ry & 0xffff, y1 = ry >> 16;
+    RowCull rw;
+    rowcull_init(cull[gid], rw);
+    for (int yb = y0; yb < y1; yb += 32) {          // 32 tile rows at a time: count, scan, emit
+      const int y = yb + lane;
+      const uint32_t c = y < y1 ? count_row(rw, y, x0, x1) : 0u;
+      uint32_t inc = c;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t v = __shfl_up_sync(0xffffffffu, inc, d);
+        if (lane >= d) inc += v;
+      }
+      if (c) emit_row(rw, y, x0, x1, gx, gid, o + inc - c, e, keys, vals);
+      o += __shfl_sync(0xffffffffu, inc, 31);
+    }
   }
 }
 
