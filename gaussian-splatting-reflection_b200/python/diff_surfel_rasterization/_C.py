@@ -68,10 +68,13 @@ def rasterize_gaussians(background, means3D, env_scope_mask, colors, refl_streng
     dev = means3D.device
     f32 = dict(dtype=torch.float32, device=dev)
     with torch.cuda.device(dev):
-        out_color = torch.zeros((NUM_CHANNELS, H, W), **f32)
-        out_others = torch.zeros((3 + 3 + 1 + 1, H, W), **f32)
-        out_refl = torch.zeros((1, H, W), **f32)
-        radii = torch.zeros((P,), dtype=torch.int32, device=dev)
+        # the reference zero-fills these (S/rasterize_points.cu:88-95); the kernels write every pixel and
+        # every radius themselves, so only the P == 0 short-circuit and the atomicMax target need zeros
+        new = torch.zeros if P == 0 else torch.empty
+        out_color = new((NUM_CHANNELS, H, W), **f32)
+        out_others = new((3 + 3 + 1 + 1, H, W), **f32)
+        out_refl = new((1, H, W), **f32)
+        radii = new((P,), dtype=torch.int32, device=dev)
         gaussian_weights = torch.zeros((P,), **f32)
         u8 = dict(dtype=torch.uint8, device=dev)
         geom = torch.empty((0,), **u8)
