@@ -97,3 +97,20 @@ def test_autograd_module_and_empty():
     empty = {k: (v[:0].contiguous() if isinstance(v, torch.Tensor) else v) for k, v in sc.items()}
     f = hz.gauss_forward(hz.new_gauss_C(), empty, cam)
     assert f["rendered"] == 0 and float(f["color"].abs().max()) == 0.0
+
+
+def test_against_cpu_oracle():
+    """sm_100a 3DGS path vs the CPU restatement (oracle/gauss_oracle.py, pinned to the reference's
+    golden vectors by tests/test_gauss_oracle_cpu.py): integer structures equal, images to 1e-4."""
+    import numpy as np
+    from oracle import gauss_oracle as go
+    sc_np, cam_np = scenes.build("tiny")
+    sc, cam = hz.gauss_scene(hz.to_dev(sc_np)), hz.to_dev(cam_np)
+    fn = hz.gauss_forward(hz.new_gauss_C(), sc, cam, bg=(0.1, 0.2, 0.3), antialiasing=True)
+    o, _ = go.forward_backward(dict(sc_np, scales3=sc["scales3"].cpu().numpy(), normals=sc["normals"].cpu().numpy()),
+                               cam_np, None, bg=(0.1, 0.2, 0.3), antialiasing=True)
+    assert o["rendered"] == fn["rendered"]
+    assert np.array_equal(o["radii"], fn["radii"].cpu().numpy())
+    for k in ("color", "invdepth", "normal_map", "refl_map"):
+        d = np.abs(o[k] - fn[k].cpu().numpy())
+        assert (d > 1e-4).mean() <= 1e-3, (k, d.max())
