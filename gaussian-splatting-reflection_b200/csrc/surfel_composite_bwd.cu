@@ -83,10 +83,7 @@ __global__ void __launch_bounds__(BATCH, 2) surfel_composite_bwd_kernel(const Co
   bg_dot_dpixel += a.bg[1] * dpix1;
   bg_dot_dpixel += a.bg[2] * dpix2;
 
-  float acc_c0 = 0.f, acc_c1 = 0.f, acc_c2 = 0.f, last_c0 = 0.f, last_c1 = 0.f, last_c2 = 0.f;
-  float acc_refl = 0.f, last_refl = 0.f;
-  float last_depth = 0.f, acc_depth = 0.f, acc_alpha = 0.f;
-  float acc_n0 = 0.f, acc_n1 = 0.f, acc_n2 = 0.f, last_n0 = 0.f, last_n1 = 0.f, last_n2 = 0.f;
+  float acc_q = 0.f, last_q = 0.f;
   float last_dL_dT = 0.f, last_alpha = 0.f;
 
   // The reference leaves the entry loop per thread (`!done`); here `done` pixels
@@ -179,45 +176,46 @@ __global__ void __launch_bounds__(BATCH, 2) surfel_composite_bwd_kernel(const Co
       if (c) {
         const float4 q3 = rb[j].q[3], q4 = rb[j].q[4];
         const float alpha = h.alpha, G = h.G;
-        T = __fdiv_rn(T, __fsub_rn(1.0f, alpha));
+        // One reciprocal each for (1 - alpha) and the depth instead of the reference's six divisions
+        // per pair (backward.cu:341,:373,:385,:412,:437-438); the backward is toleranced, not bit-exact.
+        const float inv_1ma = __frcp_rn(__fsub_rn(1.0f, alpha));
+        T = T * inv_1ma;
         const float w = alpha * T;
-        float dL_dalpha = 0.0f;
         const float om = 1.0f - last_alpha;
-        // colour (backward.cu:346-359)
-        acc_c0 = last_alpha * last_c0 + om * acc_c0; last_c0 = q4.x; dL_dalpha += (q4.x - acc_c0) * dpix0; g[12] = w * dpix0;
-        acc_c1 = last_alpha * last_c1 + om * acc_c1; last_c1 = q4.y; dL_dalpha += (q4.y - acc_c1) * dpix1; g[13] = w * dpix1;
-        acc_c2 = last_alpha * last_c2 + om * acc_c2; last_c2 = q4.z; dL_dalpha += (q4.z - acc_c2) * dpix2; g[14] = w * dpix2;
-        // reflection strength (:361-364)
-        acc_refl = last_alpha * last_refl + om * acc_refl; last_refl = q3.w;
-        dL_dalpha += (q3.w - acc_refl) * drefl; g[15] = w * drefl;
-        // distortion / depth / alpha / normal (:366-402)
         const float c_d = h.depth;
-        const float m_d = ndc_depth(c_d);
-        const float dmd_dd = (FAR_N * NEAR_N) / ((FAR_N - NEAR_N) * c_d * c_d);
+        const float rcd = __frcp_rn(c_d);
+        // Colour, reflection strength, depth, alpha and normal (backward.cu:346-364,:392-402) all
+        // enter dL_dalpha as (value - value accumulated behind) * upstream gradient.  The recurrence
+        // is linear, so the nine per-channel recurrences of the reference collapse into ONE on
+        // q = sum_ch value_ch * upstream_ch.
+        const float qv = q4.x * dpix0 + q4.y * dpix1 + q4.z * dpix2 + q3.w * drefl + c_d * ddepth + daccum +
+                         q3.x * dn0 + q3.y * dn1 + q3.z * dn2;
+        acc_q = last_alpha * last_q + om * acc_q;
+        last_q = qv;
+        float dL_dalpha = qv - acc_q;
+        g[12] = w * dpix0; g[13] = w * dpix1; g[14] = w * dpix2;
+        g[15] = w * drefl;
+        g[16] = w * dn0; g[17] = w * dn1; g[18] = w * dn2;
+        // distortion (:366-390)
+        const float m_d = (1.0f - NEAR_N * rcd) * (FAR_N / (FAR_N - NEAR_N));
+        const float dmd_dd = (FAR_N * NEAR_N / (FAR_N - NEAR_N)) * rcd * rcd;
         float dL_dz = 0.0f;
         if (contributor == median_contributor - 1u) dL_dz += dmedian;
         const float dL_dweight = (final_D2 + m_d * m_d * final_A - 2.0f * m_d * final_D) * dreg;
         dL_dalpha += dL_dweight - last_dL_dT;
         last_dL_dT = dL_dweight * alpha + (1.0f - alpha) * last_dL_dT;
-        const float dL_dmd = 2.0f * (T * alpha) * (m_d * final_A - final_D) * dreg;
+        const float dL_dmd = 2.0f * w * (m_d * final_A - final_D) * dreg;
         dL_dz += dL_dmd * dmd_dd;
-        acc_depth = last_alpha * last_depth + om * acc_depth; last_depth = c_d;
-        dL_dalpha += (c_d - acc_depth) * ddepth;
-        acc_alpha = last_alpha + om * acc_alpha;
-        dL_dalpha += (1.0f - acc_alpha) * daccum;
-        acc_n0 = last_alpha * last_n0 + om * acc_n0; last_n0 = q3.x; dL_dalpha += (q3.x - acc_n0) * dn0; g[16] = w * dn0;
-        acc_n1 = last_alpha * last_n1 + om * acc_n1; last_n1 = q3.y; dL_dalpha += (q3.y - acc_n1) * dn1; g[17] = w * dn1;
-        acc_n2 = last_alpha * last_n2 + om * acc_n2; last_n2 = q3.z; dL_dalpha += (q3.z - acc_n2) * dn2; g[18] = w * dn2;
 
         dL_dalpha *= T;
         last_alpha = alpha;
-        dL_dalpha += (-T_final / (1.0f - alpha)) * bg_dot_dpixel;  // :411-414
+        dL_dalpha += (-T_final * inv_1ma) * bg_dot_dpixel;  // :411-414
         const float dL_dG = h.opa * dL_dalpha;
         dL_dz += w * ddepth;
         if (h.rho3d <= h.rho2d) {  // :423-453
           const float dsx = dL_dG * -G * h.sx + dL_dz * h.Twx;
           const float dsy = dL_dG * -G * h.sy + dL_dz * h.Twy;
-          const float dsx_pz = dsx / h.pz, dsy_pz = dsy / h.pz;
+          const float dsx_pz = dsx * h.rpz, dsy_pz = dsy * h.rpz;
           const float dpx = dsx_pz, dpy = dsy_pz, dpz = -(dsx_pz * h.sx + dsy_pz * h.sy);
           // dL_dk = cross(l, dL_dp), dL_dl = cross(dL_dp, k)
           const float dkx = h.ly * dpz - h.lz * dpy, dky = h.lz * dpx - h.lx * dpz, dkz = h.lx * dpy - h.ly * dpx;
