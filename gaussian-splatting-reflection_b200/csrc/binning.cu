@@ -279,29 +279,55 @@ __global__ void __launch_bounds__(256) count_kept_kernel(int P, const uint32_t* 
   if (idx < P) kept[idx] = n;
 }
 
+// hist != nullptr: the digit histograms of the (<= 2) radix passes over the emitted tile ids are
+// accumulated on the fly (shared-memory REDs, flushed per block), which saves the separate
+// histogram pass over the keys (radix_histogram).
+struct EmitHist {
+  uint32_t* hist;          // [RS_MAX_PASSES][256] in the radix workspace, or nullptr
+  int shift1;              // pass 0 digit = key & mask0, pass 1 digit = (key >> shift1) & mask1
+  uint32_t mask0, mask1;
+};
+
 __global__ void __launch_bounds__(256) emit_kept_kernel(int P, const uint32_t* __restrict__ order,
                                                         const uint2* __restrict__ rects, const CullRec* __restrict__ cull,
                                                         const uint32_t* __restrict__ offsets, uint32_t* __restrict__ keys,
-                                                        uint32_t* __restrict__ vals, int gx) {
+                                                        uint32_t* __restrict__ vals, int gx, const EmitHist eh) {
+  __shared__ uint32_t s_h[2][RS_RADIX];
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int lane = threadIdx.x & 31;
+  if (eh.hist) { s_h[0][threadIdx.x] = 0u; s_h[1][threadIdx.x] = 0u; __syncthreads(); }
+  auto put = [&](uint32_t o, uint32_t key, uint32_t v) {
+    keys[o] = key; vals[o] = v;
+    if (eh.hist) { atomicAdd(&s_h[0][key & eh.mask0], 1u); atomicAdd(&s_h[1][(key >> eh.shift1) & eh.mask1], 1u); }
+  };
   uint32_t off = 0, end = 0, id = 0;
   if (i < P) { off = i == 0 ? 0u : offsets[i - 1]; end = offsets[i]; }
   const bool any = end > off;
   uint2 rc = make_uint2(0u, 0u);
   if (any) { id = order[i]; rc = rects[id]; }
   const int rows = (int)(rc.y >> 16) - (int)(rc.y & 0xffff);
-  const bool coop = any && rows >= EMIT_COOP_ROWS;
-  if (any && !coop) {
+  (void)rows; (void)lane;
+  if (any) {
     const int x0 = rc.x & 0xffff, x1 = rc.x >> 16, y0 = rc.y & 0xffff, y1 = rc.y >> 16;
     RowCull rw;
     rowcull_init(cull[id], rw);
     for (int y = y0; y < y1; ++y) {
-      const uint32_t c = count_row(rw, y, x0, x1);
-      emit_row(rw, y, x0, x1, gx, id, off, end, keys, vals);
-      off += c;
+      int a1, b1, a2, b2, d0, d1;
+      rowcull_ranges(rw, y, x0, x1, a1, b1, a2, b2, d0, d1);
+      const uint32_t row = (uint32_t)(y * gx);
+      for (int x = a1; x <= b1 && off < end; ++x) { put(off, row + (uint32_t)x, id); ++off; }
+      for (int x = a2; x <= b2 && off < end; ++x) { put(off, row + (uint32_t)x, id); ++off; }
+      for (int x = d0; x <= d1 && off < end; ++x)
+        if (!((x >= a1 && x <= b1) || (x >= a2 && x <= b2))) { put(off, row + (uint32_t)x, id); ++off; }
     }
   }
+  if (eh.hist) {
+    __syncthreads();
+    const uint32_t h0 = s_h[0][threadIdx.x], h1 = s_h[1][threadIdx.x];
+    if (h0) atomicAdd(eh.hist + threadIdx.x, h0);
+    if (h1) atomicAdd(eh.hist + RS_RADIX + threadIdx.x, h1);
+  }
+#if 0   // warp-cooperative emission of tall rects: measured slower than one thread per Gaussian (B200, bench scene)
   unsigned todo = __ballot_sync(0xffffffffu, coop);
   while (todo) {
     const int src = __ffs(todo) - 1;
@@ -326,6 +352,7 @@ __global__ void __launch_bounds__(256) emit_kept_kernel(int P, const uint32_t* _
       o += __shfl_sync(0xffffffffu, inc, 31);
     }
   }
+#endif
 }
 
 int surfel_count_kept(int P, const uint32_t* tiles_touched, const uint2* rects, const CullRec* cull, uint32_t* kept,
@@ -696,10 +723,17 @@ int bin_and_sort(const uint32_t* order, const uint2* rects, const uint32_t* offs
   uint32_t* kb = odd ? b.tile_ids : b.tmp_keys;
   uint32_t* vb = odd ? b.point_list : b.tmp_vals;
   int rc;
+  const bool fused_hist = cull != nullptr && plan.passes <= 2;   // emit_kept_kernel accumulates the digit histograms
   {
     StageScope _t(ST_DUPLICATE, s);
     if (cull != nullptr) {
-      emit_kept_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, order, rects, cull, offsets, ka, va, gx);
+      EmitHist eh;
+      eh.hist = fused_hist ? radix_hist_ptr(b.sort_ws) : nullptr;
+      eh.mask0 = (1u << plan.bits[0]) - 1u;
+      eh.shift1 = plan.passes > 1 ? plan.shift[1] : 0;
+      eh.mask1 = plan.passes > 1 ? (1u << plan.bits[1]) - 1u : 0u;
+      if (fused_hist) { rc = radix_workspace_clear(b.sort_ws, s); if (rc) return rc; }
+      emit_kept_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, order, rects, cull, offsets, ka, va, gx, eh);
       B200GS_LAUNCHED("emit_kept_kernel", debug, s);
     } else {
       duplicate_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, order, rects, offsets, ka, va, gx);
@@ -708,10 +742,12 @@ int bin_and_sort(const uint32_t* order, const uint2* rects, const uint32_t* offs
   }
   {
     StageScope _t(ST_SORT, s);
-    rc = radix_workspace_clear(b.sort_ws, s);
-    if (rc) return rc;
-    rc = radix_histogram(ka, R, plan, b.sort_ws, s, debug);
-    if (rc) return rc;
+    if (!fused_hist) {
+      rc = radix_workspace_clear(b.sort_ws, s);
+      if (rc) return rc;
+      rc = radix_histogram(ka, R, plan, b.sort_ws, s, debug);
+      if (rc) return rc;
+    }
     rc = radix_sort_pairs_u32(ka, va, kb, vb, R, plan, b.sort_ws, s, debug);
     if (rc) return rc;
   }

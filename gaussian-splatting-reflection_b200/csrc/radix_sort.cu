@@ -51,6 +51,8 @@ static inline unsigned long long* ws_state(void* ws) {
   return reinterpret_cast<unsigned long long*>(reinterpret_cast<uint32_t*>(ws) + WS_HEAD_WORDS);
 }
 
+uint32_t* radix_hist_ptr(void* workspace) { return ws_hist(workspace); }
+
 int radix_workspace_clear(void* workspace, cudaStream_t s) {
   B200GS_CUDA(cudaMemsetAsync(workspace, 0, WS_HEAD_WORDS * sizeof(uint32_t), s));
   return B200GS_OK;

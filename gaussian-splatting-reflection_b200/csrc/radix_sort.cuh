@@ -41,6 +41,9 @@ size_t radix_workspace_bytes(size_t n);
 // Zeroes histograms and tickets.  Must precede radix_histogram / radix_sort_pairs_u32.
 int radix_workspace_clear(void* workspace, cudaStream_t s);
 
+// The [RS_MAX_PASSES][256] histogram block of a workspace, for producers that count digits themselves.
+uint32_t* radix_hist_ptr(void* workspace);
+
 // Accumulates the digit histograms of all passes of `plan` over keys[0, n).
 int radix_histogram(const uint32_t* keys, int n, const RadixPlan& plan, void* workspace, cudaStream_t s, bool debug);
 
