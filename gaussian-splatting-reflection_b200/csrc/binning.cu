@@ -226,19 +226,7 @@ __global__ void __launch_bounds__(256) duplicate_kernel(int P, const uint32_t* _
 // keeps duplicate_kernel above and reproduces the reference's lists bit for bit.
 // One thread per Gaussian for rects of < COOP_ROWS tile rows; taller rects are handed to the whole
 // warp, one tile row per lane (every lane rebuilds the RowCull from the same 64-B record).
-constexpr int COOP_ROWS = 20;          // counting
-constexpr int EMIT_COOP_ROWS = 1 << 30; // emission: measured slower than one thread per Gaussian at any threshold (B200, bench scene)
-
-__device__ __forceinline__ void emit_row(const RowCull& rw, int y, int x0, int x1, int gx, uint32_t id, uint32_t off, uint32_t end,
-                                         uint32_t* __restrict__ keys, uint32_t* __restrict__ vals) {
-  int a1, b1, a2, b2, d0, d1;
-  rowcull_ranges(rw, y, x0, x1, a1, b1, a2, b2, d0, d1);
-  const uint32_t row = (uint32_t)(y * gx);
-  for (int x = a1; x <= b1 && off < end; ++x) { keys[off] = row + (uint32_t)x; vals[off] = id; ++off; }
-  for (int x = a2; x <= b2 && off < end; ++x) { keys[off] = row + (uint32_t)x; vals[off] = id; ++off; }
-  for (int x = d0; x <= d1 && off < end; ++x)
-    if (!((x >= a1 && x <= b1) || (x >= a2 && x <= b2))) { keys[off] = row + (uint32_t)x; vals[off] = id; ++off; }
-}
+constexpr int COOP_ROWS = 20;   // counting only: for the emission one thread per Gaussian measured faster at any threshold
 
 __device__ __forceinline__ uint32_t count_row(const RowCull& rw, int y, int x0, int x1) {
   int a1, b1, a2, b2, d0, d1;
@@ -294,7 +282,6 @@ __global__ void __launch_bounds__(256) emit_kept_kernel(int P, const uint32_t* _
                                                         uint32_t* __restrict__ vals, int gx, const EmitHist eh) {
   __shared__ uint32_t s_h[2][RS_RADIX];
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  const int lane = threadIdx.x & 31;
   if (eh.hist) { s_h[0][threadIdx.x] = 0u; s_h[1][threadIdx.x] = 0u; __syncthreads(); }
   auto put = [&](uint32_t o, uint32_t key, uint32_t v) {
     keys[o] = key; vals[o] = v;
@@ -305,8 +292,6 @@ __global__ void __launch_bounds__(256) emit_kept_kernel(int P, const uint32_t* _
   const bool any = end > off;
   uint2 rc = make_uint2(0u, 0u);
   if (any) { id = order[i]; rc = rects[id]; }
-  const int rows = (int)(rc.y >> 16) - (int)(rc.y & 0xffff);
-  (void)rows; (void)lane;
   if (any) {
     const int x0 = rc.x & 0xffff, x1 = rc.x >> 16, y0 = rc.y & 0xffff, y1 = rc.y >> 16;
     RowCull rw;
@@ -320,6 +305,10 @@ __global__ void __launch_bounds__(256) emit_kept_kernel(int P, const uint32_t* _
       for (int x = d0; x <= d1 && off < end; ++x)
         if (!((x >= a1 && x <= b1) || (x >= a2 && x <= b2))) { put(off, row + (uint32_t)x, id); ++off; }
     }
+    // count_kept_kernel and this loop run the same inlined fp64 code on the same inputs, so off == end
+    // here.  Should the two compilations ever disagree, no slot may stay uninitialised: repeat the
+    // Gaussian on its first tile (the `off < end` guards above cover the opposite case).
+    for (; off < end; ++off) put(off, (uint32_t)(y0 * gx + x0), id);
   }
   if (eh.hist) {
     __syncthreads();
@@ -327,32 +316,6 @@ __global__ void __launch_bounds__(256) emit_kept_kernel(int P, const uint32_t* _
     if (h0) atomicAdd(eh.hist + threadIdx.x, h0);
     if (h1) atomicAdd(eh.hist + RS_RADIX + threadIdx.x, h1);
   }
-#if 0   // warp-cooperative emission of tall rects: measured slower than one thread per Gaussian (B200, bench scene)
-  unsigned todo = __ballot_sync(0xffffffffu, coop);
-  while (todo) {
-    const int src = __ffs(todo) - 1;
-    todo &= todo - 1;
-    const uint32_t rx = __shfl_sync(0xffffffffu, rc.x, src), ry = __shfl_sync(0xffffffffu, rc.y, src);
-    const uint32_t gid = __shfl_sync(0xffffffffu, id, src);
-    uint32_t o = __shfl_sync(0xffffffffu, off, src);
-    const uint32_t e = __shfl_sync(0xffffffffu, end, src);
-    const int x0 = rx & 0xffff, x1 = rx >> 16, y0 = ry & 0xffff, y1 = ry >> 16;
-    RowCull rw;
-    rowcull_init(cull[gid], rw);
-    for (int yb = y0; yb < y1; yb += 32) {          // 32 tile rows at a time: count, scan, emit
-      const int y = yb + lane;
-      const uint32_t c = y < y1 ? count_row(rw, y, x0, x1) : 0u;
-      uint32_t inc = c;
-#pragma unroll
-      for (int d = 1; d < 32; d <<= 1) {
-        const uint32_t v = __shfl_up_sync(0xffffffffu, inc, d);
-        if (lane >= d) inc += v;
-      }
-      if (c) emit_row(rw, y, x0, x1, gx, gid, o + inc - c, e, keys, vals);
-      o += __shfl_sync(0xffffffffu, inc, 31);
-    }
-  }
-#endif
 }
 
 int surfel_count_kept(int P, const uint32_t* tiles_touched, const uint2* rects, const CullRec* cull, uint32_t* kept,
@@ -457,6 +420,9 @@ __device__ __forceinline__ bool tile_reachable(const TileForm& f) {
 __device__ __forceinline__ unsigned block_masks(const TileForm& f) {
   const float A = f.A, B = f.B, C = f.C, D = f.D, E = f.E, F = f.F, tol = f.tol;
   const float INF = __int_as_float(0x7f800000);
+  // one reciprocal per direction instead of a division per grid line (the vertex positions only
+  // select a segment and the values are compared with a tolerance 100x the fp32 error)
+  const float invA = A > 0.0f ? 1.0f / A : 0.0f, invC = C > 0.0f ? 1.0f / C : 0.0f;
   // f on the grid lines x in {0,8,16}, y in {0,4,..,16}
   float mn[4][2];
 #pragma unroll
@@ -475,8 +441,8 @@ __device__ __forceinline__ unsigned block_masks(const TileForm& f) {
     // vertex of f along the horizontal line
     float hv0 = INF, hv1 = INF;
     if (A > 0.0f) {
-      const float xs = -bx / A;
-      const float val = gy - bx * bx / A;
+      const float xs = -bx * invA;
+      const float val = gy - bx * bx * invA;
       if (xs > 0.0f && xs < 16.0f) { if (xs <= 8.0f) hv0 = val; if (xs >= 8.0f) hv1 = val; }
     }
     if (j < 4) { mn[j][0] = fminf(mn[j][0], hv0); mn[j][1] = fminf(mn[j][1], hv1); }
@@ -494,8 +460,8 @@ __device__ __forceinline__ unsigned block_masks(const TileForm& f) {
       const float x = 8.0f * i;
       const float by = B * x + E;                        // f = C y^2 + 2 by y + gx
       const float gx = (A * x + 2.0f * D) * x + F;
-      const float ys = -by / C;
-      const float val = gx - by * by / C;
+      const float ys = -by * invC;
+      const float val = gx - by * by * invC;
       if (ys > 0.0f && ys < 16.0f) {
 #pragma unroll
         for (int r = 0; r < 4; ++r)
@@ -509,7 +475,8 @@ __device__ __forceinline__ unsigned block_masks(const TileForm& f) {
   // interior critical point
   const float det = A * C - B * B;
   if (A > 0.0f && det > 0.0f) {
-    const float xs = (B * E - C * D) / det, ys = (B * D - A * E) / det;
+    const float idet = 1.0f / det;
+    const float xs = (B * E - C * D) * idet, ys = (B * D - A * E) * idet;
     if (xs > 0.0f && xs < 16.0f && ys > 0.0f && ys < 16.0f) {
       const float val = D * xs + E * ys + F;             // f at the critical point
 #pragma unroll
