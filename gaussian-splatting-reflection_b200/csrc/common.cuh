@@ -163,13 +163,14 @@ static_assert(sizeof(GaussRec) == 64, "record must be 64 B");
 struct GaussGeom {
   float* depths;            // [P]
   uint32_t* tiles_touched;  // [P]
+  uint32_t* tiles_kept;     // [P] reachable tiles (culled emission)
   uint32_t* point_offsets;  // [P] in depth order
   DepthOrder order;
   uint8_t* clamped;         // [P] bit c
   uint2* rects;             // [P]
   GaussRec* rec;            // [P]
   float* cov3D;             // [P,6] (computed from scale/rotation; unused with cov3D_precomp)
-  uint2* cull;              // [P]
+  CullRec* cull;            // [P] {alpha >= 1/255} as a point conic (an ellipse here), same record as the surfel path
   uint32_t* scan_state;
   int* flags;
   static GaussGeom carve(void* base, size_t P, size_t* bytes);
@@ -179,6 +180,7 @@ struct GaussImage {
   float* accum;         // [N] final T
   uint32_t* n_contrib;  // [N]
   uint2* ranges;        // [tiles]
+  uint2* cranges;       // [tiles] ranges into the compacted instance list
   static GaussImage carve(void* base, int W, int H, size_t* bytes);
 };
 

@@ -11,13 +11,14 @@ GaussGeom GaussGeom::carve(void* base, size_t P, size_t* bytes) {
   GaussGeom g;
   g.depths = c.take<float>(P);
   g.tiles_touched = c.take<uint32_t>(P);
+  g.tiles_kept = c.take<uint32_t>(P);
   g.point_offsets = c.take<uint32_t>(P);
   g.order = DepthOrder::carve(c, P);
   g.clamped = c.take<uint8_t>(P);
   g.rects = c.take<uint2>(P);
   g.rec = c.take<GaussRec>(P);
   g.cov3D = c.take<float>(6 * P);
-  g.cull = c.take<uint2>(P);
+  g.cull = c.take<CullRec>(P);
   g.scan_state = c.take<uint32_t>(scan_state_words((int)P));
   g.flags = c.take<int>(4);
   if (bytes) *bytes = c.used + 128;
@@ -32,6 +33,7 @@ GaussImage GaussImage::carve(void* base, int W, int H, size_t* bytes) {
   im.accum = c.take<float>(N);
   im.n_contrib = c.take<uint32_t>(N);
   im.ranges = c.take<uint2>(tiles);
+  im.cranges = c.take<uint2>(tiles);
   if (bytes) *bytes = c.used + 128;
   return im;
 }
@@ -112,7 +114,13 @@ int b200gs_gauss_forward_stage1(const b200gs_gauss_fwd* a, int* num_rendered, vo
   GaussGeom g = GaussGeom::carve(align128(a->geom), a->P, nullptr);
   rc = gauss_preprocess(*a, g, s);
   if (rc) return rc;
-  rc = depth_order_and_scan(g.depths, g.tiles_touched, a->P, g.order, g.point_offsets, g.scan_state, s, a->debug != 0);
+  const uint32_t* counts = g.tiles_touched;
+  if (g_exact_lists.load(std::memory_order_relaxed) == 0) {   // culled emission (include/b200gs.h: b200gs_set_exact_lists)
+    rc = surfel_count_kept(a->P, g.tiles_touched, g.rects, g.cull, g.tiles_kept, s, a->debug != 0);
+    if (rc) return rc;
+    counts = g.tiles_kept;
+  }
+  rc = depth_order_and_scan(g.depths, counts, a->P, g.order, g.point_offsets, g.scan_state, s, a->debug != 0);
   if (rc) return rc;
   int host[2] = {0, 0};
   B200GS_CUDA(cudaMemcpyAsync(&host[0], g.point_offsets + a->P - 1, sizeof(int), cudaMemcpyDeviceToHost, s));
@@ -133,8 +141,17 @@ int b200gs_gauss_forward_stage2(const b200gs_gauss_fwd* a, int R, void* stream) 
   GaussGeom g = GaussGeom::carve(align128(a->geom), a->P, nullptr);
   GaussImage im = GaussImage::carve(align128(a->img), a->width, a->height, nullptr);
   Binning b = Binning::carve(R > 0 ? align128(a->binning) : nullptr, R, nullptr);
-  rc = bin_and_sort(g.order.vals_a, g.rects, g.point_offsets, a->P, R, a->width, a->height, b, im.ranges, s, a->debug != 0);
+  rc = bin_and_sort(g.order.vals_a, g.rects, g.point_offsets, a->P, R, a->width, a->height, b, im.ranges, s, a->debug != 0,
+                    g_exact_lists.load(std::memory_order_relaxed) != 0 ? nullptr : g.cull);
   if (rc) return rc;
+  {
+    const size_t tiles = (size_t)((a->width + TILE_X - 1) / TILE_X) * ((a->height + TILE_Y - 1) / TILE_Y);
+    B200GS_CUDA(cudaMemsetAsync(im.cranges, 0, tiles * sizeof(uint2), s));
+  }
+  if (R > 0) {
+    rc = surfel_tile_hits(g.cull, b, R, a->width, a->height, im.ranges, im.cranges, s, a->debug != 0);
+    if (rc) return rc;
+  }
   return gauss_composite_forward(*a, g, im, b, s);
 }
 

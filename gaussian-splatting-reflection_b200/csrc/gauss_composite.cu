@@ -4,8 +4,8 @@
 // Restates FORWARD::renderCUDA (G/cuda_rasterizer/forward.cu:274-411) and BACKWARD::renderCUDA
 // (G/cuda_rasterizer/backward.cu:452-690).  Same machinery as the surfel kernels: one CTA per
 // 16x16 tile, 8x4 pixel block per warp, 256-entry batches of packed 64-B records gathered with
-// cp.async into a double-buffered ring, per-warp hit lists from conservative cull boxes, and in the
-// backward a warp reduce-scatter so each (tile, Gaussian) partial leaves as one 64-B vector of
+// cp.async into a double-buffered ring, the compacted per-tile instance lists with 8-bit warp-block
+// hit masks of tile_hits_kernel (binning.cu), and in the backward a warp reduce-scatter so each (tile, Gaussian) partial leaves as one 64-B vector of
 // RED.ADD.F32 instead of the reference's 15-16 atomicAdds per contributing pixel.
 //
 // The forward arithmetic is pinned to the reference build's contraction (SASS of renderCUDA<3>):
@@ -34,21 +34,13 @@ __device__ __forceinline__ bool gauss_eval(const float4& q0, const float4& q1, f
   return !(e.alpha < 1.0f / 255.0f);
 }
 
-__device__ __forceinline__ uint8_t warp_hits(uint2 cb, int tx0, int ty0) {
-  const int bx0 = (int)(cb.x & 0xffffu) - tx0, bx1 = (int)(cb.x >> 16) - tx0;
-  const int by0 = (int)(cb.y & 0xffffu) - ty0, by1 = (int)(cb.y >> 16) - ty0;
-  const unsigned col = ((bx0 <= 7 && bx1 >= 0) ? 0x55u : 0u) | ((bx0 <= 15 && bx1 >= 8) ? 0xAAu : 0u);
-  const unsigned row = ((by0 <= 3 && by1 >= 0) ? 0x03u : 0u) | ((by0 <= 7 && by1 >= 4) ? 0x0Cu : 0u) |
-                       ((by0 <= 11 && by1 >= 8) ? 0x30u : 0u) | ((by0 <= 15 && by1 >= 12) ? 0xC0u : 0u);
-  return (uint8_t)(col & row);
-}
-
 struct GCompFwdArgs {
   int W, H, gx;
-  const uint2* ranges;
-  const uint32_t* point_list;
+  const uint2* ranges;        // ranges into the COMPACTED instance list
+  const uint32_t* point_list; // compacted ids
+  const uint32_t* list_pos;   // position of every compacted entry in the tile's full list
   const GaussRec* rec;
-  const uint2* cull;
+  const uint8_t* hit;         // per compacted entry: warp blocks that can reach alpha >= 1/255
   const float* bg;
   float* accum;
   uint32_t* n_contrib;
@@ -60,6 +52,7 @@ struct GCompFwdArgs {
 
 __global__ void __launch_bounds__(GBATCH) gauss_composite_fwd_kernel(const GCompFwdArgs a) {
   __shared__ GaussRec s_rec[2][GBATCH];
+  __shared__ uint32_t s_pos[2][GBATCH];
   __shared__ uint8_t s_hit[2][GBATCH];
 
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
@@ -75,7 +68,6 @@ __global__ void __launch_bounds__(GBATCH) gauss_composite_fwd_kernel(const GComp
   const uint2 range = a.ranges[tile];
   const int n = (int)(range.y - range.x);
   const int rounds = (n + GBATCH - 1) / GBATCH;
-  const int tx0 = tile_x * TILE_X, ty0 = tile_y * TILE_Y;
 
   bool done = !inside;
   float T = 1.0f;
@@ -83,11 +75,14 @@ __global__ void __launch_bounds__(GBATCH) gauss_composite_fwd_kernel(const GComp
   float C0 = 0.f, C1 = 0.f, C2 = 0.f, N0 = 0.f, N1 = 0.f, N2 = 0.f, refl = 0.f, invd = 0.f;
 
   const uint32_t* pl = a.point_list + range.x;
-  uint2 cull_cur = make_uint2(0x0000ffffu, 0x0000ffffu);
+  const uint8_t* ph = a.hit + range.x;
+  const uint32_t* pp = a.list_pos + range.x;
+  unsigned hit_cur = 0u, hit_next = 0u;
+  uint32_t pos_next = 0u;
   auto stage = [&](int buf, int id) {
-    cull_cur = make_uint2(0x0000ffffu, 0x0000ffffu);
+    hit_cur = hit_next;                  // 0 for padding entries: never visited
     if (id >= 0) {
-      cull_cur = __ldg(a.cull + id);
+      s_pos[buf][t] = pos_next;
       const GaussRec* g = a.rec + id;
       GaussRec* d = &s_rec[buf][t];
 #pragma unroll
@@ -95,18 +90,21 @@ __global__ void __launch_bounds__(GBATCH) gauss_composite_fwd_kernel(const GComp
     }
     cp_async_commit();
   };
-  int id_next = (t < n) ? (int)pl[t] : -1;
+  int id_next = -1;
+  if (t < n) { id_next = (int)pl[t]; hit_next = ph[t]; pos_next = pp[t]; }
   stage(0, id_next);
-  id_next = (GBATCH + t < n) ? (int)pl[GBATCH + t] : -1;
+  id_next = -1; hit_next = 0u;
+  if (GBATCH + t < n) { id_next = (int)pl[GBATCH + t]; hit_next = ph[GBATCH + t]; pos_next = pp[GBATCH + t]; }
 
   for (int i = 0; i < rounds; ++i) {
     cp_async_wait_all();
-    s_hit[i & 1][t] = warp_hits(cull_cur, tx0, ty0);
+    s_hit[i & 1][t] = (uint8_t)hit_cur;
     if (__syncthreads_count(done) == GBATCH) break;
     if (i + 1 < rounds) {
       stage((i + 1) & 1, id_next);
       const int nx = (i + 2) * GBATCH + t;
-      id_next = (nx < n) ? (int)pl[nx] : -1;
+      id_next = -1; hit_next = 0u;
+      if (nx < n) { id_next = (int)pl[nx]; hit_next = ph[nx]; pos_next = pp[nx]; }
     }
     const int buf = i & 1;
     const GaussRec* rb = s_rec[buf];
@@ -133,7 +131,7 @@ __global__ void __launch_bounds__(GBATCH) gauss_composite_fwd_kernel(const GComp
         refl = __fmaf_rn(T, __fmul_rn(e.alpha, q1.w), refl);
         invd = __fmaf_rn(T, __fmul_rn(e.alpha, q1.z), invd);
         T = test_T;
-        last_contributor = (uint32_t)(i * GBATCH + j + 1);
+        last_contributor = s_pos[buf][j] + 1u;   // 1-based position in the tile's (full) list
       }
     }
   }
@@ -159,7 +157,7 @@ int gauss_composite_forward(const b200gs_gauss_fwd& f, const GaussGeom& g, const
   a.W = f.width; a.H = f.height;
   a.gx = (f.width + TILE_X - 1) / TILE_X;
   const int gy = (f.height + TILE_Y - 1) / TILE_Y;
-  a.ranges = im.ranges; a.point_list = b.point_list; a.rec = g.rec; a.cull = g.cull; a.bg = f.background;
+  a.ranges = im.cranges; a.point_list = b.comp_id; a.list_pos = b.comp_pos; a.rec = g.rec; a.hit = b.comp_hit; a.bg = f.background;
   a.accum = im.accum; a.n_contrib = im.n_contrib;
   a.out_color = f.out_color; a.out_normal = f.out_normal; a.out_refl = f.out_refl; a.out_invdepth = f.out_invdepth;
   StageScope _t(ST_COMPOSITE_FWD, s);
@@ -171,10 +169,11 @@ int gauss_composite_forward(const b200gs_gauss_fwd& f, const GaussGeom& g, const
 // ------------------------------------------------------------------ backward
 struct GCompBwdArgs {
   int W, H, gx;
-  const uint2* ranges;
+  const uint2* ranges;        // compacted lists, as in the forward
   const uint32_t* point_list;
+  const uint32_t* list_pos;
   const GaussRec* rec;
-  const uint2* cull;
+  const uint8_t* hit;
   const float* bg;
   const float* accum;
   const uint32_t* n_contrib;
@@ -188,7 +187,10 @@ struct GCompBwdArgs {
 __global__ void __launch_bounds__(GBATCH, 2) gauss_composite_bwd_kernel(const GCompBwdArgs a) {
   __shared__ GaussRec s_rec[2][GBATCH];
   __shared__ int s_id[2][GBATCH];
+  __shared__ uint32_t s_pos[2][GBATCH];
   __shared__ uint8_t s_hit[2][GBATCH];
+  __shared__ uint32_t s_last[GBATCH / 32];
+  __shared__ int s_n;                   // live prefix of the tile's compacted list
 
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const int tile = blockIdx.x;
@@ -201,10 +203,7 @@ __global__ void __launch_bounds__(GBATCH, 2) gauss_composite_bwd_kernel(const GC
   const size_t N = (size_t)a.W * a.H;
   const size_t pix_id = (size_t)a.W * pyi + pxi;
   const uint2 range = a.ranges[tile];
-  const int n = (int)(range.y - range.x);
-  const int rounds = (n + GBATCH - 1) / GBATCH;
-  if (n == 0) return;
-  const int tx0 = tile_x * TILE_X, ty0 = tile_y * TILE_Y;
+  if (range.y == range.x) return;
 
   // lane -> accumulator component owned after the reduce-scatter (16 values, 32 lanes)
   const int b16 = (lane >> 4) & 1, b8 = (lane >> 3) & 1, b4 = (lane >> 2) & 1, b2 = (lane >> 1) & 1;
@@ -226,17 +225,43 @@ __global__ void __launch_bounds__(GBATCH, 2) gauss_composite_bwd_kernel(const GC
   bg_dot_dpixel += a.bg[1] * dpix1;
   bg_dot_dpixel += a.bg[2] * dpix2;
   const float ddelx_dx = 0.5f * a.W, ddely_dy = 0.5f * a.H;
+  // the running-sum quirk (backward.cu:614): the mean2D gradient uses 3 t0 + 2 t1 + t2 of the colour terms
+  const float mpix0 = 3.0f * dpix0, mpix1 = 2.0f * dpix1;
 
-  float acc_c0 = 0.f, acc_c1 = 0.f, acc_c2 = 0.f, last_c0 = 0.f, last_c1 = 0.f, last_c2 = 0.f;
-  float acc_n0 = 0.f, acc_n1 = 0.f, acc_n2 = 0.f, last_n0 = 0.f, last_n1 = 0.f, last_n2 = 0.f;
-  float acc_r = 0.f, last_r = 0.f, acc_i = 0.f, last_i = 0.f, last_alpha = 0.f;
+  float acc_q = 0.f, last_q = 0.f, acc_m = 0.f, last_m = 0.f, last_alpha = 0.f;
 
   const uint32_t* pl = a.point_list + range.x;
-  uint2 cull_cur = make_uint2(0x0000ffffu, 0x0000ffffu);
+  const uint8_t* ph = a.hit + range.x;
+  const uint32_t* pp = a.list_pos + range.x;
+
+  // Entries at or behind the last contributor of every pixel of the tile are never used
+  // (backward.cu:560: `contributor >= last_contributor` -> continue): list positions ascend, so
+  // the live part is a prefix of the compacted list; find its length by bisection.
+  const uint32_t warp_last = __reduce_max_sync(0xffffffffu, inside ? last_contributor : 0u);
+  if (lane == 0) s_last[warp] = warp_last;
+  __syncthreads();
+  if (t == 0) {
+    uint32_t tile_last = 0;
+#pragma unroll
+    for (int w = 0; w < GBATCH / 32; ++w) tile_last = max(tile_last, s_last[w]);
+    int lo = 0, hi = (int)(range.y - range.x);     // first index with pos >= tile_last
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if (pp[mid] < tile_last) lo = mid + 1; else hi = mid;
+    }
+    s_n = lo;
+  }
+  __syncthreads();
+  const int n = s_n;
+  const int rounds = (n + GBATCH - 1) / GBATCH;
+  if (n == 0) return;
+
+  unsigned hit_cur = 0u, hit_next = 0u;
+  uint32_t pos_next = 0u;
   auto stage = [&](int buf, int id) {
-    cull_cur = make_uint2(0x0000ffffu, 0x0000ffffu);
+    hit_cur = hit_next;
     if (id >= 0) {
-      cull_cur = __ldg(a.cull + id);
+      s_pos[buf][t] = pos_next;
       const GaussRec* g = a.rec + id;
       GaussRec* d = &s_rec[buf][t];
 #pragma unroll
@@ -245,36 +270,34 @@ __global__ void __launch_bounds__(GBATCH, 2) gauss_composite_bwd_kernel(const GC
     }
     cp_async_commit();
   };
-  int id_next = (t < n) ? (int)pl[n - 1 - t] : -1;
+  int id_next = -1;
+  if (t < n) { id_next = (int)pl[n - 1 - t]; hit_next = ph[n - 1 - t]; pos_next = pp[n - 1 - t]; }
   stage(0, id_next);
-  id_next = (GBATCH + t < n) ? (int)pl[n - 1 - (GBATCH + t)] : -1;
-  const uint32_t warp_last = __reduce_max_sync(0xffffffffu, inside ? last_contributor : 0u);
+  id_next = -1; hit_next = 0u;
+  if (GBATCH + t < n) { const int q = n - 1 - (GBATCH + t); id_next = (int)pl[q]; hit_next = ph[q]; pos_next = pp[q]; }
 
   for (int i = 0; i < rounds; ++i) {
     cp_async_wait_all();
-    s_hit[i & 1][t] = warp_hits(cull_cur, tx0, ty0);
+    s_hit[i & 1][t] = (uint8_t)hit_cur;
     __syncthreads();
     if (i + 1 < rounds) {
       stage((i + 1) & 1, id_next);
       const int nx = (i + 2) * GBATCH + t;
-      id_next = (nx < n) ? (int)pl[n - 1 - nx] : -1;
+      id_next = -1; hit_next = 0u;
+      if (nx < n) { const int q = n - 1 - nx; id_next = (int)pl[q]; hit_next = ph[q]; pos_next = pp[q]; }
     }
     const int buf = i & 1;
     const int count = min(GBATCH, n - i * GBATCH);
     const GaussRec* rb = s_rec[buf];
-    int j0 = 0;
-    {
-      const int first_pos = n - i * GBATCH;
-      if ((uint32_t)first_pos > warp_last) j0 = min(count, first_pos - (int)warp_last);
-    }
 #pragma unroll 1
-    for (int r = j0 >> 5; r < (count + 31) >> 5; ++r) {
-      unsigned m = __ballot_sync(0xffffffffu, (s_hit[buf][r * 32 + lane] >> warp) & 1u);
-      if (r == (j0 >> 5)) m &= 0xffffffffu << (j0 & 31);
+    for (int r = 0; r < (count + 31) >> 5; ++r) {
+      // entries of other warp blocks, and entries behind every pixel's last contributor, are skipped
+      const int en = r * 32 + lane;
+      unsigned m = __ballot_sync(0xffffffffu, en < count && ((s_hit[buf][en] >> warp) & 1u) && s_pos[buf][en] < warp_last);
       while (m) {
         const int j = r * 32 + __ffs(m) - 1;
         m &= m - 1;
-        const uint32_t contributor = (uint32_t)(n - 1 - (i * GBATCH + j));
+        const uint32_t contributor = s_pos[buf][j];   // 0-based position in the tile's full list
         const float4 q0 = rb[j].q[0], q1 = rb[j].q[1];
         GaussEval e;
         bool c = inside && contributor < last_contributor;
@@ -287,27 +310,26 @@ __global__ void __launch_bounds__(GBATCH, 2) gauss_composite_bwd_kernel(const GC
         if (c) {
           const float4 q2 = rb[j].q[2], q3 = rb[j].q[3];
           const float alpha = e.alpha, G = e.G;
-          T = T / (1.f - alpha);
+          const float inv_1ma = __frcp_rn(__fsub_rn(1.0f, alpha));
+          T = T * inv_1ma;
           const float w = alpha * T;                      // dchannel_dcolor
           const float om = 1.f - last_alpha;
-          float dL_dalpha = 0.0f, dL_dalpha_m = 0.0f;     // backward.cu:596-620 (incl. the running-sum quirk :614)
-          acc_c0 = last_alpha * last_c0 + om * acc_c0; last_c0 = q2.x; dL_dalpha += (q2.x - acc_c0) * dpix0; dL_dalpha_m += dL_dalpha; g[8] = w * dpix0;
-          acc_c1 = last_alpha * last_c1 + om * acc_c1; last_c1 = q2.y; dL_dalpha += (q2.y - acc_c1) * dpix1; dL_dalpha_m += dL_dalpha; g[9] = w * dpix1;
-          acc_c2 = last_alpha * last_c2 + om * acc_c2; last_c2 = q2.z; dL_dalpha += (q2.z - acc_c2) * dpix2; dL_dalpha_m += dL_dalpha; g[10] = w * dpix2;
-          acc_n0 = last_alpha * last_n0 + om * acc_n0; last_n0 = q3.x; dL_dalpha += (q3.x - acc_n0) * dn0; g[11] = w * dn0;
-          acc_n1 = last_alpha * last_n1 + om * acc_n1; last_n1 = q3.y; dL_dalpha += (q3.y - acc_n1) * dn1; g[12] = w * dn1;
-          acc_n2 = last_alpha * last_n2 + om * acc_n2; last_n2 = q3.z; dL_dalpha += (q3.z - acc_n2) * dn2; g[13] = w * dn2;
-          acc_r = last_alpha * last_r + om * acc_r; last_r = q1.w; dL_dalpha += (q1.w - acc_r) * drefl; g[14] = w * drefl;
-          if (a.dL_dinvd) {                                // :643-650
-            const float invd = q1.z;
-            acc_i = last_alpha * last_i + om * acc_i; last_i = invd; dL_dalpha += (invd - acc_i) * dinv; g[15] = w * dinv;
-          }
-          dL_dalpha *= T;
-          dL_dalpha_m *= T;
+          // backward.cu:596-650: every channel enters dL_dalpha as (value - value accumulated behind) *
+          // upstream gradient.  The recurrence is linear, so the eight per-channel recurrences collapse
+          // into one on q = sum_ch value_ch * upstream_ch, plus one on the colour-only weighted sum the
+          // mean2D running-sum quirk (:614) needs.
+          const float cm = q2.x * mpix0 + q2.y * mpix1 + q2.z * dpix2;
+          const float qv = q2.x * dpix0 + q2.y * dpix1 + q2.z * dpix2 + q3.x * dn0 + q3.y * dn1 + q3.z * dn2 +
+                           q1.w * drefl + q1.z * dinv;
+          acc_q = last_alpha * last_q + om * acc_q; last_q = qv;
+          acc_m = last_alpha * last_m + om * acc_m; last_m = cm;
           last_alpha = alpha;
-          const float bgterm = (-T_final / (1.f - alpha)) * bg_dot_dpixel;
-          dL_dalpha += bgterm;
-          dL_dalpha_m += bgterm;
+          g[8] = w * dpix0; g[9] = w * dpix1; g[10] = w * dpix2;
+          g[11] = w * dn0; g[12] = w * dn1; g[13] = w * dn2;
+          g[14] = w * drefl; g[15] = w * dinv;
+          const float bgterm = (-T_final * inv_1ma) * bg_dot_dpixel;
+          const float dL_dalpha = (qv - acc_q) * T + bgterm;
+          const float dL_dalpha_m = (cm - acc_m) * T + bgterm;
           const float opa = q1.y;
           const float dL_dG = opa * dL_dalpha, dL_dG_m = opa * dL_dalpha_m;
           const float gdx = G * e.dx, gdy = G * e.dy;
@@ -341,7 +363,7 @@ int gauss_composite_backward(const b200gs_gauss_bwd& f, const GaussGeom& g, cons
   a.W = f.width; a.H = f.height;
   a.gx = (f.width + TILE_X - 1) / TILE_X;
   const int gy = (f.height + TILE_Y - 1) / TILE_Y;
-  a.ranges = im.ranges; a.point_list = b.point_list; a.rec = g.rec; a.cull = g.cull; a.bg = f.background;
+  a.ranges = im.cranges; a.point_list = b.comp_id; a.list_pos = b.comp_pos; a.rec = g.rec; a.hit = b.comp_hit; a.bg = f.background;
   a.accum = im.accum; a.n_contrib = im.n_contrib;
   a.dL_dpix = f.dL_dout_color; a.dL_dnormal = f.dL_dout_normal; a.dL_drefl = f.dL_dout_refl; a.dL_dinvd = f.dL_dout_invdepth;
   a.acc = acc;

@@ -39,7 +39,7 @@ struct GaussPreArgs {
   uint2* rects;
   GaussRec* rec;
   float* cov3D;
-  uint2* cull;
+  CullRec* cull;
   int* flags;
 };
 
@@ -81,22 +81,30 @@ __device__ __forceinline__ float3 cov2d(float3 mean, float focal_x, float focal_
 
 __device__ __forceinline__ float ndc2pix(float v, int S) { return (float)((((double)v + 1.0) * (double)S - 1.0) * 0.5); }
 
-// Conservative pixel box of {alpha >= 1/255} = {d^T conic d <= 2 ln(255 opa)}: half extents
-// sqrt(c2 * cov_xx), sqrt(c2 * cov_yy) of the (low-pass filtered) 2D covariance.
-__device__ __forceinline__ uint2 gauss_cull_bbox(float cx, float cy, float cov_xx, float cov_yy, float opa) {
-  const uint2 everything = make_uint2(0xffff0000u, 0xffff0000u);
-  const uint2 nothing = make_uint2(0x0000ffffu, 0x0000ffffu);  // min 65535 > max 0: misses every block, also at tile 0
-  if (!(opa >= 0.0f)) return everything;
-  if (opa < 0.0039f) return nothing;
-  const float c2 = 2.0f * logf(255.0f * opa) * 1.001f + 0.01f;
-  const float hx = sqrtf(c2 * cov_xx), hy = sqrtf(c2 * cov_yy);
-  if (!(hx == hx) || !(hy == hy) || !(hx < 1e7f) || !(hy < 1e7f) || !(fabsf(cx) < 1e7f) || !(fabsf(cy) < 1e7f)) return everything;
-  const float mx = 1.0f + 1e-4f * (fabsf(cx) + hx), my = 1.0f + 1e-4f * (fabsf(cy) + hy);
-  const float x0 = cx - hx - mx, x1 = cx + hx + mx, y0 = cy - hy - my, y1 = cy + hy + my;
-  if (x1 < 0.0f || y1 < 0.0f || x0 > 65535.0f || y0 > 65535.0f) return nothing;
-  const unsigned ix0 = (unsigned)fmaxf(floorf(x0), 0.0f), ix1 = (unsigned)fminf(ceilf(x1), 65535.0f);
-  const unsigned iy0 = (unsigned)fmaxf(floorf(y0), 0.0f), iy1 = (unsigned)fminf(ceilf(y1), 65535.0f);
-  return make_uint2(ix0 | (ix1 << 16), iy0 | (iy1 << 16));
+// {alpha >= 1/255} = {d^T conic d <= c2 = 2 ln(255 opa)}, d = centre - pixel (forward.cu:355-366), as
+// the same fp64 point-conic record the surfel path uses (common.cuh CullRec): always an ellipse
+// here, no low-pass disk.  c2 is inflated by 0.2 % + 0.02, far beyond the fp32 error of the kernels'
+// own power / expf.  Consumed by count_kept / emit_kept / tile_hits (binning.cu).
+__device__ __forceinline__ CullRec gauss_cull_record(float cx, float cy, float3 conic, float opa) {
+  CullRec r;
+  r.A = r.B = r.C = r.D = r.E = r.F = 0.0;
+  r.cx = cx; r.cy = cy; r.r2 = -1.0f; r.flag = CULL_EVERYTHING;
+  if (!(opa >= 0.0f)) return r;
+  if (opa < 0.0039f) { r.flag = CULL_NOTHING; return r; }
+  const double c2 = 2.0 * (double)logf(255.0f * opa) * 1.002 + 0.02;
+  double A = conic.x, B = conic.y, C = conic.z;
+  const double x = cx, y = cy;
+  double D = -(A * x + B * y), E = -(B * x + C * y);
+  double F = (A * x + 2.0 * B * y) * x + C * y * y - c2;
+  const double m = fmax(fmax(fabs(A), fabs(C)), fabs(B));
+  if (!(m > 0.0) || !(m < 1e300)) return r;
+  const double im = 1.0 / m;
+  A *= im; B *= im; C *= im; D *= im; E *= im; F *= im;
+  if (!(fabs(A) <= 1.0) || !(fabs(B) <= 1.0) || !(fabs(C) <= 1.0)) return r;
+  if (!(fabs(D) < 1e30) || !(fabs(E) < 1e30) || !(fabs(F) < 1e30)) return r;
+  r.A = A; r.B = B; r.C = C; r.D = D; r.E = E; r.F = F;
+  r.flag = 0.0f;
+  return r;
 }
 
 __global__ void __launch_bounds__(256) gauss_preprocess_kernel(const GaussPreArgs a) {
@@ -168,7 +176,7 @@ __global__ void __launch_bounds__(256) gauss_preprocess_kernel(const GaussPreArg
   a.radii[idx] = ri;
   a.rects[idx] = make_uint2((uint32_t)x0 | ((uint32_t)x1 << 16), (uint32_t)y0 | ((uint32_t)y1 << 16));
   const float opa = a.opacities[idx] * h_convolution_scaling;
-  a.cull[idx] = gauss_cull_bbox(cx, cy, cov.x, cov.z, opa);
+  a.cull[idx] = gauss_cull_record(cx, cy, conic, opa);
   GaussRec* r = a.rec + idx;
   r->q[0] = make_float4(cx, cy, conic.x, conic.y);
   r->q[1] = make_float4(conic.z, opa, 1.0f / vz, a.refl ? a.refl[idx] : 0.0f);

@@ -125,17 +125,24 @@ def gauss_config(name):
             f = hz.gauss_forward(Cmod, sc, cam)
             return f, hz.gauss_backward(Cmod, sc, cam, f, grads)
         return step
+    import b200gs
+    b200gs.set_exact_lists(1)
+    f_ex, _ = make(newC)()
+    out["R"], out["V"] = int(f_ex["rendered"]), int((f_ex["radii"] > 0).sum())
+    out["new_exact_ms"] = timed(make(newC))
+    b200gs.set_exact_lists(0)
     f_n, b_n = make(newC)()
-    out["R"], out["V"] = int(f_n["rendered"]), int((f_n["radii"] > 0).sum())
+    out["R_emitted"] = int(f_n["rendered"])
     out["new_ms"] = timed(make(newC))
     if refC is not None:
         f_r, b_r = make(refC)()
         out["ref_ms"] = timed(make(refC), warmup=3, iters=10)
         out["speedup"] = out["ref_ms"] / out["new_ms"]
         out["parity"] = {
-            "rendered_equal": out["R"] == int(f_r["rendered"]),
+            "rendered_equal_exact_mode": out["R"] == int(f_r["rendered"]),
             "radii_equal": bool(torch.equal(f_n["radii"], f_r["radii"])),
             "image_max_abs": max(hz.max_abs(f_n[k], f_r[k]) for k in ("color", "invdepth", "normal_map", "refl_map")),
+            "image_bit_identical": all(bool(torch.equal(f_n[k], f_r[k])) for k in ("color", "invdepth", "normal_map", "refl_map")),
             "grad_max_rel_l2": max(hz.rel_l2(b_n[k], b_r[k]) for k in b_n),
         }
     out["mpix_per_s"] = W * H / (out["new_ms"] * 1e-3) / 1e6
