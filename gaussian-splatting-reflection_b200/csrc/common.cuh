@@ -46,7 +46,8 @@ extern std::atomic<unsigned long long> g_launches;
 // bench.py can attribute the step time to kernels without a profiler attached.
 enum Stage {
   ST_PREPROCESS = 0, ST_SCAN, ST_DUPLICATE, ST_SORT, ST_RANGES, ST_COMPOSITE_FWD,
-  ST_COMPOSITE_BWD, ST_PREPROCESS_BWD, ST_CUBEMAP_FWD, ST_CUBEMAP_BWD, ST_TILE_HITS, ST_DEPTH_SORT, ST_COUNT_KEPT, ST_COUNT
+  ST_COMPOSITE_BWD, ST_PREPROCESS_BWD, ST_CUBEMAP_FWD, ST_CUBEMAP_BWD, ST_TILE_HITS, ST_DEPTH_SORT, ST_COUNT_KEPT,
+  ST_ADAM, ST_DENSIFY_STATS, ST_COUNT
 };
 extern std::atomic<int> g_timing;
 extern std::atomic<int> g_cull_audit;   // surfel_composite_fwd.cu: b200gs_debug_cull_audit

@@ -167,6 +167,25 @@ cubemap_forward = _sig("b200gs_cubemap_forward", _i, _p, _p, _p, _p, _u, _u, _u,
 cubemap_backward = _sig("b200gs_cubemap_backward", _i, _p, _p, _p, _p, _p, _p, _u, _u, _u, _u, _u, _p)
 
 
+ADAM_MAX_GROUPS = 8
+
+
+class AdamGroup(C.Structure):
+    """struct b200gs_adam_group"""
+    _fields_ = [("param", _p), ("grad", _p), ("exp_avg", _p), ("exp_avg_sq", _p), ("n", C.c_longlong),
+                ("param_row", _i), ("grad_row", _i), ("grad_col", _i), ("lr", C.c_double)]
+
+
+class Adam(C.Structure):
+    """struct b200gs_adam"""
+    _fields_ = [("groups", _i), ("group", AdamGroup * ADAM_MAX_GROUPS), ("beta1", C.c_double), ("beta2", C.c_double),
+                ("eps", C.c_double), ("step", C.c_longlong)]
+
+
+adam_step = _sig("b200gs_adam_step", _i, C.POINTER(Adam), _p)
+densify_stats = _sig("b200gs_densify_stats", _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p)
+
+
 def check(rc):
     """Map a C return code to an exception (the reference throws std::runtime_error
     -> Python RuntimeError; S/rasterize_points.cu:63-65, auxiliary.h:300-307)."""

@@ -288,6 +288,45 @@ int b200gs_cubemap_backward(const float* grad_outputs, const float* inputs, cons
                             float* grad_inputs, float* grad_fail, uint32_t interp, uint32_t seamless, uint32_t B,
                             uint32_t C, uint32_t L, void* stream);
 
+/* ------------------------------------------------------------------------ */
+/* Per-Gaussian gradient consumer ("next" row 1): the step right after the
+ * rendering path's backward.
+ *
+ * b200gs_adam_step replaces gaussians.optimizer.step() (train.py:306) for the groups
+ * torch.optim.Adam(l, lr=0.0, eps=1e-15) is built over in scene/gaussian_model.py:196-207
+ * (xyz, f_dc, f_rest, opacity, scaling, rotation, refl; the env-map group fits the same struct).
+ * All groups are updated in ONE launch.  A group's gradient may be a column slice of a wider
+ * row-major tensor (grad_row / grad_col): f_dc and f_rest both read the [P, M, 3] dL_dsh block
+ * the backward writes, as columns [0,3) and [3,3M).  `step` is the 1-based step count shared by all
+ * groups (torch keeps one per parameter; the reference steps them together).  fp32 state.  */
+#define B200GS_ADAM_MAX_GROUPS 8
+typedef struct {
+  float* param;           /* [n] updated in place */
+  const float* grad;      /* see grad_row / grad_col */
+  float* exp_avg;         /* [n] */
+  float* exp_avg_sq;      /* [n] */
+  long long n;            /* floats in param (0: group skipped) */
+  int param_row;          /* floats per row of param (0 or 1: flat) */
+  int grad_row;           /* row stride of grad in floats (0: same as param_row) */
+  int grad_col;           /* first column of this group inside a grad row */
+  double lr;
+} b200gs_adam_group;
+typedef struct {
+  int groups;
+  b200gs_adam_group group[B200GS_ADAM_MAX_GROUPS];
+  double beta1, beta2, eps;
+  long long step;         /* >= 1 */
+} b200gs_adam;
+int b200gs_adam_step(const b200gs_adam* a, void* stream);
+
+/* Densification statistics of one rendered view (train.py:242-243, scene/gaussian_model.py:579-584):
+ *   where radii > 0:  max_radii2D = max(max_radii2D, radii); xyz_gradient_accum += |dL_dmeans2D|_2; denom += 1
+ *   where w > 0:      accum_w += w; denom_w += 1       (skipped when gaussian_weights is NULL)
+ * radii [P] int32, dL_dmeans2D [P,3], the accumulators [P] fp32 (the reference's are [P,1]).  */
+int b200gs_densify_stats(int P, const int* radii, const float* dL_dmeans2D, const float* gaussian_weights,
+                         float* max_radii2D, float* xyz_gradient_accum, float* denom, float* accum_w, float* denom_w,
+                         void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -76,3 +76,40 @@ def test_two_rank_allreduce_matches_single_process(tmp_path):
             dst += torch.from_numpy(gr[k]).reshape(dst.shape)
     assert np.allclose(r0, ref.flat.numpy(), rtol=1e-5, atol=1e-6)
     assert np.abs(r0).sum() > 0
+
+
+def _stats_worker(rank, world, port, P, out_dir):
+    from b200gs.update import all_reduce_stats
+    from oracle import update_oracle as uo
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    st = _local_stats(uo, shard_views(6, rank, world), P)
+    flat = torch.from_numpy(np.stack([st[k] for k in ("xyz_gradient_accum", "denom", "accum_w", "denom_w", "max_radii2D")]))
+    all_reduce_stats(flat)
+    np.save(os.path.join(out_dir, f"stats{rank}.npy"), flat.numpy())
+    dist.destroy_process_group()
+
+
+def _local_stats(uo, views, P):
+    st = {k: np.zeros(P, np.float32) for k in ("xyz_gradient_accum", "denom", "accum_w", "denom_w", "max_radii2D")}
+    for v in views:
+        rng = np.random.default_rng(900 + v)
+        radii = (rng.integers(0, 50, P) * (rng.random(P) > 0.4)).astype(np.int32)
+        uo.densify_stats(st, rng.standard_normal((P, 3)).astype(np.float32), radii,
+                         (rng.random(P) * (rng.random(P) > 0.5)).astype(np.float32))
+    return st
+
+
+@pytest.mark.timeout(600)
+def test_two_rank_densify_stats_allreduce(tmp_path):
+    """rows 0-3 of the [5, P] statistics buffer are summed over ranks, row 4 (max_radii2D) maximised:
+    the result equals one process that saw every view."""
+    from oracle import update_oracle as uo
+    P, world = 500, 2
+    mp.spawn(_stats_worker, args=(world, _free_port(), P, str(tmp_path)), nprocs=world, join=True)
+    r0, r1 = np.load(tmp_path / "stats0.npy"), np.load(tmp_path / "stats1.npy")
+    assert np.array_equal(r0, r1)
+    one = _local_stats(uo, range(6), P)
+    assert np.array_equal(r0[1], one["denom"]) and np.array_equal(r0[3], one["denom_w"])
+    assert np.array_equal(r0[4], one["max_radii2D"])
+    assert np.allclose(r0[0], one["xyz_gradient_accum"], rtol=1e-6) and np.allclose(r0[2], one["accum_w"], rtol=1e-6)
