@@ -35,12 +35,27 @@ struct AdamGroupDev {
   long long chunk0;        // first CTA of this group
   int p_row, g_row, g_col; // parameter row length, gradient row stride and first column
   float step_size;         // lr / (1 - beta1^t)
+  int vec;                 // p, m, v are 16-B aligned: 128-bit accesses
+  int gvec;                // ... and so is the (unstrided) gradient
+  unsigned magic;          // ceil(2^32 / p_row): q / p_row == umulhi(q, magic) for q * p_row < 2^32
 };
 struct AdamArgs {
   AdamGroupDev grp[UPD_MAX_GROUPS];
   int groups;
   float one_minus_beta1, beta2, one_minus_beta2, bc2_sqrt, eps;
 };
+
+// Exact zeros (Gaussians no view has reached yet: g = m = v = 0) are stepped around the IEEE division
+// and square root, whose slow paths they would otherwise take; the results are the same bits
+// (sqrt(0) / c + eps == eps, and p - s * (+-0 / d) == p).
+__device__ __forceinline__ void adam_update(const AdamArgs& a, float step_size, float g, float& p, float& m, float& v) {
+  m = __fmaf_rn(a.one_minus_beta1, __fsub_rn(g, m), m);                              // lerp_(grad, 1 - beta1)
+  v = __fmaf_rn(__fmul_rn(g, g), a.one_minus_beta2, __fmul_rn(v, a.beta2));          // mul_(beta2).addcmul_(g, g, 1 - beta2)
+  if (m == 0.0f && (v > 0.0f || a.eps > 0.0f)) return;
+  float denom = a.eps;
+  if (v != 0.0f) denom = __fadd_rn(__fdiv_rn(__fsqrt_rn(v), a.bc2_sqrt), a.eps);
+  p = __fmaf_rn(-step_size, __fdiv_rn(m, denom), p);                                 // addcdiv_(m, denom, -step_size)
+}
 
 __global__ void __launch_bounds__(UPD_THREADS) adam_kernel(const __grid_constant__ AdamArgs a) {
   // which group does this CTA belong to (<= 8 entries)
@@ -51,29 +66,57 @@ __global__ void __launch_bounds__(UPD_THREADS) adam_kernel(const __grid_constant
   const AdamGroupDev& G = a.grp[gi];
   const long long base = ((long long)blockIdx.x - G.chunk0) * UPD_CHUNK;
   const bool strided = (G.g_row != G.p_row) || (G.g_col != 0);
+  // gradient index of parameter float base + o, o < UPD_CHUNK: one 64-bit division per thread, 32-bit ones per element
+  const long long row0 = strided ? base / G.p_row : 0;
+  const unsigned rem0 = strided ? (unsigned)(base - row0 * G.p_row) : 0u;
+  const float* gbase = strided ? G.g + row0 * G.g_row + G.g_col : G.g + base;
+  auto gidx = [&](unsigned o) -> unsigned {
+    if (!strided) return o;
+    const unsigned q = rem0 + o, r = __umulhi(q, G.magic);
+    return r * (unsigned)G.g_row + (q - r * (unsigned)G.p_row);
+  };
+
+  if (G.vec && base + UPD_CHUNK <= G.n) {              // full chunk, 128-bit accesses
+    constexpr int V = UPD_ITEMS / 4;
+    float4 pv[V], mv[V], vv[V], gv[V];
+#pragma unroll
+    for (int k = 0; k < V; ++k) {                      // all loads first
+      const unsigned o = (k * UPD_THREADS + threadIdx.x) * 4u;
+      pv[k] = *reinterpret_cast<const float4*>(G.p + base + o);
+      mv[k] = *reinterpret_cast<const float4*>(G.m + base + o);
+      vv[k] = *reinterpret_cast<const float4*>(G.v + base + o);
+      if (G.gvec) gv[k] = __ldcs(reinterpret_cast<const float4*>(gbase + o));   // gradients are read once
+      else gv[k] = make_float4(__ldcs(gbase + gidx(o)), __ldcs(gbase + gidx(o + 1)), __ldcs(gbase + gidx(o + 2)), __ldcs(gbase + gidx(o + 3)));
+    }
+#pragma unroll
+    for (int k = 0; k < V; ++k) {
+      const unsigned o = (k * UPD_THREADS + threadIdx.x) * 4u;
+      adam_update(a, G.step_size, gv[k].x, pv[k].x, mv[k].x, vv[k].x);
+      adam_update(a, G.step_size, gv[k].y, pv[k].y, mv[k].y, vv[k].y);
+      adam_update(a, G.step_size, gv[k].z, pv[k].z, mv[k].z, vv[k].z);
+      adam_update(a, G.step_size, gv[k].w, pv[k].w, mv[k].w, vv[k].w);
+      *reinterpret_cast<float4*>(G.p + base + o) = pv[k];
+      *reinterpret_cast<float4*>(G.m + base + o) = mv[k];
+      *reinterpret_cast<float4*>(G.v + base + o) = vv[k];
+    }
+    return;
+  }
 
   float pv[UPD_ITEMS], gv[UPD_ITEMS], mv[UPD_ITEMS], vv[UPD_ITEMS];
 #pragma unroll
-  for (int k = 0; k < UPD_ITEMS; ++k) {                // all loads first: 32 independent requests per thread
-    const long long i = base + k * UPD_THREADS + threadIdx.x;
-    if (i < G.n) {
-      long long gidx = i;
-      if (strided) { const long long r = i / G.p_row; gidx = r * G.g_row + G.g_col + (i - r * G.p_row); }
-      pv[k] = G.p[i]; mv[k] = G.m[i]; vv[k] = G.v[i];
-      gv[k] = __ldcs(G.g + gidx);                      // gradients are read once
+  for (int k = 0; k < UPD_ITEMS; ++k) {                // tail chunk / unaligned tensors: 32-bit accesses
+    const unsigned o = k * UPD_THREADS + threadIdx.x;
+    if (base + o < G.n) {
+      pv[k] = G.p[base + o]; mv[k] = G.m[base + o]; vv[k] = G.v[base + o];
+      gv[k] = __ldcs(gbase + gidx(o));
     }
   }
 #pragma unroll
   for (int k = 0; k < UPD_ITEMS; ++k) {
-    const long long i = base + k * UPD_THREADS + threadIdx.x;
-    if (i < G.n) {
-      const float g = gv[k];
-      const float m = __fmaf_rn(a.one_minus_beta1, __fsub_rn(g, mv[k]), mv[k]);       // lerp_(grad, 1 - beta1)
-      const float v = __fmaf_rn(__fmul_rn(g, g), a.one_minus_beta2, __fmul_rn(vv[k], a.beta2));  // mul_(beta2).addcmul_
-      const float denom = __fadd_rn(__fdiv_rn(__fsqrt_rn(v), a.bc2_sqrt), a.eps);
-      G.p[i] = __fmaf_rn(-G.step_size, __fdiv_rn(m, denom), pv[k]);                   // addcdiv_(m, denom, -step_size)
-      G.m[i] = m;
-      G.v[i] = v;
+    const unsigned o = k * UPD_THREADS + threadIdx.x;
+    if (base + o < G.n) {
+      adam_update(a, G.step_size, gv[k], pv[k], mv[k], vv[k]);
+      G.p[base + o] = pv[k]; G.m[base + o] = mv[k]; G.v[base + o] = vv[k];
     }
   }
 }
@@ -126,6 +169,13 @@ int b200gs_adam_step(const b200gs_adam* a, void* stream) {
     d.n = g.n; d.chunk0 = chunks;
     d.p_row = p_row; d.g_row = g_row; d.g_col = g.grad_col;
     d.step_size = (float)(g.lr / bc1);
+    auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15u) == 0; };
+    d.vec = (al16(g.param) && al16(g.exp_avg) && al16(g.exp_avg_sq)) ? 1 : 0;
+    d.gvec = (d.vec && g_row == p_row && g.grad_col == 0 && al16(g.grad)) ? 1 : 0;
+    d.magic = (unsigned)((0x100000000ull + (unsigned)p_row - 1u) / (unsigned)p_row);
+    if (p_row == 1) d.magic = 0xffffffffu;   // unused: a one-float row is never strided below (rows collapse)
+    if ((g_row != p_row || g.grad_col != 0) && (p_row < 2 || p_row > 32768)) { set_error("adam_step: group %d: strided gradient rows need 2 <= param_row <= 32768", i); return B200GS_EINVAL; }
+    if ((long long)(g_row / p_row + 2) * UPD_CHUNK >= 0x7fffffffll) { set_error("adam_step: group %d: gradient row too wide", i); return B200GS_EINVAL; }
     chunks += (g.n + UPD_CHUNK - 1) / UPD_CHUNK;
   }
   if (chunks == 0) return B200GS_OK;
