@@ -224,49 +224,15 @@ __global__ void __launch_bounds__(256) duplicate_kernel(int P, const uint32_t* _
 // can contribute.  Images, radii, weights and gradients are unchanged (the reference rejects those
 // pairs pixel by pixel); the lists are a subsequence of the reference's.  The exact-lists mode
 // keeps duplicate_kernel above and reproduces the reference's lists bit for bit.
-// One thread per Gaussian for rects of < COOP_ROWS tile rows; taller rects are handed to the whole
-// warp, one tile row per lane (every lane rebuilds the RowCull from the same 64-B record).
-constexpr int COOP_ROWS = 20;   // counting only: for the emission one thread per Gaussian measured faster at any threshold
-
-__device__ __forceinline__ uint32_t count_row(const RowCull& rw, int y, int x0, int x1) {
-  int a1, b1, a2, b2, d0, d1;
-  rowcull_ranges(rw, y, x0, x1, a1, b1, a2, b2, d0, d1);
-  return (uint32_t)rowcull_count(a1, b1, a2, b2, d0, d1);
-}
-
-__global__ void __launch_bounds__(256) count_kept_kernel(int P, const uint32_t* __restrict__ tiles_touched,
-                                                         const uint2* __restrict__ rects, const CullRec* __restrict__ cull,
-                                                         uint32_t* __restrict__ kept) {
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  const int lane = threadIdx.x & 31;
-  uint32_t n = 0;
-  uint2 rc = make_uint2(0u, 0u);
-  const bool vis = idx < P && tiles_touched[idx] > 0u;
-  if (vis) rc = rects[idx];
-  const int rows = (int)(rc.y >> 16) - (int)(rc.y & 0xffff);
-  const bool coop = vis && rows >= COOP_ROWS;
-  if (vis && !coop) {
-    const int x0 = rc.x & 0xffff, x1 = rc.x >> 16, y0 = rc.y & 0xffff, y1 = rc.y >> 16;
-    RowCull rw;
-    rowcull_init(cull[idx], rw);
-    for (int y = y0; y < y1; ++y) n += count_row(rw, y, x0, x1);
-  }
-  unsigned todo = __ballot_sync(0xffffffffu, coop);
-  while (todo) {
-    const int src = __ffs(todo) - 1;
-    todo &= todo - 1;
-    const uint32_t rx = __shfl_sync(0xffffffffu, rc.x, src), ry = __shfl_sync(0xffffffffu, rc.y, src);
-    const int x0 = rx & 0xffff, x1 = rx >> 16, y0 = ry & 0xffff, y1 = ry >> 16;
-    RowCull rw;
-    rowcull_init(cull[idx - lane + src], rw);
-    uint32_t part = 0;
-    for (int y = y0 + lane; y < y1; y += 32) part += count_row(rw, y, x0, x1);
-    part = __reduce_add_sync(0xffffffffu, part);
-    if (lane == src) n = part;
-  }
-  if (idx < P) kept[idx] = n;
-}
-
+// Work distribution: a Gaussian's cost is its number of tile rows, which varies from 1 to the whole
+// image height, so one thread per Gaussian leaves most lanes idle (ncu: 8 of 32 active).  Instead
+// every warp takes 32 Gaussians, parks their RowCull states in shared memory and deals the
+// (Gaussian, tile row) pairs of all 32 out to its lanes, 32 rows at a time.  The count and the
+// emission are the same template, so both run the same fp64 code on the same inputs and agree
+// exactly on the number of instances.  Within a Gaussian the emitted tiles are in no particular
+// order: the tile sort is stable across Gaussians (their slots are disjoint and in depth order),
+// and a Gaussian appears at most once per tile.
+//
 // hist != nullptr: the digit histograms of the (<= 2) radix passes over the emitted tile ids are
 // accumulated on the fly (shared-memory REDs, flushed per block), which saves the separate
 // histogram pass over the keys (radix_histogram).
@@ -276,45 +242,152 @@ struct EmitHist {
   uint32_t mask0, mask1;
 };
 
-__global__ void __launch_bounds__(256) emit_kept_kernel(int P, const uint32_t* __restrict__ order,
-                                                        const uint2* __restrict__ rects, const CullRec* __restrict__ cull,
-                                                        const uint32_t* __restrict__ offsets, uint32_t* __restrict__ keys,
-                                                        uint32_t* __restrict__ vals, int gx, const EmitHist eh) {
-  __shared__ uint32_t s_h[2][RS_RADIX];
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (eh.hist) { s_h[0][threadIdx.x] = 0u; s_h[1][threadIdx.x] = 0u; __syncthreads(); }
-  auto put = [&](uint32_t o, uint32_t key, uint32_t v) {
-    keys[o] = key; vals[o] = v;
-    if (eh.hist) { atomicAdd(&s_h[0][key & eh.mask0], 1u); atomicAdd(&s_h[1][(key >> eh.shift1) & eh.mask1], 1u); }
-  };
-  uint32_t off = 0, end = 0, id = 0;
-  if (i < P) { off = i == 0 ? 0u : offsets[i - 1]; end = offsets[i]; }
-  const bool any = end > off;
-  uint2 rc = make_uint2(0u, 0u);
-  if (any) { id = order[i]; rc = rects[id]; }
-  if (any) {
-    const int x0 = rc.x & 0xffff, x1 = rc.x >> 16, y0 = rc.y & 0xffff, y1 = rc.y >> 16;
-    RowCull rw;
-    rowcull_init(cull[id], rw);
-    for (int y = y0; y < y1; ++y) {
-      int a1, b1, a2, b2, d0, d1;
-      rowcull_ranges(rw, y, x0, x1, a1, b1, a2, b2, d0, d1);
-      const uint32_t row = (uint32_t)(y * gx);
-      for (int x = a1; x <= b1 && off < end; ++x) { put(off, row + (uint32_t)x, id); ++off; }
-      for (int x = a2; x <= b2 && off < end; ++x) { put(off, row + (uint32_t)x, id); ++off; }
-      for (int x = d0; x <= d1 && off < end; ++x)
-        if (!((x >= a1 && x <= b1) || (x >= a2 && x <= b2))) { put(off, row + (uint32_t)x, id); ++off; }
+struct KeptArgs {
+  int P, gx;
+  const uint32_t* tiles_touched;  // count: [P] in id order
+  const uint32_t* order;          // emit: ids in depth order
+  const uint32_t* offsets;        // emit: inclusive scan of the kept counts, depth order
+  const uint2* rects;
+  const CullRec* cull;
+  uint32_t* kept;                 // count: out [P]
+  uint32_t* keys;                 // emit: out
+  uint32_t* vals;
+  EmitHist eh;
+};
+
+template <bool EMIT>
+__global__ void __launch_bounds__(256) kept_rows_kernel(const KeptArgs a) {
+  __shared__ RowCull s_rc[256];
+  __shared__ int4 s_box[256];            // x0, x1, y0, rows
+  __shared__ uint32_t s_pref[256];       // inclusive prefix of rows within the warp
+  __shared__ uint32_t s_run[256];        // count: kept tiles so far; emit: next free slot
+  __shared__ uint2 s_ie[EMIT ? 256 : 1]; // emit: id, end of the Gaussian's slots
+  __shared__ uint32_t s_h[2][EMIT ? RS_RADIX : 1];
+  const int t = threadIdx.x, lane = t & 31, wb = t & ~31;
+  const int i = blockIdx.x * 256 + t;
+  const bool hist = EMIT && a.eh.hist != nullptr;
+  if (hist) { s_h[0][t] = 0u; s_h[1][t] = 0u; __syncthreads(); }
+
+  uint32_t id = 0, off = 0, end = 0;
+  bool vis = false;
+  if (i < a.P) {
+    if (EMIT) {
+      off = i == 0 ? 0u : a.offsets[i - 1]; end = a.offsets[i];
+      vis = end > off;
+      if (vis) id = a.order[i];
+    } else {
+      id = (uint32_t)i;
+      vis = a.tiles_touched[i] > 0u;
     }
-    // count_kept_kernel and this loop run the same inlined fp64 code on the same inputs, so off == end
-    // here.  Should the two compilations ever disagree, no slot may stay uninitialised: repeat the
-    // Gaussian on its first tile (the `off < end` guards above cover the opposite case).
-    for (; off < end; ++off) put(off, (uint32_t)(y0 * gx + x0), id);
   }
-  if (eh.hist) {
-    __syncthreads();
-    const uint32_t h0 = s_h[0][threadIdx.x], h1 = s_h[1][threadIdx.x];
-    if (h0) atomicAdd(eh.hist + threadIdx.x, h0);
-    if (h1) atomicAdd(eh.hist + RS_RADIX + threadIdx.x, h1);
+  int rows = 0;
+  if (vis) {
+    const uint2 rc = a.rects[id];
+    const int x0 = rc.x & 0xffff, x1 = rc.x >> 16, y0 = rc.y & 0xffff, y1 = rc.y >> 16;
+    rowcull_init(a.cull[id], s_rc[t]);
+    rows = (s_rc[t].mode == 0) ? 0 : (y1 - y0);
+    s_box[t] = make_int4(x0, x1, y0, rows);
+  }
+  s_run[t] = off;                         // 0 when counting
+  if (EMIT) s_ie[t] = make_uint2(id, end);
+  uint32_t pref = (uint32_t)rows;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const uint32_t v = __shfl_up_sync(0xffffffffu, pref, d);
+    if (lane >= d) pref += v;
+  }
+  s_pref[t] = pref;
+  const uint32_t total = __shfl_sync(0xffffffffu, pref, 31);
+  __syncwarp();
+
+  auto put = [&](uint32_t o, uint32_t key, uint32_t v) {
+    a.keys[o] = key; a.vals[o] = v;
+    if (hist) { atomicAdd(&s_h[0][key & a.eh.mask0], 1u); atomicAdd(&s_h[1][(key >> a.eh.shift1) & a.eh.mask1], 1u); }
+  };
+
+  for (uint32_t k0 = 0; k0 < total; k0 += 32) {
+    const uint32_t k = k0 + lane;
+    const bool valid = k < total;
+    int g = 0;                            // owner of row k: the first g with s_pref[g] > k
+    int a1 = 0, b1 = -1, a2 = 0, b2 = -1, d0 = 0, d1 = -1, y = 0;
+    uint32_t n = 0;
+    if (valid) {
+#pragma unroll
+      for (int st = 16; st > 0; st >>= 1)
+        if (s_pref[wb + g + st - 1] <= k) g += st;
+      const int4 bx = s_box[wb + g];
+      y = bx.z + (int)(k - (s_pref[wb + g] - (uint32_t)bx.w));
+      rowcull_ranges(s_rc[wb + g], y, bx.x, bx.y, a1, b1, a2, b2, d0, d1);
+      n = (uint32_t)rowcull_count(a1, b1, a2, b2, d0, d1);
+    }
+    uint32_t o = 0;
+    if (n) o = atomicAdd(&s_run[wb + g], n);
+    if (EMIT) {
+      // deal the tiles of these 32 rows out to the lanes: instance j of the iteration belongs to the
+      // first row whose inclusive tile prefix exceeds j; consecutive lanes write consecutive slots
+      uint32_t tp = n;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t v = __shfl_up_sync(0xffffffffu, tp, d);
+        if (lane >= d) tp += v;
+      }
+      const uint32_t T = __shfl_sync(0xffffffffu, tp, 31);
+      const uint32_t r1 = ((uint32_t)(a1 & 0xffff)) | ((uint32_t)((b1 + 1) & 0xffff) << 16);   // tile columns are 16-bit (rects)
+      const uint32_t r2 = ((uint32_t)(a2 & 0xffff)) | ((uint32_t)((b2 + 1) & 0xffff) << 16);
+      const uint32_t rd = ((uint32_t)(d0 & 0xffff)) | ((uint32_t)((d1 + 1) & 0xffff) << 16);
+      const uint32_t rowbase = (uint32_t)(y * a.gx);
+      for (uint32_t j0 = 0; j0 < T; j0 += 32) {
+        const uint32_t j = j0 + lane;
+        int ow = 0;
+#pragma unroll
+        for (int st = 16; st > 0; st >>= 1) {
+          const uint32_t v = __shfl_sync(0xffffffffu, tp, ow + st - 1);
+          if (v <= j) ow += st;
+        }
+        ow = min(ow, 31);
+        const uint32_t o_tp = __shfl_sync(0xffffffffu, tp, ow), o_n = __shfl_sync(0xffffffffu, n, ow);
+        const uint32_t o_o = __shfl_sync(0xffffffffu, o, ow);
+        const uint32_t o_r1 = __shfl_sync(0xffffffffu, r1, ow), o_r2 = __shfl_sync(0xffffffffu, r2, ow);
+        const uint32_t o_rd = __shfl_sync(0xffffffffu, rd, ow), o_base = __shfl_sync(0xffffffffu, rowbase, ow);
+        const int o_g = __shfl_sync(0xffffffffu, g, ow);
+        if (j < T) {
+          int r = (int)(j - (o_tp - o_n));                       // index within the row's tiles
+          const int ra1 = o_r1 & 0xffff, rb1 = (int)(o_r1 >> 16) - 1, ra2 = o_r2 & 0xffff, rb2 = (int)(o_r2 >> 16) - 1;
+          const int len1 = max(0, rb1 - ra1 + 1), len2 = max(0, rb2 - ra2 + 1);
+          int x;
+          if (r < len1) x = ra1 + r;
+          else if (r < len1 + len2) x = ra2 + (r - len1);
+          else {                                                 // the r-th tile of the disk's range outside both conic ranges
+            r -= len1 + len2;
+            const int rd0 = o_rd & 0xffff, rd1 = (int)(o_rd >> 16) - 1;
+            x = rd0;
+            for (; x <= rd1; ++x)
+              if (!((x >= ra1 && x <= rb1) || (x >= ra2 && x <= rb2))) { if (r == 0) break; --r; }
+          }
+          const uint2 ie = s_ie[wb + o_g];
+          const uint32_t slot = o_o + (j - (o_tp - o_n));
+          if (slot < ie.y) put(slot, o_base + (uint32_t)x, ie.x);
+        }
+      }
+    }
+  }
+  __syncwarp();
+  if (!EMIT) {
+    if (i < a.P) a.kept[i] = s_run[t];
+  } else {
+    // Count and emission are one template on the same inputs, so s_run[t] == end here.  Should two
+    // compilations ever disagree, no slot may stay uninitialised: repeat the Gaussian on its first
+    // tile (the `o < end` guards above cover the opposite case).
+    if (vis) {
+      const int4 bx = s_box[t];
+      for (uint32_t o = s_run[t]; o < end; ++o) put(o, (uint32_t)(bx.z * a.gx + bx.x), id);
+    }
+    if (hist) {
+      __syncthreads();
+      const uint32_t h0 = s_h[0][t], h1 = s_h[1][t];
+      if (h0) atomicAdd(a.eh.hist + t, h0);
+      if (h1) atomicAdd(a.eh.hist + RS_RADIX + t, h1);
+    }
   }
 }
 
@@ -322,8 +395,10 @@ int surfel_count_kept(int P, const uint32_t* tiles_touched, const uint2* rects, 
                       cudaStream_t s, bool debug) {
   if (P <= 0) return B200GS_OK;
   StageScope _t(ST_COUNT_KEPT, s);
-  count_kept_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, tiles_touched, rects, cull, kept);
-  B200GS_LAUNCHED("count_kept_kernel", debug, s);
+  KeptArgs a{};
+  a.P = P; a.tiles_touched = tiles_touched; a.rects = rects; a.cull = cull; a.kept = kept;
+  kept_rows_kernel<false><<<(P + 255) / 256, 256, 0, s>>>(a);
+  B200GS_LAUNCHED("kept_rows_kernel<count>", debug, s);
   return B200GS_OK;
 }
 
@@ -690,7 +765,7 @@ int bin_and_sort(const uint32_t* order, const uint2* rects, const uint32_t* offs
   uint32_t* kb = odd ? b.tile_ids : b.tmp_keys;
   uint32_t* vb = odd ? b.point_list : b.tmp_vals;
   int rc;
-  const bool fused_hist = cull != nullptr && plan.passes <= 2;   // emit_kept_kernel accumulates the digit histograms
+  const bool fused_hist = cull != nullptr && plan.passes <= 2;   // kept_rows_kernel<emit> accumulates the digit histograms
   {
     StageScope _t(ST_DUPLICATE, s);
     if (cull != nullptr) {
@@ -700,8 +775,11 @@ int bin_and_sort(const uint32_t* order, const uint2* rects, const uint32_t* offs
       eh.shift1 = plan.passes > 1 ? plan.shift[1] : 0;
       eh.mask1 = plan.passes > 1 ? (1u << plan.bits[1]) - 1u : 0u;
       if (fused_hist) { rc = radix_workspace_clear(b.sort_ws, s); if (rc) return rc; }
-      emit_kept_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, order, rects, cull, offsets, ka, va, gx, eh);
-      B200GS_LAUNCHED("emit_kept_kernel", debug, s);
+      KeptArgs ea{};
+      ea.P = P; ea.gx = gx; ea.order = order; ea.offsets = offsets; ea.rects = rects; ea.cull = cull;
+      ea.keys = ka; ea.vals = va; ea.eh = eh;
+      kept_rows_kernel<true><<<(P + 255) / 256, 256, 0, s>>>(ea);
+      B200GS_LAUNCHED("kept_rows_kernel<emit>", debug, s);
     } else {
       duplicate_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, order, rects, offsets, ka, va, gx);
       B200GS_LAUNCHED("duplicate_kernel", debug, s);
