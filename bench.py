@@ -37,7 +37,7 @@ for p in (ROOT, os.path.join(ROOT, "tests"), os.path.join(ROOT, "gaussian-splatt
     if p not in sys.path:
         sys.path.insert(0, p)
 
-METRIC = "surfel rasterizer fwd+bwd throughput, 3M Gaussians SH3 @1920x1080 (one view per GPU per step)"
+METRIC = "surfel rasterizer fwd+bwd throughput, 3M Gaussians SH3 @1920x1080 (32-view batch sharded over the GPUs)"
 UNIT = "Mpix/s"
 WORKLOAD = "bench"   # tests/scenes.py CONFIGS["bench"]: room scene, P=3M, 1920x1080
 
@@ -50,6 +50,9 @@ def parse():
     ap.add_argument("--impl", default="new", choices=["new", "reference"])
     ap.add_argument("--workload", default=WORKLOAD)
     ap.add_argument("--points", type=int, default=0, help="override P (debug only; result is then not the headline)")
+    ap.add_argument("--views-per-step", type=int, default=32,
+                    help="views of one step (a batch), sharded over the ranks: rank r renders views r, r+n, ... and the "
+                         "per-Gaussian gradients of the batch are summed (BASELINE.json configs[4], SURVEY.md 8e)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--exact-lists", action="store_true",
@@ -208,28 +211,50 @@ def main():
             print(json.dumps({"impl": "reference", "unavailable": impl_desc}))
         return
 
-    # ---- synthetic workload: replicated Gaussians, one ring-camera view per rank ------------
-    sc_np, cam_np = scenes.build(a.workload, P=a.points or None, view=rank, n_views=32)
+    # ---- synthetic workload: replicated Gaussians, a batch of ring-camera views sharded over the ranks ----
+    VB = a.views_per_step
+    if VB < world or VB % world:
+        raise SystemExit(f"--views-per-step {VB} must be a positive multiple of the number of GPUs ({world})")
+    from b200gs.dp import GradArena, shard_views
+    my_views = shard_views(VB, rank, world)               # r, r+n, ...  
+    sc_np, cam_np = scenes.build(a.workload, P=a.points or None, view=my_views[0] % 32, n_views=32)
     P, W, H = sc_np["means3D"].shape[0], cam_np["width"], cam_np["height"]
     N = W * H
-    sc, cam = hz.to_dev(sc_np), hz.to_dev(cam_np)
+    sc = hz.to_dev(sc_np)
+    cams_np = [cam_np] + [scenes.camera(a.workload, v % 32, 32) for v in my_views[1:]]
+    cams = [hz.to_dev(c) for c in cams_np]
+    cam = cams[0]
     grads = hz.to_dev(scenes.upstream_grads(W, H))
     GRAD_KEYS = ("means3D", "sh", "opacity", "scales", "rotations", "refl")   # the 59 floats / Gaussian of the model
 
-    arena = None
-    if a.impl == "new" and world > 1:
-        from b200gs.dp import GradArena
-        arena = GradArena(P, sc["shs"].shape[1], "cuda")
-        Cmod.use_gradient_arena(arena)       # backward writes the [59 P] gradient block in place
+    # The parameter gradients of the views of a batch are summed.  This library: the backward ADDS them into one
+    # flat [59 P] arena in place (b200gs.dp.GradArena, accumulate mode), which NCCL then reduces as it lies.
+    # Reference arm: what autograd does for it -- one add per gradient tensor per view -- and one concatenation
+    # before the all-reduce.
+    arena, ref_acc = None, None
+    if a.impl == "new":
+        arena = GradArena(P, sc["shs"].shape[1], "cuda", accumulate=True)
+        Cmod.use_gradient_arena(arena)
 
     def step():
-        f = hz.surfel_forward(Cmod, sc, cam)
-        b = hz.surfel_backward(Cmod, sc, cam, f, grads)
+        nonlocal ref_acc
+        if arena is not None:
+            arena.zero_()
+        f = b = None
+        for vi, c in enumerate(cams):
+            f = hz.surfel_forward(Cmod, sc, c)
+            b = hz.surfel_backward(Cmod, sc, c, f, grads)
+            if arena is None:
+                if vi == 0:
+                    ref_acc = {k: b[k] for k in GRAD_KEYS}
+                else:
+                    for k in GRAD_KEYS:
+                        ref_acc[k] += b[k]
         if world > 1:
             if arena is not None:
                 arena.all_reduce()
-            else:                            # reference arm: its gradients are separate tensors
-                flat = torch.cat([b[k].reshape(P, -1) for k in GRAD_KEYS], 1)
+            else:
+                flat = torch.cat([ref_acc[k].reshape(P, -1) for k in GRAD_KEYS], 1)
                 dist.all_reduce(flat)
         return f, b
 
@@ -255,14 +280,15 @@ def main():
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item())
 
+    # workload counts of this rank's first view (for the algorithmic-bytes figures of the stage table)
     R_ref = None
     if a.impl == "new":
         b200gs.set_exact_lists(1)
-        f, _ = step()
+        f = hz.surfel_forward(Cmod, sc, cam)
         R_ref = int(f["rendered"])           # the reference's instance count
         del f
         b200gs.set_exact_lists(1 if a.exact_lists else 0)
-    f, _ = step()
+    f = hz.surfel_forward(Cmod, sc, cam)
     R, V = int(f["rendered"]), int((f["radii"] > 0).sum())
     if R_ref is None:
         R_ref = R
@@ -283,7 +309,7 @@ def main():
     b200gs.timing_enable(0)
     clocks = cs.summary()
     ms_per_step = total_ms / a.steps
-    value = world * N / (ms_per_step * 1e-3) / 1e6
+    value = VB * N / (ms_per_step * 1e-3) / 1e6            # whole job: every rank's views
 
     if arena is not None:
         Cmod.use_gradient_arena(None)
@@ -297,35 +323,40 @@ def main():
             leaves = {k: sc[k].clone().requires_grad_(True) for k in ("means3D", "shs", "opacities", "scales", "rotations", "refl")}
             m2d = torch.zeros_like(leaves["means3D"], requires_grad=True)
             mask = torch.ones((P, 3), dtype=torch.bool, device="cuda")
-            host = {k: torch.from_numpy(cam_np[k]).pin_memory() for k in ("viewmatrix", "projmatrix", "campos")}
-            host["target"] = torch.rand((3, H, W)).pin_memory()
-            host["bg"] = torch.zeros(3).pin_memory()
-            h2d = sum(t.numel() * t.element_size() for t in host.values())
+            hosts = [{k: torch.from_numpy(c[k]).pin_memory() for k in ("viewmatrix", "projmatrix", "campos")} for c in cams_np]
+            target = torch.rand((3, H, W)).pin_memory()   # one pinned target image, copied H2D again for every view
+            for hv in hosts:
+                hv["target"] = target
+                hv["bg"] = torch.zeros(3).pin_memory()
+            h2d = sum(t.numel() * t.element_size() for t in hosts[0].values()) * VB     # whole job
             loss_host = torch.zeros(1).pin_memory()
 
             def e2e_step():
-                dev = {k: v.to("cuda", non_blocking=True) for k, v in host.items()}
-                rs = dsr.GaussianRasterizationSettings(
-                    image_height=H, image_width=W, tanfovx=cam_np["tanfovx"], tanfovy=cam_np["tanfovy"], bg=dev["bg"],
-                    scale_modifier=1.0, viewmatrix=dev["viewmatrix"], projmatrix=dev["projmatrix"], sh_degree=3,
-                    campos=dev["campos"], prefiltered=False, debug=False)
-                color, radii, allmap, refl_map, _ = dsr.GaussianRasterizer(rs)(
-                    means3D=leaves["means3D"], means2D=m2d, opacities=leaves["opacities"], shs=leaves["shs"],
-                    refl_strengths=leaves["refl"], scales=leaves["scales"], rotations=leaves["rotations"],
-                    env_scope_mask=mask)
-                loss = (color - dev["target"]).abs().mean() + 1e-3 * allmap[:7].mean() + 1e-3 * refl_map.mean()
                 for t in list(leaves.values()) + [m2d]:
                     t.grad = None
-                loss.backward()
+                total = None
+                for host in hosts:                       # this rank's views of the batch; autograd sums the gradients
+                    dev = {k: v.to("cuda", non_blocking=True) for k, v in host.items()}
+                    rs = dsr.GaussianRasterizationSettings(
+                        image_height=H, image_width=W, tanfovx=cam_np["tanfovx"], tanfovy=cam_np["tanfovy"], bg=dev["bg"],
+                        scale_modifier=1.0, viewmatrix=dev["viewmatrix"], projmatrix=dev["projmatrix"], sh_degree=3,
+                        campos=dev["campos"], prefiltered=False, debug=False)
+                    color, radii, allmap, refl_map, _ = dsr.GaussianRasterizer(rs)(
+                        means3D=leaves["means3D"], means2D=m2d, opacities=leaves["opacities"], shs=leaves["shs"],
+                        refl_strengths=leaves["refl"], scales=leaves["scales"], rotations=leaves["rotations"],
+                        env_scope_mask=mask)
+                    loss = (color - dev["target"]).abs().mean() + 1e-3 * allmap[:7].mean() + 1e-3 * refl_map.mean()
+                    loss.backward()
+                    total = loss.detach() if total is None else total + loss.detach()
                 if world > 1:
                     flat = torch.cat([leaves[k].grad.reshape(P, -1) for k in leaves], 1)
                     dist.all_reduce(flat)
-                loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
-                torch.cuda.current_stream().synchronize()     # the caller reads the loss every step
+                loss_host.copy_(total.reshape(1), non_blocking=True)
+                torch.cuda.current_stream().synchronize()     # the caller reads the batch loss every step
                 return float(loss_host[0])
 
             e2e_ms = timed(e2e_step, a.steps, a.warmup) / a.steps
-            e2e = {"value": world * N / (e2e_ms * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": e2e_ms,
+            e2e = {"value": VB * N / (e2e_ms * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": e2e_ms, "ms_per_view": e2e_ms * world / VB,
                    "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4,
                    "api": "diff_surfel_rasterization.GaussianRasterizer (autograd) + L1 loss"}
         finally:
@@ -361,7 +392,7 @@ def main():
         ach = stage_table[top]["gbs"]
         roofline = {"kernel": top, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s",
                     "frac": round(ach / peak, 4), "traffic": traffic, "peak_source": peak_src,
-                    "share_of_step": round(stage_table[top]["ms"] / ms_per_step, 3),
+                    "share_of_step": round(stage_table[top]["ms"] * stage_table[top]["launches_per_step"] / ms_per_step, 3),
                     "note": "compositing kernels are FP32/MUFU-issue bound, not HBM bound (DESIGN.md); the HBM "
                             "fraction is reported as the contract asks, per-stage figures are under `stages`"}
 
@@ -375,14 +406,17 @@ def main():
 
     line = {
         "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
-        "ms_per_step": round(ms_per_step, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "ms_per_step": round(ms_per_step, 4), "ms_per_view": round(ms_per_step * world / VB, 4),
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{a.workload}: room scene, replicated Gaussians, ring camera {'0' if world == 1 else '0..%d' % (world - 1)} of 32",
+        "config": {"workload": f"{a.workload}: room scene, replicated Gaussians, batch of {VB} ring-camera views per step, "
+                               f"{VB // world} per GPU (rank r renders views r, r+n, ...), gradients of the batch summed in place",
                    "gaussians": P, "width": W, "height": H, "sh_degree": 3, "visible": V, "instances": R_ref, "instances_emitted": R,
                    "lists": ("exact (reference's lists bit for bit)" if (a.exact_lists or a.impl == "reference")
                              else "culled emission (only instances that can reach alpha >= 1/255)"),
-                   "views_per_step": world, "l2": "inputs (>= 0.7 GB of Gaussian data + 1.3 GB of sort keys per step) exceed the 126 MB L2; no flush",
-                   "parallelism": f"view-parallel x{world}, replicated Gaussians" + (", NCCL all-reduce of [P,59] fp32 gradients" if world > 1 else "")},
+                   "views_per_step": VB, "views_per_gpu": VB // world,
+                   "counts": "visible / instances are those of rank 0's first view", "l2": "inputs (>= 0.7 GB of Gaussian data + 0.5-1.3 GB of sort keys per view) exceed the 126 MB L2; no flush",
+                   "parallelism": f"view-parallel x{world}, replicated Gaussians" + (", one NCCL all-reduce of the [P,59] fp32 gradient arena per batch" if world > 1 else "")},
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
         "roofline": roofline, "cpu_baseline": cpu, "stages": stage_table, "implementation": impl_desc,
     }

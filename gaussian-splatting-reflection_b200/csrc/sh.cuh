@@ -66,14 +66,19 @@ __device__ __forceinline__ V3 operator*(float f, V3 a) { return {f * a.x, f * a.
 __device__ __forceinline__ V3 operator+(V3 a, V3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
 __device__ __forceinline__ float dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 
-// SH backward (backward.cu:20-139): writes dL_dsh rows, returns dL/d(mean) through the view direction.
+// SH backward (backward.cu:20-139): writes dL_dsh rows (ACC: adds to them, for gradients accumulated
+// over the views of a batch), returns dL/d(mean) through the view direction.
+template <bool ACC = false>
 __device__ __forceinline__ V3 sh_backward(int deg, int M, const float* __restrict__ sh, V3 dir_orig, V3 dRGB,
-                                          float* __restrict__ dsh) {
+                                          float* dsh) {
   const float len = sqrtf(dir_orig.x * dir_orig.x + dir_orig.y * dir_orig.y + dir_orig.z * dir_orig.z);
   const float x = dir_orig.x / len, y = dir_orig.y / len, z = dir_orig.z / len;
   V3 dx = {0, 0, 0}, dy = {0, 0, 0}, dz = {0, 0, 0};
   auto S = [&](int k) { return V3{sh[3 * k], sh[3 * k + 1], sh[3 * k + 2]}; };
-  auto W = [&](int k, float c) { dsh[3 * k] = c * dRGB.x; dsh[3 * k + 1] = c * dRGB.y; dsh[3 * k + 2] = c * dRGB.z; };
+  auto W = [&](int k, float c) {
+    if (ACC) { dsh[3 * k] += c * dRGB.x; dsh[3 * k + 1] += c * dRGB.y; dsh[3 * k + 2] += c * dRGB.z; }
+    else { dsh[3 * k] = c * dRGB.x; dsh[3 * k + 1] = c * dRGB.y; dsh[3 * k + 2] = c * dRGB.z; }
+  };
   W(0, SH_C0);
   if (deg > 0) {
     W(1, -SH_C1 * y); W(2, SH_C1 * z); W(3, -SH_C1 * x);

@@ -41,6 +41,11 @@ struct PreBwdArgs {
   float* dL_drot;
 };
 
+// ACC: the six PARAMETER gradients (opacity, refl, means3D, sh, scales, rotations) are added to what
+// the output tensors hold -- gradients of a batch of views accumulate in place (b200gs.dp.GradArena,
+// SURVEY.md section 8e); rows of Gaussians this view culled are left alone, so no zero-fill per view.
+// The view-space outputs (means2D, colors, normal, transMat) are always overwritten.
+template <bool ACC>
 __global__ void __launch_bounds__(256) surfel_preprocess_bwd_kernel(const PreBwdArgs a) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= a.P || !(a.radii[idx] > 0)) return;
@@ -55,9 +60,9 @@ __global__ void __launch_bounds__(256) surfel_preprocess_bwd_kernel(const PreBwd
     }
   }
   // plain per-Gaussian sums straight through
-  a.dL_dopacity[idx] = g[11];
+  a.dL_dopacity[idx] = ACC ? a.dL_dopacity[idx] + g[11] : g[11];
   a.dL_dcolors[3 * idx + 0] = g[12]; a.dL_dcolors[3 * idx + 1] = g[13]; a.dL_dcolors[3 * idx + 2] = g[14];
-  if (a.dL_drefl) a.dL_drefl[idx] = g[15];
+  if (a.dL_drefl) a.dL_drefl[idx] = ACC ? a.dL_drefl[idx] + g[15] : g[15];
   a.dL_dnormal[3 * idx + 0] = g[16]; a.dL_dnormal[3 * idx + 1] = g[17]; a.dL_dnormal[3 * idx + 2] = g[18];
 
   const bool precomp = (a.scales == nullptr);  // backward.cu:639
@@ -151,8 +156,15 @@ __global__ void __launch_bounds__(256) surfel_preprocess_bwd_kernel(const PreBwd
     dq.y = 2.f * (-2.f * x * (c1.y + c2.z) + y * (c0.y + c1.x) + z * (c0.z + c2.x) + w * (c1.z - c2.y));
     dq.z = 2.f * (x * (c0.y + c1.x) - 2.f * y * (c0.x + c2.z) + z * (c1.z + c2.y) + w * (c2.x - c0.z));
     dq.w = 2.f * (x * (c0.z + c2.x) + y * (c1.z + c2.y) - 2.f * z * (c0.x + c1.y) + w * (c0.y - c1.x));
+    float2 ds = make_float2(dot(dRS0, R0), dot(dRS1, R1));
+    if (ACC) {
+      const float4 oq = reinterpret_cast<const float4*>(a.dL_drot)[idx];
+      const float2 os = reinterpret_cast<const float2*>(a.dL_dscales)[idx];
+      dq.x += oq.x; dq.y += oq.y; dq.z += oq.z; dq.w += oq.w;
+      ds.x += os.x; ds.y += os.y;
+    }
     reinterpret_cast<float4*>(a.dL_drot)[idx] = dq;
-    reinterpret_cast<float2*>(a.dL_dscales)[idx] = make_float2(dot(dRS0, R0), dot(dRS1, R1));
+    reinterpret_cast<float2*>(a.dL_dscales)[idx] = ds;
     dmean = {dM[2][0], dM[2][1], dM[2][2]};
   }
 
@@ -160,11 +172,13 @@ __global__ void __launch_bounds__(256) surfel_preprocess_bwd_kernel(const PreBwd
     const unsigned cb = a.clamped[idx];
     const V3 dRGB = {(cb & 1u) ? 0.f : g[12], (cb & 2u) ? 0.f : g[13], (cb & 4u) ? 0.f : g[14]};
     const V3 dir = {p.x - a.campos[0], p.y - a.campos[1], p.z - a.campos[2]};
-    const V3 dm = sh_backward(a.D, a.M, a.shs + (size_t)idx * a.M * 3, dir, dRGB, a.dL_dsh + (size_t)idx * a.M * 3);
+    const V3 dm = sh_backward<ACC>(a.D, a.M, a.shs + (size_t)idx * a.M * 3, dir, dRGB, a.dL_dsh + (size_t)idx * a.M * 3);
     dmean = dmean + dm;
   }
   if (!precomp || a.shs) {
-    a.dL_dmeans3D[3 * idx + 0] = dmean.x; a.dL_dmeans3D[3 * idx + 1] = dmean.y; a.dL_dmeans3D[3 * idx + 2] = dmean.z;
+    float* dm3 = a.dL_dmeans3D + 3 * (size_t)idx;
+    if (ACC) { dm3[0] += dmean.x; dm3[1] += dmean.y; dm3[2] += dmean.z; }
+    else { dm3[0] = dmean.x; dm3[1] = dmean.y; dm3[2] = dmean.z; }
   }
 
   // densification proxy (:656-659)
@@ -189,7 +203,8 @@ int surfel_preprocess_backward(const b200gs_surfel_bwd& f, const SurfelGeom& g, 
   a.dL_dtransMat = f.dL_dtransMat; a.dL_dsh = f.dL_dsh; a.dL_dscales = f.dL_dscales; a.dL_drot = f.dL_drotations;
   if (f.shs && !f.dL_dsh) { set_error("dL_dsh must be provided when shs is"); return B200GS_EINVAL; }
   StageScope _t(ST_PREPROCESS_BWD, s);
-  surfel_preprocess_bwd_kernel<<<(f.P + 255) / 256, 256, 0, s>>>(a);
+  if (f.accumulate) surfel_preprocess_bwd_kernel<true><<<(f.P + 255) / 256, 256, 0, s>>>(a);
+  else surfel_preprocess_bwd_kernel<false><<<(f.P + 255) / 256, 256, 0, s>>>(a);
   B200GS_LAUNCHED("surfel_preprocess_bwd_kernel", f.debug, s);
   return B200GS_OK;
 }

@@ -59,7 +59,7 @@ class SurfelBwd(C.Structure):
         ("accum", _p), ("accum_bytes", _sz),
         ("dL_dmeans2D", _p), ("dL_dnormal", _p), ("dL_dopacity", _p), ("dL_dcolors", _p),
         ("dL_drefl", _p), ("dL_dmeans3D", _p), ("dL_dtransMat", _p), ("dL_dsh", _p),
-        ("dL_dscales", _p), ("dL_drotations", _p),
+        ("dL_dscales", _p), ("dL_drotations", _p), ("accumulate", _i),
     ]
 
 

@@ -22,8 +22,12 @@ def shard_views(n_views, rank, world):
 class GradArena:
     """One flat fp32 buffer holding the six parameter-gradient blocks of P Gaussians."""
 
-    def __init__(self, P, sh_coeffs, device):
+    def __init__(self, P, sh_coeffs, device, accumulate=False):
+        """accumulate=False: every backward overwrites the arena (one view per step).
+        accumulate=True: backwards ADD to it -- zero_() once per batch, render the rank's views,
+        then all_reduce() (a 32-view batch sharded over the ranks)."""
         self.P, self.M = int(P), int(sh_coeffs)
+        self.accumulate = bool(accumulate)
         self.widths = {k: (w if w is not None else 3 * self.M) for k, w in BLOCKS}
         self.offsets, off = {}, 0
         for k, _ in BLOCKS:

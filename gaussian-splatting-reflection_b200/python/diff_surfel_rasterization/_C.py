@@ -143,7 +143,8 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, refl_streng
         if arena is not None and (arena.P != P or arena.M != M or not has_refl or arena.flat.device != means3D.device):
             raise RuntimeError("gradient arena does not match this call (P, SH coefficients, refl map or device)")
         if arena is not None:
-            arena.zero_()
+            if not arena.accumulate:
+                arena.zero_()
             av = arena.views()
         dL_dmeans3D = av["means3D"] if arena is not None else torch.zeros((P, 3), **o)
         dL_dmeans2D = torch.zeros((P, 3), **o)
@@ -176,7 +177,8 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, refl_streng
                 dL_dmeans2D=_b.ptr(dL_dmeans2D), dL_dnormal=_b.ptr(dL_dnormal), dL_dopacity=_b.ptr(dL_dopacity),
                 dL_dcolors=_b.ptr(dL_dcolors), dL_drefl=_b.ptr(dL_drefl), dL_dmeans3D=_b.ptr(dL_dmeans3D),
                 dL_dtransMat=_b.ptr(dL_dtransMat), dL_dsh=_b.ptr(dL_dsh), dL_dscales=_b.ptr(dL_dscales),
-                dL_drotations=_b.ptr(dL_drotations))
+                dL_drotations=_b.ptr(dL_drotations),
+                accumulate=1 if (arena is not None and arena.accumulate) else 0)
             _b.check(_b.surfel_backward(C.byref(a), _stream()))
     return (dL_dmeans2D, dL_dcolors, dL_drefl, dL_dopacity, dL_dmeans3D, dL_dtransMat, dL_dsh, dL_dscales,
             dL_drotations)

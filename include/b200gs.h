@@ -169,6 +169,12 @@ typedef struct b200gs_surfel_bwd {
   float* dL_dsh;         /* [P,M,3] or NULL */
   float* dL_dscales;     /* [P,2] */
   float* dL_drotations;  /* [P,4] */
+  /* != 0: the parameter gradients (dL_dopacity, dL_drefl, dL_dmeans3D, dL_dsh, dL_dscales,
+   * dL_drotations) are ADDED to the buffers' contents for the Gaussians this view reached and left
+   * alone for the others, so the gradients of a batch of views accumulate in place (no reference
+   * counterpart: autograd does it there with one add per tensor per view).  0: overwritten; rows
+   * of culled Gaussians are not written in either mode (callers zero-fill, S/rasterize_points.cu:186-197). */
+  int accumulate;
 } b200gs_surfel_bwd;
 
 size_t b200gs_surfel_accum_bytes(int P);

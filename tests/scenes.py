@@ -135,6 +135,15 @@ def build(name, P=None, seed=0, view=0, n_views=32):
     return scene, cam
 
 
+def camera(name, view=0, n_views=32):
+    """Camera of build(name, view=view, n_views=n_views) without rebuilding the scene."""
+    cfg = CONFIGS[name]
+    if "cam" in cfg:
+        c = dict(cfg["cam"])
+        return make_camera(c.pop("eye"), cfg["W"], cfg["H"], **c)
+    return ring_camera(view, n_views, cfg["W"], cfg["H"], **cfg["ring"])
+
+
 def upstream_grads(W, H, seed=0):
     """N(0,1) upstream gradients for every differentiable output plane (fixed seed)."""
     rng = np.random.default_rng(777 + seed)

@@ -240,3 +240,44 @@ def test_culled_lists_are_subsequence_of_exact_lists(name):
     srt = ke.sort()
     idx_in_e = srt.indices[torch.searchsorted(srt.values, kc)]
     assert bool((idx_in_e[1:] > idx_in_e[:-1]).all())
+
+
+def test_gradient_arena_accumulates_a_batch_of_views():
+    """b200gs.dp.GradArena(accumulate=True): the backwards of several views ADD their parameter gradients
+    into the flat [59 P] arena (b200gs_surfel_bwd.accumulate) -- equal to the sum of the per-view gradient
+    tensors; rows of Gaussians no view reached stay zero; overwrite mode still overwrites."""
+    from b200gs.dp import GradArena
+    C = hz.new_surfel_C()
+    sc_np, _ = scenes.build("small")
+    sc = hz.to_dev(sc_np)
+    P, M = sc["means3D"].shape[0], sc["shs"].shape[1]
+    cams = [hz.to_dev(scenes.camera("small", v, 32)) for v in (0, 5, 11)]
+    grads = hz.to_dev(scenes.upstream_grads(cams[0]["width"], cams[0]["height"]))
+    keys = ("means3D", "sh", "opacity", "scales", "rotations", "refl")
+    want = None
+    for c in cams:                                    # separate tensors, summed here
+        f = hz.surfel_forward(C, sc, c)
+        b = hz.surfel_backward(C, sc, c, f, grads)
+        want = {k: b[k].clone() for k in keys} if want is None else {k: want[k] + b[k] for k in keys}
+    arena = GradArena(P, M, "cuda", accumulate=True)
+    C.use_gradient_arena(arena)
+    try:
+        arena.flat.fill_(7.0)                         # zero_() is the caller's job, once per batch
+        arena.zero_()
+        for c in cams:
+            f = hz.surfel_forward(C, sc, c)
+            b = hz.surfel_backward(C, sc, c, f, grads)
+            assert b["sh"].data_ptr() == arena.view("sh").data_ptr()
+        torch.cuda.synchronize()
+        for k in keys:
+            got = arena.view(k).reshape(want[k].shape)
+            assert hz.rel_l2(got, want[k]) <= 1e-5, (k, hz.rel_l2(got, want[k]))
+            assert torch.equal(got.abs().reshape(P, -1).amax(1) > 0, want[k].abs().reshape(P, -1).amax(1) > 0), k
+        arena.accumulate = False                      # overwrite mode: the last view alone
+        f = hz.surfel_forward(C, sc, cams[0])
+        b = hz.surfel_backward(C, sc, cams[0], f, grads)
+        C.use_gradient_arena(None)
+        b1 = hz.surfel_backward(C, sc, cams[0], f, grads)
+        assert hz.rel_l2(arena.view("sh"), b1["sh"]) <= 1e-5    # run-to-run atomic order only
+    finally:
+        C.use_gradient_arena(None)
