@@ -55,6 +55,8 @@ def parse():
                          "per-Gaussian gradients of the batch are summed (BASELINE.json configs[4], SURVEY.md 8e)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-stage-timing", action="store_true",
+                    help="diagnosis: no per-stage CUDA events inside the timed region (then no roofline / stage table)")
     ap.add_argument("--exact-lists", action="store_true",
                     help="time the exact-lists mode (the reference's instance lists bit for bit) instead of the "
                          "default culled emission")
@@ -294,9 +296,27 @@ def main():
         R_ref = R
     del f
 
-    # ---- device-resident timing (value) with per-stage events and clock sampling -------------
-    if a.impl == "new":
+    # ---- per-stage table: a separate instrumented pass ------------------------------------------
+    # An event pair between every two kernels keeps a launch from overlapping the previous kernel's tail
+    # (measured: +0.4 ms on a 6.1 ms view), so the all-stage table comes from its own short pass and the
+    # timed region below carries events around the dominant kernel only.
+    stages_all, top_stage = {}, -1
+    if a.impl == "new" and not a.no_stage_timing:
+        step()
+        torch.cuda.synchronize()
         b200gs.timing_enable(1)
+        b200gs.timing_read()
+        step()
+        torch.cuda.synchronize()
+        stages_all = b200gs.timing_read()
+        b200gs.timing_enable(0)
+        names = [b200gs.timing_stage_name(i).decode() for i in range(b200gs.timing_stages())]
+        top_name = max((k for k, v in stages_all.items() if v[1]), key=lambda k: stages_all[k][0], default=None)
+        top_stage = names.index(top_name) if top_name else -1
+
+    # ---- device-resident timing (value), events around the dominant kernel, clock sampling -------
+    if top_stage >= 0:
+        b200gs.timing_only(top_stage)
     n0 = [0]
 
     def reset_counters():                 # warm-up launches are not part of the timed region
@@ -305,7 +325,7 @@ def main():
     with ClockSampler(local) as cs:
         total_ms = timed(step, a.steps, a.warmup, reset_counters)
     launches = b200gs.launch_count() - n0[0]
-    stages = b200gs.timing_read() if a.impl == "new" else {}
+    stages = b200gs.timing_read() if top_stage >= 0 else {}      # the dominant kernel, live in the timed region
     b200gs.timing_enable(0)
     clocks = cs.summary()
     ms_per_step = total_ms / a.steps
@@ -376,25 +396,32 @@ def main():
         pass
     alg = algorithmic_bytes(P, V, R, N)
     roofline, stage_table = None, {}
-    for name, (ms, cnt) in stages.items():
+
+    def row(name, ms, cnt, steps):
+        per = ms / cnt
+        return {"ms": round(per, 4), "launches_per_step": cnt / (steps + 0.0),
+                "alg_bytes": alg[name], "gbs": round(alg[name] / (per * 1e-3) / 1e9, 1),
+                "frac_of_hbm_peak": round(alg[name] / (per * 1e-3) / 1e9 / peak, 4)}
+    for name, (ms, cnt) in stages_all.items():           # the separate all-stage pass (1 step)
         if cnt and name in alg:
-            per = ms / cnt
-            stage_table[name] = {"ms": round(per, 4), "launches_per_step": cnt / (a.steps + 0.0),
-                                 "alg_bytes": alg[name], "gbs": round(alg[name] / (per * 1e-3) / 1e9, 1),
-                                 "frac_of_hbm_peak": round(alg[name] / (per * 1e-3) / 1e9 / peak, 4)}
-    if stage_table:
-        top = max(stage_table, key=lambda k: stage_table[k]["ms"])
+            stage_table[name] = row(name, ms, cnt, 1)
+    live = {name: row(name, ms, cnt, a.steps) for name, (ms, cnt) in stages.items() if cnt and name in alg}
+    if live:
+        top = max(live, key=lambda k: live[k]["ms"])   # one entry: the dominant kernel, timed inside the timed region
         traffic = None
         try:   # per-launch dram bytes of that kernel from the committed ncu --set full capture, if any
             traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(top)
         except Exception:  # noqa: BLE001
             pass
-        ach = stage_table[top]["gbs"]
+        ach = live[top]["gbs"]
         roofline = {"kernel": top, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s",
                     "frac": round(ach / peak, 4), "traffic": traffic, "peak_source": peak_src,
-                    "share_of_step": round(stage_table[top]["ms"] * stage_table[top]["launches_per_step"] / ms_per_step, 3),
-                    "note": "compositing kernels are FP32/MUFU-issue bound, not HBM bound (DESIGN.md); the HBM "
-                            "fraction is reported as the contract asks, per-stage figures are under `stages`"}
+                    "ms_per_launch": live[top]["ms"], "launches_per_step": live[top]["launches_per_step"],
+                    "alg_bytes_per_launch": live[top]["alg_bytes"],
+                    "share_of_step": round(live[top]["ms"] * live[top]["launches_per_step"] / ms_per_step, 3),
+                    "note": "CUDA events around this kernel inside the timed region; compositing kernels are FP32/MUFU-issue "
+                            "bound, not HBM bound (DESIGN.md), the HBM fraction is reported as the contract asks; `stages` "
+                            "holds every stage from a separate instrumented pass (all-stage events perturb the step by ~6 %)"}
 
     cpu = None
     if a.impl == "new" and world == 1 and not a.no_cpu_baseline:

@@ -128,6 +128,7 @@ void b200gs_set_exact_lists(int on) { g_exact_lists.store(on ? 1 : 0); }
 int b200gs_get_exact_lists(void) { return g_exact_lists.load(); }
 
 void b200gs_timing_enable(int on) { g_timing.store(on ? 1 : 0); }
+void b200gs_timing_only(int stage) { g_timing.store((stage >= 0 && stage < ST_COUNT) ? 2 + stage : 0); }
 int b200gs_timing_stages(void) { return ST_COUNT; }
 const char* b200gs_timing_stage_name(int stage) {
   static const char* names[ST_COUNT] = {"preprocess", "scan", "duplicate", "sort", "tile_ranges", "composite_fwd",

@@ -49,12 +49,14 @@ enum Stage {
   ST_COMPOSITE_BWD, ST_PREPROCESS_BWD, ST_CUBEMAP_FWD, ST_CUBEMAP_BWD, ST_TILE_HITS, ST_DEPTH_SORT, ST_COUNT_KEPT,
   ST_ADAM, ST_DENSIFY_STATS, ST_COUNT
 };
-extern std::atomic<int> g_timing;
+extern std::atomic<int> g_timing;        // 0 off, 1 every stage, 2 + k: stage k only
 extern std::atomic<int> g_cull_audit;   // surfel_composite_fwd.cu: b200gs_debug_cull_audit
 void stage_mark(int stage, bool begin, cudaStream_t s);
 struct StageScope {
   int st; cudaStream_t s; bool on;
-  StageScope(int stage, cudaStream_t stream) : st(stage), s(stream), on(g_timing.load(std::memory_order_relaxed) != 0) {
+  StageScope(int stage, cudaStream_t stream) : st(stage), s(stream), on(false) {
+    const int m = g_timing.load(std::memory_order_relaxed);
+    on = m == 1 || m == 2 + stage;
     if (on) stage_mark(st, true, s);
   }
   ~StageScope() { if (on) stage_mark(st, false, s); }

@@ -167,7 +167,9 @@ __global__ void __launch_bounds__(256) gauss_preprocess_kernel(const GaussPreArg
   unsigned cb = 0;
   if (a.colors_precomp == nullptr) {
     const float* cp = a.campos;
-    sh_to_rgb(a.D, a.shs + (size_t)idx * a.M * 3, p.x - cp[0], p.y - cp[1], p.z - cp[2], rgb, cb);
+    float shv[48];
+    load_sh_row(a.shs + (size_t)idx * a.M * 3, a.M, a.D, shv);
+    sh_to_rgb(a.D, shv, p.x - cp[0], p.y - cp[1], p.z - cp[2], rgb, cb);
   } else {
     rgb[0] = a.colors_precomp[3 * idx]; rgb[1] = a.colors_precomp[3 * idx + 1]; rgb[2] = a.colors_precomp[3 * idx + 2];
   }

@@ -6,7 +6,47 @@
 
 namespace b200gs {
 
-// SH degree<=3 colour (forward.cu:20-71).  sh is this Gaussian's [M][3] block.
+// A Gaussian's [M][3] coefficient block as registers.  With M == 16 (degree-3 storage, the model's
+// layout) a row is 192 B and 16-B aligned, so 12 128-bit accesses replace 48 scalar ones: one thread
+// per Gaussian means every access of a warp touches 32 different rows, and the LSU / L1 wavefront count,
+// not DRAM, bounds the preprocess kernels.
+__device__ __forceinline__ bool sh_row_vec(const float* p, int M) {
+  return M == 16 && (reinterpret_cast<uintptr_t>(p) & 15u) == 0;
+}
+__device__ __forceinline__ void load_sh_row(const float* __restrict__ sh, int M, int deg, float v[48]) {
+  if (sh_row_vec(sh, M)) {
+#pragma unroll
+    for (int g = 0; g < 12; ++g) {
+      const float4 q = __ldg(reinterpret_cast<const float4*>(sh) + g);
+      v[4 * g] = q.x; v[4 * g + 1] = q.y; v[4 * g + 2] = q.z; v[4 * g + 3] = q.w;
+    }
+  } else {
+    const int n = 3 * min(M, (deg + 1) * (deg + 1));
+#pragma unroll
+    for (int j = 0; j < 48; ++j) v[j] = j < n ? sh[j] : 0.0f;
+  }
+}
+template <bool ACC>
+__device__ __forceinline__ void store_sh_row(float* dsh, int M, int deg, const float o[48]) {
+  if (sh_row_vec(dsh, M)) {
+#pragma unroll
+    for (int g = 0; g < 12; ++g) {
+      float4 q = make_float4(o[4 * g], o[4 * g + 1], o[4 * g + 2], o[4 * g + 3]);
+      if (ACC) {
+        const float4 old = reinterpret_cast<const float4*>(dsh)[g];
+        q.x += old.x; q.y += old.y; q.z += old.z; q.w += old.w;
+      }
+      reinterpret_cast<float4*>(dsh)[g] = q;
+    }
+  } else {
+    const int n = 3 * min(M, (deg + 1) * (deg + 1));   // rows of higher degrees are not written (backward.cu:20-139)
+#pragma unroll
+    for (int j = 0; j < 48; ++j)
+      if (j < n) dsh[j] = ACC ? dsh[j] + o[j] : o[j];
+  }
+}
+
+// SH degree<=3 colour (forward.cu:20-71).  sh is this Gaussian's [M][3] block (global memory or registers).
 __device__ __forceinline__ void sh_to_rgb(int deg, const float* __restrict__ sh, float dx, float dy, float dz,
                                           float out[3], unsigned& clamp_bits) {
   // glm: dir / length(dir) is a component-wise division; keep it a division for the same rounding.
@@ -69,16 +109,17 @@ __device__ __forceinline__ float dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y 
 // SH backward (backward.cu:20-139): writes dL_dsh rows (ACC: adds to them, for gradients accumulated
 // over the views of a batch), returns dL/d(mean) through the view direction.
 template <bool ACC = false>
-__device__ __forceinline__ V3 sh_backward(int deg, int M, const float* __restrict__ sh, V3 dir_orig, V3 dRGB,
-                                          float* dsh) {
+__device__ __forceinline__ V3 sh_backward(int deg, int M, const float* __restrict__ sh_row, V3 dir_orig, V3 dRGB,
+                                          float* dsh_row) {
+  float sh[48], dsh[48];
+  load_sh_row(sh_row, M, deg, sh);
+#pragma unroll
+  for (int j = 0; j < 48; ++j) dsh[j] = 0.0f;
   const float len = sqrtf(dir_orig.x * dir_orig.x + dir_orig.y * dir_orig.y + dir_orig.z * dir_orig.z);
   const float x = dir_orig.x / len, y = dir_orig.y / len, z = dir_orig.z / len;
   V3 dx = {0, 0, 0}, dy = {0, 0, 0}, dz = {0, 0, 0};
   auto S = [&](int k) { return V3{sh[3 * k], sh[3 * k + 1], sh[3 * k + 2]}; };
-  auto W = [&](int k, float c) {
-    if (ACC) { dsh[3 * k] += c * dRGB.x; dsh[3 * k + 1] += c * dRGB.y; dsh[3 * k + 2] += c * dRGB.z; }
-    else { dsh[3 * k] = c * dRGB.x; dsh[3 * k + 1] = c * dRGB.y; dsh[3 * k + 2] = c * dRGB.z; }
-  };
+  auto W = [&](int k, float c) { dsh[3 * k] = c * dRGB.x; dsh[3 * k + 1] = c * dRGB.y; dsh[3 * k + 2] = c * dRGB.z; };
   W(0, SH_C0);
   if (deg > 0) {
     W(1, -SH_C1 * y); W(2, SH_C1 * z); W(3, -SH_C1 * x);
@@ -106,7 +147,7 @@ __device__ __forceinline__ V3 sh_backward(int deg, int M, const float* __restric
       }
     }
   }
-  (void)M;
+  store_sh_row<ACC>(dsh_row, M, deg, dsh);
   const V3 ddir = {dot(dx, dRGB), dot(dy, dRGB), dot(dz, dRGB)};
   // dnormvdv (auxiliary.h:132-142)
   const V3 v = dir_orig;

@@ -219,7 +219,9 @@ __global__ void __launch_bounds__(256) surfel_preprocess_kernel(const SurfelPreA
   unsigned cb = 0;
   if (a.colors_precomp == nullptr) {
     const float* cp = a.campos;
-    sh_to_rgb(a.D, a.shs + (size_t)idx * a.M * 3, px - cp[0], py - cp[1], pz - cp[2], rgb, cb);
+    float shv[48];
+    load_sh_row(a.shs + (size_t)idx * a.M * 3, a.M, a.D, shv);
+    sh_to_rgb(a.D, shv, px - cp[0], py - cp[1], pz - cp[2], rgb, cb);
   } else {
     rgb[0] = a.colors_precomp[3 * idx + 0];
     rgb[1] = a.colors_precomp[3 * idx + 1];

@@ -105,6 +105,7 @@ version = _sig("b200gs_version", _i)
 sm_arch = _sig("b200gs_sm_arch", _i)
 launch_count = _sig("b200gs_launch_count", C.c_ulonglong)
 timing_enable = _sig("b200gs_timing_enable", None, _i)
+timing_only = _sig("b200gs_timing_only", None, _i)
 timing_stages = _sig("b200gs_timing_stages", _i)
 timing_stage_name = _sig("b200gs_timing_stage_name", C.c_char_p, _i)
 _timing_read = _sig("b200gs_timing_read", _i, C.POINTER(_f), C.POINTER(C.c_ulonglong), _i)

@@ -49,6 +49,10 @@ unsigned long long b200gs_launch_count(void);
  * b200gs_timing_read waits for the recorded events, adds the elapsed ms and the
  * launch counts per stage into ms[0..n) / counts[0..n) and clears the record.   */
 void b200gs_timing_enable(int on);
+/* Events around ONE stage only (index as in b200gs_timing_stage_name): an event pair between every two
+ * kernels keeps the next launch from overlapping the previous kernel's tail, which costs ~6 % of a step
+ * when every stage is instrumented; one pair does not.  stage < 0: off. */
+void b200gs_timing_only(int stage);
 int b200gs_timing_stages(void);
 const char* b200gs_timing_stage_name(int stage);
 int b200gs_timing_read(float* ms, unsigned long long* counts, int n);
