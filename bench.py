@@ -351,12 +351,29 @@ def main():
             h2d = sum(t.numel() * t.element_size() for t in hosts[0].values()) * VB     # whole job
             loss_host = torch.zeros(1).pin_memory()
 
+            copy_stream = torch.cuda.Stream()
+
+            def upload(host):
+                """H2D of one view's inputs on the copy stream (a data loader's prefetch); still inside the timed region."""
+                with torch.cuda.stream(copy_stream):
+                    dev = {k: v.to("cuda", non_blocking=True) for k, v in host.items()}
+                    ev = torch.cuda.Event()
+                    ev.record(copy_stream)
+                return dev, ev
+
             def e2e_step():
                 for t in list(leaves.values()) + [m2d]:
                     t.grad = None
                 total = None
-                for host in hosts:                       # this rank's views of the batch; autograd sums the gradients
-                    dev = {k: v.to("cuda", non_blocking=True) for k, v in host.items()}
+                nxt = upload(hosts[0])
+                for vi in range(len(hosts)):             # this rank's views of the batch; autograd sums the gradients
+                    dev, ev = nxt
+                    if vi + 1 < len(hosts):
+                        nxt = upload(hosts[vi + 1])      # the next view's inputs travel while this one renders
+                    cur = torch.cuda.current_stream()
+                    cur.wait_event(ev)
+                    for t in dev.values():
+                        t.record_stream(cur)
                     rs = dsr.GaussianRasterizationSettings(
                         image_height=H, image_width=W, tanfovx=cam_np["tanfovx"], tanfovy=cam_np["tanfovy"], bg=dev["bg"],
                         scale_modifier=1.0, viewmatrix=dev["viewmatrix"], projmatrix=dev["projmatrix"], sh_degree=3,
