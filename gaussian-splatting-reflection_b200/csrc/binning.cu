@@ -492,42 +492,47 @@ __device__ __forceinline__ bool tile_reachable(const TileForm& f) {
   return mn <= f.tol || ddx * ddx + ddy * ddy <= f.r2;
 }
 
+// Bits of the blocks in tile rows [r0, r1] (clamped to 0..3), both columns.
+__host__ __device__ constexpr unsigned rows_bits(int r0, int r1) {
+  unsigned m = 0;
+  for (int r = (r0 < 0 ? 0 : r0); r <= (r1 > 3 ? 3 : r1); ++r) m |= 3u << (2 * r);
+  return m;
+}
+// Bits of the blocks in columns [c0, c1] (clamped to 0..1), all rows.
+__host__ __device__ constexpr unsigned cols_bits(int c0, int c1) {
+  unsigned m = 0;
+  for (int c = (c0 < 0 ? 0 : c0); c <= (c1 > 1 ? 1 : c1); ++c) m |= 0x55u << c;
+  return m;
+}
+
+// A block is hit when ANY candidate point of its rectangle has f <= tol, so instead of tracking the
+// eight minima every candidate ORs the bits of the blocks it belongs to.
 __device__ __forceinline__ unsigned block_masks(const TileForm& f) {
   const float A = f.A, B = f.B, C = f.C, D = f.D, E = f.E, F = f.F, tol = f.tol;
-  const float INF = __int_as_float(0x7f800000);
   // one reciprocal per direction instead of a division per grid line (the vertex positions only
   // select a segment and the values are compared with a tolerance 100x the fp32 error)
   const float invA = A > 0.0f ? 1.0f / A : 0.0f, invC = C > 0.0f ? 1.0f / C : 0.0f;
-  // f on the grid lines x in {0,8,16}, y in {0,4,..,16}
-  float mn[4][2];
-#pragma unroll
-  for (int r = 0; r < 4; ++r) { mn[r][0] = INF; mn[r][1] = INF; }
-  float corner[5][3];
+  unsigned mask = 0u;
+  // grid lines x in {0,8,16}, y in {0,4,..,16}: corners, and the vertex of f along each horizontal line
 #pragma unroll
   for (int j = 0; j < 5; ++j) {
     const float y = 4.0f * j;
     const float gy = (C * y + 2.0f * E) * y + F;      // terms without x
     const float bx = B * y + D;                         // f = A x^2 + 2 bx x + gy
+    constexpr unsigned NONE = 0u;
+    const unsigned rb = rows_bits(j - 1, j);            // blocks touching this line
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
       const float x = 8.0f * i;
-      corner[j][i] = (A * x + 2.0f * bx) * x + gy;
+      const float v = (A * x + 2.0f * bx) * x + gy;
+      mask |= (v <= tol) ? (rb & cols_bits(i - 1, i)) : NONE;
     }
-    // vertex of f along the horizontal line
-    float hv0 = INF, hv1 = INF;
     if (A > 0.0f) {
       const float xs = -bx * invA;
       const float val = gy - bx * bx * invA;
-      if (xs > 0.0f && xs < 16.0f) { if (xs <= 8.0f) hv0 = val; if (xs >= 8.0f) hv1 = val; }
+      if (val <= tol && xs > 0.0f && xs < 16.0f) mask |= rb & ((xs <= 8.0f ? 0x55u : 0u) | (xs >= 8.0f ? 0xAAu : 0u));
     }
-    if (j < 4) { mn[j][0] = fminf(mn[j][0], hv0); mn[j][1] = fminf(mn[j][1], hv1); }
-    if (j > 0) { mn[j - 1][0] = fminf(mn[j - 1][0], hv0); mn[j - 1][1] = fminf(mn[j - 1][1], hv1); }
   }
-#pragma unroll
-  for (int r = 0; r < 4; ++r)
-#pragma unroll
-    for (int c = 0; c < 2; ++c)
-      mn[r][c] = fminf(mn[r][c], fminf(fminf(corner[r][c], corner[r][c + 1]), fminf(corner[r + 1][c], corner[r + 1][c + 1])));
   // vertices along the three vertical lines
   if (C > 0.0f) {
 #pragma unroll
@@ -537,13 +542,12 @@ __device__ __forceinline__ unsigned block_masks(const TileForm& f) {
       const float gx = (A * x + 2.0f * D) * x + F;
       const float ys = -by * invC;
       const float val = gx - by * by * invC;
-      if (ys > 0.0f && ys < 16.0f) {
+      if (val <= tol && ys > 0.0f && ys < 16.0f) {
+        unsigned rsel = 0u;
 #pragma unroll
         for (int r = 0; r < 4; ++r)
-          if (ys >= 4.0f * r && ys <= 4.0f * (r + 1)) {
-            if (i < 2) mn[r][i] = fminf(mn[r][i], val);
-            if (i > 0) mn[r][i - 1] = fminf(mn[r][i - 1], val);
-          }
+          if (ys >= 4.0f * r && ys <= 4.0f * (r + 1)) rsel |= 3u << (2 * r);
+        mask |= rsel & cols_bits(i - 1, i);
       }
     }
   }
@@ -552,25 +556,24 @@ __device__ __forceinline__ unsigned block_masks(const TileForm& f) {
   if (A > 0.0f && det > 0.0f) {
     const float idet = 1.0f / det;
     const float xs = (B * E - C * D) * idet, ys = (B * D - A * E) * idet;
-    if (xs > 0.0f && xs < 16.0f && ys > 0.0f && ys < 16.0f) {
-      const float val = D * xs + E * ys + F;             // f at the critical point
+    if (xs > 0.0f && xs < 16.0f && ys > 0.0f && ys < 16.0f && D * xs + E * ys + F <= tol) {   // f at the critical point
+      unsigned rsel = 0u;
 #pragma unroll
       for (int r = 0; r < 4; ++r)
-#pragma unroll
-        for (int c = 0; c < 2; ++c)
-          if (xs >= 8.0f * c && xs <= 8.0f * (c + 1) && ys >= 4.0f * r && ys <= 4.0f * (r + 1)) mn[r][c] = fminf(mn[r][c], val);
+        if (ys >= 4.0f * r && ys <= 4.0f * (r + 1)) rsel |= 3u << (2 * r);
+      mask |= rsel & ((xs <= 8.0f ? 0x55u : 0u) | (xs >= 8.0f ? 0xAAu : 0u));
     }
   }
-  // low-pass disk
-  unsigned mask = 0u;
+  // low-pass disk: distance of its centre to each block rectangle, separable in x and y
+  {
+    const float dx0 = fmaxf(fmaxf(0.0f - f.dxc, f.dxc - 8.0f), 0.0f), dx1 = fmaxf(fmaxf(8.0f - f.dxc, f.dxc - 16.0f), 0.0f);
+    const float ex0 = dx0 * dx0, ex1 = dx1 * dx1;
 #pragma unroll
-  for (int r = 0; r < 4; ++r) {
-    const float ddy = fmaxf(fmaxf(4.0f * r - f.dyc, f.dyc - 4.0f * (r + 1)), 0.0f);
-#pragma unroll
-    for (int c = 0; c < 2; ++c) {
-      const float ddx = fmaxf(fmaxf(8.0f * c - f.dxc, f.dxc - 8.0f * (c + 1)), 0.0f);
-      const bool disk = ddx * ddx + ddy * ddy <= f.r2;
-      if (mn[r][c] <= tol || disk) mask |= 1u << (r * 2 + c);
+    for (int r = 0; r < 4; ++r) {
+      const float ddy = fmaxf(fmaxf(4.0f * r - f.dyc, f.dyc - 4.0f * (r + 1)), 0.0f);
+      const float ey = ddy * ddy;
+      mask |= (ex0 + ey <= f.r2) ? (1u << (2 * r)) : 0u;
+      mask |= (ex1 + ey <= f.r2) ? (2u << (2 * r)) : 0u;
     }
   }
   return mask;
