@@ -187,6 +187,10 @@ adam_step = _sig("b200gs_adam_step", _i, C.POINTER(Adam), _p)
 densify_stats = _sig("b200gs_densify_stats", _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p)
 
 
+ssim_forward = _sig("b200gs_ssim_forward", _i, _f, _f, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p)
+ssim_backward = _sig("b200gs_ssim_backward", _i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p)
+
+
 def check(rc):
     """Map a C return code to an exception (the reference throws std::runtime_error
     -> Python RuntimeError; S/rasterize_points.cu:63-65, auxiliary.h:300-307)."""

@@ -337,6 +337,20 @@ int b200gs_densify_stats(int P, const int* radii, const float* dL_dmeans2D, cons
                          float* max_radii2D, float* xyz_gradient_accum, float* denom, float* accum_w, float* denom_w,
                          void* stream);
 
+/* ------------------------------------------------------------------------ */
+/* SSIM image loss ("next" row 3): replaces fusedssim / fusedssim_backward of
+ * submodules/fused-ssim (ssim.h:5-26; called from train.py:168-169 through
+ * fused_ssim/__init__.py:8-47); same map as ssim() of utils/loss_utils.py:63-101.  11x11 separable
+ * Gaussian window (sigma 1.5), zero "same" padding, images [B,CH,H,W] fp32 contiguous.
+ * forward: ssim_map [B,CH,H,W]; the three derivative maps (same shape) are written when all three
+ * pointers are given (training) and skipped when all are NULL.
+ * backward: dL_dimg1 [B,CH,H,W] from dL_dmap and the maps the forward saved.  */
+int b200gs_ssim_forward(float C1, float C2, int B, int CH, int H, int W, const float* img1, const float* img2,
+                        float* ssim_map, float* dm_dmu1, float* dm_dsigma1_sq, float* dm_dsigma12, void* stream);
+int b200gs_ssim_backward(int B, int CH, int H, int W, const float* img1, const float* img2, const float* dL_dmap,
+                         const float* dm_dmu1, const float* dm_dsigma1_sq, const float* dm_dsigma12, float* dL_dimg1,
+                         void* stream);
+
 #ifdef __cplusplus
 }
 #endif

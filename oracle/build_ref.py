@@ -5,15 +5,16 @@ TEST INFRASTRUCTURE ONLY.  Nothing under oracle/ is imported by the product
 package; only tests/, __graft_entry__.smoke() and bench.py's reference /
 cpu_baseline legs may touch it.
 
-The three reference extensions are compiled straight from the sources where
+The reference extensions are compiled straight from the sources where
 they lie under /root/reference/submodules (no source is copied into this repo);
-the only outputs are the three shared objects and ninja scratch under
+the only outputs are the shared objects and ninja scratch under
 oracle/_ref/ (git-ignored, NOT gpurun-ignored, so the .so files travel to the
 GPU box, where /root/reference does not exist).
 
   ref_surfel_C   <- diff-surfel-rasterization   (S/setup.py:21-30 source list)
   ref_gauss_C    <- diff-gaussian-rasterization (G/setup.py:21-29)
   ref_cubemap_C  <- cubemapencoder              (C/setup.py:19-27, -use_fast_math)
+  ref_ssim_C     <- fused-ssim                  (submodules/fused-ssim/setup.py: ssim.cu, ext.cpp)
 
 `-include cstdint` is required on gcc 13: S|G/cuda_rasterizer/rasterizer_impl.h
 uses std::uintptr_t / uint32_t without including <cstdint>.
@@ -51,6 +52,13 @@ TARGETS = {
         nvcc=["-O3", "-std=c++17", "-DCUDA_HAS_FP16=1", "-D__CUDA_NO_HALF_OPERATORS__",
               "-D__CUDA_NO_HALF_CONVERSIONS__", "-D__CUDA_NO_HALF2_OPERATORS__", "-use_fast_math"],
         cxx=["-O3", "-std=c++17"],
+    ),
+    "ref_ssim_C": dict(
+        root="submodules/fused-ssim",
+        sources=["ssim.cu", "ext.cpp"],
+        include=[],
+        nvcc=[],
+        cxx=[],
     ),
 }
 

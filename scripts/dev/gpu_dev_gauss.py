@@ -1,6 +1,8 @@
 #!/usr/bin/env python
 """Developer tool (GPU box): 3DGS path, this repo vs the reference extension (oracle/_ref/ref_gauss_C).
   python tests/gpu_dev_gauss.py tiny small c1 [--aa]"""
+import os, sys
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "..", "tests"))
 import sys
 
 import torch

@@ -1,4 +1,6 @@
 """Dev harness (GPU): per-stage device time of one 3DGS fwd+bwd on a config."""
+import os, sys
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "..", "tests"))
 import sys
 import torch
 import harness as hz

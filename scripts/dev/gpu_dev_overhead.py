@@ -1,4 +1,6 @@
 """Dev harness (GPU): host enqueue time vs device time of one fwd+bwd on a small config."""
+import os, sys
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "..", "tests"))
 import sys, time
 import torch
 import harness as hz

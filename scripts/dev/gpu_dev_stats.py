@@ -1,5 +1,7 @@
 """Dev harness (GPU): workload statistics of a scene -- list lengths, early-termination depth,
 hit-mask density -- to see where the compositing kernels spend their pair evaluations."""
+import os, sys
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "..", "tests"))
 import sys
 import torch
 import harness as hz

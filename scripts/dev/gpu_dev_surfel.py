@@ -4,6 +4,8 @@
 
   python tests/gpu_dev_surfel.py small c1 c3 [--no-ref] [--iters 5]
 """
+import os, sys
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "..", "tests"))
 import json
 import sys
 import time
