@@ -66,10 +66,20 @@ __global__ void __launch_bounds__(SS_THREADS) ssim_fwd_kernel(int H, int W, floa
   const float* p1 = img1 + plane;
   const float* p2 = img2 + plane;
 
-  for (int e = t; e < SS_SH * SS_SW; e += SS_THREADS) {
-    const int ly = e / SS_SW, lx = e - ly * SS_SW;
-    sm.in[0][ly][lx] = plane_at(p1, y0 + ly - SS_R, x0 + lx - SS_R, H, W);
-    sm.in[1][ly][lx] = plane_at(p2, y0 + ly - SS_R, x0 + lx - SS_R, H, W);
+  {   // stage both tiles: all of a thread's loads are issued before the first store waits on one
+    constexpr int IT = (SS_SH * SS_SW + SS_THREADS - 1) / SS_THREADS;
+    float r1[IT], r2[IT];
+#pragma unroll
+    for (int k = 0; k < IT; ++k) {
+      const int e = t + k * SS_THREADS, ly = e / SS_SW, lx = e - ly * SS_SW;
+      r1[k] = plane_at(p1, y0 + ly - SS_R, x0 + lx - SS_R, H, W);
+      r2[k] = plane_at(p2, y0 + ly - SS_R, x0 + lx - SS_R, H, W);
+    }
+#pragma unroll
+    for (int k = 0; k < IT; ++k) {
+      const int e = t + k * SS_THREADS, ly = e / SS_SW, lx = e - ly * SS_SW;
+      if (e < SS_SH * SS_SW) { sm.in[0][ly][lx] = r1[k]; sm.in[1][ly][lx] = r2[k]; }
+    }
   }
   __syncthreads();
   // horizontal pass: four consecutive outputs of a staged row per work item, all five quantities from one
@@ -136,13 +146,21 @@ __global__ void __launch_bounds__(SS_THREADS) ssim_bwd_kernel(int H, int W, cons
   const float* pb = dm_dsigma1_sq + plane;
   const float* pc = dm_dsigma12 + plane;
 
-  for (int e = t; e < SS_SH * SS_SW; e += SS_THREADS) {
-    const int ly = e / SS_SW, lx = e - ly * SS_SW;
-    const int y = y0 + ly - SS_R, x = x0 + lx - SS_R;
-    const float dl = plane_at(pl, y, x, H, W);
-    sm.in[0][ly][lx] = dl * plane_at(pa, y, x, H, W);
-    sm.in[1][ly][lx] = dl * plane_at(pb, y, x, H, W);
-    sm.in[2][ly][lx] = dl * plane_at(pc, y, x, H, W);
+  {
+    constexpr int IT = (SS_SH * SS_SW + SS_THREADS - 1) / SS_THREADS;
+    float rl[IT], ra[IT], rb[IT], rc[IT];
+#pragma unroll
+    for (int k = 0; k < IT; ++k) {
+      const int e = t + k * SS_THREADS, ly = e / SS_SW, lx = e - ly * SS_SW;
+      const int y = y0 + ly - SS_R, x = x0 + lx - SS_R;
+      rl[k] = plane_at(pl, y, x, H, W); ra[k] = plane_at(pa, y, x, H, W);
+      rb[k] = plane_at(pb, y, x, H, W); rc[k] = plane_at(pc, y, x, H, W);
+    }
+#pragma unroll
+    for (int k = 0; k < IT; ++k) {
+      const int e = t + k * SS_THREADS, ly = e / SS_SW, lx = e - ly * SS_SW;
+      if (e < SS_SH * SS_SW) { sm.in[0][ly][lx] = rl[k] * ra[k]; sm.in[1][ly][lx] = rl[k] * rb[k]; sm.in[2][ly][lx] = rl[k] * rc[k]; }
+    }
   }
   __syncthreads();
   for (int e = t; e < SS_SH * (SS_TW / 4); e += SS_THREADS) {
