@@ -275,6 +275,166 @@ __global__ void __launch_bounds__(256) cubemap_bwd_kernel(const float* __restric
   grad_inputs[3 * (size_t)n] = gsum[0]; grad_inputs[3 * (size_t)n + 1] = gsum[1]; grad_inputs[3 * (size_t)n + 2] = gsum[2];
 }
 
+// ------------------------------------------------------------------ fused reflection shading
+// SURVEY.md section 8f, "next" row 2 (first half): the reflection pass the fork adds around the
+// rasterizer, gaussian_renderer/__init__.py:22-35 and :199-201, as ONE pixel kernel each way:
+//   rays_d = sample_camera_rays(HWK, R, T)            utils/general_utils.py:177-197
+//   refl   = rays_d - 2 n (rays_d . n)                 reflection(), gaussian_renderer/__init__.py:22-24
+//   env    = sigmoid(env_map(refl))                    sample_cubemap_color(), :26-30 (cubemap lookup above)
+//   final  = (1 - r) base + r env                      :201
+// where the reference runs ~12 full-image torch kernels and the [C,B] cubemap kernel.  Three channels.
+struct ShadeCam {
+  float kinv[9];   // inverse intrinsics, row major: pixel_camera = Kinv (x, y, 1)
+  float rot[9];    // the camera's stored R (3DGS keeps it transposed), row major: used as R p
+  float t[3];
+};
+
+__device__ __forceinline__ void shade_ray(const ShadeCam& c, int x, int y, float d[3]) {
+  const float px = float(x), py = float(y);
+  // pixel_camera = xy1 @ inv(K).T ; pixel_world = (pixel_camera - T) @ R.T' ; rays_o = -R'.T @ T  (R' = R.T)
+  const float pc[3] = {c.kinv[0] * px + c.kinv[1] * py + c.kinv[2], c.kinv[3] * px + c.kinv[4] * py + c.kinv[5],
+                       c.kinv[6] * px + c.kinv[7] * py + c.kinv[8]};
+  const float q[3] = {pc[0] - c.t[0], pc[1] - c.t[1], pc[2] - c.t[2]};
+  float w[3];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    const float pw = c.rot[3 * i] * q[0] + c.rot[3 * i + 1] * q[1] + c.rot[3 * i + 2] * q[2];
+    const float ro = -(c.rot[3 * i] * c.t[0] + c.rot[3 * i + 1] * c.t[1] + c.rot[3 * i + 2] * c.t[2]);
+    w[i] = pw - ro;
+  }
+  const float inv = 1.0f / sqrtf(w[0] * w[0] + w[1] * w[1] + w[2] * w[2]);
+  d[0] = w[0] * inv; d[1] = w[1] * inv; d[2] = w[2] * inv;
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(256) reflect_shade_fwd_kernel(const ShadeCam cam, int H, int W, const float* __restrict__ normal,
+                                                                const float* __restrict__ base, const float* __restrict__ refl,
+                                                                const float* __restrict__ cubemap, const float* __restrict__ fail,
+                                                                int L, float* __restrict__ out_final, float* __restrict__ out_env) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  const int N = H * W;
+  if (n >= N) return;
+  const int y = n / W, x = n - y * W;
+  float d[3];
+  shade_ray(cam, x, y, d);
+  const float nx = normal[3 * (size_t)n], ny = normal[3 * (size_t)n + 1], nz = normal[3 * (size_t)n + 2];
+  const float dn = d[0] * nx + d[1] * ny + d[2] * nz;
+  const float rx = d[0] - 2.f * nx * dn, ry = d[1] - 2.f * ny * dn, rz = d[2] - 2.f * nz * dn;
+  float e[3];
+  if (rx == 0.f && ry == 0.f && rz == 0.f) {
+    e[0] = fail[0]; e[1] = fail[1]; e[2] = fail[2];
+  } else {
+    const Taps t = make_taps<MODE>(rx, ry, rz, 3, L);
+    const int cs = L * L;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const float* tex = cubemap + (size_t)c * cs;
+      if (MODE == 0) { e[c] = tex[t.off[0]]; continue; }
+      const float v00 = tex[t.off[0]], v01 = tex[t.off[1]], v10 = tex[t.off[2]];
+      const float v11 = t.vertex ? (v00 + v01 + v10) / 3.f : tex[t.off[3]];
+      e[c] = (1 - t.ky) * ((1 - t.kx) * v00 + t.kx * v01) + t.ky * ((1 - t.kx) * v10 + t.kx * v11);
+    }
+  }
+  const float r = refl[n];
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    const float env = 1.0f / (1.0f + expf(-e[c]));
+    out_env[(size_t)c * N + n] = env;
+    out_final[(size_t)c * N + n] = (1.0f - r) * base[(size_t)c * N + n] + r * env;
+  }
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(256) reflect_shade_bwd_kernel(const ShadeCam cam, int H, int W, const float* __restrict__ normal,
+                                                                const float* __restrict__ base, const float* __restrict__ refl,
+                                                                const float* __restrict__ cubemap, int L,
+                                                                const float* __restrict__ env, const float* __restrict__ g_final,
+                                                                const float* __restrict__ g_env, float* __restrict__ g_base,
+                                                                float* __restrict__ g_refl, float* __restrict__ g_normal,
+                                                                float* __restrict__ grad_cubemap, float* __restrict__ grad_fail) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  const int N = H * W;
+  const bool in_range = n < N;
+  float d[3] = {0.f, 0.f, 1.f}, nrm[3] = {0.f, 0.f, 0.f}, go[3] = {0.f, 0.f, 0.f};
+  float dn = 0.f, rx = 0.f, ry = 0.f, rz = 0.f;
+  if (in_range) {
+    const int y = n / W, x = n - y * W;
+    shade_ray(cam, x, y, d);
+    nrm[0] = normal[3 * (size_t)n]; nrm[1] = normal[3 * (size_t)n + 1]; nrm[2] = normal[3 * (size_t)n + 2];
+    dn = d[0] * nrm[0] + d[1] * nrm[1] + d[2] * nrm[2];
+    rx = d[0] - 2.f * nrm[0] * dn; ry = d[1] - 2.f * nrm[1] * dn; rz = d[2] - 2.f * nrm[2] * dn;
+    const float r = refl[n];
+    float gr = 0.f;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const float gf = g_final[(size_t)c * N + n], ev = env[(size_t)c * N + n], b = base[(size_t)c * N + n];
+      g_base[(size_t)c * N + n] = (1.0f - r) * gf;
+      gr += gf * (ev - b);
+      const float ge = r * gf + (g_env ? g_env[(size_t)c * N + n] : 0.f);
+      go[c] = ge * ev * (1.0f - ev);                         // through the sigmoid, down to the lookup's output
+    }
+    g_refl[n] = gr;
+  }
+  const bool zero = rx == 0.f && ry == 0.f && rz == 0.f;
+  if (in_range && zero) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) atomicAdd(grad_fail + c, go[c]);
+    g_normal[3 * (size_t)n] = 0.f; g_normal[3 * (size_t)n + 1] = 0.f; g_normal[3 * (size_t)n + 2] = 0.f;
+  }
+  const bool live = in_range && !zero;
+  const int cs = L * L;
+  Taps t;
+  t.off[0] = t.off[1] = t.off[2] = t.off[3] = -1;
+  t.kx = t.ky = 0.f; t.vertex = false; t.flag = 0; t.face = 0;
+  if (live) t = make_taps<MODE>(rx, ry, rz, 3, L);
+  float w[4];
+  if (MODE == 0) { w[0] = 1.f; w[1] = w[2] = w[3] = 0.f; }
+  else {
+    const float extra = t.vertex ? t.ky * t.kx / 3.f : 0.f;
+    w[0] = (1 - t.ky) * (1 - t.kx) + extra;
+    w[1] = (1 - t.ky) * t.kx + extra;
+    w[2] = t.ky * (1 - t.kx) + extra;
+    w[3] = t.vertex ? 0.f : t.ky * t.kx;
+  }
+  const int ntaps = MODE == 0 ? 1 : 4;
+  const unsigned active = __activemask();                   // whole warp: no early returns above
+  for (int k = 0; k < ntaps; ++k) {                         // warp-aggregated texture scatter, as in cubemap_bwd_kernel
+    const bool has = live && !(k == 3 && t.vertex);
+    const int key = has ? t.off[k] : -1 - (int)(threadIdx.x & 31);
+    const unsigned peers = __match_any_sync(active, key);
+    float v[3] = {w[k] * go[0], w[k] * go[1], w[k] * go[2]};
+    if (__any_sync(active, peers != (1u << (threadIdx.x & 31)))) peer_reduce<3>(active, peers, v);
+    if (has && (peers & ((1u << (threadIdx.x & 31)) - 1u)) == 0u) {
+#pragma unroll
+      for (int c = 0; c < 3; ++c) atomicAdd(grad_cubemap + (size_t)c * cs + key, v[c]);
+    }
+  }
+  if (!live) return;
+  float gd[3] = {0.f, 0.f, 0.f};                            // dL/d(reflected direction)
+  if (MODE != 0) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const float* tex = cubemap + (size_t)c * cs;
+      const float v00 = tex[t.off[0]], v01 = tex[t.off[1]], v10 = tex[t.off[2]];
+      const float v11 = t.vertex ? (v00 + v01 + v10) / 3.f : tex[t.off[3]];
+      float gu = (1 - t.ky) * (v01 - v00) + t.ky * (v11 - v10);
+      float gv = (1 - t.kx) * (v10 - v00) + t.kx * (v11 - v01);
+      gu *= 0.5f * float(L) * go[c];
+      gv *= 0.5f * float(L) * go[c];
+      if (t.flag & 1) gu = -gu;
+      if (t.flag & 4) gv = -gv;
+      gv = -gv;
+      float g3[3];
+      uv_backward(t.face, rx, ry, rz, gu, gv, g3);
+      gd[0] += g3[0]; gd[1] += g3[1]; gd[2] += g3[2];
+    }
+  }
+  // refl = d - 2 n (d.n):  dL/dn = -2 [ (d.n) gd + (gd.n) d ]
+  const float gn = gd[0] * nrm[0] + gd[1] * nrm[1] + gd[2] * nrm[2];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) g_normal[3 * (size_t)n + i] = -2.f * (dn * gd[i] + gn * d[i]);
+}
+
 }  // namespace b200gs
 
 using namespace b200gs;
@@ -332,6 +492,60 @@ int b200gs_cubemap_backward(const float* grad_outputs, const float* inputs, cons
   }
   if (mode == 1) return launch_bwd<1>(grad_outputs, cubemap, inputs, grad_cubemap, grad_inputs, grad_fail, B, (int)C, (int)L, s);
   return launch_bwd<2>(grad_outputs, cubemap, inputs, grad_cubemap, grad_inputs, grad_fail, B, (int)C, (int)L, s);
+}
+
+
+static int shade_cam(const float* Kinv, const float* R, const float* T, ShadeCam& c) {
+  if (!Kinv || !R || !T) return 1;
+  for (int i = 0; i < 9; ++i) { c.kinv[i] = Kinv[i]; c.rot[i] = R[i]; }
+  for (int i = 0; i < 3; ++i) c.t[i] = T[i];
+  return 0;
+}
+
+int b200gs_reflect_shade_forward(int H, int W, const float* Kinv, const float* R, const float* T, const float* normal,
+                                 const float* base_color, const float* refl_strength, const float* cubemap,
+                                 const float* fail_value, uint32_t L, uint32_t interp, uint32_t seamless, float* out_final,
+                                 float* out_env, void* stream) {
+  if (H < 0 || W < 0) { set_error("reflect_shade_forward: negative size"); return B200GS_EINVAL; }
+  if (H == 0 || W == 0) return B200GS_OK;
+  ShadeCam cam;
+  if (shade_cam(Kinv, R, T, cam) || !normal || !base_color || !refl_strength || !cubemap || !fail_value || !out_final || !out_env || L == 0) {
+    set_error("reflect_shade_forward: bad argument"); return B200GS_EINVAL; }
+  if ((uint64_t)6 * 3 * L * L >= 0x7fffffffull || (long long)H * W >= 0x7fffffffll) { set_error("reflect_shade_forward: too large"); return B200GS_EINVAL; }
+  cudaStream_t s = (cudaStream_t)stream;
+  StageScope _t(ST_SHADE_FWD, s);
+  const unsigned blocks = (unsigned)(((long long)H * W + 255) / 256);
+  switch (cubemap_mode(interp, seamless)) {
+    case 0: reflect_shade_fwd_kernel<0><<<blocks, 256, 0, s>>>(cam, H, W, normal, base_color, refl_strength, cubemap, fail_value, (int)L, out_final, out_env); break;
+    case 1: reflect_shade_fwd_kernel<1><<<blocks, 256, 0, s>>>(cam, H, W, normal, base_color, refl_strength, cubemap, fail_value, (int)L, out_final, out_env); break;
+    default: reflect_shade_fwd_kernel<2><<<blocks, 256, 0, s>>>(cam, H, W, normal, base_color, refl_strength, cubemap, fail_value, (int)L, out_final, out_env); break;
+  }
+  B200GS_LAUNCHED("reflect_shade_fwd_kernel", false, s);
+  return B200GS_OK;
+}
+
+int b200gs_reflect_shade_backward(int H, int W, const float* Kinv, const float* R, const float* T, const float* normal,
+                                  const float* base_color, const float* refl_strength, const float* cubemap, uint32_t L,
+                                  uint32_t interp, uint32_t seamless, const float* env_color, const float* dL_dfinal,
+                                  const float* dL_denv, float* dL_dbase, float* dL_drefl, float* dL_dnormal,
+                                  float* grad_cubemap, float* grad_fail, void* stream) {
+  if (H < 0 || W < 0) { set_error("reflect_shade_backward: negative size"); return B200GS_EINVAL; }
+  if (H == 0 || W == 0) return B200GS_OK;
+  ShadeCam cam;
+  if (shade_cam(Kinv, R, T, cam) || !normal || !base_color || !refl_strength || !cubemap || !env_color || !dL_dfinal || !dL_dbase ||
+      !dL_drefl || !dL_dnormal || !grad_cubemap || !grad_fail || L == 0) {
+    set_error("reflect_shade_backward: bad argument"); return B200GS_EINVAL; }
+  if ((uint64_t)6 * 3 * L * L >= 0x7fffffffull || (long long)H * W >= 0x7fffffffll) { set_error("reflect_shade_backward: too large"); return B200GS_EINVAL; }
+  cudaStream_t s = (cudaStream_t)stream;
+  StageScope _t(ST_SHADE_BWD, s);
+  const unsigned blocks = (unsigned)(((long long)H * W + 255) / 256);
+  switch (cubemap_mode(interp, seamless)) {
+    case 0: reflect_shade_bwd_kernel<0><<<blocks, 256, 0, s>>>(cam, H, W, normal, base_color, refl_strength, cubemap, (int)L, env_color, dL_dfinal, dL_denv, dL_dbase, dL_drefl, dL_dnormal, grad_cubemap, grad_fail); break;
+    case 1: reflect_shade_bwd_kernel<1><<<blocks, 256, 0, s>>>(cam, H, W, normal, base_color, refl_strength, cubemap, (int)L, env_color, dL_dfinal, dL_denv, dL_dbase, dL_drefl, dL_dnormal, grad_cubemap, grad_fail); break;
+    default: reflect_shade_bwd_kernel<2><<<blocks, 256, 0, s>>>(cam, H, W, normal, base_color, refl_strength, cubemap, (int)L, env_color, dL_dfinal, dL_denv, dL_dbase, dL_drefl, dL_dnormal, grad_cubemap, grad_fail); break;
+  }
+  B200GS_LAUNCHED("reflect_shade_bwd_kernel", false, s);
+  return B200GS_OK;
 }
 
 }  // extern "C"

@@ -191,6 +191,12 @@ ssim_forward = _sig("b200gs_ssim_forward", _i, _f, _f, _i, _i, _i, _i, _p, _p, _
 ssim_backward = _sig("b200gs_ssim_backward", _i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p)
 
 
+_fp = C.POINTER(_f)
+reflect_shade_forward = _sig("b200gs_reflect_shade_forward", _i, _i, _i, _fp, _fp, _fp, _p, _p, _p, _p, _p, _u, _u, _u, _p, _p, _p)
+reflect_shade_backward = _sig("b200gs_reflect_shade_backward", _i, _i, _i, _fp, _fp, _fp, _p, _p, _p, _p, _u, _u, _u, _p, _p, _p,
+                              _p, _p, _p, _p, _p, _p)
+
+
 def check(rc):
     """Map a C return code to an exception (the reference throws std::runtime_error
     -> Python RuntimeError; S/rasterize_points.cu:63-65, auxiliary.h:300-307)."""

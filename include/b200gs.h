@@ -351,6 +351,27 @@ int b200gs_ssim_backward(int B, int CH, int H, int W, const float* img1, const f
                          const float* dm_dmu1, const float* dm_dsigma1_sq, const float* dm_dsigma12, float* dL_dimg1,
                          void* stream);
 
+/* ------------------------------------------------------------------------ */
+/* Reflection shading ("next" row 2, first half): the reflection pass around the
+ * rasterizer as one pixel kernel each way -- get_refl_color() + the final blend,
+ * gaussian_renderer/__init__.py:22-35 and :199-201 with sample_camera_rays (utils/general_utils.py:177-197):
+ *   d = normalize(R ((Kinv (x, y, 1)) - T) + R T);  refl = d - 2 n (d.n);  env = sigmoid(cubemap(refl));
+ *   final = (1 - r) base + r env.
+ * Kinv, R, T are HOST pointers (9, 9, 3 floats, row major; R is the camera's stored R, i.e. the array the
+ * reference passes as `viewpoint_camera.R`).  normal [H,W,3]; base_color, out_final, env_color [3,H,W];
+ * refl_strength [1,H,W]; cubemap [6,3,L,L]; fail_value [3]; interp / seamless as for b200gs_cubemap_forward.
+ * backward: dL_denv (gradient arriving at the refl_color_map output) may be NULL; grad_cubemap
+ * [6,3,L,L] and grad_fail [3] must be zero-filled by the caller; the other gradients are fully written. */
+int b200gs_reflect_shade_forward(int H, int W, const float* Kinv, const float* R, const float* T, const float* normal,
+                                 const float* base_color, const float* refl_strength, const float* cubemap,
+                                 const float* fail_value, uint32_t L, uint32_t interp, uint32_t seamless, float* out_final,
+                                 float* out_env, void* stream);
+int b200gs_reflect_shade_backward(int H, int W, const float* Kinv, const float* R, const float* T, const float* normal,
+                                  const float* base_color, const float* refl_strength, const float* cubemap, uint32_t L,
+                                  uint32_t interp, uint32_t seamless, const float* env_color, const float* dL_dfinal,
+                                  const float* dL_denv, float* dL_dbase, float* dL_drefl, float* dL_dnormal,
+                                  float* grad_cubemap, float* grad_fail, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
