@@ -60,7 +60,7 @@ def parse():
     ap.add_argument("--exact-lists", action="store_true",
                     help="time the exact-lists mode (the reference's instance lists bit for bit) instead of the "
                          "default culled emission")
-    ap.add_argument("--cpu-sample-tiles", type=int, default=8)
+    ap.add_argument("--cpu-sample-tiles", type=int, default=64)
     ap.add_argument("--cpu-sample-len", type=int, default=600, help="list positions walked per sampled tile")
     return ap.parse_args()
 
