@@ -197,6 +197,10 @@ reflect_shade_backward = _sig("b200gs_reflect_shade_backward", _i, _i, _i, _fp, 
                               _p, _p, _p, _p, _p, _p)
 
 
+surface_forward = _sig("b200gs_surface_forward", _i, _i, _i, _p, _fp, _fp, _fp, _f, _p, _p, _p, _p)
+surface_backward = _sig("b200gs_surface_backward", _i, _i, _i, _p, _fp, _fp, _fp, _f, _p, _p, _p, _p, _p, _p)
+
+
 def check(rc):
     """Map a C return code to an exception (the reference throws std::runtime_error
     -> Python RuntimeError; S/rasterize_points.cu:63-65, auxiliary.h:300-307)."""

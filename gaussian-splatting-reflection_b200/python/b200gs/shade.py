@@ -77,3 +77,58 @@ def reflect_shade(env_map, HWK, R, T, normal_map, base_color, refl_strength_map,
     cam = cam if cam is not None else camera_constants(HWK, R, T)
     return _ReflectShade.apply(normal_map, base_color, refl_strength_map, params["Cubemap_texture"], params["Cubemap_failv"], cam,
                                int(getattr(env_map, "interp_id", 1)), int(getattr(env_map, "seamless", 1)))
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Surface attributes (second half of row 2): gaussian_renderer/__init__.py:143-183
+class _SurfaceAttributes(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, allmap, cam, depth_ratio):
+        if not (allmap.is_cuda and allmap.dtype == torch.float32 and allmap.dim() == 3 and allmap.shape[0] == 8):
+            raise RuntimeError("allmap must be an fp32 CUDA tensor [8, H, W] (there is no CPU path)")
+        allmap = allmap.contiguous()
+        H, W = allmap.shape[1], allmap.shape[2]
+        normal = torch.empty((H, W, 3), dtype=torch.float32, device=allmap.device)
+        surf_depth = torch.empty((1, H, W), dtype=torch.float32, device=allmap.device)
+        surf_normal = torch.empty((3, H, W), dtype=torch.float32, device=allmap.device)
+        (_, mp), (_, ap), (_, op) = cam
+        _b.check(_b.surface_forward(H, W, _b.ptr(allmap), mp, ap, op, float(depth_ratio), _b.ptr(normal), _b.ptr(surf_depth),
+                                    _b.ptr(surf_normal), torch.cuda.current_stream().cuda_stream))
+        ctx.save_for_backward(allmap, surf_depth)
+        ctx.cam, ctx.ratio = cam, float(depth_ratio)
+        return normal, surf_depth, surf_normal
+
+    @staticmethod
+    def backward(ctx, g_normal, g_depth, g_sn):
+        allmap, surf_depth = ctx.saved_tensors
+        H, W = allmap.shape[1], allmap.shape[2]
+        g_all = torch.empty_like(allmap)
+        (_, mp), (_, ap), (_, op) = ctx.cam
+        cont = lambda t: None if t is None else t.contiguous()   # noqa: E731
+        g_normal, g_depth, g_sn = cont(g_normal), cont(g_depth), cont(g_sn)
+        _b.check(_b.surface_backward(H, W, _b.ptr(allmap), mp, ap, op, ctx.ratio, _b.ptr(surf_depth), _b.ptr(g_normal),
+                                     _b.ptr(g_depth), _b.ptr(g_sn), _b.ptr(g_all), torch.cuda.current_stream().cuda_stream))
+        return g_all, None, None
+
+
+def surface_camera_constants(world_view_transform, full_proj_transform, W, H):
+    """Host constants of depths_to_points (utils/point_utils.py:9-24) for one camera: the stored view rotation,
+    the ray matrix A (rays_d = (x, y, 1) @ A) and rays_o.  Keep the result; it owns the memory."""
+    wvt = np.asarray(world_view_transform.detach().cpu() if isinstance(world_view_transform, torch.Tensor) else world_view_transform, np.float64)
+    fpt = np.asarray(full_proj_transform.detach().cpu() if isinstance(full_proj_transform, torch.Tensor) else full_proj_transform, np.float64)
+    c2w = np.linalg.inv(wvt.T)
+    ndc2pix = np.array([[W / 2, 0, 0, W / 2], [0, H / 2, 0, H / 2], [0, 0, 0, 1]], np.float64).T
+    intrins = ((c2w.T @ fpt) @ ndc2pix)[:3, :3].T
+    A = np.linalg.inv(intrins).T @ c2w[:3, :3].T
+    return _host9(wvt[:3, :3], 9), _host9(A, 9), _host9(c2w[:3, 3], 3)
+
+
+def surface_attributes(allmap, viewpoint_camera, depth_ratio, cam=None):
+    """-> dict with the renderer's names: rend_alpha [1,H,W], rend_normal [3,H,W] (normalised, world space; the [H,W,3]
+    layout the reflection pass wants is `render_normal_hw3`), rend_dist, surf_depth, surf_normal, env_scope_mask."""
+    if cam is None:
+        cam = surface_camera_constants(viewpoint_camera.world_view_transform, viewpoint_camera.full_proj_transform,
+                                       int(viewpoint_camera.image_width), int(viewpoint_camera.image_height))
+    normal, surf_depth, surf_normal = _SurfaceAttributes.apply(allmap, cam, depth_ratio)
+    return {"rend_alpha": allmap[1:2], "render_normal_hw3": normal, "rend_normal": normal.permute(2, 0, 1), "rend_dist": allmap[6:7],
+            "surf_depth": surf_depth, "surf_normal": surf_normal, "env_scope_mask": allmap[7:8]}

@@ -372,6 +372,22 @@ int b200gs_reflect_shade_backward(int H, int W, const float* Kinv, const float* 
                                   const float* dL_denv, float* dL_dbase, float* dL_drefl, float* dL_dnormal,
                                   float* grad_cubemap, float* grad_fail, void* stream);
 
+/* Surface attributes from the rasterizer's auxiliary planes ("next" row 2, second half):
+ * gaussian_renderer/__init__.py:143-183 with depths_to_points / depth_to_normal (utils/point_utils.py:9-37).
+ * allmap [8,H,W] as the rasterizer returns it.  HOST constants of the camera, row major:
+ *   view3x3 = world_view_transform[:3,:3] (as stored);  raymat A with rays_d = (x, y, 1) @ A
+ *   (= intrins.inverse().T @ c2w[:3,:3].T of point_utils.py:20);  rays_o = c2w[:3,3].
+ * forward:  out_normal [H,W,3] = rotated view normal / (norm + 1e-6);  out_surf_depth [H,W] = expected depth
+ *   (allmap[0] / clamp(alpha, 1e-3)) blended with the median depth by depth_ratio, NaN/inf -> 0;
+ *   out_surf_normal [3,H,W] = depth_to_normal(surf_depth) * alpha (alpha detached, border pixels zero).
+ * backward: any of the three upstream gradients may be NULL; dL_dallmap [8,H,W] is fully written (planes 6, 7
+ *   zero: rend_dist and the scope mask are plain slices of allmap and get their gradient from autograd). */
+int b200gs_surface_forward(int H, int W, const float* allmap, const float* view3x3, const float* raymat, const float* rays_o,
+                           float depth_ratio, float* out_normal, float* out_surf_depth, float* out_surf_normal, void* stream);
+int b200gs_surface_backward(int H, int W, const float* allmap, const float* view3x3, const float* raymat, const float* rays_o,
+                            float depth_ratio, const float* surf_depth, const float* dL_dnormal, const float* dL_dsurf_depth,
+                            const float* dL_dsurf_normal, float* dL_dallmap, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

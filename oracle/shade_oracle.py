@@ -64,3 +64,48 @@ def reflect_shade(texture, failv, HWK, R, T, normal_map, base_color, refl_streng
     refl_color = outcolor.reshape(H, W, 3).permute(2, 0, 1)
     final_image = (1 - refl_strength_map) * base_color + refl_strength_map * refl_color
     return final_image, refl_color
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Surface attributes: gaussian_renderer/__init__.py:143-183 with utils/point_utils.py:9-37, restated line by line.
+# The reference module imports cv2 / matplotlib / the CUDA rasterizer and calls .cuda(), so it cannot be imported
+# here either: PARITY UNPINNED for these lines too (see the header).
+def depths_to_points(world_view_transform, full_proj_transform, W, H, depthmap):
+    dt = depthmap.dtype
+    wvt, fpt = world_view_transform.to(dt), full_proj_transform.to(dt)
+    c2w = (wvt.T).inverse()
+    ndc2pix = torch.tensor([[W / 2, 0, 0, (W) / 2], [0, H / 2, 0, (H) / 2], [0, 0, 0, 1]], dtype=dt).T
+    projection_matrix = c2w.T @ fpt
+    intrins = (projection_matrix @ ndc2pix)[:3, :3].T
+    grid_x, grid_y = torch.meshgrid(torch.arange(W, dtype=dt), torch.arange(H, dtype=dt), indexing="xy")
+    points = torch.stack([grid_x, grid_y, torch.ones_like(grid_x)], dim=-1).reshape(-1, 3)
+    rays_d = points @ intrins.inverse().T @ c2w[:3, :3].T
+    rays_o = c2w[:3, 3]
+    return depthmap.reshape(-1, 1) * rays_d + rays_o
+
+
+def depth_to_normal(world_view_transform, full_proj_transform, W, H, depth):
+    points = depths_to_points(world_view_transform, full_proj_transform, W, H, depth).reshape(*depth.shape[1:], 3)
+    output = torch.zeros_like(points)
+    dx = torch.cat([points[2:, 1:-1] - points[:-2, 1:-1]], dim=0)
+    dy = torch.cat([points[1:-1, 2:] - points[1:-1, :-2]], dim=1)
+    normal_map = torch.nn.functional.normalize(torch.cross(dx, dy, dim=-1), dim=-1)
+    output[1:-1, 1:-1, :] = normal_map
+    return output
+
+
+def surface_attributes(allmap, world_view_transform, full_proj_transform, depth_ratio):
+    """allmap [8,H,W] (torch, CPU) -> (render_normal [H,W,3], surf_depth [1,H,W], surf_normal [3,H,W])."""
+    H, W = allmap.shape[1:]
+    render_alpha = allmap[1:2]
+    render_normal = allmap[2:5]
+    render_normal = (render_normal.permute(1, 2, 0) @ (world_view_transform.to(allmap.dtype)[:3, :3].T)).permute(2, 0, 1)
+    render_depth_median = torch.nan_to_num(allmap[5:6], 0, 0)
+    render_depth_expected = allmap[0:1] / torch.clamp(render_alpha, min=1e-3)
+    render_depth_expected = torch.nan_to_num(render_depth_expected, 0, 0)
+    surf_depth = render_depth_expected * (1 - depth_ratio) + depth_ratio * render_depth_median
+    surf_normal = depth_to_normal(world_view_transform, full_proj_transform, W, H, surf_depth).permute(2, 0, 1)
+    surf_normal = surf_normal * render_alpha.detach()
+    render_normal = render_normal.permute(1, 2, 0)
+    render_normal = render_normal / (torch.norm(render_normal, dim=-1, keepdim=True) + 1e-6)
+    return render_normal, surf_depth, surf_normal

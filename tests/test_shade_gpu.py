@@ -128,3 +128,76 @@ def test_errors_and_empty():
     with pytest.raises(RuntimeError):
         reflect_shade(_Env(tex.cuda()[:, :2], fail.cuda()), HWK, R, T, n.cuda(), base.cuda(), r.cuda())
     assert b200gs.reflect_shade_forward(4, 4, None, None, None, None, None, None, None, None, 4, 1, 1, None, None, None) != 0
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# surface attributes (second half of row 2)
+def _view(H, W, seed=0):
+    """world_view_transform / full_proj_transform in the transposed storage of scene/cameras.py."""
+    import scenes
+    cam = scenes.make_camera((2.5 + 0.1 * seed, 1.0, 1.5), W, H, fovx=0.9)
+    return torch.from_numpy(cam["viewmatrix"]).reshape(4, 4).clone(), torch.from_numpy(cam["projmatrix"]).reshape(4, 4).clone()
+
+
+def _allmap(H, W, seed):
+    g = torch.Generator().manual_seed(seed)
+    yy, xx = torch.meshgrid(torch.arange(H, dtype=torch.float32), torch.arange(W, dtype=torch.float32), indexing="ij")
+    alpha = 0.2 + 0.8 * torch.rand((H, W), generator=g)
+    depth = 3.0 + 0.5 * torch.sin(xx / 7.0) + 0.4 * torch.cos(yy / 5.0) + 0.05 * torch.rand((H, W), generator=g)
+    a = torch.zeros((8, H, W))
+    a[0], a[1] = depth * alpha, alpha
+    a[2:5] = torch.randn((3, H, W), generator=g) * alpha
+    a[5] = depth + 0.1 * torch.rand((H, W), generator=g)
+    a[6], a[7] = torch.rand((H, W), generator=g), (torch.rand((H, W), generator=g) > 0.5).float()
+    a[1, 2, 3] = 1e-4                 # below the clamp
+    a[1, 4, 4], a[0, 4, 4] = 0.0, 0.0
+    a[2:5, 5, 5] = 0.0                # zero normal
+    return a
+
+
+@pytest.mark.parametrize("H,W,ratio", [(23, 31, 0.0), (16, 40, 1.0), (12, 12, 0.3)])
+def test_surface_attributes_against_cpu_oracle(H, W, ratio):
+    from b200gs.shade import _SurfaceAttributes, surface_camera_constants
+    from oracle import shade_oracle as so
+    wvt, fpt = _view(H, W, H)
+    a = _allmap(H, W, H + W)
+    ups = [torch.randn(s, generator=torch.Generator().manual_seed(k)) for k, s in enumerate(((H, W, 3), (1, H, W), (3, H, W)))]
+    ao = a.double().requires_grad_(True)
+    outs_o = so.surface_attributes(ao, wvt.double(), fpt.double(), ratio)
+    sum((o * u.double()).sum() for o, u in zip(outs_o, ups)).backward()
+    ad = a.cuda().requires_grad_(True)
+    outs_n = _SurfaceAttributes.apply(ad, surface_camera_constants(wvt, fpt, W, H), ratio)
+    sum((o * u.cuda()).sum() for o, u in zip(outs_n, ups)).backward()
+    for name, n_, o_ in zip(("render_normal", "surf_depth", "surf_normal"), outs_n, outs_o):
+        err = float((n_.detach().cpu().double() - o_.detach()).abs().max())
+        assert err <= 2e-4 * max(1.0, float(o_.detach().abs().max())), (name, err)
+    ref = ao.grad
+    for ch in range(8):
+        err = float((ad.grad[ch].cpu().double() - ref[ch]).abs().max())
+        assert err <= 2e-3 * float(ref[ch].abs().max()) + 1e-6, (ch, err, float(ref[ch].abs().max()))
+
+
+def test_surface_attributes_against_torch_lines_on_device():
+    """The reference's lines (restated in oracle/shade_oracle.py) run as fp32 torch ops on the GPU at 800x800."""
+    from b200gs.shade import _SurfaceAttributes, surface_camera_constants
+    from oracle import shade_oracle as so
+    H = W = 800
+    wvt, fpt = _view(H, W, 1)
+    a = _allmap(H, W, 9)
+    ups = [torch.randn(s, generator=torch.Generator().manual_seed(k)).cuda() for k, s in enumerate(((H, W, 3), (1, H, W), (3, H, W)))]
+    torch.set_default_device("cuda")
+    try:
+        ar = a.cuda().requires_grad_(True)
+        outs_r = so.surface_attributes(ar, wvt.cuda(), fpt.cuda(), 0.5)
+        sum((o * u).sum() for o, u in zip(outs_r, ups)).backward()
+    finally:
+        torch.set_default_device("cpu")
+    ad = a.cuda().requires_grad_(True)
+    outs_n = _SurfaceAttributes.apply(ad, surface_camera_constants(wvt, fpt, W, H), 0.5)
+    sum((o * u).sum() for o, u in zip(outs_n, ups)).backward()
+    for name, n_, r_ in zip(("render_normal", "surf_depth", "surf_normal"), outs_n, outs_r):
+        assert float((n_ - r_).abs().max()) <= 1e-3 * max(1.0, float(r_.abs().max())), name    # fp32 cross products of nearby points
+    for ch in range(8):
+        d = (ad.grad[ch] - ar.grad[ch]).abs()
+        tol = 1e-2 * float(ar.grad[ch].abs().max()) + 1e-6
+        assert float((d > tol).float().mean()) <= 1e-3, (ch, float(d.max()), tol)
