@@ -106,8 +106,59 @@ def run(H, W, L=128):
     return out
 
 
+def run_surface(H, W):
+    """Surface attributes (gaussian_renderer/__init__.py:143-183): fused kernels vs the torch lines on the device."""
+    import b200gs
+    from b200gs.shade import _SurfaceAttributes, surface_camera_constants
+    from oracle import shade_oracle as so
+    from test_shade_gpu import _allmap, _view
+    wvt, fpt = _view(H, W, 1)
+    a = _allmap(H, W, 9)
+    ups = [torch.randn(s, generator=torch.Generator().manual_seed(k)).cuda() for k, s in enumerate(((H, W, 3), (1, H, W), (3, H, W)))]
+    ar, ad = a.cuda().requires_grad_(True), a.cuda().requires_grad_(True)
+    wv, fp = wvt.cuda(), fpt.cuda()
+    cam = surface_camera_constants(wvt, fpt, W, H)
+
+    def ref_path():
+        ar.grad = None
+        torch.set_default_device("cuda")
+        try:
+            outs = so.surface_attributes(ar, wv, fp, 0.5)
+        finally:
+            torch.set_default_device("cpu")
+        sum((o * u).sum() for o, u in zip(outs, ups)).backward()
+
+    def new_path():
+        ad.grad = None
+        outs = _SurfaceAttributes.apply(ad, cam, 0.5)
+        sum((o * u).sum() for o, u in zip(outs, ups)).backward()
+
+    ref_path(); new_path()
+    out = {"what": "surface_attributes", "H": H, "W": W}
+    d = (ad.grad - ar.grad).abs()
+    out["grad_frac_over_1e-2"] = float((d > 1e-2 * ar.grad.abs().max() + 1e-6).float().mean())
+    out["ref_ms"], out["new_ms"] = batch_timed(ref_path), batch_timed(new_path)
+    out["speedup"] = out["ref_ms"] / out["new_ms"]
+    b200gs.timing_enable(1)
+    b200gs.timing_read()
+    for _ in range(10):
+        new_path()
+    torch.cuda.synchronize()
+    st = b200gs.timing_read()
+    b200gs.timing_enable(0)
+    out["fwd_kernel_ms"], out["bwd_kernel_ms"] = st["surface_fwd"][0] / st["surface_fwd"][1], st["surface_bwd"][0] / st["surface_bwd"][1]
+    N = H * W
+    peak, _ = hbm_peak()
+    # forward: 6 planes in, 3 + 1 + 3 floats out (+ surf_depth re-read); backward: 6 planes + depth + 7 upstream in, 8 planes out
+    out["fwd_gbps"], out["bwd_gbps"] = 56 * N / out["fwd_kernel_ms"] / 1e6, 88 * N / out["bwd_kernel_ms"] / 1e6
+    out["fwd_hbm_frac"], out["bwd_hbm_frac"] = out["fwd_gbps"] / peak, out["bwd_gbps"] / peak
+    return out
+
+
 if __name__ == "__main__":
     a = [int(v) for v in sys.argv[1:]]
     for H, W in (list(zip(a[::2], a[1::2])) or [(1080, 1920), (800, 800)]):
         print(json.dumps(run(H, W)), flush=True)
+        torch.cuda.empty_cache()
+        print(json.dumps(run_surface(H, W)), flush=True)
         torch.cuda.empty_cache()
