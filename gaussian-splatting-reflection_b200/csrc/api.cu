@@ -133,7 +133,7 @@ int b200gs_timing_stages(void) { return ST_COUNT; }
 const char* b200gs_timing_stage_name(int stage) {
   static const char* names[ST_COUNT] = {"preprocess", "scan", "duplicate", "sort", "tile_ranges", "composite_fwd",
                                         "composite_bwd", "preprocess_bwd", "cubemap_fwd", "cubemap_bwd", "tile_hits", "depth_sort", "count_kept",
-                                        "adam", "densify_stats", "ssim_fwd", "ssim_bwd", "shade_fwd", "shade_bwd", "surface_fwd", "surface_bwd"};
+                                        "adam", "densify_stats", "ssim_fwd", "ssim_bwd", "shade_fwd", "shade_bwd", "surface_fwd", "surface_bwd", "scene_io"};
   return (stage >= 0 && stage < ST_COUNT) ? names[stage] : "";
 }
 int b200gs_timing_read(float* ms, unsigned long long* counts, int n) {

@@ -47,7 +47,7 @@ extern std::atomic<unsigned long long> g_launches;
 enum Stage {
   ST_PREPROCESS = 0, ST_SCAN, ST_DUPLICATE, ST_SORT, ST_RANGES, ST_COMPOSITE_FWD,
   ST_COMPOSITE_BWD, ST_PREPROCESS_BWD, ST_CUBEMAP_FWD, ST_CUBEMAP_BWD, ST_TILE_HITS, ST_DEPTH_SORT, ST_COUNT_KEPT,
-  ST_ADAM, ST_DENSIFY_STATS, ST_SSIM_FWD, ST_SSIM_BWD, ST_SHADE_FWD, ST_SHADE_BWD, ST_SURFACE_FWD, ST_SURFACE_BWD, ST_COUNT
+  ST_ADAM, ST_DENSIFY_STATS, ST_SSIM_FWD, ST_SSIM_BWD, ST_SHADE_FWD, ST_SHADE_BWD, ST_SURFACE_FWD, ST_SURFACE_BWD, ST_SCENE_IO, ST_COUNT
 };
 extern std::atomic<int> g_timing;        // 0 off, 1 every stage, 2 + k: stage k only
 extern std::atomic<int> g_cull_audit;   // surfel_composite_fwd.cu: b200gs_debug_cull_audit

@@ -201,6 +201,23 @@ surface_forward = _sig("b200gs_surface_forward", _i, _i, _i, _p, _fp, _fp, _fp, 
 surface_backward = _sig("b200gs_surface_backward", _i, _i, _i, _p, _fp, _fp, _fp, _f, _p, _p, _p, _p, _p, _p)
 
 
+PLY_MAX_FIELDS, PLY_MAX_COLUMNS = 8, 128
+
+
+class PlyField(C.Structure):
+    """struct b200gs_ply_field"""
+    _fields_ = [("data", _p), ("cols", _i), ("row_stride", _i), ("first", _i)]
+
+
+class PlyLayout(C.Structure):
+    """struct b200gs_ply_layout"""
+    _fields_ = [("stride", _i), ("n_fields", _i), ("field", PlyField * PLY_MAX_FIELDS), ("map", C.c_ubyte * PLY_MAX_COLUMNS)]
+
+
+ply_unpack = _sig("b200gs_ply_unpack", _i, C.c_longlong, _p, C.POINTER(PlyLayout), _p)
+ply_pack = _sig("b200gs_ply_pack", _i, C.c_longlong, C.POINTER(PlyLayout), _p, _p)
+
+
 def check(rc):
     """Map a C return code to an exception (the reference throws std::runtime_error
     -> Python RuntimeError; S/rasterize_points.cu:63-65, auxiliary.h:300-307)."""

@@ -388,6 +388,31 @@ int b200gs_surface_backward(int H, int W, const float* allmap, const float* view
                             float depth_ratio, const float* surf_depth, const float* dL_dnormal, const float* dL_dsurf_depth,
                             const float* dL_dsurf_normal, float* dL_dallmap, void* stream);
 
+/* ------------------------------------------------------------------------ */
+/* Scene IO ("next" row 4): the vertex records of point_cloud.ply <-> the per-Gaussian
+ * arrays, replacing the per-property numpy walk of GaussianModel.load_ply (scene/gaussian_model.py:296-373)
+ * and the concatenate + tuple list of save_ply (:239-257).  `records` is the DEVICE copy of the binary
+ * vertex block: P rows of `stride` little-endian fp32 properties, exactly the bytes after "end_header\n".
+ * A field is one destination array [P, cols] with `row_stride` floats between rows (row_stride > cols lets
+ * features_dc / features_rest be the two column ranges of ONE packed [P,K,3] SH block, the layout the
+ * preprocess kernels read); map[first + c] is the record column that holds column c of the field
+ * (e.g. features_rest[:, j, ch] <- property f_rest_{ch*(K-1)+j}).  Fields must list `first` consecutively.
+ * unpack: records -> fields (unmapped properties are skipped).
+ * pack:   fields -> records (unmapped properties, the reference's nx ny nz, are written as 0). */
+#define B200GS_PLY_MAX_FIELDS 8
+#define B200GS_PLY_MAX_COLUMNS 128
+typedef struct b200gs_ply_field {
+  float* data;
+  int cols, row_stride, first;
+} b200gs_ply_field;
+typedef struct b200gs_ply_layout {
+  int stride, n_fields;
+  b200gs_ply_field field[B200GS_PLY_MAX_FIELDS];
+  unsigned char map[B200GS_PLY_MAX_COLUMNS];
+} b200gs_ply_layout;
+int b200gs_ply_unpack(long long P, const float* records, const b200gs_ply_layout* layout, void* stream);
+int b200gs_ply_pack(long long P, const b200gs_ply_layout* layout, float* records, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
