@@ -18,6 +18,7 @@
 // in one read of the keys, match.any-aggregated shared-memory atomics).
 #include "common.cuh"
 #include "radix_sort.cuh"
+#include <stdlib.h>
 
 namespace b200gs {
 
@@ -149,71 +150,109 @@ struct PassArgs {
   uint32_t* ticket;
 };
 
-__global__ void __launch_bounds__(RS_THREADS) radix_pass_kernel(const PassArgs a) {
+// MODE 0: match.any per key inside the counter loop, values fetched during the reorder.
+// MODE 1: the RS_ITEMS match.any of a thread issued back to back (independent), values fetched with the keys.
+// MODE 2: as 1, with the peer masks built from one ballot per digit bit instead of match.any.
+template <int MODE>
+__device__ __forceinline__ unsigned digit_peers(uint32_t d, bool valid, int nbits) {
+  if (MODE != 2) return __match_any_sync(0xffffffffu, valid ? d : (uint32_t)RS_RADIX);
+  unsigned peers = __ballot_sync(0xffffffffu, valid);
+#pragma unroll
+  for (int b = 0; b < 8; ++b) {
+    if (b < nbits) {
+      const bool bit = (d >> b) & 1u;
+      const unsigned vote = __ballot_sync(0xffffffffu, bit);
+      peers &= bit ? vote : ~vote;
+    }
+  }
+  return peers;   // meaningful on valid lanes only
+}
+
+template <int MODE, int THREADS, int ITEMS>
+__global__ void __launch_bounds__(THREADS, THREADS == 256 ? 3 : 2) radix_pass_kernel(const PassArgs a) {
+  static_assert(THREADS * ITEMS == RS_TILE && THREADS >= RS_RADIX, "tile shape");
+  constexpr int WARPS = THREADS / 32;
   __shared__ uint32_t s_keys[RS_TILE];
   __shared__ uint32_t s_vals[RS_TILE];
-  __shared__ uint32_t s_cnt[RS_THREADS / 32][RS_RADIX];
+  __shared__ uint32_t s_cnt[WARPS][RS_RADIX];
   __shared__ uint32_t s_excl[RS_RADIX];    // exclusive prefix of the block's digit counts
   __shared__ uint32_t s_gbase[RS_RADIX];   // global position of local position 0 of each digit's run (mod 2^32)
-  __shared__ uint32_t s_wsum[RS_THREADS / 32];
+  __shared__ uint32_t s_wsum[RS_RADIX / 32];
   __shared__ uint32_t s_blk;
 
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const uint32_t dmask = (1u << a.nbits) - 1u;
   if (t == 0) s_blk = atomicAdd(a.ticket, 1u);
-#pragma unroll
-  for (int w = 0; w < RS_THREADS / 32; ++w) s_cnt[w][t] = 0u;
+  for (int e = t; e < WARPS * RS_RADIX; e += THREADS) (&s_cnt[0][0])[e] = 0u;
   __syncthreads();
   const uint32_t blk = s_blk;
   const int blk_base = (int)blk * RS_TILE;
-  const int wbase = blk_base + warp * (32 * RS_ITEMS);
+  const int wbase = blk_base + warp * (32 * ITEMS);
 
-  uint32_t key[RS_ITEMS], rank[RS_ITEMS];
+  uint32_t key[ITEMS], rank[ITEMS], val[MODE ? ITEMS : 1];
 #pragma unroll
-  for (int k = 0; k < RS_ITEMS; ++k) {
+  for (int k = 0; k < ITEMS; ++k) {
     const int i = wbase + k * 32 + lane;
     key[k] = i < a.n ? a.keys_in[i] : 0xffffffffu;
   }
-  uint32_t* cnt = s_cnt[warp];
+  if (MODE) {
 #pragma unroll
-  for (int k = 0; k < RS_ITEMS; ++k) {
+    for (int k = 0; k < ITEMS; ++k) {
+      const int i = wbase + k * 32 + lane;
+      val[k] = i < a.n ? a.vals_in[i] : 0u;
+    }
+  }
+  uint32_t* cnt = s_cnt[warp];
+  if (MODE) {
+#pragma unroll
+    for (int k = 0; k < ITEMS; ++k) {
+      const bool valid = wbase + k * 32 + lane < a.n;
+      rank[k] = digit_peers<MODE>((key[k] >> a.shift) & dmask, valid, a.nbits);   // peer mask for now
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < ITEMS; ++k) {
     const bool valid = wbase + k * 32 + lane < a.n;
-    const uint32_t d = valid ? ((key[k] >> a.shift) & dmask) : (uint32_t)RS_RADIX;
-    const unsigned peers = __match_any_sync(0xffffffffu, d);
+    const uint32_t d = (key[k] >> a.shift) & dmask;
+    const unsigned peers = MODE ? rank[k] : digit_peers<0>(d, valid, a.nbits);
     const int leader = __ffs(peers) - 1;
     uint32_t old = 0u;
     if (lane == leader && valid) { old = cnt[d]; cnt[d] = old + (uint32_t)__popc(peers); }
-    old = __shfl_sync(0xffffffffu, old, leader);
+    old = __shfl_sync(0xffffffffu, old, valid ? leader : lane);
     rank[k] = old + (uint32_t)__popc(peers & ((1u << lane) - 1u));
     __syncwarp();
   }
   __syncthreads();
 
-  // thread t owns digit t
-  uint32_t total = 0u;
-#pragma unroll
-  for (int w = 0; w < RS_THREADS / 32; ++w) {
-    const uint32_t c = s_cnt[w][t];
-    s_cnt[w][t] = total;          // offset of warp w's keys inside the digit's run
-    total += c;
-  }
+  // thread t < 256 owns digit t
   const int nb = 1 << a.nbits;
   volatile unsigned long long* st = a.state;
-  if (t < nb) st[(size_t)blk * nb + t] = ((blk == 0 ? 2ull : 1ull) << 62) | total;
-
-  uint32_t inc = total;
+  uint32_t total = 0u, excl = 0u;
+  if (t < RS_RADIX) {
 #pragma unroll
-  for (int d = 1; d < 32; d <<= 1) {
-    const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
-    if (lane >= d) inc += o;
+    for (int w = 0; w < WARPS; ++w) {
+      const uint32_t c = s_cnt[w][t];
+      s_cnt[w][t] = total;          // offset of warp w's keys inside the digit's run
+      total += c;
+    }
+    if (t < nb) st[(size_t)blk * nb + t] = ((blk == 0 ? 2ull : 1ull) << 62) | total;
+    uint32_t inc = total;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
+      if (lane >= d) inc += o;
+    }
+    if (lane == 31) s_wsum[warp] = inc;
+    excl = inc - total;
   }
-  if (lane == 31) s_wsum[warp] = inc;
   __syncthreads();
-  uint32_t woff = 0u;
+  if (t < RS_RADIX) {
+    uint32_t woff = 0u;
 #pragma unroll
-  for (int w = 0; w < RS_THREADS / 32; ++w) if (w < warp) woff += s_wsum[w];
-  const uint32_t excl = woff + inc - total;
-  s_excl[t] = excl;
+    for (int w = 0; w < RS_RADIX / 32; ++w) if (w < warp) woff += s_wsum[w];
+    excl += woff;
+    s_excl[t] = excl;
+  }
 
   if (t < nb) {
     uint32_t prev = 0u;
@@ -234,23 +273,34 @@ __global__ void __launch_bounds__(RS_THREADS) radix_pass_kernel(const PassArgs a
 
   // reorder through shared memory
 #pragma unroll
-  for (int k = 0; k < RS_ITEMS; ++k) {
+  for (int k = 0; k < ITEMS; ++k) {
     const int i = wbase + k * 32 + lane;
     if (i < a.n) {
       const uint32_t d = (key[k] >> a.shift) & dmask;
       const uint32_t pos = s_excl[d] + cnt[d] + rank[k];
       s_keys[pos] = key[k];
-      s_vals[pos] = a.vals_in[i];
+      s_vals[pos] = MODE ? val[k] : a.vals_in[i];
     }
   }
   __syncthreads();
   const int nvalid = min(RS_TILE, a.n - blk_base);
-  for (int p = t; p < nvalid; p += RS_THREADS) {
+  for (int p = t; p < nvalid; p += THREADS) {
     const uint32_t k = s_keys[p];
     const uint32_t g = s_gbase[(k >> a.shift) & dmask] + (uint32_t)p;
     a.keys_out[g] = k;
     a.vals_out[g] = s_vals[p];
   }
+}
+
+// Ranking variant of the pass kernel; B200GS_RADIX_RANK=0|1|2 overrides the default (development switch).
+static int radix_rank_mode() {
+  static int mode = -1;
+  if (mode < 0) {
+    const char* e = getenv("B200GS_RADIX_RANK");
+    mode = e ? atoi(e) : RS_DEFAULT_RANK_MODE;
+    if (mode < 0 || mode > 5) mode = RS_DEFAULT_RANK_MODE;
+  }
+  return mode;
 }
 
 int radix_sort_pairs_u32(uint32_t* keys_a, uint32_t* vals_a, uint32_t* keys_b, uint32_t* vals_b, int n,
@@ -268,7 +318,14 @@ int radix_sort_pairs_u32(uint32_t* keys_a, uint32_t* vals_a, uint32_t* keys_b, u
     a.state = ws_state(workspace);
     a.ticket = ws_tickets(workspace) + p;
     B200GS_CUDA(cudaMemsetAsync(a.state, 0, (size_t)blocks * ((size_t)1 << a.nbits) * sizeof(unsigned long long), s));
-    radix_pass_kernel<<<blocks, RS_THREADS, 0, s>>>(a);
+    switch (radix_rank_mode()) {   // 0-2: 256 threads x 16 keys, 3-5: 512 threads x 8 keys
+      case 0: radix_pass_kernel<0, 256, 16><<<blocks, 256, 0, s>>>(a); break;
+      case 2: radix_pass_kernel<2, 256, 16><<<blocks, 256, 0, s>>>(a); break;
+      case 3: radix_pass_kernel<0, 512, 8><<<blocks, 512, 0, s>>>(a); break;
+      case 4: radix_pass_kernel<1, 512, 8><<<blocks, 512, 0, s>>>(a); break;
+      case 5: radix_pass_kernel<2, 512, 8><<<blocks, 512, 0, s>>>(a); break;
+      default: radix_pass_kernel<1, 256, 16><<<blocks, 256, 0, s>>>(a); break;
+    }
     B200GS_LAUNCHED("radix_pass_kernel", debug, s);
     uint32_t* x;
     x = ki; ki = ko; ko = x;

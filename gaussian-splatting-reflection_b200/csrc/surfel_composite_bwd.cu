@@ -11,6 +11,7 @@
 // row (ACC_STRIDE floats per Gaussian).  Warps none of whose pixels touch a
 // Gaussian skip the reduction altogether.
 #include "surfel_composite.cuh"
+#include <stdlib.h>
 
 namespace b200gs {
 
@@ -32,7 +33,9 @@ struct CompBwdArgs {
 
 constexpr int BATCH = 256;
 
-__global__ void __launch_bounds__(BATCH, 2) surfel_composite_bwd_kernel(const CompBwdArgs a) {
+// MINB = resident CTAs per SM the register allocation is bounded for (2: 98 registers, 3: <= 80).
+template <int MINB>
+__global__ void __launch_bounds__(BATCH, MINB) surfel_composite_bwd_kernel(const CompBwdArgs a) {
   __shared__ SurfelRec s_rec[2][BATCH];
   __shared__ int s_id[2][BATCH];
   __shared__ uint32_t s_pos[2][BATCH];
@@ -262,7 +265,10 @@ int surfel_composite_backward(const b200gs_surfel_bwd& f, const SurfelGeom& g, c
   a.acc = acc;
   StageScope _t(ST_COMPOSITE_BWD, s);
   B200GS_CUDA(cudaMemsetAsync(acc, 0, (size_t)f.P * ACC_STRIDE * sizeof(float), s));
-  surfel_composite_bwd_kernel<<<a.gx * gy, BATCH, 0, s>>>(a);
+  static const int minb = []() { const char* e = getenv("B200GS_BWD_CTAS"); return e ? atoi(e) : 3; }();   // development switch
+  if (minb == 2) surfel_composite_bwd_kernel<2><<<a.gx * gy, BATCH, 0, s>>>(a);
+  else if (minb == 4) surfel_composite_bwd_kernel<4><<<a.gx * gy, BATCH, 0, s>>>(a);
+  else surfel_composite_bwd_kernel<3><<<a.gx * gy, BATCH, 0, s>>>(a);
   B200GS_LAUNCHED("surfel_composite_bwd_kernel", f.debug, s);
   return B200GS_OK;
 }
