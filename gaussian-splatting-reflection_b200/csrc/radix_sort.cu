@@ -19,6 +19,7 @@
 #include "common.cuh"
 #include "radix_sort.cuh"
 #include <stdlib.h>
+#include <type_traits>
 
 namespace b200gs {
 
@@ -174,7 +175,10 @@ __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 3 : 2) radix_pass_ke
   constexpr int WARPS = THREADS / 32;
   __shared__ uint32_t s_keys[RS_TILE];
   __shared__ uint32_t s_vals[RS_TILE];
-  __shared__ uint32_t s_cnt[WARPS][RS_RADIX];
+  // per-warp digit counters, then offsets inside the block's digit runs: < RS_TILE = 4096, so 16 bits do
+  // (and keep the 16-warp shape inside the 48 KB of static shared memory)
+  using cnt_t = typename std::conditional<(WARPS > 8), uint16_t, uint32_t>::type;
+  __shared__ cnt_t s_cnt[WARPS][RS_RADIX];
   __shared__ uint32_t s_excl[RS_RADIX];    // exclusive prefix of the block's digit counts
   __shared__ uint32_t s_gbase[RS_RADIX];   // global position of local position 0 of each digit's run (mod 2^32)
   __shared__ uint32_t s_wsum[RS_RADIX / 32];
@@ -183,7 +187,7 @@ __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 3 : 2) radix_pass_ke
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const uint32_t dmask = (1u << a.nbits) - 1u;
   if (t == 0) s_blk = atomicAdd(a.ticket, 1u);
-  for (int e = t; e < WARPS * RS_RADIX; e += THREADS) (&s_cnt[0][0])[e] = 0u;
+  for (int e = t; e < WARPS * RS_RADIX; e += THREADS) (&s_cnt[0][0])[e] = (cnt_t)0;
   __syncthreads();
   const uint32_t blk = s_blk;
   const int blk_base = (int)blk * RS_TILE;
@@ -202,7 +206,7 @@ __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 3 : 2) radix_pass_ke
       val[k] = i < a.n ? a.vals_in[i] : 0u;
     }
   }
-  uint32_t* cnt = s_cnt[warp];
+  cnt_t* cnt = s_cnt[warp];
   if (MODE) {
 #pragma unroll
     for (int k = 0; k < ITEMS; ++k) {
@@ -217,7 +221,7 @@ __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 3 : 2) radix_pass_ke
     const unsigned peers = MODE ? rank[k] : digit_peers<0>(d, valid, a.nbits);
     const int leader = __ffs(peers) - 1;
     uint32_t old = 0u;
-    if (lane == leader && valid) { old = cnt[d]; cnt[d] = old + (uint32_t)__popc(peers); }
+    if (lane == leader && valid) { old = cnt[d]; cnt[d] = (cnt_t)(old + (uint32_t)__popc(peers)); }
     old = __shfl_sync(0xffffffffu, old, valid ? leader : lane);
     rank[k] = old + (uint32_t)__popc(peers & ((1u << lane) - 1u));
     __syncwarp();
@@ -232,7 +236,7 @@ __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 3 : 2) radix_pass_ke
 #pragma unroll
     for (int w = 0; w < WARPS; ++w) {
       const uint32_t c = s_cnt[w][t];
-      s_cnt[w][t] = total;          // offset of warp w's keys inside the digit's run
+      s_cnt[w][t] = (cnt_t)total;   // offset of warp w's keys inside the digit's run
       total += c;
     }
     if (t < nb) st[(size_t)blk * nb + t] = ((blk == 0 ? 2ull : 1ull) << 62) | total;
