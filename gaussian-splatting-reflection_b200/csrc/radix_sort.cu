@@ -19,7 +19,6 @@
 #include "common.cuh"
 #include "radix_sort.cuh"
 #include <stdlib.h>
-#include <type_traits>
 
 namespace b200gs {
 
@@ -169,15 +168,13 @@ __device__ __forceinline__ unsigned digit_peers(uint32_t d, bool valid, int nbit
   return peers;   // meaningful on valid lanes only
 }
 
-template <int MODE, int THREADS, int ITEMS>
-__global__ void __launch_bounds__(THREADS, THREADS == 256 ? 3 : 2) radix_pass_kernel(const PassArgs a) {
+template <int MODE, int THREADS, int ITEMS, int LB>
+__global__ void __launch_bounds__(THREADS, 3) radix_pass_kernel(const PassArgs a) {
   static_assert(THREADS * ITEMS == RS_TILE && THREADS >= RS_RADIX, "tile shape");
   constexpr int WARPS = THREADS / 32;
   __shared__ uint32_t s_keys[RS_TILE];
   __shared__ uint32_t s_vals[RS_TILE];
-  // per-warp digit counters, then offsets inside the block's digit runs: < RS_TILE = 4096, so 16 bits do
-  // (and keep the 16-warp shape inside the 48 KB of static shared memory)
-  using cnt_t = typename std::conditional<(WARPS > 8), uint16_t, uint32_t>::type;
+  using cnt_t = uint32_t;   // per-warp digit counters, then offsets inside the block's digit runs
   __shared__ cnt_t s_cnt[WARPS][RS_RADIX];
   __shared__ uint32_t s_excl[RS_RADIX];    // exclusive prefix of the block's digit counts
   __shared__ uint32_t s_gbase[RS_RADIX];   // global position of local position 0 of each digit's run (mod 2^32)
@@ -261,13 +258,23 @@ __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 3 : 2) radix_pass_ke
   if (t < nb) {
     uint32_t prev = 0u;
     if (blk > 0) {
+      // Walk back over the preceding blocks' words, LB of them per step: the loads of one step are
+      // independent, so a walk over k aggregate-only predecessors costs k / LB memory round trips.
       long long look = (long long)blk - 1;
-      while (true) {
-        unsigned long long w;
-        do { w = st[(size_t)look * nb + t]; } while ((w >> 62) == 0ull);
-        prev += (uint32_t)w;
-        if ((w >> 62) == 2ull) break;
-        --look;
+      bool done = false;
+      while (!done) {
+        unsigned long long w[LB];
+#pragma unroll
+        for (int j = 0; j < LB; ++j) w[j] = look - j >= 0 ? st[(size_t)(look - j) * nb + t] : (2ull << 62);
+#pragma unroll
+        for (int j = 0; j < LB; ++j) {
+          if (!done) {
+            while ((w[j] >> 62) == 0ull) w[j] = st[(size_t)(look - j) * nb + t];
+            prev += (uint32_t)w[j];
+            done = (w[j] >> 62) == 2ull;
+          }
+        }
+        look -= LB;
       }
       st[(size_t)blk * nb + t] = (2ull << 62) | (unsigned long long)(prev + total);
     }
@@ -302,7 +309,7 @@ static int radix_rank_mode() {
   if (mode < 0) {
     const char* e = getenv("B200GS_RADIX_RANK");
     mode = e ? atoi(e) : RS_DEFAULT_RANK_MODE;
-    if (mode < 0 || mode > 5) mode = RS_DEFAULT_RANK_MODE;
+    if (mode < 0 || mode > 2) mode = RS_DEFAULT_RANK_MODE;
   }
   return mode;
 }
@@ -322,13 +329,17 @@ int radix_sort_pairs_u32(uint32_t* keys_a, uint32_t* vals_a, uint32_t* keys_b, u
     a.state = ws_state(workspace);
     a.ticket = ws_tickets(workspace) + p;
     B200GS_CUDA(cudaMemsetAsync(a.state, 0, (size_t)blocks * ((size_t)1 << a.nbits) * sizeof(unsigned long long), s));
-    switch (radix_rank_mode()) {   // 0-2: 256 threads x 16 keys, 3-5: 512 threads x 8 keys
-      case 0: radix_pass_kernel<0, 256, 16><<<blocks, 256, 0, s>>>(a); break;
-      case 2: radix_pass_kernel<2, 256, 16><<<blocks, 256, 0, s>>>(a); break;
-      case 3: radix_pass_kernel<0, 512, 8><<<blocks, 512, 0, s>>>(a); break;
-      case 4: radix_pass_kernel<1, 512, 8><<<blocks, 512, 0, s>>>(a); break;
-      case 5: radix_pass_kernel<2, 512, 8><<<blocks, 512, 0, s>>>(a); break;
-      default: radix_pass_kernel<1, 256, 16><<<blocks, 256, 0, s>>>(a); break;
+    static const int lb = []() { const char* e = getenv("B200GS_RADIX_LB"); return e ? atoi(e) : 4; }();   // development switch
+    // Measured on the bench workload (tile sort of 33.8M pairs, two passes): rank mode 0 0.76 ms, 1 0.64, 2 0.64;
+    // look-back batch 1 0.66, 4 0.61, 8 0.65; 512 threads x 8 keys 0.70-0.85 (removed).
+    switch (radix_rank_mode() * 10 + lb) {
+      case 1: radix_pass_kernel<0, 256, 16, 1><<<blocks, 256, 0, s>>>(a); break;
+      case 21: radix_pass_kernel<2, 256, 16, 1><<<blocks, 256, 0, s>>>(a); break;
+      case 14: radix_pass_kernel<1, 256, 16, 4><<<blocks, 256, 0, s>>>(a); break;
+      case 18: radix_pass_kernel<1, 256, 16, 8><<<blocks, 256, 0, s>>>(a); break;
+      case 24: radix_pass_kernel<2, 256, 16, 4><<<blocks, 256, 0, s>>>(a); break;
+      case 11: radix_pass_kernel<1, 256, 16, 1><<<blocks, 256, 0, s>>>(a); break;
+      default: radix_pass_kernel<1, 256, 16, 4><<<blocks, 256, 0, s>>>(a); break;
     }
     B200GS_LAUNCHED("radix_pass_kernel", debug, s);
     uint32_t* x;

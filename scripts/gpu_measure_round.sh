@@ -2,13 +2,15 @@
 # (tests, smoke, config table, both bench arms, update / loss harnesses, ncu launch list + full capture)
 set -x
 cd $GRAFT_REPO_ROOT
-T=${TAG:-r1i}
+T=${TAG:-r1k}
 timeout 900 python -m pytest tests -x -q -m gpu > gpurun_out/${T}_pytest_gpu.log 2>&1; tail -2 gpurun_out/${T}_pytest_gpu.log
 timeout 300 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > gpurun_out/${T}_smoke.log 2>&1; tail -1 gpurun_out/${T}_smoke.log
 timeout 900 python tests/run_configs.py c1 c2 c3 c4 c3g c5 > gpurun_out/${T}_configs.jsonl 2> gpurun_out/${T}_configs.err
 timeout 300 python tests/run_update.py > gpurun_out/${T}_update.jsonl 2>/dev/null
 timeout 300 python tests/run_ssim.py > gpurun_out/${T}_ssim.jsonl 2>/dev/null
 timeout 300 python tests/run_shade.py > gpurun_out/${T}_shade.jsonl 2>/dev/null
+timeout 300 python tests/run_iteration.py > gpurun_out/${T}_iteration.jsonl 2>/dev/null
+timeout 300 python tests/run_scene_io.py > gpurun_out/${T}_scene_io.jsonl 2>/dev/null
 timeout 600 python bench.py --impl reference --steps 3 --warmup 3 2>/dev/null | tail -1 > gpurun_out/${T}_bench_reference.json
 timeout 600 python bench.py --steps 5 --warmup 3 2>/dev/null | tail -1 > gpurun_out/${T}_bench_new.json
 timeout 300 python bench.py --steps 3 --warmup 3 --exact-lists --no-cpu-baseline 2>/dev/null | tail -1 > gpurun_out/${T}_bench_new_exact.json
