@@ -12,6 +12,10 @@
 //   power = fma(fma(dx, con.x*dx, (con.z*dy)*dy), -0.5, -((con.y*dx)*dy));  acc = fma(T, alpha*f, acc).
 #include "surfel_composite.cuh"
 
+#ifndef B200GS_GBWD_CTAS
+#define B200GS_GBWD_CTAS 2   // resident CTAs per SM the register allocation is bounded for
+#endif
+
 namespace b200gs {
 
 constexpr int GBATCH = 256;
@@ -184,7 +188,7 @@ struct GCompBwdArgs {
   float* acc;                // [P, GACC_STRIDE]
 };
 
-__global__ void __launch_bounds__(GBATCH, 2) gauss_composite_bwd_kernel(const GCompBwdArgs a) {
+__global__ void __launch_bounds__(GBATCH, B200GS_GBWD_CTAS) gauss_composite_bwd_kernel(const GCompBwdArgs a) {
   __shared__ GaussRec s_rec[2][GBATCH];
   __shared__ int s_id[2][GBATCH];
   __shared__ uint32_t s_pos[2][GBATCH];

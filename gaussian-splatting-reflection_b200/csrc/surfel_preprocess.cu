@@ -20,6 +20,10 @@
 #include "common.cuh"
 #include "sh.cuh"
 
+#ifndef B200GS_PRE_CTAS
+#define B200GS_PRE_CTAS 2   // resident CTAs per SM the register allocation is bounded for
+#endif
+
 namespace b200gs {
 
 struct SurfelPreArgs {
@@ -96,7 +100,7 @@ __device__ __forceinline__ CullRec cull_record(const float* Tu, const float* Tv,
   return r;
 }
 
-__global__ void __launch_bounds__(256) surfel_preprocess_kernel(const SurfelPreArgs a) {
+__global__ void __launch_bounds__(256, B200GS_PRE_CTAS) surfel_preprocess_kernel(const SurfelPreArgs a) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= a.P) return;
 

@@ -13,6 +13,10 @@
 #include "common.cuh"
 #include "sh.cuh"
 
+#ifndef B200GS_PREBWD_CTAS
+#define B200GS_PREBWD_CTAS 2   // resident CTAs per SM the register allocation is bounded for
+#endif
+
 namespace b200gs {
 
 struct PreBwdArgs {
@@ -46,7 +50,7 @@ struct PreBwdArgs {
 // SURVEY.md section 8e); rows of Gaussians this view culled are left alone, so no zero-fill per view.
 // The view-space outputs (means2D, colors, normal, transMat) are always overwritten.
 template <bool ACC>
-__global__ void __launch_bounds__(256) surfel_preprocess_bwd_kernel(const PreBwdArgs a) {
+__global__ void __launch_bounds__(256, B200GS_PREBWD_CTAS) surfel_preprocess_bwd_kernel(const PreBwdArgs a) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= a.P || !(a.radii[idx] > 0)) return;
 
