@@ -14,7 +14,7 @@
 #include "sh.cuh"
 
 #ifndef B200GS_PREBWD_CTAS
-#define B200GS_PREBWD_CTAS 2   // resident CTAs per SM the register allocation is bounded for
+#define B200GS_PREBWD_CTAS 2   // resident CTAs per SM the register allocation is bounded for (2: 119 registers 0.47 ms; 3: 80 registers, 380 B of spills, 1.40 ms)
 #endif
 
 namespace b200gs {
