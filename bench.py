@@ -1,28 +1,36 @@
 #!/usr/bin/env python
-"""bench.py -- fwd+bwd throughput of the surfel (2DGS, reflection channels) differentiable
-rasterizer on the workload BASELINE.json's metric is quoted on: 3M Gaussians, SH degree 3,
-1920x1080, one camera view per GPU per step.
+"""bench.py -- fwd+bwd throughput of the surfel (2DGS, reflection channels) differentiable rasterizer on the
+workload BASELINE.json's metric is quoted on: 3M Gaussians, SH degree 3, 1920x1080.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl new|reference]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl new|reference] [--workload bench|c5|...]
 
-One process per GPU (torchrun for N>1).  A "step" = one pass of the hot path over one view per
-rank: forward (preprocess, scan, duplicate, 64-bit sort, tile ranges, compositing) + backward
-(compositing backward, preprocess backward) with non-zero upstream gradients on every
-differentiable output plane, then -- for N>1 -- one NCCL all-reduce of the per-Gaussian gradients
-(Gaussians replicated, views sharded: SURVEY.md section 8e).  Per-GPU work is fixed -> weak scaling.
+One process per GPU (torchrun for N > 1).  A "step" is one BATCH of --views-per-step (default 32) ring-camera views
+of the replicated scene, dealt to the ranks (rank r renders views r, r+N, ...): per view forward (preprocess, depth
+order, scan, emission, tile sort, tile ranges, block masks, compositing) + backward (compositing backward, preprocess
+backward) with non-zero upstream gradients on every differentiable output plane; the parameter gradients of the batch
+are summed in place in one flat [59 P] arena and, for N > 1, all-reduced once per batch.  Total
+work is fixed as N grows -> "scaling": "strong".
 
-  value        Mpix/s over all ranks, inputs resident in HBM, CUDA-event timed, max over ranks.
-  e2e          same metric through the drop-in Python API (GaussianRasterizer autograd module)
-               with the step's host inputs (camera matrices + target image, pinned) copied
-               H2D and the loss read back D2H inside the timed region.
-  roofline     dominant kernel: algorithmic bytes per launch / its mean duration, measured with
-               CUDA event pairs recorded by the library on the launching stream during the
-               timed region (b200gs_timing_*), against MEASURED_PEAKS.json's HBM copy figure.
-  cpu_baseline the CPU oracle (oracle/surfel_oracle.py, "port": the reference has no CPU path)
-               on a bounded sample of the same view, rank 0 at N=1 only.
-  --impl reference  runs the UNMODIFIED reference CUDA extension (oracle/_ref/ref_surfel_C.so)
-               on the same inputs through the same driver: the reference's implementation of
-               this path exists only as CUDA, so "the reference on this box" is that, on the GPU.
+  value        Mpix/s over all ranks (views x W x H / step time), inputs resident in HBM, CUDA events, max over ranks.
+  e2e          the same batch through the drop-in Python API (GaussianRasterizer autograd module + an L1 loss) with each
+               view's host inputs (camera matrices + target image, pinned) copied H2D and the batch loss read back D2H
+               inside the timed region; gradients land in the arena too (GaussianRasterizer(grad_arena=...)).
+  roofline     the dominant kernel, timed with CUDA event pairs recorded by the library on the launching stream inside
+               the timed region (b200gs_timing_only).  The compositing kernels are instruction-issue bound (DRAM at
+               1-2 % of peak, the staged records are re-served from L2), so for them "bound" is "issue": achieved = warp
+               instructions per second (instruction count per launch from the committed ncu capture,
+               profiles/traffic.json) against 148 SMs x 4 schedulers x the SM clock sampled during the run.  The
+               contract's HBM figure of the same kernel (algorithmic bytes / duration / measured copy peak) is kept in
+               `hbm_view`, and `roofline_hbm` is the slowest HBM-bound stage with its own fraction.
+  cpu_baseline the CPU oracle (oracle/surfel_oracle.py, kind "port": the reference has no CPU path) on the WHOLE c1 view
+               (BASELINE.json configs[0]: 100k Gaussians, 256x256, fwd + autograd bwd) on all host cores, with this
+               library's time for the same view next to it; rank 0 at N=1 only.
+  scale        N > 1: per-rank compute ms (min / max over ranks), all-reduce ms, bus GB/s against NVLink 5, and the
+               fraction of the all-reduce hidden behind compute.
+  forward_only the render_fast()-shaped inference call (torch.no_grad, eval_fps.py:25-59): ms per view and fps.
+  --impl reference  runs the UNMODIFIED reference CUDA extension (oracle/_ref/ref_surfel_C.so) on the same inputs
+               through the same driver; this arm imports nothing of this repo's library.  The reference's
+               implementation of this path exists only as CUDA, so "the reference on this box" is that, on the GPU.
 """
 import argparse
 import json
@@ -40,6 +48,7 @@ for p in (ROOT, os.path.join(ROOT, "tests"), os.path.join(ROOT, "gaussian-splatt
 METRIC = "surfel rasterizer fwd+bwd throughput, 3M Gaussians SH3 @1920x1080 (32-view batch sharded over the GPUs)"
 UNIT = "Mpix/s"
 WORKLOAD = "bench"   # tests/scenes.py CONFIGS["bench"]: room scene, P=3M, 1920x1080
+NVLINK5_GBS = 900.0  # per direction per GPU
 
 
 def parse():
@@ -60,8 +69,8 @@ def parse():
     ap.add_argument("--exact-lists", action="store_true",
                     help="time the exact-lists mode (the reference's instance lists bit for bit) instead of the "
                          "default culled emission")
-    ap.add_argument("--cpu-sample-tiles", type=int, default=64)
-    ap.add_argument("--cpu-sample-len", type=int, default=600, help="list positions walked per sampled tile")
+    ap.add_argument("--nccl-allreduce", action="store_true",
+                    help="N > 1: reduce the arena with ncclAllReduce instead of the library's NVLS multimem kernel")
     return ap.parse_args()
 
 
@@ -120,10 +129,9 @@ class ClockSampler:
 
 
 def algorithmic_bytes(P, V, R, N):
-    """compulsory HBM bytes per launch of each stage (surfel path, SH
-    degree 3, colours from SH), each datum moved once.  P Gaussians, V visible, R (Gaussian,tile)
-    instances the stage works on (the emitted ones: all of the reference's in exact-lists mode,
-    the reachable ones in the default culled-emission mode), N pixels."""
+    """compulsory HBM bytes per launch of each stage (surfel path, SH degree 3, colours from
+    SH), each datum moved once.  P Gaussians, V visible, R (Gaussian, tile) instances the stage works on (the emitted
+    ones: all of the reference's in exact-lists mode, the reachable ones in the default culled-emission mode), N pixels."""
     return {
         "count_kept": 4 * P + 72 * V + 4 * P,           # tiles_touched; rect + cull record of visible ones; count out
         "preprocess": 237 * P + 87 * V + 8 * P,        # inputs; state of visible ones; radii + tiles_touched
@@ -139,64 +147,64 @@ def algorithmic_bytes(P, V, R, N):
     }
 
 
-def cpu_baseline(scene_np, cam_np, n_tiles, max_len, R_total):
-    """Oracle (CPU, torch fp32) on a bounded sample of the same view: the full per-Gaussian
-    preprocess, then binning + compositing forward + autograd backward over the first `max_len`
-    list positions of `n_tiles` 16x16 tiles spread over the image.  Like a CTA of the CUDA kernels
-    the vectorised oracle walks a tile's list for all 256 pixels together, so the cost of a whole
-    view is extrapolated per (tile, list entry): R_total entries in the view."""
+ISSUE_BOUND = ("composite_fwd", "composite_bwd", "tile_hits", "count_kept")   # what bounds each stage
+
+
+def cpu_baseline():
+    """BASELINE.json configs[0]: the WHOLE c1 view (100k Gaussians, SH degree 3, 256x256), forward + autograd
+    backward, through the CPU oracle on all host cores.  Tiles are processed in chunks so the autograd tape of a chunk
+    fits in memory; every tile, every list entry and every Gaussian is processed -- nothing is extrapolated."""
     import numpy as np
     import torch
     from oracle import surfel_oracle as so
     import scenes
-    cores = 1      # [S,256]-sized tensors: intra-op threading only adds overhead (measured 3.5x slower with 8)
+    cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
+    sc_np, cam_np = scenes.build("c1")
     W, H = cam_np["width"], cam_np["height"]
     gx, gy = (W + 15) // 16, (H + 15) // 16
-    tiles = sorted({int((gy * (2 * k + 1)) // (2 * n_tiles)) * gx + int((gx * (2 * k + 1)) // (2 * n_tiles))
-                    for k in range(n_tiles)})
     grads = scenes.upstream_grads(W, H)
+    gc, go, gr = (torch.from_numpy(grads[k]) for k in ("color", "others", "refl"))
+    go = go.clone()
+    go[7] = 0
     t0 = time.time()
-    with torch.no_grad():
-        pre = so.preprocess(so._leaves(scene_np, torch.float32, False), cam_np)      # every Gaussian, forward
-    t_pre = time.time() - t0
-    keys, plist, ranges = so.binning(pre, W, H, tiles=tiles)
-    ranges = ranges.copy()
-    ranges[:, 1] = ranges[:, 0] + (ranges[:, 1] - ranges[:, 0]).clip(max=max_len)
-    entries = int(sum(ranges[t, 1] - ranges[t, 0] for t in tiles))
-    # The per-pair cost is timed on the Gaussians of the sampled lists only: autograd through the preprocess of
-    # all P Gaussians makes every backward op a dense P-row scatter (60 s for 1200 entries at P = 3M), which
-    # says nothing about the per-pair work being extrapolated.
-    Pn = scene_np["means3D"].shape[0]
-    ids = np.unique(np.concatenate([plist[ranges[t, 0]:ranges[t, 1]] for t in tiles])) if entries else np.zeros(0, np.int64)
-    sub_np = {k: (v[ids] if isinstance(v, np.ndarray) and v.ndim >= 1 and v.shape[0] == Pn else v) for k, v in scene_np.items()}
-    plist_sub = np.searchsorted(ids, np.clip(plist, ids.min() if len(ids) else 0, ids.max() if len(ids) else 0)).astype(plist.dtype)
-    t0 = time.time()
-    pre_sub = so.preprocess(so._leaves(sub_np, torch.float32, True), cam_np)
-    comp = so.composite(pre_sub, plist_sub, ranges, cam_np, (0.0, 0.0, 0.0), tiles=tiles, collect_weights=False)
-    color, others, refl, _, _ = so.assemble(comp, W, H, torch.float32)
-    loss = ((color * torch.from_numpy(grads["color"])).sum() + (others[:7] * torch.from_numpy(grads["others"][:7])).sum()
-            + (refl * torch.from_numpy(grads["refl"])).sum())
-    loss.backward()
-    t_tiles = time.time() - t0
-    t_view = 2.0 * t_pre + t_tiles * R_total / max(entries, 1)     # preprocess forward + (about as much) backward
+    leaves = so._leaves(sc_np, torch.float32, True)
+    pre = so.preprocess(leaves, cam_np)
+    keys, plist, ranges = so.binning(pre, W, H)
+    tiles = np.arange(gx * gy)
+    chunk = 32
+    for c0 in range(0, gx * gy, chunk):
+        comp = so.composite(pre, plist, ranges, cam_np, (0.0, 0.0, 0.0), tiles=tiles[c0:c0 + chunk], collect_weights=False)
+        color, others, refl, _, _ = so.assemble(comp, W, H, torch.float32)
+        ((color * gc).sum() + (others * go).sum() + (refl * gr).sum()).backward(retain_graph=True)
+    t_view = time.time() - t0
     return {"value": W * H / t_view / 1e6, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"oracle/surfel_oracle.py: full preprocess of P={scene_np['means3D'].shape[0]} ({t_pre:.1f} s) + "
-                      f"compositing fwd + autograd bwd (through the preprocess of the {len(ids)} Gaussians involved) over the first <={max_len} list positions of {len(tiles)} "
-                      f"of {gx * gy} tiles = {entries} (tile, entry) pairs ({t_tiles:.1f} s); whole view (R={R_total} "
-                      f"pairs) extrapolated per pair to {t_view:.0f} s",
-            "seconds_measured": round(t_pre + t_tiles, 1)}
+            "sample": f"oracle/surfel_oracle.py (torch fp32 on the host, {cores} threads): the whole c1 view -- P={sc_np['means3D'].shape[0]}, "
+                      f"{W}x{H}, R={int(keys.size)} instances, forward + autograd backward of all {gx * gy} tiles in chunks of {chunk} -- "
+                      f"{t_view:.1f} s; the reference has no CPU implementation of this path",
+            "workload": "c1", "seconds": round(t_view, 2)}
 
 
-def load_impl(impl):
-    """-> (module with the reference's `_C` signature, description) or (None, reason)."""
+def gpu_c1_ms(Cmod):
+    """This library on the same c1 view the CPU baseline renders (median of 20 fwd+bwd after 5 warm-ups)."""
+    import torch
     import harness as hz
-    if impl == "new":
-        return hz.new_surfel_C(), "libb200gs.so (sm_100a) via diff_surfel_rasterization._C"
-    m = hz.ref_module("ref_surfel_C")
-    if m is None:
-        return None, "oracle/_ref/ref_surfel_C.so not built (python oracle/build_ref.py needs /root/reference)"
-    return m, "unmodified reference CUDA extension oracle/_ref/ref_surfel_C.so (built for sm_100a)"
+    import scenes
+    sc_np, cam_np = scenes.build("c1")
+    sc, cam = hz.to_dev(sc_np), hz.to_dev(cam_np)
+    grads = hz.to_dev(scenes.upstream_grads(cam_np["width"], cam_np["height"]))
+    ts = []
+    for i in range(25):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        f = hz.surfel_forward(Cmod, sc, cam)
+        hz.surfel_backward(Cmod, sc, cam, f, grads)
+        e1.record()
+        torch.cuda.synchronize()
+        if i >= 5:
+            ts.append(e0.elapsed_time(e1))
+    ts.sort()
+    return ts[len(ts) // 2]
 
 
 def main():
@@ -213,23 +221,31 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
-    import b200gs
     import harness as hz
     import scenes
-    Cmod, impl_desc = load_impl(a.impl)
-    if Cmod is None:
-        if rank == 0:
-            print(json.dumps({"impl": "reference", "unavailable": impl_desc}))
-        return
+    new = a.impl == "new"
+    b200gs = None
+    if new:
+        import b200gs                                   # the reference arm never loads libb200gs.so
+        Cmod = hz.new_surfel_C()
+        impl_desc = "libb200gs.so (sm_100a) via diff_surfel_rasterization._C"
+    else:
+        Cmod = hz.ref_module("ref_surfel_C")
+        impl_desc = "unmodified reference CUDA extension oracle/_ref/ref_surfel_C.so (built for sm_100a)"
+        if Cmod is None:
+            if rank == 0:
+                print(json.dumps({"impl": "reference", "unavailable":
+                                  "oracle/_ref/ref_surfel_C.so not built (python oracle/build_ref.py needs /root/reference)"}))
+            return
 
     # ---- synthetic workload: replicated Gaussians, a batch of ring-camera views sharded over the ranks ----
     VB = a.views_per_step
     if VB < world or VB % world:
         raise SystemExit(f"--views-per-step {VB} must be a positive multiple of the number of GPUs ({world})")
-    from b200gs.dp import GradArena, shard_views
-    my_views = shard_views(VB, rank, world)               # r, r+n, ...  
+    my_views = list(range(rank, VB, world))               # r, r+n, ...  
     sc_np, cam_np = scenes.build(a.workload, P=a.points or None, view=my_views[0] % 32, n_views=32)
     P, W, H = sc_np["means3D"].shape[0], cam_np["width"], cam_np["height"]
+    M = sc_np["shs"].shape[1]
     N = W * H
     sc = hz.to_dev(sc_np)
     cams_np = [cam_np] + [scenes.camera(a.workload, v % 32, 32) for v in my_views[1:]]
@@ -237,36 +253,51 @@ def main():
     cam = cams[0]
     grads = hz.to_dev(scenes.upstream_grads(W, H))
     GRAD_KEYS = ("means3D", "sh", "opacity", "scales", "rotations", "refl")   # the 59 floats / Gaussian of the model
+    exact = bool(a.exact_lists)
 
     # The parameter gradients of the views of a batch are summed.  This library: the backward ADDS them into one
-    # flat [59 P] arena in place (b200gs.dp.GradArena, accumulate mode), which NCCL then reduces as it lies.
-    # Reference arm: what autograd does for it -- one add per gradient tensor per view -- and one concatenation
-    # before the all-reduce.
+    # flat [59 P] arena in place (b200gs.dp.GradArena, accumulate mode, a per-call argument of the backward), which
+    # is then reduced over the ranks as it lies.  Reference arm: what autograd does for it -- one add per gradient
+    # tensor per view -- and one concatenation before the all-reduce.
     arena, ref_acc = None, None
-    if a.impl == "new":
-        arena = GradArena(P, sc["shs"].shape[1], "cuda", accumulate=True)
-        Cmod.use_gradient_arena(arena)
+    if new:
+        from b200gs.dp import GradArena
+        arena = GradArena(P, M, "cuda", accumulate=True, symmetric=(world > 1 and not a.nccl_allreduce))
+
+    ev = {}                                                # optional event marks of the scale pass
+
+    def mark(name):
+        if ev.get("on"):
+            e = torch.cuda.Event(enable_timing=True)
+            e.record()
+            ev.setdefault("marks", []).append((name, e))
 
     def step():
         nonlocal ref_acc
+        mark("begin")
         if arena is not None:
             arena.zero_()
         f = b = None
         for vi, c in enumerate(cams):
-            f = hz.surfel_forward(Cmod, sc, c)
-            b = hz.surfel_backward(Cmod, sc, c, f, grads)
-            if arena is None:
+            if new:
+                f = hz.surfel_forward(Cmod, sc, c, exact=exact)
+                b = hz.surfel_backward(Cmod, sc, c, f, grads, grad_arena=arena)
+            else:
+                f = hz.surfel_forward(Cmod, sc, c)
+                b = hz.surfel_backward(Cmod, sc, c, f, grads)
                 if vi == 0:
                     ref_acc = {k: b[k] for k in GRAD_KEYS}
                 else:
                     for k in GRAD_KEYS:
                         ref_acc[k] += b[k]
+        mark("compute_end")
         if world > 1:
             if arena is not None:
                 arena.all_reduce()
             else:
                 flat = torch.cat([ref_acc[k].reshape(P, -1) for k in GRAD_KEYS], 1)
                 dist.all_reduce(flat)
+        mark("end")
         return f, b
 
     def timed(fn, steps, warmup, after_warmup=None):
@@ -293,13 +324,11 @@ def main():
 
     # workload counts of this rank's first view (for the algorithmic-bytes figures of the stage table)
     R_ref = None
-    if a.impl == "new":
-        b200gs.set_exact_lists(1)
-        f = hz.surfel_forward(Cmod, sc, cam)
+    if new:
+        f = hz.surfel_forward(Cmod, sc, cam, exact=True)
         R_ref = int(f["rendered"])           # the reference's instance count
         del f
-        b200gs.set_exact_lists(1 if a.exact_lists else 0)
-    f = hz.surfel_forward(Cmod, sc, cam)
+    f = hz.surfel_forward(Cmod, sc, cam, **({"exact": exact} if new else {}))
     R, V = int(f["rendered"]), int((f["radii"] > 0).sum())
     if R_ref is None:
         R_ref = R
@@ -310,7 +339,7 @@ def main():
     # (measured: +0.4 ms on a 6.1 ms view), so the all-stage table comes from its own short pass and the
     # timed region below carries events around the dominant kernel only.
     stages_all, top_stage = {}, -1
-    if a.impl == "new" and not a.no_stage_timing:
+    if new and not a.no_stage_timing:
         step()
         torch.cuda.synchronize()
         b200gs.timing_enable(1)
@@ -329,26 +358,87 @@ def main():
     n0 = [0]
 
     def reset_counters():                 # warm-up launches are not part of the timed region
-        b200gs.timing_read()
-        n0[0] = b200gs.launch_count()
+        if new:
+            b200gs.timing_read()
+            n0[0] = b200gs.launch_count()
     with ClockSampler(local) as cs:
         total_ms = timed(step, a.steps, a.warmup, reset_counters)
-    launches = b200gs.launch_count() - n0[0]
+    launches = (b200gs.launch_count() - n0[0]) if new else None
     stages = b200gs.timing_read() if top_stage >= 0 else {}      # the dominant kernel, live in the timed region
-    b200gs.timing_enable(0)
+    if new:
+        b200gs.timing_enable(0)
     clocks = cs.summary()
     ms_per_step = total_ms / a.steps
     value = VB * N / (ms_per_step * 1e-3) / 1e6            # whole job: every rank's views
 
-    if arena is not None:
-        Cmod.use_gradient_arena(None)
+    # ---- N > 1: where the step's time goes on every rank -----------------------------------------
+    scale = None
+    if world > 1:
+        ev["on"] = True
+        per = []
+        for _ in range(3):
+            ev["marks"] = []
+            dist.barrier()
+            step()
+            torch.cuda.synchronize()
+            m = dict(ev["marks"])
+            per.append((m["begin"].elapsed_time(m["compute_end"]), m["compute_end"].elapsed_time(m["end"])))
+        ev["on"] = False
+        comp_ms = sorted(p[0] for p in per)[1]
+        tail_ms = sorted(p[1] for p in per)[1]             # all-reduce as seen by this rank: includes waiting for the slowest rank
+        # the collective alone: every rank enters it at the same time
+        ar = []
+        probe = None if arena is not None else torch.zeros(P * 59, device="cuda")
+        for _ in range(5):
+            dist.barrier()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            if arena is not None:
+                arena.all_reduce()
+            else:
+                dist.all_reduce(probe)
+            e1.record()
+            torch.cuda.synchronize()
+            ar.append(e0.elapsed_time(e1))
+        ar_ms = sorted(ar)[len(ar) // 2]
+        t = torch.tensor([comp_ms, -comp_ms, tail_ms, ar_ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        comp_max, comp_min, tail_max, ar_max = float(t[0]), -float(t[1]), float(t[2]), float(t[3])
+        nbytes = P * 59 * 4
+        scale = {"compute_ms_per_rank_min": round(comp_min, 3), "compute_ms_per_rank_max": round(comp_max, 3),
+                 "allreduce_ms": round(ar_max, 3), "allreduce_bytes": nbytes,
+                 "allreduce_algo": ("ncclAllReduce" if (arena is None or not arena.symmetric) else arena.algo),
+                 "bus_gbs": round(2 * (world - 1) / world * nbytes / (ar_max * 1e-3) / 1e9, 1),
+                 "alg_gbs": round(nbytes / (ar_max * 1e-3) / 1e9, 1), "nvlink5_gbs_per_direction": NVLINK5_GBS,
+                 # time of the step not covered by the slowest rank's compute, against the collective's own time
+                 "exposed_comm_ms": round(ms_per_step - comp_max, 3),
+                 "overlap_fraction": round(max(0.0, 1.0 - max(ms_per_step - comp_max, 0.0) / ar_max), 3),
+                 "imbalance_ms": round(comp_max - comp_min, 3),
+                 "note": "compute = zero_() + this rank's views; allreduce timed alone after a barrier (median of 5, max over ranks); "
+                         "bus_gbs = 2(n-1)/n x bytes / time"}
+
+    # ---- forward only (render_fast-shaped inference, eval_fps.py:25-59) ---------------------------
+    fwd_only = None
+    if rank == 0 or world > 1:
+        with torch.no_grad():
+            def fstep():
+                for c in cams:
+                    hz.surfel_forward(Cmod, sc, c, **({"exact": exact} if new else {}))
+            f_ms = timed(fstep, max(3, a.steps // 4), 2) / max(3, a.steps // 4) / len(cams)
+        fwd_only = {"ms_per_view": round(f_ms, 4), "fps_per_gpu": round(1e3 / f_ms, 1),
+                    "api": "_C.rasterize_gaussians under torch.no_grad(), device-resident inputs"}
+
     # ---- end to end through the drop-in Python API, host inputs ------------------------------
     e2e = None
     if not a.no_e2e:
-        import diff_surfel_rasterization as dsr
-        saved_C = dsr._C
-        dsr._C = Cmod                                   # the reference arm drives the reference's _C
-        try:
+        if new:
+            import diff_surfel_rasterization as dsr
+        else:
+            import refpy                                   # the reference's own python package on its own extension
+            arm = refpy.load_arm("ref")
+            dsr = arm.diff_surfel_rasterization if arm is not None else None
+        if dsr is not None:
             leaves = {k: sc[k].clone().requires_grad_(True) for k in ("means3D", "shs", "opacities", "scales", "rotations", "refl")}
             m2d = torch.zeros_like(leaves["means3D"], requires_grad=True)
             mask = torch.ones((P, 3), dtype=torch.bool, device="cuda")
@@ -359,35 +449,45 @@ def main():
                 hv["bg"] = torch.zeros(3).pin_memory()
             h2d = sum(t.numel() * t.element_size() for t in hosts[0].values()) * VB     # whole job
             loss_host = torch.zeros(1).pin_memory()
-
             copy_stream = torch.cuda.Stream()
+            kw = {}
+            if new:
+                # the leaves' .grad ARE the arena blocks: the backward of every view adds into them in place, the
+                # all-reduce runs on that memory, the optimizer would read .grad -- no per-view adds, no concatenation
+                arena.bind_grads({"means3D": leaves["means3D"], "sh": leaves["shs"], "opacity": leaves["opacities"],
+                                  "scales": leaves["scales"], "rotations": leaves["rotations"], "refl": leaves["refl"]})
+                kw = dict(grad_arena=arena, exact_lists=exact)
 
             def upload(host):
                 """H2D of one view's inputs on the copy stream (a data loader's prefetch); still inside the timed region."""
                 with torch.cuda.stream(copy_stream):
                     dev = {k: v.to("cuda", non_blocking=True) for k, v in host.items()}
-                    ev = torch.cuda.Event()
-                    ev.record(copy_stream)
-                return dev, ev
+                    e = torch.cuda.Event()
+                    e.record(copy_stream)
+                return dev, e
 
             def e2e_step():
-                for t in list(leaves.values()) + [m2d]:
-                    t.grad = None
+                if new:
+                    arena.zero_()
+                    m2d.grad = None
+                else:
+                    for t in list(leaves.values()) + [m2d]:
+                        t.grad = None
                 total = None
                 nxt = upload(hosts[0])
-                for vi in range(len(hosts)):             # this rank's views of the batch; autograd sums the gradients
-                    dev, ev = nxt
+                for vi in range(len(hosts)):             # this rank's views of the batch; the gradients are summed
+                    dev, e = nxt
                     if vi + 1 < len(hosts):
                         nxt = upload(hosts[vi + 1])      # the next view's inputs travel while this one renders
                     cur = torch.cuda.current_stream()
-                    cur.wait_event(ev)
+                    cur.wait_event(e)
                     for t in dev.values():
                         t.record_stream(cur)
                     rs = dsr.GaussianRasterizationSettings(
                         image_height=H, image_width=W, tanfovx=cam_np["tanfovx"], tanfovy=cam_np["tanfovy"], bg=dev["bg"],
                         scale_modifier=1.0, viewmatrix=dev["viewmatrix"], projmatrix=dev["projmatrix"], sh_degree=3,
                         campos=dev["campos"], prefiltered=False, debug=False)
-                    color, radii, allmap, refl_map, _ = dsr.GaussianRasterizer(rs)(
+                    color, radii, allmap, refl_map, _ = dsr.GaussianRasterizer(rs, **kw)(
                         means3D=leaves["means3D"], means2D=m2d, opacities=leaves["opacities"], shs=leaves["shs"],
                         refl_strengths=leaves["refl"], scales=leaves["scales"], rotations=leaves["rotations"],
                         env_scope_mask=mask)
@@ -395,8 +495,11 @@ def main():
                     loss.backward()
                     total = loss.detach() if total is None else total + loss.detach()
                 if world > 1:
-                    flat = torch.cat([leaves[k].grad.reshape(P, -1) for k in leaves], 1)
-                    dist.all_reduce(flat)
+                    if new:
+                        arena.all_reduce()
+                    else:
+                        flat = torch.cat([leaves[k].grad.reshape(P, -1) for k in leaves], 1)
+                        dist.all_reduce(flat)
                 loss_host.copy_(total.reshape(1), non_blocking=True)
                 torch.cuda.current_stream().synchronize()     # the caller reads the batch loss every step
                 return float(loss_host[0])
@@ -404,16 +507,15 @@ def main():
             e2e_ms = timed(e2e_step, a.steps, a.warmup) / a.steps
             e2e = {"value": VB * N / (e2e_ms * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": e2e_ms, "ms_per_view": e2e_ms * world / VB,
                    "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4,
-                   "api": "diff_surfel_rasterization.GaussianRasterizer (autograd) + L1 loss"}
-        finally:
-            dsr._C = saved_C
+                   "api": "diff_surfel_rasterization.GaussianRasterizer (autograd) + L1 loss"
+                          + (", gradients accumulated in the GradArena the leaves' .grad are bound to" if new else "")}
 
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
 
-    # ---- rank 0: roofline of the dominant kernel, CPU baseline, the JSON line ----------------
+    # ---- rank 0: rooflines, CPU baseline, the JSON line ----------------
     peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
     try:
         peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
@@ -421,38 +523,59 @@ def main():
     except Exception:  # noqa: BLE001
         pass
     alg = algorithmic_bytes(P, V, R, N)
-    roofline, stage_table = None, {}
+    roofline, roofline_hbm, stage_table = None, None, {}
+    prof = {}
+    try:   # per-launch dram bytes / warp instructions from the committed ncu captures of this workload
+        prof = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+    except Exception:  # noqa: BLE001
+        pass
 
     def row(name, ms, cnt, steps):
         per = ms / cnt
         return {"ms": round(per, 4), "launches_per_step": cnt / (steps + 0.0),
                 "alg_bytes": alg[name], "gbs": round(alg[name] / (per * 1e-3) / 1e9, 1),
-                "frac_of_hbm_peak": round(alg[name] / (per * 1e-3) / 1e9 / peak, 4)}
+                "frac_of_hbm_peak": round(alg[name] / (per * 1e-3) / 1e9 / peak, 4),
+                "bound": "issue" if name in ISSUE_BOUND else "hbm"}
     for name, (ms, cnt) in stages_all.items():           # the separate all-stage pass (1 step)
         if cnt and name in alg:
             stage_table[name] = row(name, ms, cnt, 1)
     live = {name: row(name, ms, cnt, a.steps) for name, (ms, cnt) in stages.items() if cnt and name in alg}
     if live:
         top = max(live, key=lambda k: live[k]["ms"])   # one entry: the dominant kernel, timed inside the timed region
-        traffic = None
-        try:   # per-launch dram bytes of that kernel from the committed ncu --set full capture, if any
-            traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(top)
-        except Exception:  # noqa: BLE001
-            pass
-        ach = live[top]["gbs"]
-        roofline = {"kernel": top, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s",
-                    "frac": round(ach / peak, 4), "traffic": traffic, "peak_source": peak_src,
-                    "ms_per_launch": live[top]["ms"], "launches_per_step": live[top]["launches_per_step"],
-                    "alg_bytes_per_launch": live[top]["alg_bytes"],
-                    "share_of_step": round(live[top]["ms"] * live[top]["launches_per_step"] / ms_per_step, 3),
-                    "note": "CUDA events around this kernel inside the timed region; compositing kernels are FP32/MUFU-issue "
-                            "bound, not HBM bound (DESIGN.md), the HBM fraction is reported as the contract asks; `stages` "
-                            "holds every stage from a separate instrumented pass (all-stage events perturb the step by ~6 %)"}
+        t_s = live[top]["ms"] * 1e-3
+        common = {"kernel": top, "ms_per_launch": live[top]["ms"], "launches_per_step": live[top]["launches_per_step"],
+                  "share_of_step": round(live[top]["ms"] * live[top]["launches_per_step"] / ms_per_step, 3),
+                  "traffic": (prof.get(top) if not isinstance(prof.get(top), dict) else prof[top].get("dram_bytes")),
+                  "hbm_view": {"alg_bytes_per_launch": live[top]["alg_bytes"], "achieved_gbs": live[top]["gbs"], "peak_gbs": peak,
+                               "frac": live[top]["frac_of_hbm_peak"], "peak_source": peak_src}}
+        inst = prof.get(top + "_warp_inst") if top in ISSUE_BOUND else None
+        if inst:
+            sm_mhz = clocks.get("sm_mhz") or 1965.0
+            ipeak = 148 * 4 * sm_mhz * 1e6 / 1e9          # G warp-instructions / s at one issue per scheduler per cycle
+            ach = inst / t_s / 1e9
+            roofline = dict(common, bound="issue", achieved=round(ach, 1), peak=round(ipeak, 1), unit="Gwarp-inst/s",
+                            frac=round(ach / ipeak, 4), warp_inst_per_launch=inst,
+                            note="the kernel's DRAM traffic is 1-2 % of peak (staged records are re-served from L2): it is bound by "
+                                 "instruction issue; achieved = warp instructions per launch (ncu smsp__inst_executed.sum, "
+                                 "profiles/traffic.json, mean over the batch's views) / measured duration; peak = 148 SMs x 4 "
+                                 "schedulers x the SM clock sampled during the timed region")
+        else:
+            roofline = dict(common, bound="hbm", achieved=live[top]["gbs"], peak=peak, unit="GB/s", frac=live[top]["frac_of_hbm_peak"],
+                            peak_source=peak_src)
+    hbm_rows = {k: v for k, v in stage_table.items() if v["bound"] == "hbm"}
+    if hbm_rows:
+        k = max(hbm_rows, key=lambda k: hbm_rows[k]["ms"])
+        roofline_hbm = {"kernel": k, "bound": "hbm", "achieved": hbm_rows[k]["gbs"], "peak": peak, "unit": "GB/s",
+                        "frac": hbm_rows[k]["frac_of_hbm_peak"], "ms_per_launch": hbm_rows[k]["ms"],
+                        "traffic": (prof.get(k) if not isinstance(prof.get(k), dict) else prof[k].get("dram_bytes")),
+                        "note": "the slowest HBM-bound stage (separate all-stage pass)"}
 
     cpu = None
-    if a.impl == "new" and world == 1 and not a.no_cpu_baseline:
-        cpu = cpu_baseline(sc_np, cam_np, a.cpu_sample_tiles, a.cpu_sample_len, R_ref)   # the oracle walks the reference's full lists
-    elif a.impl == "reference":
+    if new and world == 1 and not a.no_cpu_baseline:
+        cpu = cpu_baseline()
+        cpu["gpu_same_view_ms"] = round(gpu_c1_ms(Cmod), 4)
+        cpu["gpu_same_view_mpix_s"] = round(256 * 256 / (cpu["gpu_same_view_ms"] * 1e-3) / 1e6, 2)
+    elif not new:
         cpu = {"value": value, "unit": UNIT, "cores": 0, "kind": "reference",
                "sample": "the reference has no CPU implementation of this path (CUDA only): this arm is its "
                          "unmodified CUDA extension on the same B200, same inputs, whole workload"}
@@ -462,19 +585,24 @@ def main():
         "ms_per_step": round(ms_per_step, 4), "ms_per_view": round(ms_per_step * world / VB, 4),
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
+        # workload only: identical for both arms
         "config": {"workload": f"{a.workload}: room scene, replicated Gaussians, batch of {VB} ring-camera views per step, "
-                               f"{VB // world} per GPU (rank r renders views r, r+n, ...), gradients of the batch summed in place",
-                   "gaussians": P, "width": W, "height": H, "sh_degree": 3, "visible": V, "instances": R_ref, "instances_emitted": R,
-                   "lists": ("exact (reference's lists bit for bit)" if (a.exact_lists or a.impl == "reference")
-                             else "culled emission (only instances that can reach alpha >= 1/255)"),
+                               f"{VB // world} per GPU (rank r renders views r, r+n, ...), gradients of the batch summed",
+                   "gaussians": P, "width": W, "height": H, "sh_degree": 3, "visible": V, "instances": R_ref,
                    "views_per_step": VB, "views_per_gpu": VB // world,
-                   "counts": "visible / instances are those of rank 0's first view", "l2": "inputs (>= 0.7 GB of Gaussian data + 0.5-1.3 GB of sort keys per view) exceed the 126 MB L2; no flush",
-                   "parallelism": f"view-parallel x{world}, replicated Gaussians" + (", one NCCL all-reduce of the [P,59] fp32 gradient arena per batch" if world > 1 else "")},
-        "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
-        "roofline": roofline, "cpu_baseline": cpu, "stages": stage_table, "implementation": impl_desc,
+                   "counts": "visible / instances are those of rank 0's first view",
+                   "l2": "inputs (>= 0.7 GB of Gaussian data + 0.5-1.3 GB of sort keys per view) exceed the 126 MB L2; no flush",
+                   "parallelism": f"view-parallel x{world}, replicated Gaussians" + (", one all-reduce of the [P,59] fp32 gradients per batch" if world > 1 else "")},
+        "impl_detail": {"implementation": impl_desc, "instances_emitted": R,
+                        "lists": ("exact (reference's lists bit for bit)" if (exact or not new)
+                                  else "culled emission (only instances that can reach alpha >= 1/255)")},
+        "clocks": clocks, "e2e": e2e, "gpu_launches": (int(launches) if launches is not None else None),
+        "roofline": roofline, "roofline_hbm": roofline_hbm, "cpu_baseline": cpu, "stages": stage_table,
+        "scale": scale, "forward_only": fwd_only,
     }
-    if a.impl == "reference":
+    if not new:
         line["impl"] = "reference"
+        line["gpu_launches"] = None
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

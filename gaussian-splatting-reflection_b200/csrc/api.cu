@@ -11,7 +11,6 @@ namespace b200gs {
 
 static thread_local char t_err[512] = "";
 std::atomic<unsigned long long> g_launches{0};
-std::atomic<int> g_exact_lists{0};
 
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -124,9 +123,6 @@ int b200gs_version(void) { return 1; }
 int b200gs_sm_arch(void) { return 100; }
 unsigned long long b200gs_launch_count(void) { return g_launches.load(); }
 
-void b200gs_set_exact_lists(int on) { g_exact_lists.store(on ? 1 : 0); }
-int b200gs_get_exact_lists(void) { return g_exact_lists.load(); }
-
 void b200gs_timing_enable(int on) { g_timing.store(on ? 1 : 0); }
 void b200gs_timing_only(int stage) { g_timing.store((stage >= 0 && stage < ST_COUNT) ? 2 + stage : 0); }
 int b200gs_timing_stages(void) { return ST_COUNT; }
@@ -181,7 +177,7 @@ int b200gs_surfel_forward_stage1(const b200gs_surfel_fwd* a, int* num_rendered, 
   SurfelGeom g = SurfelGeom::carve(align128(a->geom), a->P, nullptr);
   rc = surfel_preprocess(*a, g, s);
   if (rc) return rc;
-  const bool exact = g_exact_lists.load(std::memory_order_relaxed) != 0;
+  const bool exact = a->exact_lists != 0;
   const uint32_t* counts = g.tiles_touched;
   if (!exact) {
     rc = surfel_count_kept(a->P, g.tiles_touched, g.rects, g.cull, g.tiles_kept, s, a->debug != 0);
@@ -210,14 +206,15 @@ int b200gs_surfel_forward_stage2(const b200gs_surfel_fwd* a, int R, void* stream
   SurfelImage im = SurfelImage::carve(align128(a->img), a->width, a->height, nullptr);
   Binning b = Binning::carve(R > 0 ? align128(a->binning) : nullptr, R, nullptr);
   rc = bin_and_sort(g.order.vals_a, g.rects, g.point_offsets, a->P, R, a->width, a->height, b, im.ranges, s, a->debug != 0,
-                    g_exact_lists.load(std::memory_order_relaxed) != 0 ? nullptr : g.cull);
+                    a->exact_lists != 0 ? nullptr : g.cull);
   if (rc) return rc;
   {
     const size_t tiles = (size_t)((a->width + TILE_X - 1) / TILE_X) * ((a->height + TILE_Y - 1) / TILE_Y);
     B200GS_CUDA(cudaMemsetAsync(im.cranges, 0, tiles * sizeof(uint2), s));
   }
   if (R > 0) {
-    rc = surfel_tile_hits(g.cull, b, R, a->width, a->height, im.ranges, im.cranges, s, a->debug != 0);
+    rc = surfel_tile_hits(g.cull, b, R, a->width, a->height, im.ranges, im.cranges, s, a->debug != 0,
+                          a->exact_lists != 0, a->cull_audit != 0);
     if (rc) return rc;
   }
   return surfel_composite_forward(*a, g, im, b, s);
@@ -229,6 +226,12 @@ int b200gs_surfel_backward(const b200gs_surfel_bwd* a, void* stream) {
   if (a->P <= 0) return B200GS_OK;
   if (!a->geom || !a->img || !a->accum || a->accum_bytes < b200gs_surfel_accum_bytes(a->P)) {
     set_error("missing scratch / accum too small"); return B200GS_ESIZE; }
+  if (a->width <= 0 || a->height <= 0 || a->num_rendered < 0) { set_error("bad sizes W=%d H=%d R=%d", a->width, a->height, a->num_rendered); return B200GS_EINVAL; }
+  if (a->geom_bytes < b200gs_surfel_geom_bytes(a->P) || a->img_bytes < b200gs_surfel_image_bytes(a->width, a->height) ||
+      (a->num_rendered > 0 && (!a->binning || a->binning_bytes < b200gs_binning_bytes(a->num_rendered)))) {
+    set_error("backward: geom / img / binning scratch smaller than the forward's (P=%d, %dx%d, num_rendered=%d)", a->P, a->width,
+              a->height, a->num_rendered);
+    return B200GS_ESIZE; }
   if (!a->dL_dout_color || !a->dL_dout_others || !a->dL_dmeans2D || !a->dL_dnormal || !a->dL_dopacity || !a->dL_dcolors ||
       !a->dL_dmeans3D || !a->dL_dtransMat || !a->dL_dscales || !a->dL_drotations || !a->radii || !a->means3D) {
     set_error("missing gradient pointer"); return B200GS_EINVAL; }

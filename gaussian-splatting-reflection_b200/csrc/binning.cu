@@ -218,7 +218,7 @@ __global__ void __launch_bounds__(256) duplicate_kernel(int P, const uint32_t* _
 }
 
 // ------------------------------------------------------------------ culled emission
-// Default mode of the surfel path (b200gs_set_exact_lists(0)): instances whose tile the Gaussian
+// Default mode of the surfel path (exact_lists = 0): instances whose tile the Gaussian
 // cannot reach with alpha >= 1/255 (cull_rows.cuh) are never emitted, so everything downstream --
 // sort, ranges, block masks, compositing -- works on the few per cent of the reference's list that
 // can contribute.  Images, radii, weights and gradients are unchanged (the reference rejects those
@@ -708,13 +708,13 @@ __global__ void __launch_bounds__(TH_THREADS) tile_hits_kernel(int R, const uint
 size_t tile_hits_state_words(size_t R) { return 2 * ((R + TH_TILE - 1) / TH_TILE + 2); }
 
 int surfel_tile_hits(const CullRec* cull, const Binning& b, int R, int W, int H, const uint2* ranges, uint2* cranges,
-                     cudaStream_t s, bool debug) {
+                     cudaStream_t s, bool debug, bool exact_lists, bool audit) {
   (void)H;
   const int gx = (W + TILE_X - 1) / TILE_X;
   StageScope _t(ST_TILE_HITS, s);
   B200GS_CUDA(cudaMemsetAsync(b.hit_state, 0, tile_hits_state_words(R) * sizeof(uint32_t), s));
-  const int keep_all = g_cull_audit.load(std::memory_order_relaxed);
-  if (g_exact_lists.load(std::memory_order_relaxed))
+  const int keep_all = audit ? 1 : 0;   // the cull audit walks the full lists
+  if (exact_lists)
     tile_hits_kernel<true><<<(R + TH_TILE - 1) / TH_TILE, TH_THREADS, 0, s>>>(R, b.tile_ids, b.point_list, cull, gx, ranges, cranges,
                                                                              b.comp_id, b.comp_pos, b.comp_hit, b.hit_state, keep_all);
   else

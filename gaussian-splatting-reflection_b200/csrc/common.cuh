@@ -50,7 +50,6 @@ enum Stage {
   ST_ADAM, ST_DENSIFY_STATS, ST_SSIM_FWD, ST_SSIM_BWD, ST_SHADE_FWD, ST_SHADE_BWD, ST_SURFACE_FWD, ST_SURFACE_BWD, ST_SCENE_IO, ST_COUNT
 };
 extern std::atomic<int> g_timing;        // 0 off, 1 every stage, 2 + k: stage k only
-extern std::atomic<int> g_cull_audit;   // surfel_composite_fwd.cu: b200gs_debug_cull_audit
 void stage_mark(int stage, bool begin, cudaStream_t s);
 struct StageScope {
   int st; cudaStream_t s; bool on;
@@ -248,9 +247,8 @@ int bin_and_sort(const uint32_t* order, const uint2* rects, const uint32_t* offs
                  const CullRec* cull = nullptr);
 int surfel_count_kept(int P, const uint32_t* tiles_touched, const uint2* rects, const CullRec* cull, uint32_t* kept,
                       cudaStream_t s, bool debug);
-extern std::atomic<int> g_exact_lists;  // api.cu: b200gs_set_exact_lists
 int surfel_tile_hits(const CullRec* cull, const Binning& b, int R, int W, int H, const uint2* ranges, uint2* cranges,
-                     cudaStream_t s, bool debug);
+                     cudaStream_t s, bool debug, bool exact_lists, bool keep_all);
 size_t tile_hits_state_words(size_t R);
 int surfel_composite_forward(const b200gs_surfel_fwd& a, const SurfelGeom& g, const SurfelImage& im,
                              const Binning& b, cudaStream_t s);

@@ -115,7 +115,7 @@ int b200gs_gauss_forward_stage1(const b200gs_gauss_fwd* a, int* num_rendered, vo
   rc = gauss_preprocess(*a, g, s);
   if (rc) return rc;
   const uint32_t* counts = g.tiles_touched;
-  if (g_exact_lists.load(std::memory_order_relaxed) == 0) {   // culled emission (include/b200gs.h: b200gs_set_exact_lists)
+  if (a->exact_lists == 0) {   // culled emission (include/b200gs.h: exact_lists)
     rc = surfel_count_kept(a->P, g.tiles_touched, g.rects, g.cull, g.tiles_kept, s, a->debug != 0);
     if (rc) return rc;
     counts = g.tiles_kept;
@@ -142,14 +142,14 @@ int b200gs_gauss_forward_stage2(const b200gs_gauss_fwd* a, int R, void* stream) 
   GaussImage im = GaussImage::carve(align128(a->img), a->width, a->height, nullptr);
   Binning b = Binning::carve(R > 0 ? align128(a->binning) : nullptr, R, nullptr);
   rc = bin_and_sort(g.order.vals_a, g.rects, g.point_offsets, a->P, R, a->width, a->height, b, im.ranges, s, a->debug != 0,
-                    g_exact_lists.load(std::memory_order_relaxed) != 0 ? nullptr : g.cull);
+                    a->exact_lists != 0 ? nullptr : g.cull);
   if (rc) return rc;
   {
     const size_t tiles = (size_t)((a->width + TILE_X - 1) / TILE_X) * ((a->height + TILE_Y - 1) / TILE_Y);
     B200GS_CUDA(cudaMemsetAsync(im.cranges, 0, tiles * sizeof(uint2), s));
   }
   if (R > 0) {
-    rc = surfel_tile_hits(g.cull, b, R, a->width, a->height, im.ranges, im.cranges, s, a->debug != 0);
+    rc = surfel_tile_hits(g.cull, b, R, a->width, a->height, im.ranges, im.cranges, s, a->debug != 0, a->exact_lists != 0, false);
     if (rc) return rc;
   }
   return gauss_composite_forward(*a, g, im, b, s);
@@ -161,6 +161,12 @@ int b200gs_gauss_backward(const b200gs_gauss_bwd* a, void* stream) {
   if (a->P <= 0) return B200GS_OK;
   if (!a->geom || !a->img || !a->accum || a->accum_bytes < b200gs_gauss_accum_bytes(a->P)) {
     set_error("missing scratch / accum too small"); return B200GS_ESIZE; }
+  if (a->width <= 0 || a->height <= 0 || a->num_rendered < 0) { set_error("bad sizes W=%d H=%d R=%d", a->width, a->height, a->num_rendered); return B200GS_EINVAL; }
+  if (a->geom_bytes < b200gs_gauss_geom_bytes(a->P) || a->img_bytes < b200gs_gauss_image_bytes(a->width, a->height) ||
+      (a->num_rendered > 0 && (!a->binning || a->binning_bytes < b200gs_binning_bytes(a->num_rendered)))) {
+    set_error("backward: geom / img / binning scratch smaller than the forward's (P=%d, %dx%d, num_rendered=%d)", a->P, a->width,
+              a->height, a->num_rendered);
+    return B200GS_ESIZE; }
   if (!a->dL_dout_color || !a->dL_dout_normal || !a->dL_dmeans2D || !a->dL_dopacity || !a->dL_dcolors || !a->dL_dnormals ||
       !a->dL_dmeans3D || !a->dL_dcov3D || !a->dL_dscales || !a->dL_drotations || !a->radii || !a->means3D || !a->opacities) {
     set_error("missing gradient pointer"); return B200GS_EINVAL; }

@@ -18,7 +18,6 @@
 // in one read of the keys, match.any-aggregated shared-memory atomics).
 #include "common.cuh"
 #include "radix_sort.cuh"
-#include <stdlib.h>
 
 namespace b200gs {
 
@@ -303,17 +302,6 @@ __global__ void __launch_bounds__(THREADS, 3) radix_pass_kernel(const PassArgs a
   }
 }
 
-// Ranking variant of the pass kernel; B200GS_RADIX_RANK=0|1|2 overrides the default (development switch).
-static int radix_rank_mode() {
-  static int mode = -1;
-  if (mode < 0) {
-    const char* e = getenv("B200GS_RADIX_RANK");
-    mode = e ? atoi(e) : RS_DEFAULT_RANK_MODE;
-    if (mode < 0 || mode > 2) mode = RS_DEFAULT_RANK_MODE;
-  }
-  return mode;
-}
-
 int radix_sort_pairs_u32(uint32_t* keys_a, uint32_t* vals_a, uint32_t* keys_b, uint32_t* vals_b, int n,
                          const RadixPlan& plan, void* workspace, cudaStream_t s, bool debug) {
   if (n <= 0) return B200GS_OK;
@@ -329,18 +317,10 @@ int radix_sort_pairs_u32(uint32_t* keys_a, uint32_t* vals_a, uint32_t* keys_b, u
     a.state = ws_state(workspace);
     a.ticket = ws_tickets(workspace) + p;
     B200GS_CUDA(cudaMemsetAsync(a.state, 0, (size_t)blocks * ((size_t)1 << a.nbits) * sizeof(unsigned long long), s));
-    static const int lb = []() { const char* e = getenv("B200GS_RADIX_LB"); return e ? atoi(e) : 4; }();   // development switch
-    // Measured on the bench workload (tile sort of 33.8M pairs, two passes): rank mode 0 0.76 ms, 1 0.64, 2 0.64;
-    // look-back batch 1 0.66, 4 0.61, 8 0.65; 512 threads x 8 keys 0.70-0.85 (removed).
-    switch (radix_rank_mode() * 10 + lb) {
-      case 1: radix_pass_kernel<0, 256, 16, 1><<<blocks, 256, 0, s>>>(a); break;
-      case 21: radix_pass_kernel<2, 256, 16, 1><<<blocks, 256, 0, s>>>(a); break;
-      case 14: radix_pass_kernel<1, 256, 16, 4><<<blocks, 256, 0, s>>>(a); break;
-      case 18: radix_pass_kernel<1, 256, 16, 8><<<blocks, 256, 0, s>>>(a); break;
-      case 24: radix_pass_kernel<2, 256, 16, 4><<<blocks, 256, 0, s>>>(a); break;
-      case 11: radix_pass_kernel<1, 256, 16, 1><<<blocks, 256, 0, s>>>(a); break;
-      default: radix_pass_kernel<1, 256, 16, 4><<<blocks, 256, 0, s>>>(a); break;
-    }
+    // Measured on the bench workload (round 1; tile sort of 33.8M pairs, two passes): ranking inside the counter loop
+    // 0.76 ms, independent match.any 0.64, ballots per digit bit 0.64; look-back batch 1 0.66, 4 0.61, 8 0.65;
+    // 512 threads x 8 keys 0.70-0.85.  Kept: independent match.any, 4-wide look-back.
+    radix_pass_kernel<1, 256, 16, 4><<<blocks, 256, 0, s>>>(a);
     B200GS_LAUNCHED("radix_pass_kernel", debug, s);
     uint32_t* x;
     x = ki; ki = ko; ko = x;

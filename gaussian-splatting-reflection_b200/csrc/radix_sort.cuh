@@ -24,7 +24,6 @@ constexpr int RS_ITEMS = 16;
 constexpr int RS_TILE = RS_THREADS * RS_ITEMS;  // pairs per block
 constexpr int RS_RADIX = 256;                   // bins per pass (digits of <= 8 bits)
 constexpr int RS_MAX_PASSES = 4;
-constexpr int RS_DEFAULT_RANK_MODE = 1;           // see radix_pass_kernel<MODE>
 
 // How a key range of `total_bits` bits is cut into passes of <= 8 bits.
 struct RadixPlan {

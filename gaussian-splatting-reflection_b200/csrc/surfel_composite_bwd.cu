@@ -11,7 +11,6 @@
 // row (ACC_STRIDE floats per Gaussian).  Warps none of whose pixels touch a
 // Gaussian skip the reduction altogether.
 #include "surfel_composite.cuh"
-#include <stdlib.h>
 
 namespace b200gs {
 
@@ -33,10 +32,9 @@ struct CompBwdArgs {
 
 constexpr int BATCH = 256;
 
-// MINB = resident CTAs per SM the register allocation is bounded for.  Measured on the bench workload:
-// 2 (98 registers) 1.87 ms, 3 (77 registers, no spills) 1.63 ms, 4 (64 registers, 48 B of spills) 1.61 ms.
-template <int MINB>
-__global__ void __launch_bounds__(BATCH, MINB) surfel_composite_bwd_kernel(const CompBwdArgs a) {
+// Register allocation bounded for 3 resident CTAs per SM.  Measured on the bench workload (round 1):
+// 2 CTAs (98 registers) 1.87 ms, 3 (77 registers, no spills) 1.63 ms, 4 (64 registers, 48 B of spills) 1.61 ms.
+__global__ void __launch_bounds__(BATCH, 3) surfel_composite_bwd_kernel(const CompBwdArgs a) {
   __shared__ SurfelRec s_rec[2][BATCH];
   __shared__ int s_id[2][BATCH];
   __shared__ uint32_t s_pos[2][BATCH];
@@ -180,14 +178,13 @@ __global__ void __launch_bounds__(BATCH, MINB) surfel_composite_bwd_kernel(const
       if (c) {
         const float4 q3 = rb[j].q[3], q4 = rb[j].q[4];
         const float alpha = h.alpha, G = h.G;
-        // One reciprocal each for (1 - alpha) and the depth instead of the reference's six divisions
-        // per pair (backward.cu:341,:373,:385,:412,:437-438); the backward is toleranced, not bit-exact.
+        // One reciprocal for (1 - alpha) and one for p.z instead of the reference's divisions
+        // (backward.cu:341,:412,:437-438): nothing cancels behind them.
         const float inv_1ma = __frcp_rn(__fsub_rn(1.0f, alpha));
         T = T * inv_1ma;
         const float w = alpha * T;
         const float om = 1.0f - last_alpha;
         const float c_d = h.depth;
-        const float rcd = __frcp_rn(c_d);
         // Colour, reflection strength, depth, alpha and normal (backward.cu:346-364,:392-402) all
         // enter dL_dalpha as (value - value accumulated behind) * upstream gradient.  The recurrence
         // is linear, so the nine per-channel recurrences of the reference collapse into ONE on
@@ -200,16 +197,21 @@ __global__ void __launch_bounds__(BATCH, MINB) surfel_composite_bwd_kernel(const
         g[12] = w * dpix0; g[13] = w * dpix1; g[14] = w * dpix2;
         g[15] = w * drefl;
         g[16] = w * dn0; g[17] = w * dn1; g[18] = w * dn2;
-        // distortion (:366-390)
-        const float m_d = (1.0f - NEAR_N * rcd) * (FAR_N / (FAR_N - NEAR_N));
-        const float dmd_dd = (FAR_N * NEAR_N / (FAR_N - NEAR_N)) * rcd * rcd;
+        // distortion (:366-390).  final_D2 + m^2 final_A - 2 m final_D and m final_A - final_D cancel in fp32, so
+        // m_d and both expressions are written in exactly the rounding shape of the reference build (SASS of
+        // renderCUDA<3>, nvcc 12.9: IEEE -0.2/c_d, +1, *far/(far-near); fma(2m, -D, fma(A, m*m, D2)); fma(A, m, -D)):
+        // with the forward's final_* bit-identical, dL_dweight and the last_dL_dT recurrence are then the reference's
+        // bit for bit, and only T (reciprocal instead of division, nothing cancels there) differs in the last place.
+        const float m_d = ndc_depth(c_d);
+        const float dmd_dd = __fdiv_rn(FAR_N * NEAR_N, __fmul_rn(c_d, __fmul_rn(c_d, FAR_N - NEAR_N)));
         float dL_dz = 0.0f;
-        if (contributor == median_contributor - 1u) dL_dz += dmedian;
-        const float dL_dweight = (final_D2 + m_d * m_d * final_A - 2.0f * m_d * final_D) * dreg;
-        dL_dalpha += dL_dweight - last_dL_dT;
-        last_dL_dT = dL_dweight * alpha + (1.0f - alpha) * last_dL_dT;
-        const float dL_dmd = 2.0f * w * (m_d * final_A - final_D) * dreg;
-        dL_dz += dL_dmd * dmd_dd;
+        if (contributor == median_contributor - 1u) dL_dz = dmedian;
+        const float dL_dweight =
+            __fmul_rn(dreg, __fmaf_rn(__fadd_rn(m_d, m_d), -final_D, __fmaf_rn(final_A, __fmul_rn(m_d, m_d), final_D2)));
+        dL_dalpha += __fsub_rn(dL_dweight, last_dL_dT);
+        last_dL_dT = __fmaf_rn(alpha, dL_dweight, __fmul_rn(last_dL_dT, __fsub_rn(1.0f, alpha)));
+        const float dL_dmd = __fmul_rn(dreg, __fmul_rn(__fadd_rn(w, w), __fmaf_rn(final_A, m_d, -final_D)));
+        dL_dz = __fmaf_rn(dL_dmd, dmd_dd, dL_dz);
 
         dL_dalpha *= T;
         last_alpha = alpha;
@@ -266,10 +268,7 @@ int surfel_composite_backward(const b200gs_surfel_bwd& f, const SurfelGeom& g, c
   a.acc = acc;
   StageScope _t(ST_COMPOSITE_BWD, s);
   B200GS_CUDA(cudaMemsetAsync(acc, 0, (size_t)f.P * ACC_STRIDE * sizeof(float), s));
-  static const int minb = []() { const char* e = getenv("B200GS_BWD_CTAS"); return e ? atoi(e) : 3; }();   // development switch
-  if (minb == 2) surfel_composite_bwd_kernel<2><<<a.gx * gy, BATCH, 0, s>>>(a);
-  else if (minb == 4) surfel_composite_bwd_kernel<4><<<a.gx * gy, BATCH, 0, s>>>(a);
-  else surfel_composite_bwd_kernel<3><<<a.gx * gy, BATCH, 0, s>>>(a);
+  surfel_composite_bwd_kernel<<<a.gx * gy, BATCH, 0, s>>>(a);
   B200GS_LAUNCHED("surfel_composite_bwd_kernel", f.debug, s);
   return B200GS_OK;
 }

@@ -31,7 +31,7 @@ struct CompFwdArgs {
 
 constexpr int BATCH = 256;
 
-// Cull audit (b200gs_debug_cull_audit): the AUDIT instantiation ignores the hit masks, evaluates
+// Cull audit (b200gs_surfel_fwd.cull_audit): the AUDIT instantiation ignores the hit masks, evaluates
 // every (warp, entry) pair like the reference does and counts the pairs that pass the
 // reference's alpha cut although their mask bit is clear -- [0] with the forward's
 // `unstable` threshold, [1] with the backward's.  Both must stay 0.
@@ -40,7 +40,6 @@ __device__ unsigned long long g_cull_violations[2];
 // the hit bit set, [1] those with >= 1 contributing lane, [2] lane contributions, [3] sum over
 // (warp, batch) of the busiest lane's contributions, [4] (warp, batch) count.
 __device__ unsigned long long g_cull_stats[8];
-std::atomic<int> g_cull_audit{0};
 
 template <bool AUDIT>
 __global__ void __launch_bounds__(BATCH) surfel_composite_fwd_kernel(const CompFwdArgs a) {
@@ -229,7 +228,7 @@ int surfel_composite_forward(const b200gs_surfel_fwd& f, const SurfelGeom& g, co
   a.out_color = f.out_color; a.out_others = f.out_others; a.out_refl = f.out_refl;
   a.gaussian_weights = f.gaussian_weights;
   StageScope _t(ST_COMPOSITE_FWD, s);
-  if (g_cull_audit.load(std::memory_order_relaxed))
+  if (f.cull_audit)
     surfel_composite_fwd_kernel<true><<<a.gx * gy, BATCH, 0, s>>>(a);
   else
     surfel_composite_fwd_kernel<false><<<a.gx * gy, BATCH, 0, s>>>(a);
@@ -240,7 +239,6 @@ int surfel_composite_forward(const b200gs_surfel_fwd& f, const SurfelGeom& g, co
 }  // namespace b200gs
 
 extern "C" {
-void b200gs_debug_cull_audit(int on) { b200gs::g_cull_audit.store(on ? 1 : 0); }
 int b200gs_debug_cull_stats(unsigned long long* out8, int reset) {
   using namespace b200gs;
   B200GS_CUDA(cudaDeviceSynchronize());

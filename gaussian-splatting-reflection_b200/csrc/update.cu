@@ -35,6 +35,7 @@ struct AdamGroupDev {
   long long chunk0;        // first CTA of this group
   int p_row, g_row, g_col; // parameter row length, gradient row stride and first column
   float step_size;         // lr / (1 - beta1^t)
+  float bc2_sqrt;          // sqrt(1 - beta2^t), t = the group's step
   int vec;                 // p, m, v are 16-B aligned: 128-bit accesses
   int gvec;                // ... and so is the (unstrided) gradient
   unsigned magic;          // ceil(2^32 / p_row): q / p_row == umulhi(q, magic) for q * p_row < 2^32
@@ -42,23 +43,23 @@ struct AdamGroupDev {
 struct AdamArgs {
   AdamGroupDev grp[UPD_MAX_GROUPS];
   int groups;
-  float one_minus_beta1, beta2, one_minus_beta2, bc2_sqrt, eps;
+  float one_minus_beta1, beta2, one_minus_beta2, eps;
 };
 
 // Exact zeros (Gaussians no view has reached yet: g = m = v = 0) are stepped around the IEEE division
 // and square root, whose slow paths they would otherwise take; the results are the same bits
 // (sqrt(0) / c + eps == eps, and p - s * (+-0 / d) == p).
-__device__ __forceinline__ void adam_update(const AdamArgs& a, float step_size, float g, float& p, float& m, float& v) {
+__device__ __forceinline__ void adam_update(const AdamArgs& a, float step_size, float bc2_sqrt, float g, float& p, float& m, float& v) {
   m = __fmaf_rn(a.one_minus_beta1, __fsub_rn(g, m), m);                              // lerp_(grad, 1 - beta1)
   v = __fmaf_rn(__fmul_rn(g, g), a.one_minus_beta2, __fmul_rn(v, a.beta2));          // mul_(beta2).addcmul_(g, g, 1 - beta2)
   if (m == 0.0f && (v > 0.0f || a.eps > 0.0f)) return;
   float denom = a.eps;
-  if (v != 0.0f) denom = __fadd_rn(__fdiv_rn(__fsqrt_rn(v), a.bc2_sqrt), a.eps);
+  if (v != 0.0f) denom = __fadd_rn(__fdiv_rn(__fsqrt_rn(v), bc2_sqrt), a.eps);
   p = __fmaf_rn(-step_size, __fdiv_rn(m, denom), p);                                 // addcdiv_(m, denom, -step_size)
 }
 
 __global__ void __launch_bounds__(UPD_THREADS) adam_kernel(const __grid_constant__ AdamArgs a) {
-  // which group does this CTA belong to (<= 8 entries)
+  // which group does this CTA belong to (<= 16 entries)
   int gi = 0;
 #pragma unroll
   for (int k = 1; k < UPD_MAX_GROUPS; ++k)
@@ -91,10 +92,10 @@ __global__ void __launch_bounds__(UPD_THREADS) adam_kernel(const __grid_constant
 #pragma unroll
     for (int k = 0; k < V; ++k) {
       const unsigned o = (k * UPD_THREADS + threadIdx.x) * 4u;
-      adam_update(a, G.step_size, gv[k].x, pv[k].x, mv[k].x, vv[k].x);
-      adam_update(a, G.step_size, gv[k].y, pv[k].y, mv[k].y, vv[k].y);
-      adam_update(a, G.step_size, gv[k].z, pv[k].z, mv[k].z, vv[k].z);
-      adam_update(a, G.step_size, gv[k].w, pv[k].w, mv[k].w, vv[k].w);
+      adam_update(a, G.step_size, G.bc2_sqrt, gv[k].x, pv[k].x, mv[k].x, vv[k].x);
+      adam_update(a, G.step_size, G.bc2_sqrt, gv[k].y, pv[k].y, mv[k].y, vv[k].y);
+      adam_update(a, G.step_size, G.bc2_sqrt, gv[k].z, pv[k].z, mv[k].z, vv[k].z);
+      adam_update(a, G.step_size, G.bc2_sqrt, gv[k].w, pv[k].w, mv[k].w, vv[k].w);
       *reinterpret_cast<float4*>(G.p + base + o) = pv[k];
       *reinterpret_cast<float4*>(G.m + base + o) = mv[k];
       *reinterpret_cast<float4*>(G.v + base + o) = vv[k];
@@ -115,7 +116,7 @@ __global__ void __launch_bounds__(UPD_THREADS) adam_kernel(const __grid_constant
   for (int k = 0; k < UPD_ITEMS; ++k) {
     const unsigned o = k * UPD_THREADS + threadIdx.x;
     if (base + o < G.n) {
-      adam_update(a, G.step_size, gv[k], pv[k], mv[k], vv[k]);
+      adam_update(a, G.step_size, G.bc2_sqrt, gv[k], pv[k], mv[k], vv[k]);
       G.p[base + o] = pv[k]; G.m[base + o] = mv[k]; G.v[base + o] = vv[k];
     }
   }
@@ -155,8 +156,6 @@ int b200gs_adam_step(const b200gs_adam* a, void* stream) {
   AdamArgs k;
   k.groups = 0;
   long long chunks = 0;
-  const double bc1 = 1.0 - pow(a->beta1, (double)a->step);
-  const double bc2 = 1.0 - pow(a->beta2, (double)a->step);
   for (int i = 0; i < a->groups; ++i) {
     const b200gs_adam_group& g = a->group[i];
     if (g.n == 0) continue;
@@ -164,11 +163,16 @@ int b200gs_adam_step(const b200gs_adam* a, void* stream) {
     const int p_row = g.param_row > 0 ? g.param_row : 1;
     const int g_row = g.grad_row > 0 ? g.grad_row : p_row;
     if (g.grad_col < 0 || g.grad_col + p_row > g_row || g.n % p_row != 0) { set_error("adam_step: group %d: bad row layout", i); return B200GS_EINVAL; }
+    const long long step = g.step > 0 ? g.step : a->step;
+    if (step < 1) { set_error("adam_step: group %d: step must be >= 1", i); return B200GS_EINVAL; }
+    const double bc1 = 1.0 - pow(a->beta1, (double)step);
+    const double bc2 = 1.0 - pow(a->beta2, (double)step);
     AdamGroupDev& d = k.grp[k.groups++];
     d.p = g.param; d.g = g.grad; d.m = g.exp_avg; d.v = g.exp_avg_sq;
     d.n = g.n; d.chunk0 = chunks;
     d.p_row = p_row; d.g_row = g_row; d.g_col = g.grad_col;
     d.step_size = (float)(g.lr / bc1);
+    d.bc2_sqrt = (float)sqrt(bc2);
     auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15u) == 0; };
     d.vec = (al16(g.param) && al16(g.exp_avg) && al16(g.exp_avg_sq)) ? 1 : 0;
     d.gvec = (d.vec && g_row == p_row && g.grad_col == 0 && al16(g.grad)) ? 1 : 0;
@@ -183,7 +187,6 @@ int b200gs_adam_step(const b200gs_adam* a, void* stream) {
   k.one_minus_beta1 = (float)(1.0 - a->beta1);
   k.beta2 = (float)a->beta2;
   k.one_minus_beta2 = (float)(1.0 - a->beta2);
-  k.bc2_sqrt = (float)sqrt(bc2);
   k.eps = (float)a->eps;
   cudaStream_t s = (cudaStream_t)stream;
   StageScope _t(ST_ADAM, s);

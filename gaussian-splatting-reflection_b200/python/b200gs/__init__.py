@@ -42,7 +42,7 @@ class SurfelFwd(C.Structure):
         ("geom", _p), ("geom_bytes", _sz), ("img", _p), ("img_bytes", _sz),
         ("binning", _p), ("binning_bytes", _sz),
         ("out_color", _p), ("out_others", _p), ("out_refl", _p), ("radii", _p),
-        ("gaussian_weights", _p),
+        ("gaussian_weights", _p), ("exact_lists", _i), ("cull_audit", _i),
     ]
 
 
@@ -60,6 +60,7 @@ class SurfelBwd(C.Structure):
         ("dL_dmeans2D", _p), ("dL_dnormal", _p), ("dL_dopacity", _p), ("dL_dcolors", _p),
         ("dL_drefl", _p), ("dL_dmeans3D", _p), ("dL_dtransMat", _p), ("dL_dsh", _p),
         ("dL_dscales", _p), ("dL_drotations", _p), ("accumulate", _i),
+        ("geom_bytes", _sz), ("binning_bytes", _sz), ("img_bytes", _sz),
     ]
 
 
@@ -74,6 +75,7 @@ class GaussFwd(C.Structure):
         ("viewmatrix", _p), ("projmatrix", _p), ("campos", _p),
         ("geom", _p), ("geom_bytes", _sz), ("img", _p), ("img_bytes", _sz), ("binning", _p), ("binning_bytes", _sz),
         ("out_color", _p), ("out_invdepth", _p), ("out_normal", _p), ("out_refl", _p), ("radii", _p),
+        ("exact_lists", _i),
     ]
 
 
@@ -90,6 +92,7 @@ class GaussBwd(C.Structure):
         ("dL_dmeans2D", _p), ("dL_dconic", _p), ("dL_dopacity", _p), ("dL_dcolors", _p), ("dL_dnormals", _p),
         ("dL_drefl", _p), ("dL_dinvdepths", _p), ("dL_dmeans3D", _p), ("dL_dcov3D", _p), ("dL_dsh", _p),
         ("dL_dscales", _p), ("dL_drotations", _p),
+        ("geom_bytes", _sz), ("binning_bytes", _sz), ("img_bytes", _sz),
     ]
 
 
@@ -120,9 +123,6 @@ def timing_read():
     return {timing_stage_name(i).decode(): (float(ms[i]), int(cnt[i])) for i in range(n)}
 
 
-set_exact_lists = _sig("b200gs_set_exact_lists", None, _i)
-get_exact_lists = _sig("b200gs_get_exact_lists", _i)
-debug_cull_audit = _sig("b200gs_debug_cull_audit", None, _i)
 _cull_violations = _sig("b200gs_debug_cull_violations", _i, _p, _i)
 
 
@@ -168,13 +168,13 @@ cubemap_forward = _sig("b200gs_cubemap_forward", _i, _p, _p, _p, _p, _u, _u, _u,
 cubemap_backward = _sig("b200gs_cubemap_backward", _i, _p, _p, _p, _p, _p, _p, _u, _u, _u, _u, _u, _p)
 
 
-ADAM_MAX_GROUPS = 8
+ADAM_MAX_GROUPS = 16
 
 
 class AdamGroup(C.Structure):
     """struct b200gs_adam_group"""
     _fields_ = [("param", _p), ("grad", _p), ("exp_avg", _p), ("exp_avg_sq", _p), ("n", C.c_longlong),
-                ("param_row", _i), ("grad_row", _i), ("grad_col", _i), ("lr", C.c_double)]
+                ("param_row", _i), ("grad_row", _i), ("grad_col", _i), ("lr", C.c_double), ("step", C.c_longlong)]
 
 
 class Adam(C.Structure):
@@ -185,6 +185,9 @@ class Adam(C.Structure):
 
 adam_step = _sig("b200gs_adam_step", _i, C.POINTER(Adam), _p)
 densify_stats = _sig("b200gs_densify_stats", _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p)
+
+
+peer_allreduce_f32 = _sig("b200gs_peer_allreduce_f32", _i, _p, C.POINTER(_p), _i, _i, _sz, _p)
 
 
 ssim_forward = _sig("b200gs_ssim_forward", _i, _f, _f, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p)

@@ -7,11 +7,13 @@ right after the rendering path's backward, on the sm_100a kernels of csrc/update
   DensifyStats      <- max_radii2D update (train.py:242-243) + add_densification_stats
                        (scene/gaussian_model.py:579-584)
 
-Same names, argument meaning and state layout (`param_groups` with "name"/"lr", `state[...]` with
-exp_avg / exp_avg_sq) as the torch optimizer the reference builds, so `update_learning_rate`
-(scene/gaussian_model.py:216-222) works unchanged.  Gradients are read where the backward left
-them: separate tensors, or the blocks of a b200gs.dp.GradArena after its all-reduce; f_dc and
-f_rest both read the [P, M, 3] dL_dsh block (columns [0,3) and [3,3M)), no split/copy.
+GaussianAdam IS a torch.optim.Optimizer (same constructor call, `param_groups` with "name"/"lr", `state`
+keyed by the parameter tensor with step / exp_avg / exp_avg_sq, state_dict / load_state_dict), so
+`update_learning_rate` (scene/gaussian_model.py:216-222), the densify / prune / reset-opacity state surgery
+(:383-478) and capture / restore (:55-94) work on it unchanged.  Gradients are read from .grad, or -- for
+callers that feed the parameters straight into the rasterizer -- from the blocks of a b200gs.dp.GradArena
+after its all-reduce; f_dc and f_rest then both read the [P, M, 3] dL_dsh block (columns [0,3) and [3,3M)),
+no split/copy.
 
 There is no CPU path: tensors must live on a CUDA device.
 """
@@ -23,76 +25,105 @@ import b200gs
 _SH_SPLIT = {"f_dc": (0, 3), "f_rest": (3, None)}
 
 
-class GaussianAdam:
-    """Adam over named parameter groups, all groups in ONE kernel launch per step."""
+class GaussianAdam(torch.optim.Optimizer):
+    """Adam with torch.optim.Adam's surface -- `param_groups`, `state` KEYED BY THE PARAMETER TENSOR with
+    `step` / `exp_avg` / `exp_avg_sq` entries, `state_dict()` / `load_state_dict()`, `zero_grad()` -- so the
+    reference's optimizer surgery (replace_tensor_to_optimizer, _prune_optimizer, cat_tensors_to_optimizer,
+    construct_list_of_attributes, capture / restore; scene/gaussian_model.py:55-94, :383-478) works on it
+    unchanged, and with ONE kernel launch per step() over all parameter tensors instead of torch's ~10
+    multi-tensor passes.  Construct it exactly like the reference does:
+    `GaussianAdam(l, lr=0.0, eps=1e-15)` (scene/gaussian_model.py:207); groups may hold several tensors (the
+    reference's "env" group holds the cube-map texture and its fail value).
 
-    def __init__(self, groups, betas=(0.9, 0.999), eps=1e-15):
-        """groups: list of {"params": [tensor], "lr": float, "name": str} as in training_setup()."""
-        if len(groups) > b200gs.ADAM_MAX_GROUPS:
-            raise ValueError(f"at most {b200gs.ADAM_MAX_GROUPS} groups per launch")
-        self.param_groups, self.state = [], {}
-        for g in groups:
-            ps = list(g["params"])
-            if len(ps) != 1:
-                raise ValueError("one tensor per group (the reference's Gaussian groups hold one each)")
-            p = ps[0]
-            if not (p.is_cuda and p.dtype == torch.float32 and p.is_contiguous()):
-                raise ValueError(f"group {g.get('name')}: parameters must be contiguous fp32 CUDA tensors")
-            self.param_groups.append({"params": [p], "lr": float(g["lr"]), "name": g["name"]})
-            self.state[g["name"]] = {"step": 0, "exp_avg": torch.zeros_like(p), "exp_avg_sq": torch.zeros_like(p)}
-        self.betas, self.eps = (float(betas[0]), float(betas[1])), float(eps)
-        self.step_count = 0
+    State entries are created lazily at a parameter's first step, like torch's; `step` is a CPU fp32 scalar
+    tensor like torch's default (non-capturable) Adam, so state dicts are interchangeable with
+    torch.optim.Adam's.  A parameter whose gradient is None is skipped and its step does not advance."""
 
-    def step(self, grads=None):
-        """grads: {group name: tensor}; "sh" may stand in for both f_dc and f_rest ([P, M, 3], the
-        rasterizer's dL_dsh).  Without `grads` every parameter's .grad is used (like torch's step())."""
-        a = b200gs.Adam()
-        a.beta1, a.beta2, a.eps = self.betas[0], self.betas[1], self.eps
-        self.step_count += 1
-        a.step = self.step_count
-        k, keep = 0, []
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8):
+        if not 0.0 <= eps:
+            raise ValueError(f"Invalid epsilon value: {eps}")
+        if not (0.0 <= betas[0] < 1.0 and 0.0 <= betas[1] < 1.0):
+            raise ValueError(f"Invalid beta parameters: {betas}")
+        super().__init__(params, dict(lr=lr, betas=betas, eps=eps))
+
+    @staticmethod
+    def _check(p, what, name):
+        if not (p.is_cuda and p.dtype == torch.float32 and p.is_contiguous()):
+            raise ValueError(f"group {name}: {what} must be a contiguous fp32 CUDA tensor")
+
+    def _state_of(self, p):
+        st = self.state[p]
+        if len(st) == 0:
+            st["step"] = torch.tensor(0.0, dtype=torch.float32)
+            st["exp_avg"] = torch.zeros_like(p, memory_format=torch.preserve_format)
+            st["exp_avg_sq"] = torch.zeros_like(p, memory_format=torch.preserve_format)
+        return st
+
+    @torch.no_grad()
+    def step(self, grads=None, closure=None):
+        """grads: optional {group name: tensor} read INSTEAD of .grad -- the blocks of an all-reduced
+        b200gs.dp.GradArena; "sh" may stand in for both f_dc and f_rest ([P, M, 3], the rasterizer's dL_dsh,
+        read as column slices, no split / copy).  Only meaningful when the rasterizer inputs ARE the
+        parameters; a model with activations in between (the reference's) propagates the arena with
+        GradArena.backward_through() and then calls step() with no argument, which reads every .grad."""
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
+        batches = {}          # (beta1, beta2, eps) -> list of kernel group entries
+        keep = []
         for g in self.param_groups:
-            p, name = g["params"][0], g["name"]
-            if p.numel() == 0:
-                continue
-            row = p[0].numel() if p.dim() > 1 else 1
-            grad, grow, gcol = None, row, 0
-            if grads is not None:
-                if name in grads:
+            name = g.get("name")
+            for p in g["params"]:
+                if p.numel() == 0:
+                    continue
+                row = p[0].numel() if p.dim() > 1 else 1
+                grad, grow, gcol = None, row, 0
+                if grads is not None and name in grads:
                     grad = grads[name]
-                elif name in _SH_SPLIT and "sh" in grads:
+                elif grads is not None and name in _SH_SPLIT and "sh" in grads:
                     grad = grads["sh"]
                     grow = grad[0].numel()
                     gcol = _SH_SPLIT[name][0]
                     if gcol + row > grow:
                         raise ValueError(f"{name}: parameter row {row} does not fit the sh gradient row {grow}")
-            else:
-                grad = p.grad
-            if grad is None:
-                continue
-            if not (grad.is_cuda and grad.dtype == torch.float32 and grad.is_contiguous()):
-                raise ValueError(f"group {name}: gradients must be contiguous fp32 CUDA tensors")
-            if grad.numel() != (p.numel() // row) * grow:
-                raise ValueError(f"group {name}: gradient has {grad.numel()} floats, expected {(p.numel() // row) * grow}")
-            st = self.state[name]
-            st["step"] = self.step_count
-            e = a.group[k]
-            e.param, e.grad, e.exp_avg, e.exp_avg_sq = p.data_ptr(), grad.data_ptr(), st["exp_avg"].data_ptr(), st["exp_avg_sq"].data_ptr()
-            e.n, e.param_row, e.grad_row, e.grad_col, e.lr = p.numel(), row, grow, gcol, g["lr"]
-            keep.append(grad)
-            k += 1
-        a.groups = k
-        if k:
-            b200gs.check(b200gs.adam_step(a, torch.cuda.current_stream().cuda_stream))
-
-    def zero_grad(self, set_to_none=True):
-        for g in self.param_groups:
-            p = g["params"][0]
-            if p.grad is not None:
-                if set_to_none:
-                    p.grad = None
-                else:
-                    p.grad.zero_()
+                elif grads is None:
+                    grad = p.grad
+                if grad is None:
+                    continue
+                if grad.is_sparse:
+                    raise RuntimeError("GaussianAdam does not support sparse gradients")
+                self._check(p, "parameters", name)
+                self._check(grad, "gradients", name)
+                if grad.numel() != (p.numel() // row) * grow:
+                    raise ValueError(f"group {name}: gradient has {grad.numel()} floats, expected {(p.numel() // row) * grow}")
+                st = self._state_of(p)
+                m, v = st["exp_avg"], st["exp_avg_sq"]
+                if m.shape != p.shape or v.shape != p.shape:
+                    # the reference's densify / prune surgery resizes parameter and moments together; a mismatch
+                    # here would make the kernel run over the moments' old extent
+                    raise RuntimeError(f"group {name}: optimizer state {tuple(m.shape)} / {tuple(v.shape)} does not "
+                                       f"match the parameter {tuple(p.shape)}")
+                self._check(m, "exp_avg", name)
+                self._check(v, "exp_avg_sq", name)
+                st["step"] += 1
+                e = b200gs.AdamGroup()
+                e.param, e.grad, e.exp_avg, e.exp_avg_sq = p.data_ptr(), grad.data_ptr(), m.data_ptr(), v.data_ptr()
+                e.n, e.param_row, e.grad_row, e.grad_col = p.numel(), row, grow, gcol
+                e.lr, e.step = float(g["lr"]), int(st["step"])
+                batches.setdefault((float(g["betas"][0]), float(g["betas"][1]), float(g["eps"])), []).append(e)
+                keep.append(grad)
+        stream = torch.cuda.current_stream().cuda_stream if batches else None
+        for (b1, b2, eps), entries in batches.items():
+            for i in range(0, len(entries), b200gs.ADAM_MAX_GROUPS):
+                a = b200gs.Adam()
+                a.beta1, a.beta2, a.eps, a.step = b1, b2, eps, 1
+                chunk = entries[i:i + b200gs.ADAM_MAX_GROUPS]
+                for k, e in enumerate(chunk):
+                    a.group[k] = e
+                a.groups = len(chunk)
+                b200gs.check(b200gs.adam_step(a, stream))
+        return loss
 
 
 def surfel_param_groups(xyz, f_dc, f_rest, opacity, scaling, rotation, refl, lrs):
@@ -106,7 +137,11 @@ GRAD_TO_GROUP = {"means3D": "xyz", "sh": "sh", "opacity": "opacity", "scales": "
 
 
 def arena_grads(arena):
-    """{group name: gradient block} of a b200gs.dp.GradArena (after arena.all_reduce())."""
+    """{group name: gradient block} of a b200gs.dp.GradArena (after arena.all_reduce()) for GaussianAdam.step().
+    The blocks are gradients with respect to the rasterizer's INPUTS: valid as parameter gradients only when
+    the parameters are fed to the rasterizer as they are.  The reference's model puts sigmoid / exp / normalize
+    between them (scene/gaussian_model.py:124-147): there, use arena.backward_through({...activated tensors...})
+    and a plain optimizer.step()."""
     return {GRAD_TO_GROUP[k]: v for k, v in arena.views().items()}
 
 

@@ -26,7 +26,7 @@ def _stream():
 
 def rasterize_gaussians(background, means3D, colors, normals, refl_strengths, opacity, scales, rotations, scale_modifier,
                         cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh,
-                        degree, campos, prefiltered, antialiasing, debug):
+                        degree, campos, prefiltered, antialiasing, debug, *, exact_lists=False):
     """-> (rendered, out_color[3,H,W], radii[P], geomBuffer, binningBuffer, imgBuffer, out_invdepth[1,H,W],
     normal_map[3,H,W], refl_strength_map[1,H,W])   (G/rasterize_points.cu:39-141)"""
     if means3D.dim() != 2 or means3D.size(1) != 3:
@@ -70,7 +70,8 @@ def rasterize_gaussians(background, means3D, colors, normals, refl_strengths, op
                 viewmatrix=_b.ptr(viewmatrix), projmatrix=_b.ptr(projmatrix), campos=_b.ptr(campos),
                 geom=geom.data_ptr(), geom_bytes=geom.numel(), img=img.data_ptr(), img_bytes=img.numel(),
                 binning=None, binning_bytes=0, out_color=out_color.data_ptr(), out_invdepth=out_invdepth.data_ptr(),
-                out_normal=out_normal.data_ptr(), out_refl=out_refl.data_ptr(), radii=radii.data_ptr())
+                out_normal=out_normal.data_ptr(), out_refl=out_refl.data_ptr(), radii=radii.data_ptr(),
+                exact_lists=int(bool(exact_lists)))
             n = C.c_int(0)
             st = _stream()
             _b.check(_b.gauss_forward_stage1(C.byref(a), C.byref(n), st))
@@ -140,7 +141,8 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, normals, re
                 dL_dmeans2D=_b.ptr(dL_dmeans2D), dL_dconic=None, dL_dopacity=_b.ptr(dL_dopacity),
                 dL_dcolors=_b.ptr(dL_dcolors), dL_dnormals=_b.ptr(dL_dnormals), dL_drefl=_b.ptr(dL_drefl),
                 dL_dinvdepths=_b.ptr(dL_dinvdepths), dL_dmeans3D=_b.ptr(dL_dmeans3D), dL_dcov3D=_b.ptr(dL_dcov3D),
-                dL_dsh=_b.ptr(dL_dsh), dL_dscales=_b.ptr(dL_dscales), dL_drotations=_b.ptr(dL_drotations))
+                dL_dsh=_b.ptr(dL_dsh), dL_dscales=_b.ptr(dL_dscales), dL_drotations=_b.ptr(dL_drotations),
+                geom_bytes=geomBuffer.numel(), binning_bytes=binningBuffer.numel(), img_bytes=imageBuffer.numel())
             _b.check(_b.gauss_backward(C.byref(a), _stream()))
     return (dL_dmeans2D, dL_dcolors, dL_dnormals, dL_drefl, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales,
             dL_drotations)

@@ -14,17 +14,6 @@ import b200gs as _b
 
 NUM_CHANNELS = 3
 
-# Optional destination for the parameter gradients (b200gs.dp.GradArena): when set, the backward
-# writes dL_dmeans3D / dL_dsh / dL_dopacity / dL_dscales / dL_drotations / dL_drefl into views of
-# that flat buffer (zero-copy NCCL all-reduce) instead of freshly allocated tensors.
-_grad_arena = None
-
-
-def use_gradient_arena(arena):
-    global _grad_arena
-    _grad_arena = arena
-
-
 def _cuda_f32(name, t):
     if not t.is_cuda:
         raise RuntimeError(f"{name} must be a CUDA tensor")
@@ -39,9 +28,14 @@ def _stream():
 
 def rasterize_gaussians(background, means3D, env_scope_mask, colors, refl_strengths, opacity, scales, rotations,
                         scale_modifier, transMat_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy,
-                        image_height, image_width, sh, degree, campos, prefiltered, debug):
+                        image_height, image_width, sh, degree, campos, prefiltered, debug, *, exact_lists=False,
+                        cull_audit=False):
     """-> (rendered, out_color[3,H,W], out_others[8,H,W], radii[P], geomBuffer, binningBuffer,
-    imgBuffer, out_refl_strength_map[1,H,W], gaussian_weights[P])   (S/rasterize_points.cu:39-151)"""
+    imgBuffer, out_refl_strength_map[1,H,W], gaussian_weights[P])   (S/rasterize_points.cu:39-151)
+
+    The 21 positional arguments are the reference's.  Keyword-only extras of this library, per call (the
+    library keeps no mode of its own): exact_lists -- emit the reference's instance lists bit for bit
+    instead of only the reachable instances (include/b200gs.h); cull_audit -- test infrastructure."""
     if means3D.dim() != 2 or means3D.size(1) != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")
     background = _cuda_f32("background", background)
@@ -97,7 +91,8 @@ def rasterize_gaussians(background, means3D, env_scope_mask, colors, refl_streng
                 geom=geom.data_ptr(), geom_bytes=geom.numel(), img=img.data_ptr(), img_bytes=img.numel(),
                 binning=None, binning_bytes=0,
                 out_color=out_color.data_ptr(), out_others=out_others.data_ptr(), out_refl=out_refl.data_ptr(),
-                radii=radii.data_ptr(), gaussian_weights=gaussian_weights.data_ptr())
+                radii=radii.data_ptr(), gaussian_weights=gaussian_weights.data_ptr(),
+                exact_lists=int(bool(exact_lists)), cull_audit=int(bool(cull_audit)))
             n = C.c_int(0)
             st = _stream()
             _b.check(_b.surfel_forward_stage1(C.byref(a), C.byref(n), st))
@@ -112,9 +107,14 @@ def rasterize_gaussians(background, means3D, env_scope_mask, colors, refl_streng
 def rasterize_gaussians_backward(background, means3D, radii, colors, refl_strengths, scales, rotations, scale_modifier,
                                  transMat_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color,
                                  dL_dout_others, dL_dout_refl_strength_map, sh, degree, campos, geomBuffer, R,
-                                 binningBuffer, imageBuffer, debug):
+                                 binningBuffer, imageBuffer, debug, *, grad_arena=None):
     """-> (dL_dmeans2D[P,3], dL_dcolors[P,3], dL_drefl[P,1], dL_dopacity[P,1], dL_dmeans3D[P,3],
-    dL_dtransMat[P,9], dL_dsh[P,M,3], dL_dscales[P,2], dL_drotations[P,4])   (S/rasterize_points.cu:153-267)"""
+    dL_dtransMat[P,9], dL_dsh[P,M,3], dL_dscales[P,2], dL_drotations[P,4])   (S/rasterize_points.cu:153-267)
+
+    The 24 positional arguments are the reference's.  grad_arena (keyword-only, per call): a
+    b200gs.dp.GradArena -- the parameter gradients dL_dmeans3D / dL_dsh / dL_dopacity / dL_dscales /
+    dL_drotations / dL_drefl are then written into (accumulate mode: ADDED to) the blocks of that flat
+    buffer, which NCCL reduces as it lies, and the returned tensors are views of it."""
     background = _cuda_f32("background", background)
     means3D = _cuda_f32("means3D", means3D)
     colors = _cuda_f32("colors", colors)
@@ -139,7 +139,7 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, refl_streng
     M = sh.size(1) if sh.numel() else 0
     o = dict(dtype=torch.float32, device=means3D.device)
     with torch.cuda.device(means3D.device):
-        arena = _grad_arena
+        arena = grad_arena
         if arena is not None and (arena.P != P or arena.M != M or not has_refl or arena.flat.device != means3D.device):
             raise RuntimeError("gradient arena does not match this call (P, SH coefficients, refl map or device)")
         if arena is not None:
@@ -178,7 +178,8 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, refl_streng
                 dL_dcolors=_b.ptr(dL_dcolors), dL_drefl=_b.ptr(dL_drefl), dL_dmeans3D=_b.ptr(dL_dmeans3D),
                 dL_dtransMat=_b.ptr(dL_dtransMat), dL_dsh=_b.ptr(dL_dsh), dL_dscales=_b.ptr(dL_dscales),
                 dL_drotations=_b.ptr(dL_drotations),
-                accumulate=1 if (arena is not None and arena.accumulate) else 0)
+                accumulate=1 if (arena is not None and arena.accumulate) else 0,
+                geom_bytes=geomBuffer.numel(), binning_bytes=binningBuffer.numel(), img_bytes=imageBuffer.numel())
             _b.check(_b.surfel_backward(C.byref(a), _stream()))
     return (dL_dmeans2D, dL_dcolors, dL_drefl, dL_dopacity, dL_dmeans3D, dL_dtransMat, dL_dsh, dL_dscales,
             dL_drotations)

@@ -6,6 +6,12 @@ Public surface and behaviour follow the reference package
 `rasterize_gaussians` (:21-46) and the autograd function behind it (:48-168), so
 the reference's gaussian_renderer/__init__.py, train.py and render.py import and
 call it unchanged.
+
+Two keyword-only extras exist for callers that know this library (the reference's callers never pass
+them): `exact_lists` (emit the reference's instance lists bit for bit, include/b200gs.h) and `grad_arena`
+(a b200gs.dp.GradArena the backward accumulates the parameter gradients of a batch of views into, for
+the one NCCL all-reduce of view-parallel training).  Both are per-call state of the module instance;
+the library itself keeps no mode.
 """
 from typing import NamedTuple
 
@@ -38,12 +44,12 @@ def _snapshot(args):
     return tuple(a.detach().cpu().clone() if isinstance(a, torch.Tensor) else a for a in args)
 
 
-def _call_with_dump(fn, args, debug, dump_path, what):
+def _call_with_dump(fn, args, debug, dump_path, what, **kw):
     if not debug:
-        return fn(*args)
+        return fn(*args, **kw)
     saved = _snapshot(args)
     try:
-        return fn(*args)
+        return fn(*args, **kw)
     except Exception:
         torch.save(saved, dump_path)
         print(f"\nAn error occured in {what}. Please forward {dump_path} for debugging.")
@@ -53,14 +59,17 @@ def _call_with_dump(fn, args, debug, dump_path, what):
 class _RasterizeGaussians(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means3D, means2D, sh, colors_precomp, refl_strengths, opacities, scales, rotations,
-                cov3Ds_precomp, raster_settings, env_scope_mask):
+                cov3Ds_precomp, raster_settings, env_scope_mask, opts=None):
         rs = raster_settings
+        opts = opts or {}
         args = (rs.bg, means3D, env_scope_mask, colors_precomp, refl_strengths, opacities, scales, rotations,
                 rs.scale_modifier, cov3Ds_precomp, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy,
                 rs.image_height, rs.image_width, sh, rs.sh_degree, rs.campos, rs.prefiltered, rs.debug)
         (num_rendered, color, depth, radii, geomBuffer, binningBuffer, imgBuffer, refl_strength_map,
-         gaussian_weights) = _call_with_dump(_C.rasterize_gaussians, args, rs.debug, "snapshot_fw.dump", "forward")
+         gaussian_weights) = _call_with_dump(_C.rasterize_gaussians, args, rs.debug, "snapshot_fw.dump", "forward",
+                                             exact_lists=bool(opts.get("exact_lists", False)))
         ctx.raster_settings = rs
+        ctx.grad_arena = opts.get("grad_arena")
         ctx.num_rendered = num_rendered
         ctx.save_for_backward(colors_precomp, refl_strengths, means3D, scales, rotations, cov3Ds_precomp, radii, sh,
                               geomBuffer, binningBuffer, imgBuffer)
@@ -77,22 +86,32 @@ class _RasterizeGaussians(torch.autograd.Function):
                 imgBuffer, rs.debug)
         (grad_means2D, grad_colors_precomp, grad_refl, grad_opacities, grad_means3D, grad_cov3Ds_precomp, grad_sh,
          grad_scales, grad_rotations) = _call_with_dump(_C.rasterize_gaussians_backward, args, rs.debug,
-                                                        "snapshot_bw.dump", "backward")
-        # input order of forward(); None for raster_settings and env_scope_mask
+                                                        "snapshot_bw.dump", "backward", grad_arena=ctx.grad_arena)
+        if ctx.grad_arena is not None:
+            # The parameter gradients of this view now sit (summed with the batch's other views) in the arena.
+            # Handing arena views to autograd would alias them with .grad / be added a second time, and would
+            # run the activation backward once per view; the arena is propagated ONCE per batch instead
+            # (b200gs.dp.GradArena.backward_through / bind_grads).  means2D (the densification statistic) and the
+            # precomputed-input gradients stay ordinary per-view tensors.
+            return (None, grad_means2D, None, grad_colors_precomp, None, None, None, None, grad_cov3Ds_precomp,
+                    None, None, None)
+        # input order of forward(); None for raster_settings, env_scope_mask and opts
         return (grad_means3D, grad_means2D, grad_sh, grad_colors_precomp, grad_refl, grad_opacities, grad_scales,
-                grad_rotations, grad_cov3Ds_precomp, None, None)
+                grad_rotations, grad_cov3Ds_precomp, None, None, None)
 
 
 def rasterize_gaussians(means3D, means2D, sh, colors_precomp, refl_strengths, opacities, scales, rotations,
-                        cov3Ds_precomp, raster_settings, env_scope_mask):
+                        cov3Ds_precomp, raster_settings, env_scope_mask, opts=None):
     return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, refl_strengths, opacities, scales,
-                                     rotations, cov3Ds_precomp, raster_settings, env_scope_mask)
+                                     rotations, cov3Ds_precomp, raster_settings, env_scope_mask, opts)
 
 
 class GaussianRasterizer(nn.Module):
-    def __init__(self, raster_settings):
+    def __init__(self, raster_settings, *, exact_lists=False, grad_arena=None):
         super().__init__()
         self.raster_settings = raster_settings
+        self.exact_lists = bool(exact_lists)
+        self.grad_arena = grad_arena
 
     def markVisible(self, positions):
         """Boolean mask of the points in front of the camera's near plane."""
@@ -117,5 +136,8 @@ class GaussianRasterizer(nn.Module):
         rotations = empty() if rotations is None else rotations
         cov3D_precomp = empty() if cov3D_precomp is None else cov3D_precomp
         env_scope_mask = empty() if env_scope_mask is None else env_scope_mask
+        opts = None
+        if self.exact_lists or self.grad_arena is not None:
+            opts = {"exact_lists": self.exact_lists, "grad_arena": self.grad_arena}
         return rasterize_gaussians(means3D, means2D, shs, colors_precomp, refl_strengths, opacities, scales, rotations,
-                                   cov3D_precomp, self.raster_settings, env_scope_mask)
+                                   cov3D_precomp, self.raster_settings, env_scope_mask, opts)

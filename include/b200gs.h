@@ -57,24 +57,24 @@ int b200gs_timing_stages(void);
 const char* b200gs_timing_stage_name(int stage);
 int b200gs_timing_read(float* ms, unsigned long long* counts, int n);
 
-/* Instance lists of the surfel path.  0 (default): culled emission -- a (Gaussian, tile) instance is
+/* Instance lists (field `exact_lists` of b200gs_surfel_fwd / b200gs_gauss_fwd; a per-call argument, the
+ * library keeps no mode of its own).  0: culled emission -- a (Gaussian, tile) instance is
  * only emitted if the Gaussian can reach alpha >= 1/255 somewhere in the tile, so num_rendered and
  * the sorted lists are a subsequence of the reference's (typically a few per cent of it when splats
  * cross the camera plane); colour/aux/reflection images, radii, weights and gradients are
  * unchanged.  1: exact lists -- num_rendered, the sorted (key, value) lists, the tile ranges and
  * n_contrib are the reference's, bit for bit (S/cuda_rasterizer/rasterizer_impl.cu:282-321); the
  * compositing kernels then skip the unreachable instances through the compacted list instead.
- * Process-wide; must not change between a forward's stage 1 and its backward.               */
-void b200gs_set_exact_lists(int on);
-int b200gs_get_exact_lists(void);
+ * Stage 1 and stage 2 of one forward must be given the same struct.                          */
 
-/* Cull audit (test infrastructure for the sub-tile culling of the surfel compositing):
- * while on, the forward compositing ignores the per-instance hit masks, evaluates every
+/* Cull audit (test infrastructure for the sub-tile culling of the surfel compositing; field `cull_audit`
+ * of b200gs_surfel_fwd, to be combined with exact_lists = 1): the forward compositing ignores the
+ * per-instance hit masks, evaluates every
  * (warp block, Gaussian) pair the way the reference does and counts the pairs that pass the
  * reference's alpha >= 1/255 cut although their mask bit is clear -- out2[0] with the forward's
  * `unstable` threshold (S/cuda_rasterizer/forward.cu:373), out2[1] with the backward's
- * (backward.cu:302).  Both must read 0: the masks may only drop pairs the reference drops.  */
-void b200gs_debug_cull_audit(int on);
+ * (backward.cu:302).  Both must read 0: the masks may only drop pairs the reference drops.
+ * The counters live on the device the call ran on.                                          */
 int b200gs_debug_cull_violations(unsigned long long* out2, int reset);
 /* Workload counters of the audit pass: out8[0] (warp block, entry) pairs visited with the hit
  * bit set, [1] those with >= 1 contributing pixel, [2] contributing (pixel, entry) pairs,
@@ -123,6 +123,8 @@ typedef struct b200gs_surfel_fwd {
   float* out_refl;         /* [1,H,W]                                         */
   int* radii;              /* [P]                                             */
   float* gaussian_weights; /* [P], must be zero-filled by the caller          */
+  int exact_lists;         /* instance-list mode of this call, see above      */
+  int cull_audit;          /* != 0: audit pass (test infrastructure), see above */
 } b200gs_surfel_fwd;
 
 size_t b200gs_surfel_geom_bytes(int P);
@@ -179,6 +181,9 @@ typedef struct b200gs_surfel_bwd {
    * counterpart: autograd does it there with one add per tensor per view).  0: overwritten; rows
    * of culled Gaussians are not written in either mode (callers zero-fill, S/rasterize_points.cu:186-197). */
   int accumulate;
+  /* sizes of the forward's scratch as handed back (checked against what P, width x height and num_rendered need;
+   * the reference re-derives pointers from the raw bytes unchecked, rasterizer_impl.cu:393-395) */
+  size_t geom_bytes, binning_bytes, img_bytes;
 } b200gs_surfel_bwd;
 
 size_t b200gs_surfel_accum_bytes(int P);
@@ -231,6 +236,7 @@ typedef struct b200gs_gauss_fwd {
   float* out_normal;      /* [3,H,W] */
   float* out_refl;        /* [1,H,W] */
   int* radii;             /* [P]     */
+  int exact_lists;        /* instance-list mode of this call (see b200gs_surfel_fwd) */
 } b200gs_gauss_fwd;
 
 size_t b200gs_gauss_geom_bytes(int P);
@@ -273,6 +279,7 @@ typedef struct b200gs_gauss_bwd {
   float* dL_dsh;          /* [P,M,3] or NULL */
   float* dL_dscales;      /* [P,3] */
   float* dL_drotations;   /* [P,4] */
+  size_t geom_bytes, binning_bytes, img_bytes;   /* sizes of the forward's scratch as handed back (checked) */
 } b200gs_gauss_bwd;
 
 size_t b200gs_gauss_accum_bytes(int P);
@@ -309,7 +316,7 @@ int b200gs_cubemap_backward(const float* grad_outputs, const float* inputs, cons
  * row-major tensor (grad_row / grad_col): f_dc and f_rest both read the [P, M, 3] dL_dsh block
  * the backward writes, as columns [0,3) and [3,3M).  `step` is the 1-based step count shared by all
  * groups (torch keeps one per parameter; the reference steps them together).  fp32 state.  */
-#define B200GS_ADAM_MAX_GROUPS 8
+#define B200GS_ADAM_MAX_GROUPS 16
 typedef struct {
   float* param;           /* [n] updated in place */
   const float* grad;      /* see grad_row / grad_col */
@@ -320,12 +327,14 @@ typedef struct {
   int grad_row;           /* row stride of grad in floats (0: same as param_row) */
   int grad_col;           /* first column of this group inside a grad row */
   double lr;
+  long long step;         /* this group's 1-based step count; 0: b200gs_adam.step (torch keeps one per parameter, and a
+                           * parameter whose .grad is None in some iteration falls behind the others)          */
 } b200gs_adam_group;
 typedef struct {
   int groups;
   b200gs_adam_group group[B200GS_ADAM_MAX_GROUPS];
   double beta1, beta2, eps;
-  long long step;         /* >= 1 */
+  long long step;         /* >= 1; used by the groups whose own step is 0 */
 } b200gs_adam;
 int b200gs_adam_step(const b200gs_adam* a, void* stream);
 
@@ -336,6 +345,19 @@ int b200gs_adam_step(const b200gs_adam* a, void* stream);
 int b200gs_densify_stats(int P, const int* radii, const float* dL_dmeans2D, const float* gaussian_weights,
                          float* max_radii2D, float* xyz_gradient_accum, float* denom, float* accum_w, float* denom_w,
                          void* stream);
+
+/* ------------------------------------------------------------------------ */
+/* The one collective of the path: in-place sum over the ranks of a flat fp32 buffer that
+ * lives in SYMMETRIC memory (the gradient arena of a view-parallel batch), by this library's own kernel over
+ * NVLink / NVSwitch peer memory.  No reference counterpart (the reference is single-GPU).
+ *   multicast_ptr != NULL: the multicast address of the buffer (NVLS): rank r reduces its 1/world slice with
+ *     multimem.ld_reduce and broadcasts it with multimem.st -- the adds happen in the switch;
+ *   multicast_ptr == NULL: peer_ptrs (HOST array of `world` device pointers, entry i = rank i's copy as mapped in
+ *     this process) are read and written directly; world in {2, 4, 8}.
+ * n_floats must be a multiple of 4 and the addresses 16-B aligned.  The caller orders the ranks: a device-side
+ * barrier over all ranks on `stream` before this call (all arenas complete) and one after it (all slices landed). */
+int b200gs_peer_allreduce_f32(void* multicast_ptr, void* const* peer_ptrs, int rank, int world, size_t n_floats,
+                              void* stream);
 
 /* ------------------------------------------------------------------------ */
 /* SSIM image loss ("next" row 3): replaces fusedssim / fusedssim_backward of

@@ -63,6 +63,44 @@ TARGETS = {
 }
 
 
+# The reference's Python around the extensions, copied VERBATIM (byte for byte, checked below) next to the .so
+# files so that tests can run the reference's own `gaussian_renderer.render()` / `GaussianModel` on the GPU box,
+# where /root/reference does not exist.  Same treatment as the compiled extensions: outputs only under
+# oracle/_ref/ (git-ignored, not gpurun-ignored); nothing is copied into the tracked tree.
+#   oracle/_ref/py/      the fork's glue: gaussian_renderer, scene.{cameras,gaussian_model}, utils.*, arguments
+#   oracle/_ref/py_ext/  the Python halves of the reference EXTENSION packages (their `_C` / `_cubemapencoder`
+#                        compiled halves are the ref_*_C.so above, put into sys.modules by tests/refpy.py)
+PY_GLUE = ["gaussian_renderer/__init__.py", "scene/cameras.py", "scene/gaussian_model.py", "arguments/__init__.py",
+           "utils/general_utils.py", "utils/point_utils.py", "utils/graphics_utils.py", "utils/sh_utils.py",
+           "utils/loss_utils.py", "utils/system_utils.py", "utils/image_utils.py"]
+PY_EXT = {"submodules/diff-surfel-rasterization/diff_surfel_rasterization/__init__.py": "diff_surfel_rasterization/__init__.py",
+          "submodules/diff-gaussian-rasterization/diff_gaussian_rasterization/__init__.py": "diff_gaussian_rasterization/__init__.py",
+          "submodules/cubemapencoder/cubemapencoder/__init__.py": "cubemapencoder/__init__.py",
+          "submodules/cubemapencoder/cubemapencoder/cubemap_encoder.py": "cubemapencoder/cubemap_encoder.py",
+          "submodules/fused-ssim/fused_ssim/__init__.py": "fused_ssim/__init__.py"}
+
+
+def copy_python():
+    """-> list of files now present under oracle/_ref/py*.  No-op (returns what is there) without /root/reference."""
+    import filecmp
+    import shutil
+    pairs = [(os.path.join(REF, f), os.path.join(OUT, "py", f)) for f in PY_GLUE]
+    pairs += [(os.path.join(REF, a), os.path.join(OUT, "py_ext", b)) for a, b in PY_EXT.items()]
+    have = []
+    for src, dst in pairs:
+        if os.path.isdir(REF):
+            if not os.path.exists(src):
+                print(f"[build_ref] missing in the reference: {src}", file=sys.stderr)
+                continue
+            os.makedirs(os.path.dirname(dst), exist_ok=True)
+            if not (os.path.exists(dst) and filecmp.cmp(src, dst, shallow=False)):
+                shutil.copyfile(src, dst)
+            assert filecmp.cmp(src, dst, shallow=False), dst
+        if os.path.exists(dst):
+            have.append(os.path.relpath(dst, OUT))
+    return have
+
+
 def built(name):
     return os.path.exists(os.path.join(OUT, name, name + ".so"))
 
@@ -72,6 +110,7 @@ def build(names=None, verbose=False):
     list of names that are available afterwards.  A missing /root/reference is
     not an error: prebuilt .so files (if any) are used as they are."""
     names = list(names or TARGETS)
+    copy_python()
     if not os.path.isdir(REF):
         return [n for n in names if built(n)]
     os.environ.setdefault("TORCH_CUDA_ARCH_LIST", "10.0a")

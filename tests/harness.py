@@ -21,17 +21,24 @@ for p in (ROOT, PKG_PY):
 import contextlib
 
 
+_EXACT = [False]     # list mode the drivers below pass to THIS library's `_C` calls (a per-call keyword there)
+
+
 @contextlib.contextmanager
 def exact_lists(on=True):
-    """Run the surfel path in exact-lists mode (the reference's instance lists bit for bit) or in
-    the default culled-emission mode (include/b200gs.h: b200gs_set_exact_lists)."""
-    import b200gs
-    old = b200gs.get_exact_lists()
-    b200gs.set_exact_lists(1 if on else 0)
+    """Drive the new library in exact-lists mode (the reference's instance lists bit for bit) or in the
+    default culled-emission mode (include/b200gs.h: `exact_lists` of the forward struct).  The library has
+    no mode of its own: this only sets what surfel_forward / gauss_forward below pass per call."""
+    old = _EXACT[0]
+    _EXACT[0] = bool(on)
     try:
         yield
     finally:
-        b200gs.set_exact_lists(old)
+        _EXACT[0] = old
+
+
+def _is_new(Cmod):
+    return getattr(Cmod, "__name__", "").startswith(("diff_surfel_rasterization", "diff_gaussian_rasterization"))
 
 
 def new_surfel_C():
@@ -49,27 +56,42 @@ def ref_module(name):
         return None
 
 
+_BG = {}
+
+
+def _bg(bg, dev):
+    """Background colour on the device, uploaded once per value (a per-call torch.tensor(bg, device=...) is a
+    pageable H2D copy + sync that would be timed with every small-scene call)."""
+    key = (tuple(float(x) for x in bg), str(dev))
+    if key not in _BG:
+        _BG[key] = torch.tensor(key[0], dtype=torch.float32, device=dev)
+    return _BG[key]
+
+
 def to_dev(d, device="cuda"):
     return {k: (torch.from_numpy(np.ascontiguousarray(v)).to(device) if isinstance(v, np.ndarray) else v)
             for k, v in d.items()}
 
 
 def surfel_forward(Cmod, scene, cam, bg=(0.0, 0.0, 0.0), sh_degree=3, mask=None, scale_modifier=1.0,
-                   colors_precomp=None, transMat_precomp=None, debug=False):
+                   colors_precomp=None, transMat_precomp=None, debug=False, prefiltered=False, exact=None, cull_audit=False):
     """scene/cam: dicts of CUDA tensors (see scenes.py).  Returns the 9-tuple as a dict."""
     dev = scene["means3D"].device
     e = torch.empty((0,), dtype=torch.float32, device=dev)
     P = scene["means3D"].shape[0]
     if mask is None:
         mask = torch.ones((P, 3), dtype=torch.bool, device=dev)
-    bgt = torch.tensor(bg, dtype=torch.float32, device=dev)
+    bgt = _bg(bg, dev)
     use_sh = colors_precomp is None
+    kw = {}
+    if _is_new(Cmod):
+        kw = dict(exact_lists=_EXACT[0] if exact is None else bool(exact), cull_audit=cull_audit)
     out = Cmod.rasterize_gaussians(
         bgt, scene["means3D"], mask, e if use_sh else colors_precomp, scene["refl"], scene["opacities"],
         e if transMat_precomp is not None else scene["scales"], e if transMat_precomp is not None else scene["rotations"],
         scale_modifier, e if transMat_precomp is None else transMat_precomp, cam["viewmatrix"], cam["projmatrix"],
         cam["tanfovx"], cam["tanfovy"], cam["height"], cam["width"], scene["shs"] if use_sh else e, sh_degree,
-        cam["campos"], False, debug)
+        cam["campos"], prefiltered, debug, **kw)
     keys = ("rendered", "color", "others", "radii", "geom", "binning", "img", "refl_map", "weights")
     r = dict(zip(keys, out))
     r.update(bg=bgt, sh_degree=sh_degree, scale_modifier=scale_modifier, colors_precomp=colors_precomp,
@@ -77,8 +99,9 @@ def surfel_forward(Cmod, scene, cam, bg=(0.0, 0.0, 0.0), sh_degree=3, mask=None,
     return r
 
 
-def surfel_backward(Cmod, scene, cam, fwd, grads):
+def surfel_backward(Cmod, scene, cam, fwd, grads, grad_arena=None):
     dev = scene["means3D"].device
+    kw = dict(grad_arena=grad_arena) if grad_arena is not None else {}
     e = torch.empty((0,), dtype=torch.float32, device=dev)
     use_sh = fwd["colors_precomp"] is None
     tp = fwd["transMat_precomp"]
@@ -87,7 +110,7 @@ def surfel_backward(Cmod, scene, cam, fwd, grads):
         e if tp is not None else scene["scales"], e if tp is not None else scene["rotations"], fwd["scale_modifier"],
         e if tp is None else tp, cam["viewmatrix"], cam["projmatrix"], cam["tanfovx"], cam["tanfovy"],
         grads["color"], grads["others"], grads["refl"], scene["shs"] if use_sh else e, fwd["sh_degree"],
-        cam["campos"], fwd["geom"], fwd["rendered"], fwd["binning"], fwd["img"], False)
+        cam["campos"], fwd["geom"], fwd["rendered"], fwd["binning"], fwd["img"], False, **kw)
     keys = ("means2D", "colors", "refl", "opacity", "means3D", "transMat", "sh", "scales", "rotations")
     return dict(zip(keys, out))
 
@@ -206,14 +229,15 @@ def gauss_forward(Cmod, scene, cam, bg=(0.0, 0.0, 0.0), sh_degree=3, scale_modif
                   colors_precomp=None, cov3D_precomp=None, debug=False):
     dev = scene["means3D"].device
     e = torch.empty((0,), dtype=torch.float32, device=dev)
-    bgt = torch.tensor(bg, dtype=torch.float32, device=dev)
+    bgt = _bg(bg, dev)
     use_sh = colors_precomp is None
+    kw = dict(exact_lists=_EXACT[0]) if _is_new(Cmod) else {}
     out = Cmod.rasterize_gaussians(
         bgt, scene["means3D"], e if use_sh else colors_precomp, scene["normals"], scene["refl"], scene["opacities"],
         e if cov3D_precomp is not None else scene["scales3"], e if cov3D_precomp is not None else scene["rotations"],
         scale_modifier, e if cov3D_precomp is None else cov3D_precomp, cam["viewmatrix"], cam["projmatrix"],
         cam["tanfovx"], cam["tanfovy"], cam["height"], cam["width"], scene["shs"] if use_sh else e, sh_degree,
-        cam["campos"], False, antialiasing, debug)
+        cam["campos"], False, antialiasing, debug, **kw)
     keys = ("rendered", "color", "radii", "geom", "binning", "img", "invdepth", "normal_map", "refl_map")
     r = dict(zip(keys, out))
     r.update(bg=bgt, sh_degree=sh_degree, scale_modifier=scale_modifier, antialiasing=antialiasing,

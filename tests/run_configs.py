@@ -85,11 +85,10 @@ def surfel_config(name, n_views=1, with_cubemap=False):
             return last
         return step
 
-    b200gs.set_exact_lists(1)
-    f_ex, b_ex = make(newC, None)()
-    out["R"], out["V"] = int(f_ex["rendered"]), int((f_ex["radii"] > 0).sum())
-    out["new_exact_ms"] = timed(make(newC, cm_new))
-    b200gs.set_exact_lists(0)
+    with hz.exact_lists(True):
+        f_ex, b_ex = make(newC, None)()
+        out["R"], out["V"] = int(f_ex["rendered"]), int((f_ex["radii"] > 0).sum())
+        out["new_exact_ms"] = timed(make(newC, cm_new))
     f_cu, b_cu = make(newC, None)()
     out["R_emitted"] = int(f_cu["rendered"])
     out["new_ms"] = timed(make(newC, cm_new))
@@ -125,12 +124,10 @@ def gauss_config(name):
             f = hz.gauss_forward(Cmod, sc, cam)
             return f, hz.gauss_backward(Cmod, sc, cam, f, grads)
         return step
-    import b200gs
-    b200gs.set_exact_lists(1)
-    f_ex, _ = make(newC)()
-    out["R"], out["V"] = int(f_ex["rendered"]), int((f_ex["radii"] > 0).sum())
-    out["new_exact_ms"] = timed(make(newC))
-    b200gs.set_exact_lists(0)
+    with hz.exact_lists(True):
+        f_ex, _ = make(newC)()
+        out["R"], out["V"] = int(f_ex["rendered"]), int((f_ex["radii"] > 0).sum())
+        out["new_exact_ms"] = timed(make(newC))
     f_n, b_n = make(newC)()
     out["R_emitted"] = int(f_n["rendered"])
     out["new_ms"] = timed(make(newC))

@@ -86,7 +86,7 @@ def build_arm(arm, sc_np, cam_np):
         import fused_ssim as fs
         from b200gs.shade import camera_constants, reflect_shade, surface_attributes, surface_camera_constants
         from b200gs.update import DensifyStats, GaussianAdam, surfel_param_groups
-        opt = GaussianAdam(surfel_param_groups(**params, lrs=LRS), eps=1e-15)
+        opt = GaussianAdam(surfel_param_groups(**params, lrs=LRS), lr=0.0, eps=1e-15)
         stats = DensifyStats(P)
         cam_s = surface_camera_constants(view.world_view_transform, view.full_proj_transform, W, H)
         cam_r = camera_constants(view.HWK, view.R, view.T)

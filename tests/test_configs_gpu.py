@@ -1,0 +1,298 @@
+"""GPU parity on the BASELINE.json configs themselves (c2, c3, the bench workload, c5) and on the input
+variants the reference accepts but round 1's tests never drove, all against the UNMODIFIED reference extension
+(oracle/_ref/ref_surfel_C) on identical inputs:
+
+  * full parity per config: integer structures bit-exact in exact-lists mode, images <= 1e-5 (bit-identical in
+    practice), every gradient tensor <= 1e-4 relative in BOTH list modes;
+  * the distortion plane (others[6]) as the ONLY upstream gradient -- the term whose fp32 cancellation
+    (S/cuda_rasterizer/backward.cu:366-390) round 1 got wrong by a rounding-shape difference;
+  * the gradient mix a training iteration produces (colour dominant, small normal / depth / alpha terms);
+  * surfel `transMat_precomp` (gaussian_renderer/__init__.py:95-106, forward.cu:193-208, backward.cu:639-653);
+  * `env_scope_mask` random, and of shape (P,) (gaussian_renderer/__init__.py:79-85, forward.cu:444-445,482);
+  * markVisible against ref_surfel_C.mark_visible (S/rasterize_points.cu:269-288);
+  * debug=True / prefiltered=True conventions (auxiliary.h:206-210,:300-307; S/diff_surfel_rasterization/__init__.py:91-98).
+
+Gradient bar: rel-L2 <= max(1e-4, 4 x the reference's own run-to-run difference) -- its backward sums with
+order-nondeterministic atomicAdd, so that difference is the resolution of the yardstick; both numbers are printed.
+"""
+import functools
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import harness as hz
+import scenes
+
+pytestmark = pytest.mark.gpu
+
+IMG_ATOL = 1e-5
+GRAD_RTOL = 1e-4
+
+
+@pytest.fixture(scope="module")
+def refC():
+    m = hz.ref_module("ref_surfel_C")
+    if m is None:
+        pytest.skip("oracle/_ref/ref_surfel_C not built")
+    return m
+
+
+@functools.lru_cache(maxsize=1)
+def _scene(name):
+    sc_np, cam_np = scenes.build(name)
+    return sc_np, cam_np, hz.to_dev(sc_np), hz.to_dev(cam_np)
+
+
+def _check_grads(bn, br, br2, what):
+    worst = {}
+    for k in bn:
+        assert bn[k].shape == br[k].shape, (what, k)
+        noise = hz.rel_l2(br2[k], br[k])
+        err = hz.rel_l2(bn[k], br[k])
+        worst[k] = (err, noise)
+        assert torch.isfinite(bn[k]).all(), (what, k)
+        assert err <= max(GRAD_RTOL, 4 * noise), (what, k, err, noise)
+    print(what, {k: (f"{e:.2e}", f"noise {n:.2e}") for k, (e, n) in worst.items()})
+
+
+@pytest.mark.parametrize("name", ["c2", "c3", "bench"])
+def test_baseline_config_full_parity(name, refC):
+    newC = hz.new_surfel_C()
+    sc_np, cam_np, sc, cam = _scene(name)
+    P, W, H = sc["means3D"].shape[0], cam_np["width"], cam_np["height"]
+    grads = hz.to_dev(scenes.upstream_grads(W, H))
+    bg = (1.0, 1.0, 1.0) if name == "c2" else (0.0, 0.0, 0.0)          # c2: white background
+    fr = hz.surfel_forward(refC, sc, cam, bg=bg)
+    br = hz.surfel_backward(refC, sc, cam, fr, grads)
+    br2 = hz.surfel_backward(refC, sc, cam, fr, grads)
+    sr = hz.ref_surfel_state(fr, P, W, H)
+    for exact in (True, False):
+        fn = hz.surfel_forward(newC, sc, cam, bg=bg, exact=exact)
+        bn = hz.surfel_backward(newC, sc, cam, fn, grads)
+        torch.cuda.synchronize()
+        assert torch.equal(fn["radii"], fr["radii"])
+        if exact:
+            assert fn["rendered"] == fr["rendered"]
+            sn = hz.new_surfel_state(fn, P, W, H)
+            for k in ("tiles_touched", "point_offsets", "keys", "point_list", "ranges", "n_contrib"):
+                assert torch.equal(sn[k], sr[k]), (name, k)
+            del sn
+        else:
+            assert 0 < fn["rendered"] <= fr["rendered"]
+        for k in ("color", "others", "refl_map"):
+            assert hz.max_abs(fn[k], fr[k]) <= IMG_ATOL, (name, exact, k)
+        assert int((fr["weights"] > fn["weights"]).sum()) == 0              # the reference's max is racy: ref <= exact max
+        _check_grads(bn, br, br2, f"{name} exact={exact}")
+        del fn, bn
+
+
+def test_c5_forward_parity(refC):
+    """c5 (6M Gaussians, 1080p): forward of view 0 -- radii, images, and in exact mode the instance count."""
+    newC = hz.new_surfel_C()
+    _scene.cache_clear()
+    sc_np, cam_np, sc, cam = _scene("c5")
+    fr = hz.surfel_forward(refC, sc, cam)
+    fr = {k: fr[k] for k in ("rendered", "radii", "color", "others", "refl_map")}     # drop the 2.5 GB of scratch
+    for exact in (True, False):
+        fn = hz.surfel_forward(newC, sc, cam, exact=exact)
+        torch.cuda.synchronize()
+        assert torch.equal(fn["radii"], fr["radii"])
+        assert (fn["rendered"] == fr["rendered"]) if exact else (0 < fn["rendered"] <= fr["rendered"])
+        for k in ("color", "others", "refl_map"):
+            assert hz.max_abs(fn[k], fr[k]) <= IMG_ATOL, (exact, k)
+        del fn
+    _scene.cache_clear()
+
+
+def _plane_grads(W, H, plane=None, mix=False, seed=0):
+    g = {k: np.zeros_like(v) for k, v in scenes.upstream_grads(W, H).items()}
+    if plane is not None:
+        g["others"][plane] = 1.0 / (W * H)                         # d mean(plane)
+    if mix:
+        # what one training iteration sends back (train.py:167-190 through gaussian_renderer/__init__.py:143-201):
+        # an L1/SSIM-sized colour gradient, a small reflection-strength gradient, and the normal-consistency loss
+        # reaching the normal, depth and alpha planes two to three orders of magnitude below the colour
+        rng = np.random.default_rng(4242 + seed)
+        n = W * H
+        g["color"] = (rng.choice([-1.0, 1.0], (3, H, W)) * 0.8 / (3 * n) + rng.normal(0, 0.05 / n, (3, H, W))).astype(np.float32)
+        g["refl"] = rng.normal(0, 0.1 / n, (1, H, W)).astype(np.float32)
+        g["others"][0] = rng.normal(0, 1e-2 / n, (H, W))
+        g["others"][1] = rng.normal(0, 1e-2 / n, (H, W))
+        g["others"][2:5] = rng.normal(0, 0.05 / n, (3, H, W))
+    return g
+
+
+@pytest.mark.parametrize("name", ["small", "c2"])
+@pytest.mark.parametrize("what", ["distortion-only", "median-only", "training-mix", "training-mix+distortion"])
+def test_single_plane_and_training_mix_gradients(name, what, refC):
+    newC = hz.new_surfel_C()
+    sc_np, cam_np, sc, cam = _scene(name)
+    W, H = cam_np["width"], cam_np["height"]
+    g = _plane_grads(W, H, plane={"distortion-only": 6, "median-only": 5}.get(what), mix=what.startswith("training-mix"))
+    if what == "training-mix+distortion":
+        g["others"][6] = 100.0 / (W * H)                            # 2DGS's lambda_dist * rend_dist.mean()
+    gd = hz.to_dev(g)
+    fr = hz.surfel_forward(refC, sc, cam)
+    br = hz.surfel_backward(refC, sc, cam, fr, gd)
+    br2 = hz.surfel_backward(refC, sc, cam, fr, gd)
+    for exact in (True, False):
+        fn = hz.surfel_forward(newC, sc, cam, exact=exact)
+        bn = hz.surfel_backward(newC, sc, cam, fn, gd)
+        _check_grads(bn, br, br2, f"{name} {what} exact={exact}")
+
+
+def _transmat_python(sc, cam_np):
+    """gaussian_renderer/__init__.py:95-106 (pipe.compute_cov3D_python) with build_covariance_from_scaling_rotation
+    (scene/gaussian_model.py:35-41) and build_rotation (utils/general_utils.py:78-110), as literal torch."""
+    W, H = cam_np["width"], cam_np["height"]
+    r = sc["rotations"]
+    q = r / torch.sqrt(r[:, 0] * r[:, 0] + r[:, 1] * r[:, 1] + r[:, 2] * r[:, 2] + r[:, 3] * r[:, 3])[:, None]
+    R = torch.zeros((q.size(0), 3, 3), device="cuda")
+    rr, x, y, z = q[:, 0], q[:, 1], q[:, 2], q[:, 3]
+    R[:, 0, 0] = 1 - 2 * (y * y + z * z); R[:, 0, 1] = 2 * (x * y - rr * z); R[:, 0, 2] = 2 * (x * z + rr * y)
+    R[:, 1, 0] = 2 * (x * y + rr * z); R[:, 1, 1] = 1 - 2 * (x * x + z * z); R[:, 1, 2] = 2 * (y * z - rr * x)
+    R[:, 2, 0] = 2 * (x * z - rr * y); R[:, 2, 1] = 2 * (y * z + rr * x); R[:, 2, 2] = 1 - 2 * (x * x + y * y)
+    s = torch.cat([sc["scales"], torch.ones_like(sc["scales"])], dim=-1)
+    L = torch.zeros((q.size(0), 3, 3), device="cuda")
+    L[:, 0, 0], L[:, 1, 1], L[:, 2, 2] = s[:, 0], s[:, 1], s[:, 2]
+    RS = (R @ L).permute(0, 2, 1)
+    trans = torch.zeros((q.size(0), 4, 4), device="cuda")
+    trans[:, :3, :3] = RS
+    trans[:, 3, :3] = sc["means3D"]
+    trans[:, 3, 3] = 1
+    near, far = 0.01, 100.0
+    ndc2pix = torch.tensor([[W / 2, 0, 0, (W - 1) / 2], [0, H / 2, 0, (H - 1) / 2], [0, 0, far - near, near],
+                            [0, 0, 0, 1]]).float().cuda().T
+    world2pix = cam_np_t(cam_np) @ ndc2pix
+    return (trans[:, [0, 1, 3]] @ world2pix[:, [0, 1, 3]]).permute(0, 2, 1).reshape(-1, 9).contiguous()
+
+
+def cam_np_t(cam_np):
+    return torch.from_numpy(cam_np["projmatrix"]).reshape(4, 4).cuda()
+
+
+@pytest.mark.parametrize("name", ["tiny", "small", "c2"])
+def test_transmat_precomp_path(name, refC):
+    newC = hz.new_surfel_C()
+    sc_np, cam_np, sc, cam = _scene(name)
+    W, H = cam_np["width"], cam_np["height"]
+    grads = hz.to_dev(scenes.upstream_grads(W, H))
+    tm = _transmat_python(sc, cam_np)
+    fr = hz.surfel_forward(refC, sc, cam, transMat_precomp=tm)
+    br = hz.surfel_backward(refC, sc, cam, fr, grads)
+    br2 = hz.surfel_backward(refC, sc, cam, fr, grads)
+    assert int((fr["radii"] > 0).sum()) > 0
+    for exact in (True, False):
+        fn = hz.surfel_forward(newC, sc, cam, transMat_precomp=tm, exact=exact)
+        bn = hz.surfel_backward(newC, sc, cam, fn, grads)
+        assert torch.equal(fn["radii"], fr["radii"])
+        assert (fn["rendered"] == fr["rendered"]) if exact else (0 < fn["rendered"] <= fr["rendered"])
+        for k in ("color", "others", "refl_map"):
+            assert hz.max_abs(fn[k], fr[k]) <= IMG_ATOL, (name, exact, k)
+        assert float(bn["transMat"].abs().sum()) > 0                    # the gradient the caller backpropagates through python
+        _check_grads(bn, br, br2, f"{name} transMat_precomp exact={exact}")
+
+
+@pytest.mark.parametrize("shape", ["P3-random", "P-random", "P-radius", "all-false"])
+def test_env_scope_mask_variants(shape, refC):
+    newC = hz.new_surfel_C()
+    sc_np, cam_np, sc, cam = _scene("small")
+    P = sc["means3D"].shape[0]
+    g = torch.Generator().manual_seed(5)
+    if shape == "P3-random":
+        # the kernels read mask[idx] of a [P,3] bool buffer (forward.cu:444): only the first P bytes matter
+        mask = (torch.rand((P, 3), generator=g) > 0.5).cuda()
+    elif shape == "P-random":
+        mask = (torch.rand((P,), generator=g) > 0.7).cuda()
+    elif shape == "P-radius":
+        mask = (torch.sum(sc["means3D"] ** 2, dim=-1) < 0.8 ** 2)          # gaussian_renderer/__init__.py:83
+    else:
+        mask = torch.zeros((P, 3), dtype=torch.bool, device="cuda")
+    fr = hz.surfel_forward(refC, sc, cam, mask=mask)
+    for exact in (True, False):
+        fn = hz.surfel_forward(newC, sc, cam, mask=mask, exact=exact)
+        for k in ("color", "others", "refl_map"):
+            assert torch.equal(fn[k], fr[k]), (shape, exact, k)
+    m = fr["others"][7]
+    assert set(m.unique().tolist()) <= {0.0, 1.0}
+    if shape == "all-false":
+        assert float(m.sum()) == 0.0
+    else:
+        assert 0 < float(m.sum()) < m.numel()
+
+
+@pytest.mark.parametrize("name", ["small", "c3"])
+def test_mark_visible_matches_reference(name, refC):
+    newC = hz.new_surfel_C()
+    sc_np, cam_np, sc, cam = _scene(name)
+    pos = sc["means3D"]
+    if name == "small":                                            # put half the points behind / beside the camera
+        pos = (torch.rand((50_000, 3), generator=torch.Generator().manual_seed(2)) * 16 - 8).cuda()
+    vn = newC.mark_visible(pos, cam["viewmatrix"], cam["projmatrix"])
+    vr = refC.mark_visible(pos, cam["viewmatrix"], cam["projmatrix"])
+    assert vn.dtype == torch.bool and vn.shape == vr.shape
+    assert torch.equal(vn, vr)
+    assert 0 < int(vn.sum()) < vn.numel()
+    import diff_surfel_rasterization as d
+    rs = d.GaussianRasterizationSettings(
+        image_height=cam["height"], image_width=cam["width"], tanfovx=cam["tanfovx"], tanfovy=cam["tanfovy"],
+        bg=torch.zeros(3, device="cuda"), scale_modifier=1.0, viewmatrix=cam["viewmatrix"], projmatrix=cam["projmatrix"],
+        sh_degree=3, campos=cam["campos"], prefiltered=False, debug=False)
+    assert torch.equal(d.GaussianRasterizer(rs).markVisible(pos), vr)
+    assert newC.mark_visible(pos[:0], cam["viewmatrix"], cam["projmatrix"]).shape == (0,)
+
+
+def test_debug_mode_same_results_and_prefiltered_violation_dumps(tmp_path, monkeypatch):
+    """debug=True: every stage is followed by a stream sync + error check (auxiliary.h:300-307) -- same bits out.
+    prefiltered=True with a culled point: the reference printf()s and __trap()s (auxiliary.h:206-210), which kills
+    the CUDA context of the whole process; this library reports the same condition as a RuntimeError with the
+    reference's message and leaves the context usable, and with debug=True the Python wrapper writes
+    snapshot_fw.dump first (S/diff_surfel_rasterization/__init__.py:91-98).  The reference arm cannot be run for
+    this case (it would take the test process down), so it is a convention test of this library alone."""
+    import diff_surfel_rasterization as d
+    newC = hz.new_surfel_C()
+    sc_np, cam_np, sc, cam = _scene("tiny")
+    f0 = hz.surfel_forward(newC, sc, cam)
+    f1 = hz.surfel_forward(newC, sc, cam, debug=True)
+    for k in ("color", "others", "refl_map", "radii"):
+        assert torch.equal(f0[k], f1[k]), k
+    bad = dict(sc)
+    bad["means3D"] = sc["means3D"].clone()
+    bad["means3D"][7] += torch.tensor([100.0, 0.0, 0.0], device="cuda")     # behind the camera -> culled
+    with pytest.raises(RuntimeError, match="filtered although prefiltered"):
+        hz.surfel_forward(newC, bad, cam, prefiltered=True)
+    f2 = hz.surfel_forward(newC, sc, cam, prefiltered=False)                 # the context survived
+    assert torch.equal(f0["color"], f2["color"])
+    # through the autograd module with debug=True: the dump is written before the error propagates
+    monkeypatch.chdir(tmp_path)
+    rs = d.GaussianRasterizationSettings(
+        image_height=cam["height"], image_width=cam["width"], tanfovx=cam["tanfovx"], tanfovy=cam["tanfovy"],
+        bg=torch.zeros(3, device="cuda"), scale_modifier=1.0, viewmatrix=cam["viewmatrix"], projmatrix=cam["projmatrix"],
+        sh_degree=3, campos=cam["campos"], prefiltered=True, debug=True)
+    P = bad["means3D"].shape[0]
+    with pytest.raises(RuntimeError, match="filtered although prefiltered"):
+        d.GaussianRasterizer(rs)(means3D=bad["means3D"], means2D=torch.zeros_like(bad["means3D"]), opacities=bad["opacities"],
+                                 shs=bad["shs"], refl_strengths=bad["refl"], scales=bad["scales"], rotations=bad["rotations"],
+                                 env_scope_mask=torch.ones((P, 3), dtype=torch.bool, device="cuda"))
+    assert os.path.exists(tmp_path / "snapshot_fw.dump")
+    dumped = torch.load(tmp_path / "snapshot_fw.dump", weights_only=False)
+    assert isinstance(dumped, tuple) and len(dumped) == 21 and torch.equal(dumped[1], bad["means3D"].cpu())
+    # a backward failure dumps snapshot_bw.dump: hand the backward a scratch buffer that is too small
+    rs_ok = rs._replace(prefiltered=False)
+    leaves = {k: sc[k].clone().requires_grad_(True) for k in ("means3D", "shs", "opacities", "scales", "rotations", "refl")}
+    out = d.GaussianRasterizer(rs_ok)(means3D=leaves["means3D"], means2D=torch.zeros_like(leaves["means3D"], requires_grad=True),
+                                      opacities=leaves["opacities"], shs=leaves["shs"], refl_strengths=leaves["refl"],
+                                      scales=leaves["scales"], rotations=leaves["rotations"],
+                                      env_scope_mask=torch.ones((P, 3), dtype=torch.bool, device="cuda"))
+    orig = d._C.rasterize_gaussians_backward
+
+    def truncated_geom(*a, **k):                                             # geomBuffer (argument 20 of 24) cut short
+        a = list(a)
+        a[19] = a[19][:64].clone()
+        return orig(*a, **k)
+    monkeypatch.setattr(d._C, "rasterize_gaussians_backward", truncated_geom)
+    with pytest.raises(RuntimeError, match="scratch smaller than the forward's"):
+        out[0].sum().backward()
+    assert os.path.exists(tmp_path / "snapshot_bw.dump")

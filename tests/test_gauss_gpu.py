@@ -90,8 +90,9 @@ def _variants(exact, refC):
         for k in ("color", "invdepth", "normal_map", "refl_map"):
             assert hz.max_abs(fn[k], fr[k]) <= IMG_ATOL, (k, kw)
         bn, br = hz.gauss_backward(newC, sc, cam, fn, grads), hz.gauss_backward(refC, sc, cam, fr, grads)
-        for k in bn:
-            assert hz.rel_l2(bn[k], br[k]) <= 5e-4, (k, kw)
+        br2 = hz.gauss_backward(refC, sc, cam, fr, grads)
+        for k in bn:      # the contract's bar, or the reference's own run-to-run atomic noise where that is larger
+            assert hz.rel_l2(bn[k], br[k]) <= max(1e-4, 4 * hz.rel_l2(br2[k], br[k])), (k, kw, hz.rel_l2(bn[k], br[k]))
 
 
 def test_autograd_module_and_empty():

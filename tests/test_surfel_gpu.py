@@ -105,8 +105,9 @@ def _variants(exact, refC):
             assert hz.max_abs(fn[k], fr[k]) <= IMG_ATOL, (k, kw)
         bn = hz.surfel_backward(newC, sc, cam, fn, grads)
         br = hz.surfel_backward(refC, sc, cam, fr, grads)
-        for k in bn:
-            assert hz.rel_l2(bn[k], br[k]) <= 5e-4, (k, kw)
+        br2 = hz.surfel_backward(refC, sc, cam, fr, grads)
+        for k in bn:      # the contract's bar, or the reference's own run-to-run atomic noise where that is larger
+            assert hz.rel_l2(bn[k], br[k]) <= max(GRAD_RTOL, 4 * hz.rel_l2(br2[k], br[k])), (k, kw, hz.rel_l2(bn[k], br[k]))
 
 
 def test_empty_and_all_culled():
@@ -169,7 +170,7 @@ def test_against_committed_reference_golden():
         assert hz.rel_l2(v, r) <= GRAD_RTOL, k
 
 
-@pytest.mark.parametrize("name", ["small", "c1", "c4"])
+@pytest.mark.parametrize("name", ["small", "c1", "c2", "c4", "bench"])
 def test_cull_audit_no_violation(name):
     """Sub-tile culling may only drop (warp block, Gaussian) pairs the reference drops with its
     alpha < 1/255 cut: the audit kernel evaluates every pair and counts mask misses."""
@@ -179,13 +180,8 @@ def test_cull_audit_no_violation(name):
     sc, cam = hz.to_dev(sc_np), hz.to_dev(cam_np)
     f0 = hz.surfel_forward(newC, sc, cam)
     b200gs.cull_violations(reset=True)
-    b200gs.debug_cull_audit(1)
-    try:
-        with hz.exact_lists(True):       # the audit walks the reference's full lists
-            f1 = hz.surfel_forward(newC, sc, cam)
-        viol = b200gs.cull_violations(reset=True)
-    finally:
-        b200gs.debug_cull_audit(0)
+    f1 = hz.surfel_forward(newC, sc, cam, exact=True, cull_audit=True)     # the audit walks the reference's full lists
+    viol = b200gs.cull_violations(reset=True)
     assert viol == (0, 0), viol
     for k in ("color", "others", "refl_map"):      # culled and unculled evaluation: same bits
         assert torch.equal(f0[k], f1[k]), k
@@ -260,24 +256,20 @@ def test_gradient_arena_accumulates_a_batch_of_views():
         b = hz.surfel_backward(C, sc, c, f, grads)
         want = {k: b[k].clone() for k in keys} if want is None else {k: want[k] + b[k] for k in keys}
     arena = GradArena(P, M, "cuda", accumulate=True)
-    C.use_gradient_arena(arena)
-    try:
-        arena.flat.fill_(7.0)                         # zero_() is the caller's job, once per batch
-        arena.zero_()
-        for c in cams:
-            f = hz.surfel_forward(C, sc, c)
-            b = hz.surfel_backward(C, sc, c, f, grads)
-            assert b["sh"].data_ptr() == arena.view("sh").data_ptr()
-        torch.cuda.synchronize()
-        for k in keys:
-            got = arena.view(k).reshape(want[k].shape)
-            assert hz.rel_l2(got, want[k]) <= 1e-5, (k, hz.rel_l2(got, want[k]))
-            assert torch.equal(got.abs().reshape(P, -1).amax(1) > 0, want[k].abs().reshape(P, -1).amax(1) > 0), k
-        arena.accumulate = False                      # overwrite mode: the last view alone
-        f = hz.surfel_forward(C, sc, cams[0])
-        b = hz.surfel_backward(C, sc, cams[0], f, grads)
-        C.use_gradient_arena(None)
-        b1 = hz.surfel_backward(C, sc, cams[0], f, grads)
-        assert hz.rel_l2(arena.view("sh"), b1["sh"]) <= 1e-5    # run-to-run atomic order only
-    finally:
-        C.use_gradient_arena(None)
+    arena.flat.fill_(7.0)                         # zero_() is the caller's job, once per batch
+    arena.zero_()
+    for c in cams:
+        f = hz.surfel_forward(C, sc, c)
+        b = hz.surfel_backward(C, sc, c, f, grads, grad_arena=arena)     # a per-call argument
+        assert b["sh"].data_ptr() == arena.view("sh").data_ptr()
+    torch.cuda.synchronize()
+    for k in keys:
+        got = arena.view(k).reshape(want[k].shape)
+        assert hz.rel_l2(got, want[k]) <= 1e-5, (k, hz.rel_l2(got, want[k]))
+        assert torch.equal(got.abs().reshape(P, -1).amax(1) > 0, want[k].abs().reshape(P, -1).amax(1) > 0), k
+    arena.accumulate = False                      # overwrite mode: the last view alone
+    f = hz.surfel_forward(C, sc, cams[0])
+    b = hz.surfel_backward(C, sc, cams[0], f, grads, grad_arena=arena)
+    b1 = hz.surfel_backward(C, sc, cams[0], f, grads)                    # no arena: fresh tensors
+    assert b1["sh"].data_ptr() != arena.view("sh").data_ptr()
+    assert hz.rel_l2(arena.view("sh"), b1["sh"]) <= 1e-5    # run-to-run atomic order only

@@ -26,7 +26,7 @@ def test_adam_step_matches_oracle_and_torch(P):
     from oracle import update_oracle as uo
     params = make_params(P, 3)
     dev = {k: v.cuda().contiguous() for k, v in params.items()}
-    opt = GaussianAdam(surfel_param_groups(**dev, lrs=LRS), eps=1e-15)
+    opt = GaussianAdam(surfel_param_groups(**dev, lrs=LRS), lr=0.0, eps=1e-15)     # scene/gaussian_model.py:207
     tp = {k: torch.nn.Parameter(v.cuda().clone()) for k, v in params.items()}
     topt = torch.optim.Adam([{"params": [tp[k]], "lr": LRS[k], "name": k} for k in SHAPES], lr=0.0, eps=1e-15)
     o = {k: (v.numpy().copy(), np.zeros(v.shape, np.float32), np.zeros(v.shape, np.float32)) for k, v in params.items()}
@@ -47,7 +47,7 @@ def test_adam_step_matches_oracle_and_torch(P):
         opt.step({k: v.cuda().contiguous() for k, v in gr.items()})
         torch.cuda.synchronize()
         for k in SHAPES:
-            st = opt.state[k]
+            st = opt.state[dev[k]]              # keyed by the parameter tensor, like torch's
             _close_moment(st["exp_avg"].cpu().numpy(), o[k][1], f"{k} exp_avg it{it} (oracle)")
             _close_moment(st["exp_avg_sq"].cpu().numpy(), o[k][2], f"{k} exp_avg_sq it{it} (oracle)")
             _close_moment(st["exp_avg"].cpu().numpy(), topt.state[tp[k]]["exp_avg"].cpu().numpy(), f"{k} exp_avg it{it} (torch)")
@@ -56,7 +56,7 @@ def test_adam_step_matches_oracle_and_torch(P):
             got = dev[k].cpu().numpy()
             for want, who in ((o[k][0], "oracle"), (tp[k].detach().cpu().numpy(), "torch")):
                 assert np.abs(got - want).max() <= 1e-5 * max(LRS[k], lr) * it + 2e-7 * np.abs(want).max(), (k, it, who)
-    assert opt.state["xyz"]["step"] == 5
+    assert float(opt.state[dev["xyz"]]["step"]) == 5.0 and set(opt.state[dev["xyz"]]) == set(topt.state[tp["xyz"]])
 
 
 def test_adam_reads_arena_blocks_and_rejects_bad_input():
@@ -68,7 +68,7 @@ def test_adam_reads_arena_blocks_and_rejects_bad_input():
     before = {k: v.clone() for k, v in dev.items()}
     arena = GradArena(P, 16, "cuda")
     arena.flat.normal_()
-    opt = GaussianAdam(surfel_param_groups(**dev, lrs=LRS))
+    opt = GaussianAdam(surfel_param_groups(**dev, lrs=LRS), lr=0.0, eps=1e-15)
     opt.step(arena_grads(arena))
     torch.cuda.synchronize()
     # first Adam step: every parameter moves by lr * sign(g) (m / sqrt(v) = +-1)
@@ -137,7 +137,7 @@ def test_training_iteration_end_to_end():
     f_dc, f_rest = shs[:, :1, :].contiguous(), shs[:, 1:, :].contiguous()
     groups = [dict(params=[sc["means3D"]], lr=LRS["xyz"], name="xyz"), dict(params=[f_dc], lr=LRS["f_dc"], name="f_dc"),
               dict(params=[f_rest], lr=LRS["f_rest"], name="f_rest"), dict(params=[sc["opacities"]], lr=LRS["opacity"], name="opacity")]
-    opt, ds = GaussianAdam(groups), DensifyStats(P)
+    opt, ds = GaussianAdam(groups, lr=0.0, eps=1e-15), DensifyStats(P)
     x0 = sc["means3D"].clone()
     f = hz.surfel_forward(C, sc, cam)
     b = hz.surfel_backward(C, sc, cam, f, grads)
