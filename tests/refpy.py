@@ -133,7 +133,9 @@ def make_camera(arm, cam_np, image=None, uid=0):
     W, H = cam_np["width"], cam_np["height"]
     w2c = np.asarray(cam_np["w2c"], np.float64)
     R, T = np.ascontiguousarray(w2c[:3, :3].T), np.ascontiguousarray(w2c[:3, 3])
-    K = np.array([[W / (2 * cam_np["tanfovx"]), 0, W / 2], [0, H / (2 * cam_np["tanfovy"]), H / 2], [0, 0, 1]], np.float32)
+    # float64 like a dataset reader's intrinsics: getProjectionMatrixCorrect (utils/graphics_utils.py:72-91) assigns
+    # expressions of K's entries into a torch tensor, which this torch accepts for numpy.float64 (a Python float) only
+    K = np.array([[W / (2 * cam_np["tanfovx"]), 0, W / 2], [0, H / (2 * cam_np["tanfovy"]), H / 2], [0, 0, 1]], np.float64)
     return arm.Camera(resolution=(W, H), colmap_id=uid, R=R, T=T, FoVx=cam_np["fovx"], FoVy=cam_np["fovy"], image=image,
                       gt_alpha_mask=None, image_name=f"view{uid}", uid=uid, HWK=(H, W, K))
 

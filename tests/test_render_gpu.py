@@ -205,7 +205,10 @@ def test_fused_glue_kernels_against_reference_render(arms):
     for k in up:
         assert got[k].shape == pkg[k].shape, k
         d = hz.max_abs(got[k], pkg[k].detach())
-        assert d <= (2e-5 if k != "surf_depth" else 2e-5 * float(pkg[k].abs().max())), (k, d)
+        # surf_normal normalises cross products of finite differences of neighbouring surface points: the differences
+        # cancel, so a last-place change in a point moves a component of the unit normal by up to ~1e-4
+        tol = {"surf_depth": 2e-5 * float(pkg[k].abs().max()), "surf_normal": 1e-4}.get(k, 2e-5)
+        assert d <= tol, (k, d)
     new_scalar = sum((got[k] * up[k]).sum() for k in up)
     g_new = torch.autograd.grad(new_scalar, [allmap_n, base_n, refl_n, env_new.params["Cubemap_texture"]])
     for name, a, b in zip(("allmap", "base", "refl_map", "env_texture"), g_new, g_ref):
@@ -229,8 +232,9 @@ def test_reference_optimizer_surgery_on_gaussian_adam(arms):
     sc_np, _ = scenes.build("tiny")
     P0 = sc_np["means3D"].shape[0]
     models = []
+    env_tex = torch.rand((6, 3, 16, 16), generator=torch.Generator().manual_seed(1)) - 0.5
     for use_new in (False, True):
-        gm = refpy.make_model(new, sc_np, None, cubemap_resol=16)
+        gm = refpy.make_model(new, sc_np, env_tex, cubemap_resol=16)
         opt_args = new.opt()
         gm.spatial_lr_scale = 1.0
         gm.training_setup(opt_args)                              # builds torch.optim.Adam(l, lr=0.0, eps=1e-15)
@@ -254,7 +258,7 @@ def test_reference_optimizer_surgery_on_gaussian_adam(arms):
     def check(tag):
         for (k, a), (_, b) in zip(_params(models[0]).items(), _params(models[1]).items()):
             assert a.shape == b.shape, (tag, k)
-            assert torch.allclose(a, b, rtol=0, atol=1e-7), (tag, k, float((a - b).abs().max()))
+            assert torch.allclose(a, b, rtol=0, atol=1e-7), (tag, k, float((a.detach() - b.detach()).abs().max()))
         for grp in models[1].optimizer.param_groups:
             for p in grp["params"]:
                 st = models[1].optimizer.state.get(p)
