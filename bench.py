@@ -530,9 +530,12 @@ def main():
     except Exception:  # noqa: BLE001
         pass
 
+    views_per_rank = VB // world
+
     def row(name, ms, cnt, steps):
-        per = ms / cnt
-        return {"ms": round(per, 4), "launches_per_step": cnt / (steps + 0.0),
+        # a stage may launch several times per view (one launch per depth slice): `ms` is the stage's time PER VIEW
+        per = ms / (steps * views_per_rank)
+        return {"ms": round(per, 4), "launches_per_step": cnt / (steps + 0.0), "launches_per_view": round(cnt / (steps * views_per_rank + 0.0), 2),
                 "alg_bytes": alg[name], "gbs": round(alg[name] / (per * 1e-3) / 1e9, 1),
                 "frac_of_hbm_peak": round(alg[name] / (per * 1e-3) / 1e9 / peak, 4),
                 "bound": "issue" if name in ISSUE_BOUND else "hbm"}
@@ -544,7 +547,7 @@ def main():
         top = max(live, key=lambda k: live[k]["ms"])   # one entry: the dominant kernel, timed inside the timed region
         t_s = live[top]["ms"] * 1e-3
         common = {"kernel": top, "ms_per_launch": live[top]["ms"], "launches_per_step": live[top]["launches_per_step"],
-                  "share_of_step": round(live[top]["ms"] * live[top]["launches_per_step"] / ms_per_step, 3),
+                  "share_of_step": round(live[top]["ms"] * views_per_rank / ms_per_step, 3),
                   "traffic": (prof.get(top) if not isinstance(prof.get(top), dict) else prof[top].get("dram_bytes")),
                   "hbm_view": {"alg_bytes_per_launch": live[top]["alg_bytes"], "achieved_gbs": live[top]["gbs"], "peak_gbs": peak,
                                "frac": live[top]["frac_of_hbm_peak"], "peak_source": peak_src}}

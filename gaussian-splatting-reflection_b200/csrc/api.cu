@@ -69,6 +69,7 @@ SurfelGeom SurfelGeom::carve(void* base, size_t P, size_t* bytes) {
   g.cull = c.take<CullRec>(P);
   g.scan_state = c.take<uint32_t>(scan_state_words((int)P));
   g.flags = c.take<int>(4);
+  g.plan = c.take<int>(PLAN_INTS);
   if (bytes) *bytes = c.used + 128;
   return g;
 }
@@ -80,8 +81,12 @@ SurfelImage SurfelImage::carve(void* base, int W, int H, size_t* bytes) {
   const size_t tiles = (size_t)((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
   im.accum = c.take<float>(3 * N);
   im.n_contrib = c.take<uint32_t>(2 * N);
-  im.ranges = c.take<uint2>(tiles);
-  im.cranges = c.take<uint2>(tiles);
+  im.ranges = c.take<uint2>((size_t)MAX_SLICES * (tiles + 1));
+  im.cranges = c.take<uint2>((size_t)MAX_SLICES * (tiles + 1));
+  im.tile_base = c.take<uint32_t>((size_t)(MAX_SLICES + 1) * tiles);
+  im.tile_done = c.take<uint8_t>(tiles);
+  im.live = c.take<uint32_t>(4);
+  im.state = c.take<float>((size_t)STATE_PLANES * N);
   if (bytes) *bytes = c.used + 128;
   return im;
 }
@@ -122,6 +127,17 @@ const char* b200gs_last_error(void) { return t_err; }
 int b200gs_version(void) { return 1; }
 int b200gs_sm_arch(void) { return 100; }
 unsigned long long b200gs_launch_count(void) { return g_launches.load(); }
+size_t b200gs_struct_bytes(int which) {
+  switch (which) {
+    case 0: return sizeof(b200gs_surfel_fwd);
+    case 1: return sizeof(b200gs_surfel_bwd);
+    case 2: return sizeof(b200gs_gauss_fwd);
+    case 3: return sizeof(b200gs_gauss_bwd);
+    case 4: return sizeof(b200gs_adam);
+    case 5: return sizeof(b200gs_ply_layout);
+    default: return 0;
+  }
+}
 
 void b200gs_timing_enable(int on) { g_timing.store(on ? 1 : 0); }
 void b200gs_timing_only(int stage) { g_timing.store((stage >= 0 && stage < ST_COUNT) ? 2 + stage : 0); }
@@ -167,12 +183,13 @@ size_t b200gs_binning_bytes(int num_rendered) {
 }
 size_t b200gs_surfel_accum_bytes(int P) { return (size_t)(P > 0 ? P : 0) * ACC_STRIDE * sizeof(float) + 128; }
 
-int b200gs_surfel_forward_stage1(const b200gs_surfel_fwd* a, int* num_rendered, void* stream) {
+int b200gs_surfel_forward_stage1(const b200gs_surfel_fwd* a, int* plan, void* stream) {
   int rc = check_fwd(a);
   if (rc) return rc;
-  if (!num_rendered) { set_error("num_rendered is null"); return B200GS_EINVAL; }
+  if (!plan) { set_error("plan is null"); return B200GS_EINVAL; }
   cudaStream_t s = (cudaStream_t)stream;
-  *num_rendered = 0;
+  for (int i = 0; i < PLAN_INTS; ++i) plan[i] = 0;
+  plan[1] = 1;
   if (a->P == 0) return B200GS_OK;
   SurfelGeom g = SurfelGeom::carve(align128(a->geom), a->P, nullptr);
   rc = surfel_preprocess(*a, g, s);
@@ -186,38 +203,58 @@ int b200gs_surfel_forward_stage1(const b200gs_surfel_fwd* a, int* num_rendered, 
   }
   rc = depth_order_and_scan(g.depths, counts, a->P, g.order, g.point_offsets, g.scan_state, s, a->debug != 0);
   if (rc) return rc;
-  int host[2] = {0, 0};
-  B200GS_CUDA(cudaMemcpyAsync(&host[0], g.point_offsets + a->P - 1, sizeof(int), cudaMemcpyDeviceToHost, s));
-  B200GS_CUDA(cudaMemcpyAsync(&host[1], g.flags, sizeof(int), cudaMemcpyDeviceToHost, s));
+  // depth slices only make sense for the culled emission (the exact lists are the reference's, in one piece)
+  rc = slice_plan(g.point_offsets, a->P, exact ? 1 : a->depth_slices, a->slice_frac, g.plan, s, a->debug != 0);
+  if (rc) return rc;
+  int flag = 0;
+  B200GS_CUDA(cudaMemcpyAsync(plan, g.plan, PLAN_INTS * sizeof(int), cudaMemcpyDeviceToHost, s));
+  B200GS_CUDA(cudaMemcpyAsync(&flag, g.flags, sizeof(int), cudaMemcpyDeviceToHost, s));
   B200GS_CUDA(cudaStreamSynchronize(s));
-  *num_rendered = host[0];
-  if (host[1]) { set_error("Point is filtered although prefiltered is set. This shouldn't happen!"); return B200GS_EINVAL; }
+  if (flag) { set_error("Point is filtered although prefiltered is set. This shouldn't happen!"); return B200GS_EINVAL; }
   return B200GS_OK;
 }
 
-int b200gs_surfel_forward_stage2(const b200gs_surfel_fwd* a, int R, void* stream) {
+int b200gs_surfel_forward_stage2(const b200gs_surfel_fwd* a, const int* plan, void* stream) {
   int rc = check_fwd(a);
   if (rc) return rc;
   cudaStream_t s = (cudaStream_t)stream;
   if (a->P == 0) return B200GS_OK;
-  if (R < 0) { set_error("negative num_rendered"); return B200GS_EINVAL; }
+  if (!plan) { set_error("plan is null"); return B200GS_EINVAL; }
+  const int R = plan[0], S = plan[1];
+  if (R < 0 || S < 1 || S > MAX_SLICES || plan[PLAN_G] != 0 || plan[PLAN_OFF] != 0 || plan[PLAN_G + S] != a->P || plan[PLAN_OFF + S] != R) {
+    set_error("bad slice plan (num_rendered %d, %d slices)", R, S); return B200GS_EINVAL; }
+  for (int k = 0; k < S; ++k)
+    if (plan[PLAN_G + k + 1] < plan[PLAN_G + k] || plan[PLAN_OFF + k + 1] < plan[PLAN_OFF + k]) { set_error("slice plan not ascending"); return B200GS_EINVAL; }
+  if (S > 1 && (a->exact_lists || a->cull_audit)) { set_error("depth slices need the culled emission"); return B200GS_EINVAL; }
   if (R > 0 && (!a->binning || a->binning_bytes < b200gs_binning_bytes(R))) { set_error("binning scratch too small"); return B200GS_ESIZE; }
   SurfelGeom g = SurfelGeom::carve(align128(a->geom), a->P, nullptr);
   SurfelImage im = SurfelImage::carve(align128(a->img), a->width, a->height, nullptr);
   Binning b = Binning::carve(R > 0 ? align128(a->binning) : nullptr, R, nullptr);
-  rc = bin_and_sort(g.order.vals_a, g.rects, g.point_offsets, a->P, R, a->width, a->height, b, im.ranges, s, a->debug != 0,
-                    a->exact_lists != 0 ? nullptr : g.cull);
+  BinJob j{};
+  j.order = g.order.vals_a; j.rects = g.rects; j.offsets = g.point_offsets;
+  j.cull = a->exact_lists != 0 ? nullptr : g.cull; j.cull_for_hits = g.cull;
+  j.P = a->P; j.W = a->width; j.H = a->height; j.R = R;
+  j.slices = S; j.g = plan + PLAN_G; j.off = plan + PLAN_OFF;
+  j.ranges = im.ranges; j.cranges = im.cranges; j.tile_done = im.tile_done; j.live = im.live;
+  j.debug = a->debug != 0; j.audit = a->cull_audit != 0;
+  rc = bin_clear(b, j, s);
   if (rc) return rc;
-  {
-    const size_t tiles = (size_t)((a->width + TILE_X - 1) / TILE_X) * ((a->height + TILE_Y - 1) / TILE_Y);
-    B200GS_CUDA(cudaMemsetAsync(im.cranges, 0, tiles * sizeof(uint2), s));
+  if (S > 1) {
+    const uint32_t tiles = (uint32_t)j.tiles();
+    B200GS_CUDA(cudaMemsetAsync(im.tile_done, 0, tiles, s));
+    const uint32_t live0[4] = {tiles, 0u, 0u, 0u};
+    B200GS_CUDA(cudaMemcpyAsync(im.live, live0, sizeof(live0), cudaMemcpyHostToDevice, s));
   }
-  if (R > 0) {
-    rc = surfel_tile_hits(g.cull, b, R, a->width, a->height, im.ranges, im.cranges, s, a->debug != 0,
-                          a->exact_lists != 0, a->cull_audit != 0);
+  size_t zcursor = 0;
+  for (int k = 0; k < S; ++k) {
+    if (R > 0) {
+      rc = bin_slice(j, k, b, zcursor, s);
+      if (rc) return rc;
+    }
+    rc = surfel_composite_forward(*a, g, im, b, k, S, s);
     if (rc) return rc;
   }
-  return surfel_composite_forward(*a, g, im, b, s);
+  return B200GS_OK;
 }
 
 int b200gs_surfel_backward(const b200gs_surfel_bwd* a, void* stream) {

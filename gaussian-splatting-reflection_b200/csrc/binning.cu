@@ -147,7 +147,7 @@ DepthOrder DepthOrder::carve(Carver& c, size_t P) {
   o.vals_a = c.take<uint32_t>(P);
   o.keys_b = c.take<uint32_t>(P);
   o.vals_b = c.take<uint32_t>(P);
-  o.ws_bytes = radix_workspace_bytes(P);
+  o.ws_bytes = radix_workspace_bytes(P, 4);
   o.ws = c.take<char>(o.ws_bytes);
   return o;
 }
@@ -159,7 +159,7 @@ int depth_order_and_scan(const float* depths, const uint32_t* tiles_touched, int
   if (P <= 0) return B200GS_OK;
   {
     StageScope _t(ST_DEPTH_SORT, s);
-    int rc = radix_workspace_clear(o.ws, s);
+    int rc = radix_workspace_clear(o.ws, (size_t)P, 4, s);
     if (rc) return rc;
     depth_keys_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, depths, tiles_touched, o.keys_a, o.vals_a);
     B200GS_LAUNCHED("depth_keys_kernel", debug, s);
@@ -244,6 +244,10 @@ struct EmitHist {
 
 struct KeptArgs {
   int P, gx;
+  int g0, g1;                     // emit: the Gaussians [g0, g1) of the depth order (one depth slice)
+  const uint8_t* done;            // emit, slices > 0: tiles whose pixels all saturated in an earlier slice ...
+  uint32_t sentinel;              // ... get this key instead (sorts behind every tile, never read)
+  const uint32_t* live;           // emit: number of unfinished tiles; 0 -> this slice is not needed at all
   const uint32_t* tiles_touched;  // count: [P] in id order
   const uint32_t* order;          // emit: ids in depth order
   const uint32_t* offsets;        // emit: inclusive scan of the kept counts, depth order
@@ -264,13 +268,14 @@ __global__ void __launch_bounds__(256) kept_rows_kernel(const KeptArgs a) {
   __shared__ uint2 s_ie[EMIT ? 256 : 1]; // emit: id, end of the Gaussian's slots
   __shared__ uint32_t s_h[2][EMIT ? RS_RADIX : 1];
   const int t = threadIdx.x, lane = t & 31, wb = t & ~31;
-  const int i = blockIdx.x * 256 + t;
+  const int i = (EMIT ? a.g0 : 0) + blockIdx.x * 256 + t;
+  if (EMIT && a.live != nullptr && *a.live == 0u) return;
   const bool hist = EMIT && a.eh.hist != nullptr;
   if (hist) { s_h[0][t] = 0u; s_h[1][t] = 0u; __syncthreads(); }
 
   uint32_t id = 0, off = 0, end = 0;
   bool vis = false;
-  if (i < a.P) {
+  if (i < (EMIT ? a.g1 : a.P)) {
     if (EMIT) {
       off = i == 0 ? 0u : a.offsets[i - 1]; end = a.offsets[i];
       vis = end > off;
@@ -301,6 +306,7 @@ __global__ void __launch_bounds__(256) kept_rows_kernel(const KeptArgs a) {
   __syncwarp();
 
   auto put = [&](uint32_t o, uint32_t key, uint32_t v) {
+    if (a.done != nullptr && a.done[key]) key = a.sentinel;
     a.keys[o] = key; a.vals[o] = v;
     if (hist) { atomicAdd(&s_h[0][key & a.eh.mask0], 1u); atomicAdd(&s_h[1][(key >> a.eh.shift1) & a.eh.mask1], 1u); }
   };
@@ -402,18 +408,21 @@ int surfel_count_kept(int P, const uint32_t* tiles_touched, const uint2* rects, 
   return B200GS_OK;
 }
 
-// identifyTileRanges (rasterizer_impl.cu:116-138)
-__global__ void __launch_bounds__(256) tile_ranges_kernel(int L, const uint32_t* __restrict__ keys, uint2* ranges) {
+// identifyTileRanges (rasterizer_impl.cu:116-138) over the sorted keys [first, first + L) of one depth slice
+// (the whole list when there is one slice); ranges hold absolute positions.
+__global__ void __launch_bounds__(256) tile_ranges_kernel(int first, int L, const uint32_t* __restrict__ keys, uint2* ranges,
+                                                          const uint32_t* __restrict__ live) {
+  if (live != nullptr && *live == 0u) return;
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= L) return;
-  const uint32_t cur = keys[idx];
+  const uint32_t cur = keys[first + idx];
   if (idx == 0) {
-    ranges[cur].x = 0;
+    ranges[cur].x = first;
   } else {
-    const uint32_t prev = keys[idx - 1];
-    if (cur != prev) { ranges[prev].y = idx; ranges[cur].x = idx; }
+    const uint32_t prev = keys[first + idx - 1];
+    if (cur != prev) { ranges[prev].y = first + idx; ranges[cur].x = first + idx; }
   }
-  if (idx == L - 1) ranges[cur].y = L;
+  if (idx == L - 1) ranges[cur].y = first + L;
 }
 
 // ------------------------------------------------------------------ tile hits
@@ -583,14 +592,19 @@ __device__ __forceinline__ unsigned block_masks(const TileForm& f) {
 // PREFILTER: whole-tile test first, per-block refinement only for the survivors (exact-lists mode,
 // where most instances miss their tile); without it every instance goes straight to the per-block
 // test (culled emission already dropped the instances that miss their tile).
+// One depth slice = the sorted instances [first, first + R); its survivors go to comp_*[first ...] (absolute
+// positions, like ranges / cranges).  Instances carrying the sentinel key `ntiles` (their tile was finished by an
+// earlier slice) are dropped.
 template <bool PREFILTER>
-__global__ void __launch_bounds__(TH_THREADS) tile_hits_kernel(int R, const uint32_t* __restrict__ keys,
+__global__ void __launch_bounds__(TH_THREADS) tile_hits_kernel(int first, int R, const uint32_t* __restrict__ keys,
                                                                const uint32_t* __restrict__ point_list,
-                                                               const CullRec* __restrict__ cull, int gx,
+                                                               const CullRec* __restrict__ cull, int gx, uint32_t ntiles,
                                                                const uint2* __restrict__ ranges, uint2* __restrict__ cranges,
                                                                uint32_t* __restrict__ comp_id, uint32_t* __restrict__ comp_pos,
                                                                uint8_t* __restrict__ comp_hit, uint32_t* state,
-                                                               int keep_all) {
+                                                               int keep_all, const uint32_t* __restrict__ live) {
+  if (live != nullptr && *live == 0u) return;
+  keys += first; point_list += first;
   __shared__ uint32_t s_tile;
   __shared__ uint32_t s_cnt[TH_ITEMS][TH_THREADS / 32];
   __shared__ uint32_t s_base;
@@ -613,7 +627,7 @@ __global__ void __launch_bounds__(TH_THREADS) tile_hits_kernel(int R, const uint
     id[k] = 0u; tile[k] = 0u;
     unsigned m = 0u;
     bool refine = false;
-    if (i < R) {
+    if (i < R && keys[i] < ntiles) {
       tile[k] = keys[i];
       id[k] = point_list[i];
       TileForm f;
@@ -648,7 +662,8 @@ __global__ void __launch_bounds__(TH_THREADS) tile_hits_kernel(int R, const uint
   for (int k = 0; k < TH_ITEMS; ++k) {
     const int i = base + k * TH_THREADS + t;
     mask[k] = s_mask[k * TH_THREADS + t];
-    keep[k] = i < R && (mask[k] != 0u || keep_all);   // keep_all: cull audit walks the full lists
+    if (i < R) tile[k] = keys[i];
+    keep[k] = i < R && tile[k] < ntiles && (mask[k] != 0u || keep_all);   // keep_all: cull audit walks the full lists
     const unsigned bal = __ballot_sync(0xffffffffu, keep[k]);
     wexcl[k] = __popc(bal & ((1u << lane) - 1u));
     if (lane == 0) s_cnt[k][warp] = __popc(bal);
@@ -692,37 +707,99 @@ __global__ void __launch_bounds__(TH_THREADS) tile_hits_kernel(int R, const uint
 #pragma unroll
   for (int k = 0; k < TH_ITEMS; ++k) {
     const int i = base + k * TH_THREADS + t;
-    if (i >= R) continue;
-    const uint32_t off = gbase + mine[k] + wexcl[k];
+    if (i >= R || tile[k] >= ntiles) continue;
+    const uint32_t off = (uint32_t)first + gbase + mine[k] + wexcl[k];
     const uint2 rg = ranges[tile[k]];
+    const uint32_t ia = (uint32_t)(first + i);        // absolute position in the sorted list
     if (keep[k]) {
       comp_id[off] = id[k];
-      comp_pos[off] = (uint32_t)i - rg.x;
+      comp_pos[off] = ia - rg.x;
       comp_hit[off] = (uint8_t)mask[k];
     }
-    if ((uint32_t)i == rg.x) cranges[tile[k]].x = off;
-    if ((uint32_t)i + 1u == rg.y) cranges[tile[k]].y = off + (keep[k] ? 1u : 0u);
+    if (ia == rg.x) cranges[tile[k]].x = off;
+    if (ia + 1u == rg.y) cranges[tile[k]].y = off + (keep[k] ? 1u : 0u);
   }
 }
 
-size_t tile_hits_state_words(size_t R) { return 2 * ((R + TH_TILE - 1) / TH_TILE + 2); }
+// ------------------------------------------------------------------ slice plan
+// Cuts the depth-ordered Gaussians into slices at given fractions of the cumulated instance count.  One warp per
+// boundary: 32-ary search for the first Gaussian whose inclusive offset reaches the target.  Thread 0 then
+// assembles the plan (common.cuh: PLAN_G / PLAN_OFF), dropping empty slices.
+struct SlicePlanArgs {
+  const uint32_t* offsets;
+  int P, n_bounds;
+  float frac[MAX_SLICES - 1];
+  uint32_t min_instances;        // fewer instances than this: one slice
+  int* plan;
+};
 
-int surfel_tile_hits(const CullRec* cull, const Binning& b, int R, int W, int H, const uint2* ranges, uint2* cranges,
-                     cudaStream_t s, bool debug, bool exact_lists, bool audit) {
-  (void)H;
-  const int gx = (W + TILE_X - 1) / TILE_X;
-  StageScope _t(ST_TILE_HITS, s);
-  B200GS_CUDA(cudaMemsetAsync(b.hit_state, 0, tile_hits_state_words(R) * sizeof(uint32_t), s));
-  const int keep_all = audit ? 1 : 0;   // the cull audit walks the full lists
-  if (exact_lists)
-    tile_hits_kernel<true><<<(R + TH_TILE - 1) / TH_TILE, TH_THREADS, 0, s>>>(R, b.tile_ids, b.point_list, cull, gx, ranges, cranges,
-                                                                             b.comp_id, b.comp_pos, b.comp_hit, b.hit_state, keep_all);
-  else
-    tile_hits_kernel<false><<<(R + TH_TILE - 1) / TH_TILE, TH_THREADS, 0, s>>>(R, b.tile_ids, b.point_list, cull, gx, ranges, cranges,
-                                                                              b.comp_id, b.comp_pos, b.comp_hit, b.hit_state, keep_all);
-  B200GS_LAUNCHED("tile_hits_kernel", debug, s);
+__global__ void __launch_bounds__(32 * (MAX_SLICES - 1)) slice_plan_kernel(const SlicePlanArgs a) {
+  __shared__ int s_g[MAX_SLICES - 1];
+  __shared__ uint32_t s_off[MAX_SLICES - 1];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const uint32_t R = a.offsets[a.P - 1];
+  if (w < a.n_bounds) {
+    const uint32_t target = (uint32_t)fminf((float)R * a.frac[w], (float)R);
+    // first i with offsets[i] >= target; invariant: the answer lies in [lo, hi] (hi == P: none)
+    int lo = 0, hi = a.P;
+    while (hi - lo > 32) {
+      const int step = (hi - lo) / 32;
+      const int idx = lo + (lane + 1) * step - 1;            // <= hi - 1
+      const unsigned m = __ballot_sync(0xffffffffu, a.offsets[idx] >= target);
+      if (m == 0u) { lo += 32 * step; continue; }
+      const int f = __ffs(m) - 1;
+      hi = lo + (f + 1) * step - 1;
+      lo = lo + f * step;                                     // probe f-1 (index lo + f*step - 1) was still below
+    }
+    {
+      const int idx = lo + lane;
+      const unsigned m = __ballot_sync(0xffffffffu, idx < hi && a.offsets[idx] >= target);
+      lo = m ? lo + __ffs(m) - 1 : hi;
+    }
+    if (lane == 0) { s_g[w] = min(lo + 1, a.P); s_off[w] = lo < a.P ? a.offsets[lo] : R; }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int S = 0;
+    a.plan[0] = (int)R;
+    a.plan[PLAN_G] = 0; a.plan[PLAN_OFF] = 0;
+    if (R >= a.min_instances) {
+      for (int k = 0; k < a.n_bounds; ++k) {
+        const int g = s_g[k]; const uint32_t off = s_off[k];
+        if (g > a.plan[PLAN_G + S] && g < a.P && off > (uint32_t)a.plan[PLAN_OFF + S] && off < R) {
+          ++S;
+          a.plan[PLAN_G + S] = g; a.plan[PLAN_OFF + S] = (int)off;
+        }
+      }
+    }
+    ++S;
+    a.plan[PLAN_G + S] = a.P; a.plan[PLAN_OFF + S] = (int)R;
+    a.plan[1] = S;
+  }
+}
+
+int slice_plan(const uint32_t* point_offsets, int P, int max_slices, const float* frac, int* plan_dev, cudaStream_t s, bool debug) {
+  SlicePlanArgs a{};
+  a.offsets = point_offsets; a.P = P; a.plan = plan_dev;
+  a.min_instances = 1u << 21;
+  // measured on the 1080p scenes (scripts/gpu_slices.py, profiles/r2d_slices.jsonl): the first 5 % of the instances finish
+  // all but a few tiles, 25 % finish all; finer schedules pay more launches than they save
+  static const float sched[MAX_SLICES - 1] = {0.05f, 0.25f, 0, 0, 0, 0, 0};
+  int n = max_slices <= 0 ? 3 : (max_slices > MAX_SLICES ? MAX_SLICES : max_slices);
+  const bool own = frac != nullptr && frac[0] > 0.0f;
+  if (max_slices > 1 && own) a.min_instances = 0;         // an explicit schedule is taken literally
+  a.n_bounds = 0;
+  for (int k = 0; k < n - 1; ++k) {
+    const float f = own ? frac[k] : sched[k];
+    if (!(f > 0.0f && f < 1.0f)) break;
+    a.frac[a.n_bounds++] = f;
+  }
+  slice_plan_kernel<<<1, 32 * (MAX_SLICES - 1), 0, s>>>(a);
+  B200GS_LAUNCHED("slice_plan_kernel", debug, s);
   return B200GS_OK;
 }
+
+size_t tile_hits_state_words(size_t R) { return 2 * ((R + TH_TILE - 1) / TH_TILE + 2); }
 
 // getHigherMsb (rasterizer_impl.cu:35-50)
 static uint32_t higher_msb(uint32_t n) {
@@ -735,6 +812,9 @@ static uint32_t higher_msb(uint32_t n) {
   return msb;
 }
 
+static inline size_t al256(size_t b) { return (b + 255) / 256 * 256; }
+constexpr int TILE_SORT_MAX_PASSES = 3;   // tile ids stay below 2^24
+
 Binning Binning::carve(void* base, size_t R, size_t* bytes) {
   Carver c(base);
   Binning b;
@@ -745,63 +825,101 @@ Binning Binning::carve(void* base, size_t R, size_t* bytes) {
   b.comp_id = c.take<uint32_t>(R);
   b.comp_pos = c.take<uint32_t>(R);
   b.comp_hit = c.take<uint8_t>(R);
-  b.hit_state = c.take<uint32_t>(tile_hits_state_words(R));
-  b.sort_ws_bytes = radix_workspace_bytes(R);
-  b.sort_ws = c.take<char>(b.sort_ws_bytes);
+  // Every depth slice sorts and compacts its own range with its own look-back words; all of them live in one region
+  // that is cleared once per forward.  Bound over any split of R into <= MAX_SLICES ranges.
+  b.zero_bytes = al256(radix_workspace_bytes(R, TILE_SORT_MAX_PASSES)) + al256(tile_hits_state_words(R) * sizeof(uint32_t)) +
+                 (size_t)MAX_SLICES * (al256(radix_workspace_bytes(RS_TILE, TILE_SORT_MAX_PASSES)) +
+                                       al256(tile_hits_state_words(TH_TILE) * sizeof(uint32_t)));
+  b.zero = c.take<char>(b.zero_bytes);
   if (bytes) *bytes = c.used + 128;
   return b;
 }
 
-// order: Gaussian ids in depth order; offsets: inclusive prefix of tiles_touched in that order.
-// cull != nullptr: culled emission (offsets then count the kept tiles), else the reference's full lists.
-int bin_and_sort(const uint32_t* order, const uint2* rects, const uint32_t* offsets, int P, int R, int W, int H,
-                 const Binning& b, uint2* ranges, cudaStream_t s, bool debug, const CullRec* cull) {
-  const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
-  B200GS_CUDA(cudaMemsetAsync(ranges, 0, (size_t)gx * gy * sizeof(uint2), s));
-  if (R <= 0) return B200GS_OK;
-  // same bit count as the reference's sort range above the depth word (rasterizer_impl.cu:306)
-  const RadixPlan plan = radix_plan((int)higher_msb((uint32_t)(gx * gy)));
+int bin_clear(const Binning& b, const BinJob& j, cudaStream_t s) {
+  const size_t tiles1 = (size_t)j.tiles() + 1;
+  B200GS_CUDA(cudaMemsetAsync(j.ranges, 0, (size_t)j.slices * tiles1 * sizeof(uint2), s));
+  B200GS_CUDA(cudaMemsetAsync(j.cranges, 0, (size_t)j.slices * tiles1 * sizeof(uint2), s));
+  if (j.R > 0) B200GS_CUDA(cudaMemsetAsync(b.zero, 0, b.zero_bytes, s));
+  return B200GS_OK;
+}
+
+// One depth slice k of the instance list: emission of the Gaussians [g[k], g[k+1]) of the depth order into the slots
+// [off[k], off[k+1]), stable sort of that range by tile id, its tile ranges, its block masks + compaction.
+// `zcursor`: running offset into b.zero (the slice's sort workspace and compaction words are carved from it).
+int bin_slice(const BinJob& j, int k, const Binning& b, size_t& zcursor, cudaStream_t s) {
+  const int gx = (j.W + TILE_X - 1) / TILE_X;
+  const int tiles = j.tiles();
+  const int first = j.off[k], n = j.off[k + 1] - j.off[k];
+  if (n <= 0) return B200GS_OK;
+  const bool sliced = j.slices > 1;
+  const uint32_t* live = sliced && k > 0 ? j.live : nullptr;     // nothing is finished before the first slice ran
+  uint2* ranges = j.ranges + (size_t)k * (tiles + 1);
+  uint2* cranges = j.cranges + (size_t)k * (tiles + 1);
+  // same bit count as the reference's sort range above the depth word (rasterizer_impl.cu:306); one more value
+  // (the sentinel key `tiles`) when later slices skip finished tiles
+  const RadixPlan plan = radix_plan((int)higher_msb((uint32_t)(sliced ? tiles + 1 : tiles)));
+  if (plan.passes > TILE_SORT_MAX_PASSES) { set_error("too many tiles (%d)", tiles); return B200GS_EINVAL; }
+  void* ws = b.zero + zcursor;
+  zcursor += al256(radix_workspace_bytes((size_t)n, plan.passes));
+  uint32_t* hit_state = reinterpret_cast<uint32_t*>(b.zero + zcursor);
+  zcursor += al256(tile_hits_state_words((size_t)n) * sizeof(uint32_t));
+  if (zcursor > b.zero_bytes) { set_error("binning scratch: slice workspaces exceed the carved region"); return B200GS_ESIZE; }
   // the sorted pairs must end up in (tile_ids, point_list): start there for an even pass count
   const bool odd = (plan.passes & 1) != 0;
-  uint32_t* ka = odd ? b.tmp_keys : b.tile_ids;
-  uint32_t* va = odd ? b.tmp_vals : b.point_list;
-  uint32_t* kb = odd ? b.tile_ids : b.tmp_keys;
-  uint32_t* vb = odd ? b.point_list : b.tmp_vals;
+  uint32_t* ka = (odd ? b.tmp_keys : b.tile_ids);
+  uint32_t* va = (odd ? b.tmp_vals : b.point_list);
+  uint32_t* kb = (odd ? b.tile_ids : b.tmp_keys);
+  uint32_t* vb = (odd ? b.point_list : b.tmp_vals);
   int rc;
-  const bool fused_hist = cull != nullptr && plan.passes <= 2;   // kept_rows_kernel<emit> accumulates the digit histograms
+  const bool fused_hist = j.cull != nullptr && plan.passes <= 2;   // kept_rows_kernel<emit> accumulates the digit histograms
   {
     StageScope _t(ST_DUPLICATE, s);
-    if (cull != nullptr) {
+    if (j.cull != nullptr) {
       EmitHist eh;
-      eh.hist = fused_hist ? radix_hist_ptr(b.sort_ws) : nullptr;
+      eh.hist = fused_hist ? radix_hist_ptr(ws) : nullptr;
       eh.mask0 = (1u << plan.bits[0]) - 1u;
       eh.shift1 = plan.passes > 1 ? plan.shift[1] : 0;
       eh.mask1 = plan.passes > 1 ? (1u << plan.bits[1]) - 1u : 0u;
-      if (fused_hist) { rc = radix_workspace_clear(b.sort_ws, s); if (rc) return rc; }
       KeptArgs ea{};
-      ea.P = P; ea.gx = gx; ea.order = order; ea.offsets = offsets; ea.rects = rects; ea.cull = cull;
-      ea.keys = ka; ea.vals = va; ea.eh = eh;
-      kept_rows_kernel<true><<<(P + 255) / 256, 256, 0, s>>>(ea);
-      B200GS_LAUNCHED("kept_rows_kernel<emit>", debug, s);
+      ea.P = j.P; ea.gx = gx; ea.order = j.order; ea.offsets = j.offsets; ea.rects = j.rects; ea.cull = j.cull;
+      ea.g0 = j.g[k]; ea.g1 = j.g[k + 1];
+      ea.done = sliced && k > 0 ? j.tile_done : nullptr; ea.sentinel = (uint32_t)tiles; ea.live = live;
+      ea.keys = ka; ea.vals = va; ea.eh = eh;     // slots are absolute positions (offsets is the global prefix sum)
+      const int ng = ea.g1 - ea.g0;
+      if (ng > 0) {
+        kept_rows_kernel<true><<<(ng + 255) / 256, 256, 0, s>>>(ea);
+        B200GS_LAUNCHED("kept_rows_kernel<emit>", j.debug, s);
+      }
     } else {
-      duplicate_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, order, rects, offsets, ka, va, gx);
-      B200GS_LAUNCHED("duplicate_kernel", debug, s);
+      duplicate_kernel<<<(j.P + 255) / 256, 256, 0, s>>>(j.P, j.order, j.rects, j.offsets, ka, va, gx);
+      B200GS_LAUNCHED("duplicate_kernel", j.debug, s);
     }
   }
   {
     StageScope _t(ST_SORT, s);
     if (!fused_hist) {
-      rc = radix_workspace_clear(b.sort_ws, s);
-      if (rc) return rc;
-      rc = radix_histogram(ka, R, plan, b.sort_ws, s, debug);
+      rc = radix_histogram(ka + first, n, plan, ws, s, j.debug);
       if (rc) return rc;
     }
-    rc = radix_sort_pairs_u32(ka, va, kb, vb, R, plan, b.sort_ws, s, debug);
+    rc = radix_sort_pairs_u32(ka + first, va + first, kb + first, vb + first, n, plan, ws, s, j.debug, live);
     if (rc) return rc;
   }
-  StageScope _t(ST_RANGES, s);
-  tile_ranges_kernel<<<(R + 255) / 256, 256, 0, s>>>(R, b.tile_ids, ranges);
-  B200GS_LAUNCHED("tile_ranges_kernel", debug, s);
+  {
+    StageScope _t(ST_RANGES, s);
+    tile_ranges_kernel<<<(n + 255) / 256, 256, 0, s>>>(first, n, b.tile_ids, ranges, live);
+    B200GS_LAUNCHED("tile_ranges_kernel", j.debug, s);
+  }
+  StageScope _t(ST_TILE_HITS, s);
+  const int keep_all = j.audit ? 1 : 0;   // the cull audit walks the full lists
+  const int blocks = (n + TH_TILE - 1) / TH_TILE;
+  if (j.cull_for_hits == nullptr) { set_error("bin_slice: no cull records"); return B200GS_EINVAL; }
+  if (j.cull == nullptr)     // exact lists: most instances miss their tile, test the whole tile first
+    tile_hits_kernel<true><<<blocks, TH_THREADS, 0, s>>>(first, n, b.tile_ids, b.point_list, j.cull_for_hits, gx, (uint32_t)tiles, ranges,
+                                                         cranges, b.comp_id, b.comp_pos, b.comp_hit, hit_state, keep_all, live);
+  else
+    tile_hits_kernel<false><<<blocks, TH_THREADS, 0, s>>>(first, n, b.tile_ids, b.point_list, j.cull_for_hits, gx, (uint32_t)tiles, ranges,
+                                                          cranges, b.comp_id, b.comp_pos, b.comp_hit, hit_state, keep_all, live);
+  B200GS_LAUNCHED("tile_hits_kernel", j.debug, s);
   return B200GS_OK;
 }
 

@@ -19,6 +19,17 @@ constexpr float NEAR_N = 0.2f;
 constexpr float FAR_N = 100.0f;
 constexpr float FILTER_INV_SQUARE = 2.0f;
 
+// ---------------------------------------------------------------- depth slices
+// Occlusion-aware binning (culled-emission mode): the Gaussians are cut, in depth order, into up to MAX_SLICES
+// slices; slice k is emitted, sorted and composited before slice k+1 is emitted, and tiles whose pixels have all
+// saturated (T < 1e-4 reached) receive no further instances.  On scenes with occlusion the compositing only ever
+// visits the first few per cent of a tile's list (measured: 1.4-3.3 % at 1080p / 3M Gaussians), so almost all of the
+// emission / sort / block-mask work on the later slices disappears.  Plan layout (host ints, b200gs.h):
+//   [0] R   [1] S   [2 .. 2+MAX_SLICES] first Gaussian (depth order) of slice k   [11 .. 11+MAX_SLICES] first instance
+constexpr int MAX_SLICES = B200GS_MAX_SLICES;
+constexpr int PLAN_G = 2, PLAN_OFF = 2 + MAX_SLICES + 1, PLAN_INTS = B200GS_PLAN_INTS;
+static_assert(PLAN_OFF + MAX_SLICES + 1 <= PLAN_INTS, "plan layout");
+
 // ---------------------------------------------------------------- errors
 void set_error(const char* fmt, ...);
 int cuda_fail(cudaError_t e, const char* what);
@@ -120,14 +131,20 @@ struct SurfelGeom {
   CullRec* cull;            // [P] region where alpha >= 1/255 is reachable
   uint32_t* scan_state;     // decoupled look-back tile states
   int* flags;               // [4] error flags (prefiltered violation, ...)
+  int* plan;                // [PLAN_INTS] the slice plan of this forward (device copy; the backward reads S from it)
   static SurfelGeom carve(void* base, size_t P, size_t* bytes);
 };
 
+constexpr int STATE_PLANES = 16;   // per-pixel compositing state carried from one depth slice to the next
 struct SurfelImage {
   float* accum;        // [3,N]: final T, M1, M2
   uint32_t* n_contrib; // [2,N]: last contributor, median contributor
-  uint2* ranges;       // [tiles]
-  uint2* cranges;      // [tiles] ranges into the compacted instance list (Binning::comp_*)
+  uint2* ranges;       // [MAX_SLICES][tiles+1] absolute ranges of every slice's sorted list (+1: the sentinel key)
+  uint2* cranges;      // [MAX_SLICES][tiles+1] ranges into the compacted instance list (Binning::comp_*)
+  uint32_t* tile_base; // [MAX_SLICES+1][tiles] entries of the tile's (uncompacted) lists in the slices before k
+  uint8_t* tile_done;  // [tiles] every pixel of the tile saturated in an earlier slice
+  uint32_t* live;      // [4] [0] = tiles not yet done
+  float* state;        // [STATE_PLANES,N] (only touched when a forward has more than one slice)
   static SurfelImage carve(void* base, int W, int H, size_t* bytes);
 };
 
@@ -141,11 +158,32 @@ struct Binning {
   uint32_t* comp_id;              // [<=R] Gaussian id
   uint32_t* comp_pos;             // [<=R] 0-based position in the tile's (uncompacted) list
   uint8_t* comp_hit;              // [<=R] bit w = warp block w of the tile can be reached
-  uint32_t* hit_state;            // look-back words + ticket of the compaction
-  void* sort_ws;                  // radix workspace (radix_sort.cuh)
-  size_t sort_ws_bytes;
+  char* zero;                     // radix workspaces + compaction look-back words of all depth slices:
+  size_t zero_bytes;              //   cleared once per forward (bin_clear), carved slice by slice (bin_slice)
   static Binning carve(void* base, size_t R, size_t* bytes);
 };
+
+// What one forward bins: the depth-ordered Gaussians, their instance offsets and the slice plan.
+struct BinJob {
+  const uint32_t* order;          // Gaussian ids in depth order
+  const uint2* rects;
+  const uint32_t* offsets;        // inclusive prefix sum of the per-Gaussian instance counts, depth order
+  const CullRec* cull;            // culled emission: the cull records; nullptr: the reference's full lists
+  const CullRec* cull_for_hits;   // the cull records (block masks are computed in both modes)
+  int P, W, H, R;
+  int slices;
+  const int* g;                   // [slices+1] host
+  const int* off;                 // [slices+1] host
+  uint2* ranges;                  // [slices][tiles+1]
+  uint2* cranges;
+  const uint8_t* tile_done;       // device, read by the emission of slices > 0
+  const uint32_t* live;           // device
+  bool debug, audit;
+  int tiles() const { return ((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y); }
+};
+int bin_clear(const Binning& b, const BinJob& j, cudaStream_t s);
+int bin_slice(const BinJob& j, int k, const Binning& b, size_t& zcursor, cudaStream_t s);
+int slice_plan(const uint32_t* point_offsets, int P, int max_slices, const float* frac, int* plan_dev, cudaStream_t s, bool debug);
 
 // Backward accumulator: 20 floats per Gaussian, one contiguous 80-B segment so a
 // (tile, Gaussian) partial is flushed with one vector of RED.ADD.F32.
@@ -181,8 +219,8 @@ struct GaussGeom {
 struct GaussImage {
   float* accum;         // [N] final T
   uint32_t* n_contrib;  // [N]
-  uint2* ranges;        // [tiles]
-  uint2* cranges;       // [tiles] ranges into the compacted instance list
+  uint2* ranges;        // [tiles+1]
+  uint2* cranges;       // [tiles+1] ranges into the compacted instance list
   static GaussImage carve(void* base, int W, int H, size_t* bytes);
 };
 
@@ -242,16 +280,12 @@ int inclusive_scan_u32(const uint32_t* in, uint32_t* out, int n, uint32_t* state
                        const uint32_t* gather = nullptr);
 int depth_order_and_scan(const float* depths, const uint32_t* tiles_touched, int P, const DepthOrder& o,
                          uint32_t* point_offsets, uint32_t* scan_state, cudaStream_t s, bool debug);
-int bin_and_sort(const uint32_t* order, const uint2* rects, const uint32_t* offsets,
-                 int P, int R, int W, int H, const Binning& b, uint2* ranges, cudaStream_t s, bool debug,
-                 const CullRec* cull = nullptr);
 int surfel_count_kept(int P, const uint32_t* tiles_touched, const uint2* rects, const CullRec* cull, uint32_t* kept,
                       cudaStream_t s, bool debug);
-int surfel_tile_hits(const CullRec* cull, const Binning& b, int R, int W, int H, const uint2* ranges, uint2* cranges,
-                     cudaStream_t s, bool debug, bool exact_lists, bool keep_all);
 size_t tile_hits_state_words(size_t R);
+// slice k of S (S == 1: the whole list in one go, no state carried)
 int surfel_composite_forward(const b200gs_surfel_fwd& a, const SurfelGeom& g, const SurfelImage& im,
-                             const Binning& b, cudaStream_t s);
+                             const Binning& b, int k, int S, cudaStream_t s);
 int surfel_composite_backward(const b200gs_surfel_bwd& a, const SurfelGeom& g, const SurfelImage& im,
                               const Binning& b, float* acc, cudaStream_t s);
 int surfel_preprocess_backward(const b200gs_surfel_bwd& a, const SurfelGeom& g, const float* acc, cudaStream_t s);

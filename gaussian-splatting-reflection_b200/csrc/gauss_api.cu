@@ -32,8 +32,8 @@ GaussImage GaussImage::carve(void* base, int W, int H, size_t* bytes) {
   const size_t tiles = (size_t)((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
   im.accum = c.take<float>(N);
   im.n_contrib = c.take<uint32_t>(N);
-  im.ranges = c.take<uint2>(tiles);
-  im.cranges = c.take<uint2>(tiles);
+  im.ranges = c.take<uint2>(tiles + 1);
+  im.cranges = c.take<uint2>(tiles + 1);
   if (bytes) *bytes = c.used + 128;
   return im;
 }
@@ -141,15 +141,19 @@ int b200gs_gauss_forward_stage2(const b200gs_gauss_fwd* a, int R, void* stream) 
   GaussGeom g = GaussGeom::carve(align128(a->geom), a->P, nullptr);
   GaussImage im = GaussImage::carve(align128(a->img), a->width, a->height, nullptr);
   Binning b = Binning::carve(R > 0 ? align128(a->binning) : nullptr, R, nullptr);
-  rc = bin_and_sort(g.order.vals_a, g.rects, g.point_offsets, a->P, R, a->width, a->height, b, im.ranges, s, a->debug != 0,
-                    a->exact_lists != 0 ? nullptr : g.cull);
+  BinJob j{};
+  const int g01[2] = {0, a->P}, off01[2] = {0, R};           // one depth slice
+  j.order = g.order.vals_a; j.rects = g.rects; j.offsets = g.point_offsets;
+  j.cull = a->exact_lists != 0 ? nullptr : g.cull; j.cull_for_hits = g.cull;
+  j.P = a->P; j.W = a->width; j.H = a->height; j.R = R;
+  j.slices = 1; j.g = g01; j.off = off01;
+  j.ranges = im.ranges; j.cranges = im.cranges; j.tile_done = nullptr; j.live = nullptr;
+  j.debug = a->debug != 0; j.audit = false;
+  rc = bin_clear(b, j, s);
   if (rc) return rc;
-  {
-    const size_t tiles = (size_t)((a->width + TILE_X - 1) / TILE_X) * ((a->height + TILE_Y - 1) / TILE_Y);
-    B200GS_CUDA(cudaMemsetAsync(im.cranges, 0, tiles * sizeof(uint2), s));
-  }
   if (R > 0) {
-    rc = surfel_tile_hits(g.cull, b, R, a->width, a->height, im.ranges, im.cranges, s, a->debug != 0, a->exact_lists != 0, false);
+    size_t zcursor = 0;
+    rc = bin_slice(j, 0, b, zcursor, s);
     if (rc) return rc;
   }
   return gauss_composite_forward(*a, g, im, b, s);

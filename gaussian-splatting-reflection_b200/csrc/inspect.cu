@@ -112,4 +112,14 @@ int b200gs_surfel_inspect_image(const void* img, int W, int H, float* accum_alph
   return B200GS_OK;
 }
 
+int b200gs_surfel_inspect_tiles(const void* img, int W, int H, uint8_t* tile_done, uint32_t* live, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  void* base = reinterpret_cast<void*>((reinterpret_cast<uintptr_t>(img) + 127) & ~uintptr_t(127));
+  SurfelImage im = SurfelImage::carve(base, W, H, nullptr);
+  const size_t tiles = (size_t)((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
+  if (tile_done) B200GS_CUDA(cudaMemcpyAsync(tile_done, im.tile_done, tiles, cudaMemcpyDeviceToDevice, s));
+  if (live) B200GS_CUDA(cudaMemcpyAsync(live, im.live, sizeof(uint32_t), cudaMemcpyDeviceToDevice, s));
+  return B200GS_OK;
+}
+
 }  // extern "C"

@@ -8,7 +8,9 @@
 //     the lowest one bumps the warp's private digit counter in shared memory, and every lane's
 //     rank is the old counter value plus the number of equal-digit lanes below it -- stable in
 //     (iteration, lane) order, which is memory order;
-//   * thread d owns digit d: it turns the per-warp counters into warp offsets, publishes the
+//   * thread d owns digit d: it turns the global digit histogram into the digit's bucket base (a block-wide
+//     exclusive scan every block repeats for itself: cheaper than a separate launch), the per-warp counters
+//     into warp offsets, publishes the
 //     block's count of digit d as a 64-bit (flag | count) word and walks back over the preceding
 //     blocks' words (aggregate -> keep walking, inclusive prefix -> stop) -- the chained scan that
 //     makes a single pass possible;
@@ -37,24 +39,24 @@ RadixPlan radix_plan(int total_bits) {
   return p;
 }
 
-// workspace layout (u32 words): hist[RS_MAX_PASSES][256] | tickets[RS_MAX_PASSES] | pad | u64 state[blocks][256]
+// workspace layout (u32 words): hist[RS_MAX_PASSES][256] | tickets[RS_MAX_PASSES] | pad | u64 state[passes][blocks][256]
 static constexpr size_t WS_HIST_WORDS = (size_t)RS_MAX_PASSES * RS_RADIX;
 static constexpr size_t WS_HEAD_WORDS = WS_HIST_WORDS + 32;
 static inline size_t ws_blocks(size_t n) { return (n + RS_TILE - 1) / RS_TILE; }
 
-size_t radix_workspace_bytes(size_t n) {
-  return WS_HEAD_WORDS * sizeof(uint32_t) + ws_blocks(n) * RS_RADIX * sizeof(unsigned long long) + 256;
+size_t radix_workspace_bytes(size_t n, int passes) {
+  return WS_HEAD_WORDS * sizeof(uint32_t) + (size_t)passes * ws_blocks(n) * RS_RADIX * sizeof(unsigned long long) + 256;
 }
 static inline uint32_t* ws_hist(void* ws) { return reinterpret_cast<uint32_t*>(ws); }
 static inline uint32_t* ws_tickets(void* ws) { return reinterpret_cast<uint32_t*>(ws) + WS_HIST_WORDS; }
-static inline unsigned long long* ws_state(void* ws) {
-  return reinterpret_cast<unsigned long long*>(reinterpret_cast<uint32_t*>(ws) + WS_HEAD_WORDS);
+static inline unsigned long long* ws_state(void* ws, size_t n, int pass) {
+  return reinterpret_cast<unsigned long long*>(reinterpret_cast<uint32_t*>(ws) + WS_HEAD_WORDS) + (size_t)pass * ws_blocks(n) * RS_RADIX;
 }
 
 uint32_t* radix_hist_ptr(void* workspace) { return ws_hist(workspace); }
 
-int radix_workspace_clear(void* workspace, cudaStream_t s) {
-  B200GS_CUDA(cudaMemsetAsync(workspace, 0, WS_HEAD_WORDS * sizeof(uint32_t), s));
+int radix_workspace_clear(void* workspace, size_t n, int passes, cudaStream_t s) {
+  B200GS_CUDA(cudaMemsetAsync(workspace, 0, radix_workspace_bytes(n, passes), s));
   return B200GS_OK;
 }
 
@@ -106,26 +108,6 @@ __global__ void __launch_bounds__(256) radix_hist_kernel(const HistArgs a) {
   }
 }
 
-// in place: digit counts -> exclusive bucket bases, one block per pass
-__global__ void __launch_bounds__(RS_RADIX) radix_bases_kernel(uint32_t* hist) {
-  __shared__ uint32_t s_w[RS_RADIX / 32];
-  uint32_t* h = hist + blockIdx.x * RS_RADIX;
-  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-  const uint32_t v = h[t];
-  uint32_t inc = v;
-#pragma unroll
-  for (int d = 1; d < 32; d <<= 1) {
-    const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
-    if (lane >= d) inc += o;
-  }
-  if (lane == 31) s_w[warp] = inc;
-  __syncthreads();
-  uint32_t off = 0;
-#pragma unroll
-  for (int w = 0; w < RS_RADIX / 32; ++w) if (w < warp) off += s_w[w];
-  h[t] = off + inc - v;
-}
-
 int radix_histogram(const uint32_t* keys, int n, const RadixPlan& plan, void* workspace, cudaStream_t s, bool debug) {
   if (n <= 0) return B200GS_OK;
   HistArgs a;
@@ -144,9 +126,10 @@ struct PassArgs {
   uint32_t* keys_out;
   uint32_t* vals_out;
   int n, shift, nbits;
-  const uint32_t* bases;        // [256] exclusive bucket bases of this pass
+  const uint32_t* hist;         // [256] digit counts of this pass over all n keys
   unsigned long long* state;    // [blocks][1 << nbits], zeroed: flag << 62 | count  (1 = aggregate, 2 = inclusive)
   uint32_t* ticket;
+  const uint32_t* live;         // optional: *live == 0 -> nothing to do
 };
 
 // MODE 0: match.any per key inside the counter loop, values fetched during the reorder.
@@ -180,11 +163,31 @@ __global__ void __launch_bounds__(THREADS, 3) radix_pass_kernel(const PassArgs a
   __shared__ uint32_t s_wsum[RS_RADIX / 32];
   __shared__ uint32_t s_blk;
 
+  __shared__ uint32_t s_hsum[RS_RADIX / 32];
+
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  if (a.live != nullptr && *a.live == 0u) return;
   const uint32_t dmask = (1u << a.nbits) - 1u;
   if (t == 0) s_blk = atomicAdd(a.ticket, 1u);
   for (int e = t; e < WARPS * RS_RADIX; e += THREADS) (&s_cnt[0][0])[e] = (cnt_t)0;
+  // exclusive bucket base of digit t over all n keys (the histogram is small and L2-resident)
+  uint32_t dbase = 0u;
+  {
+    const uint32_t hv = t < RS_RADIX ? a.hist[t] : 0u;
+    uint32_t inc = hv;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
+      if (lane >= d) inc += o;
+    }
+    if (lane == 31 && t < RS_RADIX) s_hsum[warp] = inc;
+    dbase = inc - hv;
+  }
   __syncthreads();
+  if (t < RS_RADIX) {
+#pragma unroll
+    for (int w = 0; w < RS_RADIX / 32; ++w) if (w < warp) dbase += s_hsum[w];
+  }
   const uint32_t blk = s_blk;
   const int blk_base = (int)blk * RS_TILE;
   const int wbase = blk_base + warp * (32 * ITEMS);
@@ -277,7 +280,7 @@ __global__ void __launch_bounds__(THREADS, 3) radix_pass_kernel(const PassArgs a
       }
       st[(size_t)blk * nb + t] = (2ull << 62) | (unsigned long long)(prev + total);
     }
-    s_gbase[t] = a.bases[t] + prev - excl;
+    s_gbase[t] = dbase + prev - excl;
   }
   __syncthreads();
 
@@ -303,20 +306,18 @@ __global__ void __launch_bounds__(THREADS, 3) radix_pass_kernel(const PassArgs a
 }
 
 int radix_sort_pairs_u32(uint32_t* keys_a, uint32_t* vals_a, uint32_t* keys_b, uint32_t* vals_b, int n,
-                         const RadixPlan& plan, void* workspace, cudaStream_t s, bool debug) {
+                         const RadixPlan& plan, void* workspace, cudaStream_t s, bool debug, const uint32_t* live) {
   if (n <= 0) return B200GS_OK;
-  radix_bases_kernel<<<plan.passes, RS_RADIX, 0, s>>>(ws_hist(workspace));
-  B200GS_LAUNCHED("radix_bases_kernel", debug, s);
   const int blocks = (int)ws_blocks((size_t)n);
   uint32_t *ki = keys_a, *vi = vals_a, *ko = keys_b, *vo = vals_b;
   for (int p = 0; p < plan.passes; ++p) {
     PassArgs a;
     a.keys_in = ki; a.vals_in = vi; a.keys_out = ko; a.vals_out = vo;
     a.n = n; a.shift = plan.shift[p]; a.nbits = plan.bits[p];
-    a.bases = ws_hist(workspace) + p * RS_RADIX;
-    a.state = ws_state(workspace);
+    a.hist = ws_hist(workspace) + p * RS_RADIX;
+    a.state = ws_state(workspace, (size_t)n, p);
     a.ticket = ws_tickets(workspace) + p;
-    B200GS_CUDA(cudaMemsetAsync(a.state, 0, (size_t)blocks * ((size_t)1 << a.nbits) * sizeof(unsigned long long), s));
+    a.live = live;
     // Measured on the bench workload (round 1; tile sort of 33.8M pairs, two passes): ranking inside the counter loop
     // 0.76 ms, independent match.any 0.64, ballots per digit bit 0.64; look-back batch 1 0.66, 4 0.61, 8 0.65;
     // 512 threads x 8 keys 0.70-0.85.  Kept: independent match.any, 4-wide look-back.

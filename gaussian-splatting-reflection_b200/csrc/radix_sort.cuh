@@ -33,13 +33,13 @@ struct RadixPlan {
 };
 RadixPlan radix_plan(int total_bits);
 
-// Workspace: [RS_MAX_PASSES][256] digit histograms (turned into exclusive bucket bases),
-// RS_MAX_PASSES block tickets, and one 64-bit look-back word per (block, digit) -- reused
-// by every pass (cleared in between).
-size_t radix_workspace_bytes(size_t n);
+// Workspace: [RS_MAX_PASSES][256] digit histograms, RS_MAX_PASSES block tickets, and one 64-bit look-back word
+// per (pass, block, digit) -- every pass has its own words, so ONE clear before the first pass suffices (a caller
+// that sorts several independent ranges carves one workspace per range out of a single zeroed region).
+size_t radix_workspace_bytes(size_t n, int passes);
 
-// Zeroes histograms and tickets.  Must precede radix_histogram / radix_sort_pairs_u32.
-int radix_workspace_clear(void* workspace, cudaStream_t s);
+// Zeroes a workspace of radix_workspace_bytes(n, passes).  Must precede radix_histogram / radix_sort_pairs_u32.
+int radix_workspace_clear(void* workspace, size_t n, int passes, cudaStream_t s);
 
 // The [RS_MAX_PASSES][256] histogram block of a workspace, for producers that count digits themselves.
 uint32_t* radix_hist_ptr(void* workspace);
@@ -50,7 +50,10 @@ int radix_histogram(const uint32_t* keys, int n, const RadixPlan& plan, void* wo
 // Sorts n pairs stably on key bits [0, total_bits).  (keys_a, vals_a) hold the input and are
 // overwritten; the result is in (keys_a, vals_a) when plan.passes is even and in (keys_b, vals_b)
 // when it is odd.  The histograms must already be in the workspace (radix_histogram).
+// `live` (optional, device): when *live == 0 at launch every block returns at once (depth-sliced binning: all
+// tiles were finished by an earlier slice, nothing downstream reads this slice).
 int radix_sort_pairs_u32(uint32_t* keys_a, uint32_t* vals_a, uint32_t* keys_b, uint32_t* vals_b, int n,
-                         const RadixPlan& plan, void* workspace, cudaStream_t s, bool debug);
+                         const RadixPlan& plan, void* workspace, cudaStream_t s, bool debug,
+                         const uint32_t* live = nullptr);
 
 }  // namespace b200gs

@@ -16,7 +16,10 @@ namespace b200gs {
 
 struct CompBwdArgs {
   int W, H, gx;
-  const uint2* ranges;        // ranges into the COMPACTED instance list
+  int tiles;                  // depth slices: ranges / tile_base of slice k start at k * (tiles + 1) / k * tiles
+  const int* plan;            // device copy of the forward's slice plan: [1] = number of slices
+  const uint32_t* tile_base;  // [slices+1][tiles] list position at which slice k starts in every tile
+  const uint2* ranges;        // [slices][tiles+1] ranges into the COMPACTED instance list
   const uint32_t* point_list; // compacted ids
   const uint32_t* list_pos;   // position of every compacted entry in the tile's full list (ascending)
   const SurfelRec* rec;
@@ -51,9 +54,6 @@ __global__ void __launch_bounds__(BATCH, 3) surfel_composite_bwd_kernel(const Co
   const float fx = (float)pxi, fy = (float)pyi;
   const size_t N = (size_t)a.W * a.H;
   const size_t pix_id = (size_t)a.W * pyi + pxi;
-
-  const uint2 range = a.ranges[tile];
-  if (range.y == range.x) return;
 
   // lane -> accumulator component owned after the reduce-scatter
   const int b16 = (lane >> 4) & 1, b8 = (lane >> 3) & 1, b4 = (lane >> 2) & 1, b2 = (lane >> 1) & 1, b1 = lane & 1;
@@ -92,34 +92,49 @@ __global__ void __launch_bounds__(BATCH, 3) surfel_composite_bwd_kernel(const Co
   // (outside the image) simply never contribute.
   const bool live = inside;
 
+  // Entries at or behind the last contributor of every pixel of the tile are never used
+  // (backward.cu:290: `contributor >= last_contributor` -> continue).
+  const uint32_t warp_last = __reduce_max_sync(0xffffffffu, inside ? last_contributor : 0u);
+  __shared__ uint32_t s_last[BATCH / 32];
+  __shared__ uint32_t s_tile_last;
+  if (lane == 0) s_last[warp] = warp_last;
+  __syncthreads();
+  if (t == 0) {
+    uint32_t tile_last = 0;
+#pragma unroll
+    for (int w = 0; w < BATCH / 32; ++w) tile_last = max(tile_last, s_last[w]);
+    s_tile_last = tile_last;
+  }
+  __syncthreads();
+  const uint32_t tile_last = s_tile_last;
+  if (tile_last == 0u) return;
+
+  // The tile's list is the concatenation of its depth slices' lists (one slice unless the forward was sliced): walk
+  // the slices back to front, each slice's entries back to front.  The per-pixel recurrences simply carry on.
+  const int S = a.plan[1];
+  for (int sl = S - 1; sl >= 0; --sl) {
+  const uint32_t base = sl == 0 ? 0u : a.tile_base[(size_t)sl * a.tiles + tile];     // list position of the slice's first entry
+  if (base >= tile_last) continue;
+  const uint2 range = a.ranges[(size_t)sl * (a.tiles + 1) + tile];
+  if (range.y == range.x) continue;
   const uint32_t* pl = a.point_list + range.x;
   const uint8_t* ph = a.hit + range.x;
   const uint32_t* pp = a.list_pos + range.x;
-
-  // Entries at or behind the last contributor of every pixel of the tile are never used
-  // (backward.cu:290: `contributor >= last_contributor` -> continue): list positions ascend, so
-  // the live part is a prefix of the compacted list; find its length by bisection.
-  const uint32_t warp_last = __reduce_max_sync(0xffffffffu, inside ? last_contributor : 0u);
-  {
-    __shared__ uint32_t s_last[BATCH / 32];
-    if (lane == 0) s_last[warp] = warp_last;
-    __syncthreads();
-    if (t == 0) {
-      uint32_t tile_last = 0;
-#pragma unroll
-      for (int w = 0; w < BATCH / 32; ++w) tile_last = max(tile_last, s_last[w]);
-      int lo = 0, hi = (int)(range.y - range.x);     // first index with pos >= tile_last
-      while (lo < hi) {
-        const int mid = (lo + hi) >> 1;
-        if (pp[mid] < tile_last) lo = mid + 1; else hi = mid;
-      }
-      s_n = lo;
+  // list positions ascend, so the live part is a prefix of the slice's compacted list; find its length by bisection
+  __syncthreads();                                  // everyone has left the previous slice's shared buffers
+  if (t == 0) {
+    const uint32_t lim = tile_last - base;
+    int lo = 0, hi = (int)(range.y - range.x);     // first index with pos >= lim
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if (pp[mid] < lim) lo = mid + 1; else hi = mid;
     }
-    __syncthreads();
+    s_n = lo;
   }
+  __syncthreads();
   const int n = s_n;
   const int rounds = (n + BATCH - 1) / BATCH;
-  if (n == 0) return;
+  if (n == 0) continue;
 
   unsigned hit_cur = 0u, hit_next = 0u;
   uint32_t pos_next = 0u;
@@ -161,11 +176,11 @@ __global__ void __launch_bounds__(BATCH, 3) surfel_composite_bwd_kernel(const Co
     for (int r = 0; r < (count + 31) >> 5; ++r) {
       // entries of other warp blocks, and entries behind every pixel's last contributor, are skipped
       const int e = r * 32 + lane;
-      unsigned m = __ballot_sync(0xffffffffu, e < count && ((s_hit[buf][e] >> warp) & 1u) && s_pos[buf][e] < warp_last);
+      unsigned m = __ballot_sync(0xffffffffu, e < count && ((s_hit[buf][e] >> warp) & 1u) && base + s_pos[buf][e] < warp_last);
       while (m) {
       const int j = r * 32 + __ffs(m) - 1;
       m &= m - 1;
-      const uint32_t contributor = s_pos[buf][j];   // 0-based position in the tile's full list
+      const uint32_t contributor = base + s_pos[buf][j];   // 0-based position in the tile's full list
       const float4 q0 = rb[j].q[0], q1 = rb[j].q[1], q2 = rb[j].q[2];
       SurfelHit h;
       bool c = live && contributor < last_contributor;
@@ -254,6 +269,7 @@ __global__ void __launch_bounds__(BATCH, 3) surfel_composite_bwd_kernel(const Co
     }
   }
   cp_async_wait_all();
+  }   // slices
 }
 
 int surfel_composite_backward(const b200gs_surfel_bwd& f, const SurfelGeom& g, const SurfelImage& im, const Binning& b,
@@ -262,6 +278,7 @@ int surfel_composite_backward(const b200gs_surfel_bwd& f, const SurfelGeom& g, c
   a.W = f.width; a.H = f.height;
   a.gx = (f.width + TILE_X - 1) / TILE_X;
   const int gy = (f.height + TILE_Y - 1) / TILE_Y;
+  a.tiles = a.gx * gy; a.plan = g.plan; a.tile_base = im.tile_base;
   a.ranges = im.cranges; a.point_list = b.comp_id; a.list_pos = b.comp_pos; a.rec = g.rec; a.hit = b.comp_hit; a.bg = f.background;
   a.accum = im.accum; a.n_contrib = im.n_contrib;
   a.dL_dpix = f.dL_dout_color; a.dL_dothers = f.dL_dout_others; a.dL_drefl = f.dL_dout_refl;

@@ -27,6 +27,14 @@ struct CompFwdArgs {
   float* out_others;
   float* out_refl;
   float* gaussian_weights;
+  // depth slices (common.cuh): this launch composites slice k of S; S == 1 is the whole list in one go
+  int k, S;
+  const uint2* uranges;       // slice k's ranges in the UNcompacted list (their lengths number the contributors)
+  const uint32_t* base_k;     // [tiles] list position at which slice k starts in every tile
+  uint32_t* base_next;        // [tiles] the same for slice k+1 (written here)
+  uint8_t* tile_done;         // [tiles] set when every pixel of the tile has saturated
+  uint32_t* live;             // [0] tiles not done
+  float* state;               // [STATE_PLANES,N] compositing state of unfinished pixels between slices
 };
 
 constexpr int BATCH = 256;
@@ -60,6 +68,10 @@ __global__ void __launch_bounds__(BATCH) surfel_composite_fwd_kernel(const CompF
   const size_t N = (size_t)a.W * a.H;
   const size_t pix_id = (size_t)a.W * pyi + pxi;
 
+  const bool sliced = a.S > 1;
+  if (sliced && a.k > 0 && a.tile_done[tile]) return;      // finished (and its outputs written) by an earlier slice
+  const uint32_t base = a.k > 0 ? a.base_k[tile] : 0u;     // contributors are numbered through all slices of the tile
+
   const uint2 range = a.ranges[tile];
   const int n = (int)(range.y - range.x);
   const int rounds = (n + BATCH - 1) / BATCH;
@@ -70,6 +82,16 @@ __global__ void __launch_bounds__(BATCH) surfel_composite_fwd_kernel(const CompF
   float C0 = 0.f, C1 = 0.f, C2 = 0.f, refl = 0.f, mask = 0.f;
   float N0 = 0.f, N1 = 0.f, N2 = 0.f, D = 0.f, M1 = 0.f, M2 = 0.f, distortion = 0.f, median_depth = 0.f;
   float median_contributor = -1.0f;
+  if (sliced && a.k > 0 && inside) {                        // pick up where the previous slice left this pixel
+    const float* st = a.state + pix_id;
+    const float Ts = st[0];
+    done = Ts < 0.0f; T = fabsf(Ts);                        // T >= 1e-4 > 0: the sign carries `done`
+    C0 = st[1 * N]; C1 = st[2 * N]; C2 = st[3 * N];
+    N0 = st[4 * N]; N1 = st[5 * N]; N2 = st[6 * N];
+    D = st[7 * N]; M1 = st[8 * N]; M2 = st[9 * N]; distortion = st[10 * N];
+    median_depth = st[11 * N]; median_contributor = st[12 * N]; refl = st[13 * N]; mask = st[14 * N];
+    last_contributor = __float_as_uint(st[15 * N]);
+  }
 
   s_wmax[0][t] = 0;
   s_wmax[1][t] = 0;
@@ -130,7 +152,7 @@ __global__ void __launch_bounds__(BATCH) surfel_composite_fwd_kernel(const CompF
         if (__all_sync(0xffffffffu, done)) { warp_done = true; break; }
         const int j = r * 32 + __ffs(m) - 1;
         m &= m - 1;
-        const uint32_t contributor = s_pos[buf][j] + 1u;  // 1-based position in the tile's (full) list
+        const uint32_t contributor = base + s_pos[buf][j] + 1u;  // 1-based position in the tile's (full) list
         const float4 q0 = rb[j].q[0], q1 = rb[j].q[1], q2 = rb[j].q[2];
         SurfelHit h;
         bool c = surfel_eval<false>(q0, q1, q2, fx, fy, h);
@@ -196,7 +218,28 @@ __global__ void __launch_bounds__(BATCH) surfel_composite_fwd_kernel(const CompF
   }
   cp_async_wait_all();
 
-  if (inside) {  // forward.cu:465-488
+  bool finalize = true;
+  if (sliced) {
+    const bool last = a.k == a.S - 1;
+    const bool all_done = __syncthreads_count(done) == BATCH;
+    finalize = last || all_done;
+    if (t == 0 && !last) {
+      const uint2 ur = a.uranges[tile];
+      a.base_next[tile] = base + (ur.y - ur.x);
+      if (all_done) { a.tile_done[tile] = 1; atomicSub(a.live, 1u); }   // later slices emit nothing into this tile
+    }
+    if (!finalize && inside) {
+      float* st = a.state + pix_id;
+      st[0] = done ? -T : T;
+      st[1 * N] = C0; st[2 * N] = C1; st[3 * N] = C2;
+      st[4 * N] = N0; st[5 * N] = N1; st[6 * N] = N2;
+      st[7 * N] = D; st[8 * N] = M1; st[9 * N] = M2; st[10 * N] = distortion;
+      st[11 * N] = median_depth; st[12 * N] = median_contributor; st[13 * N] = refl; st[14 * N] = mask;
+      st[15 * N] = __uint_as_float(last_contributor);
+    }
+  }
+
+  if (finalize && inside) {  // forward.cu:465-488
     a.accum[pix_id] = T;
     a.accum[pix_id + N] = M1;
     a.accum[pix_id + 2 * N] = M2;
@@ -218,12 +261,17 @@ __global__ void __launch_bounds__(BATCH) surfel_composite_fwd_kernel(const CompF
 }
 
 int surfel_composite_forward(const b200gs_surfel_fwd& f, const SurfelGeom& g, const SurfelImage& im, const Binning& b,
-                             cudaStream_t s) {
+                             int k, int S, cudaStream_t s) {
   CompFwdArgs a;
   a.W = f.width; a.H = f.height;
   a.gx = (f.width + TILE_X - 1) / TILE_X;
   const int gy = (f.height + TILE_Y - 1) / TILE_Y;
-  a.ranges = im.cranges; a.point_list = b.comp_id; a.list_pos = b.comp_pos; a.rec = g.rec; a.hit = b.comp_hit; a.bg = f.background;
+  const size_t tiles = (size_t)a.gx * gy;
+  a.k = k; a.S = S;
+  a.ranges = im.cranges + (size_t)k * (tiles + 1); a.uranges = im.ranges + (size_t)k * (tiles + 1);
+  a.base_k = im.tile_base + (size_t)k * tiles; a.base_next = im.tile_base + (size_t)(k + 1) * tiles;
+  a.tile_done = im.tile_done; a.live = im.live; a.state = im.state;
+  a.point_list = b.comp_id; a.list_pos = b.comp_pos; a.rec = g.rec; a.hit = b.comp_hit; a.bg = f.background;
   a.accum = im.accum; a.n_contrib = im.n_contrib;
   a.out_color = f.out_color; a.out_others = f.out_others; a.out_refl = f.out_refl;
   a.gaussian_weights = f.gaussian_weights;

@@ -42,7 +42,8 @@ class SurfelFwd(C.Structure):
         ("geom", _p), ("geom_bytes", _sz), ("img", _p), ("img_bytes", _sz),
         ("binning", _p), ("binning_bytes", _sz),
         ("out_color", _p), ("out_others", _p), ("out_refl", _p), ("radii", _p),
-        ("gaussian_weights", _p), ("exact_lists", _i), ("cull_audit", _i),
+        ("gaussian_weights", _p), ("exact_lists", _i), ("cull_audit", _i), ("depth_slices", _i),
+        ("slice_frac", _f * 7),
     ]
 
 
@@ -147,12 +148,16 @@ surfel_geom_bytes = _sig("b200gs_surfel_geom_bytes", _sz, _i)
 surfel_image_bytes = _sig("b200gs_surfel_image_bytes", _sz, _i, _i)
 binning_bytes = _sig("b200gs_binning_bytes", _sz, _i)
 surfel_accum_bytes = _sig("b200gs_surfel_accum_bytes", _sz, _i)
+MAX_SLICES, PLAN_INTS = 8, 24
 surfel_forward_stage1 = _sig("b200gs_surfel_forward_stage1", _i, C.POINTER(SurfelFwd), C.POINTER(_i), _p)
-surfel_forward_stage2 = _sig("b200gs_surfel_forward_stage2", _i, C.POINTER(SurfelFwd), _i, _p)
+surfel_forward_stage2 = _sig("b200gs_surfel_forward_stage2", _i, C.POINTER(SurfelFwd), C.POINTER(_i), _p)
 surfel_backward = _sig("b200gs_surfel_backward", _i, C.POINTER(SurfelBwd), _p)
 surfel_inspect_geom = _sig("b200gs_surfel_inspect_geom", _i, _p, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p)
 inspect_binning = _sig("b200gs_inspect_binning", _i, _p, _i, _p, _p, _p, _p)
 surfel_inspect_image = _sig("b200gs_surfel_inspect_image", _i, _p, _i, _i, _p, _p, _p, _p)
+
+
+surfel_inspect_tiles = _sig("b200gs_surfel_inspect_tiles", _i, _p, _i, _i, _p, _p, _p)
 
 
 gauss_geom_bytes = _sig("b200gs_gauss_geom_bytes", _sz, _i)
@@ -219,6 +224,13 @@ class PlyLayout(C.Structure):
 
 ply_unpack = _sig("b200gs_ply_unpack", _i, C.c_longlong, _p, C.POINTER(PlyLayout), _p)
 ply_pack = _sig("b200gs_ply_pack", _i, C.c_longlong, C.POINTER(PlyLayout), _p, _p)
+
+
+struct_bytes = _sig("b200gs_struct_bytes", _sz, _i)
+for _k, _cls in enumerate((SurfelFwd, SurfelBwd, GaussFwd, GaussBwd, Adam, PlyLayout)):
+    if struct_bytes(_k) != C.sizeof(_cls):
+        raise ImportError(f"libb200gs.so and its Python binding disagree on the layout of {_cls.__name__} "
+                          f"({struct_bytes(_k)} vs {C.sizeof(_cls)} bytes): rebuild the library")
 
 
 def check(rc):

@@ -29,13 +29,14 @@ def _stream():
 def rasterize_gaussians(background, means3D, env_scope_mask, colors, refl_strengths, opacity, scales, rotations,
                         scale_modifier, transMat_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy,
                         image_height, image_width, sh, degree, campos, prefiltered, debug, *, exact_lists=False,
-                        cull_audit=False):
+                        cull_audit=False, depth_slices=0, slice_fractions=None):
     """-> (rendered, out_color[3,H,W], out_others[8,H,W], radii[P], geomBuffer, binningBuffer,
     imgBuffer, out_refl_strength_map[1,H,W], gaussian_weights[P])   (S/rasterize_points.cu:39-151)
 
     The 21 positional arguments are the reference's.  Keyword-only extras of this library, per call (the
     library keeps no mode of its own): exact_lists -- emit the reference's instance lists bit for bit
-    instead of only the reachable instances (include/b200gs.h); cull_audit -- test infrastructure."""
+    instead of only the reachable instances (include/b200gs.h); cull_audit -- test infrastructure; depth_slices
+    (0 automatic, 1 off, n at most n) / slice_fractions -- the occlusion-aware binning of b200gs_surfel_forward_stage1."""
     if means3D.dim() != 2 or means3D.size(1) != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")
     background = _cuda_f32("background", background)
@@ -92,15 +93,18 @@ def rasterize_gaussians(background, means3D, env_scope_mask, colors, refl_streng
                 binning=None, binning_bytes=0,
                 out_color=out_color.data_ptr(), out_others=out_others.data_ptr(), out_refl=out_refl.data_ptr(),
                 radii=radii.data_ptr(), gaussian_weights=gaussian_weights.data_ptr(),
-                exact_lists=int(bool(exact_lists)), cull_audit=int(bool(cull_audit)))
-            n = C.c_int(0)
+                exact_lists=int(bool(exact_lists)), cull_audit=int(bool(cull_audit)), depth_slices=int(depth_slices))
+            if slice_fractions:
+                for i, fr in enumerate(list(slice_fractions)[:7]):
+                    a.slice_frac[i] = float(fr)
+            plan = (C.c_int * _b.PLAN_INTS)()
             st = _stream()
-            _b.check(_b.surfel_forward_stage1(C.byref(a), C.byref(n), st))
-            rendered = n.value
+            _b.check(_b.surfel_forward_stage1(C.byref(a), plan, st))
+            rendered = plan[0]
             binning = torch.empty((_b.binning_bytes(rendered),), **u8)
             a.binning = binning.data_ptr()
             a.binning_bytes = binning.numel()
-            _b.check(_b.surfel_forward_stage2(C.byref(a), rendered, st))
+            _b.check(_b.surfel_forward_stage2(C.byref(a), plan, st))
     return rendered, out_color, out_others, radii, geom, binning, img, out_refl, gaussian_weights
 
 

@@ -67,7 +67,8 @@ class _RasterizeGaussians(torch.autograd.Function):
                 rs.image_height, rs.image_width, sh, rs.sh_degree, rs.campos, rs.prefiltered, rs.debug)
         (num_rendered, color, depth, radii, geomBuffer, binningBuffer, imgBuffer, refl_strength_map,
          gaussian_weights) = _call_with_dump(_C.rasterize_gaussians, args, rs.debug, "snapshot_fw.dump", "forward",
-                                             exact_lists=bool(opts.get("exact_lists", False)))
+                                             exact_lists=bool(opts.get("exact_lists", False)),
+                                             depth_slices=int(opts.get("depth_slices", 0)))
         ctx.raster_settings = rs
         ctx.grad_arena = opts.get("grad_arena")
         ctx.num_rendered = num_rendered
@@ -107,11 +108,12 @@ def rasterize_gaussians(means3D, means2D, sh, colors_precomp, refl_strengths, op
 
 
 class GaussianRasterizer(nn.Module):
-    def __init__(self, raster_settings, *, exact_lists=False, grad_arena=None):
+    def __init__(self, raster_settings, *, exact_lists=False, grad_arena=None, depth_slices=0):
         super().__init__()
         self.raster_settings = raster_settings
         self.exact_lists = bool(exact_lists)
         self.grad_arena = grad_arena
+        self.depth_slices = int(depth_slices)
 
     def markVisible(self, positions):
         """Boolean mask of the points in front of the camera's near plane."""
@@ -137,7 +139,7 @@ class GaussianRasterizer(nn.Module):
         cov3D_precomp = empty() if cov3D_precomp is None else cov3D_precomp
         env_scope_mask = empty() if env_scope_mask is None else env_scope_mask
         opts = None
-        if self.exact_lists or self.grad_arena is not None:
-            opts = {"exact_lists": self.exact_lists, "grad_arena": self.grad_arena}
+        if self.exact_lists or self.grad_arena is not None or self.depth_slices:
+            opts = {"exact_lists": self.exact_lists, "grad_arena": self.grad_arena, "depth_slices": self.depth_slices}
         return rasterize_gaussians(means3D, means2D, shs, colors_precomp, refl_strengths, opacities, scales, rotations,
                                    cov3D_precomp, self.raster_settings, env_scope_mask, opts)

@@ -43,6 +43,10 @@ int b200gs_sm_arch(void);
 /* Number of kernel launches this library has issued since load (all threads);
  * bench.py reads it around the timed region for its "gpu_launches" claim.    */
 unsigned long long b200gs_launch_count(void);
+/* sizeof() of the argument structs of this header as the library was compiled, for bindings to check their own
+ * layout against: 0 b200gs_surfel_fwd, 1 b200gs_surfel_bwd, 2 b200gs_gauss_fwd, 3 b200gs_gauss_bwd, 4 b200gs_adam,
+ * 5 b200gs_ply_layout; 0 for any other index.                                                                  */
+size_t b200gs_struct_bytes(int which);
 
 /* Per-stage device timing for bench.py: when enabled, every stage (kernel) is
  * bracketed by a CUDA event pair on the stream it is launched on.
@@ -125,20 +129,32 @@ typedef struct b200gs_surfel_fwd {
   float* gaussian_weights; /* [P], must be zero-filled by the caller          */
   int exact_lists;         /* instance-list mode of this call, see above      */
   int cull_audit;          /* != 0: audit pass (test infrastructure), see above */
+  int depth_slices;        /* culled emission only.  0: automatic; 1: one slice (no occlusion-aware binning);
+                            * n <= B200GS_MAX_SLICES: at most n depth slices -- see b200gs_surfel_forward_stage1 */
+  float slice_frac[7];     /* with depth_slices = n > 1 and slice_frac[0] > 0: slice k ends where the cumulated instance
+                            * count reaches slice_frac[k] * num_rendered (ascending, < 1; n - 1 values); otherwise the
+                            * library's schedule (0.05, 0.25)                                                        */
 } b200gs_surfel_fwd;
 
 size_t b200gs_surfel_geom_bytes(int P);
 size_t b200gs_surfel_image_bytes(int width, int height);
 size_t b200gs_binning_bytes(int num_rendered);
 
-/* Stage 1: preprocess + tiles_touched prefix sum.  Writes the total number of
- * (Gaussian,tile) instances to *num_rendered (host memory) and returns after
- * the stream has drained -- the same single host sync the reference has at
- * rasterizer_impl.cu:285-286.  Needs geom + img only.                        */
-int b200gs_surfel_forward_stage1(const b200gs_surfel_fwd* a, int* num_rendered, void* stream);
-/* Stage 2: duplicate-with-keys, 64-bit tile|depth sort, tile ranges, per-tile
- * compositing.  Needs binning sized for num_rendered.  Asynchronous.         */
-int b200gs_surfel_forward_stage2(const b200gs_surfel_fwd* a, int num_rendered, void* stream);
+/* Stage 1: preprocess, reachable-tile counts, depth order, prefix sum, slice plan.  Writes the plan of the forward
+ * to plan[0 .. B200GS_PLAN_INTS) (host memory) and returns after the stream has drained -- the same single host
+ * sync the reference has at rasterizer_impl.cu:285-286.  plan[0] = num_rendered (the total number of
+ * (Gaussian, tile) instances: size `binning` for it), plan[1] = S, the number of depth slices, then the first
+ * Gaussian (in depth order) and the first instance of every slice.  Needs geom + img only.
+ * Depth slices (culled emission): the instance list is built and composited front to back in S pieces; tiles whose
+ * pixels have all reached the reference's T < 1e-4 stop (forward.cu:430-434) receive no instances from later pieces,
+ * which are then not emitted, sorted or tested at all.  The blending order within a tile is unchanged, so the
+ * images, radii, weights and gradients are the same bits as with one slice.                                       */
+#define B200GS_MAX_SLICES 8
+#define B200GS_PLAN_INTS 24
+int b200gs_surfel_forward_stage1(const b200gs_surfel_fwd* a, int* plan, void* stream);
+/* Stage 2: per slice duplicate-with-keys, tile sort, tile ranges, block masks, per-tile compositing.  `plan` as
+ * written by stage 1; needs binning sized for plan[0].  Asynchronous.         */
+int b200gs_surfel_forward_stage2(const b200gs_surfel_fwd* a, const int* plan, void* stream);
 
 /* Backward; mirrors CudaRasterizer::Rasterizer::backward
  * (S/cuda_rasterizer/rasterizer_impl.cu:358-466).  All dL_d* outputs must be
@@ -205,6 +221,11 @@ int b200gs_inspect_binning(const void* binning, int num_rendered, const float* d
 int b200gs_surfel_inspect_image(const void* img, int width, int height,
                                 float* accum_alpha /*[3,N]*/, uint32_t* n_contrib /*[2,N]*/,
                                 uint32_t* ranges /*[T,2]*/, void* stream);
+
+/* Depth-slice bookkeeping of the last forward that used this img scratch (meaningful when it had more than one
+ * slice): tile_done [tiles] = 1 where every pixel of the tile saturated before the last slice; live [1] = tiles
+ * that did not.  Either may be NULL.                                                                          */
+int b200gs_surfel_inspect_tiles(const void* img, int width, int height, uint8_t* tile_done, uint32_t* live, void* stream);
 
 /* ------------------------------------------------------------------------ */
 /* 3DGS (EWA) rasterizer with normal / reflection-strength / inverse-depth channels.

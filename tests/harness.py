@@ -21,6 +21,7 @@ for p in (ROOT, PKG_PY):
 import contextlib
 
 
+_SLICES = [0]        # depth slices the drivers pass (0: the library's automatic choice)
 _EXACT = [False]     # list mode the drivers below pass to THIS library's `_C` calls (a per-call keyword there)
 
 
@@ -74,7 +75,8 @@ def to_dev(d, device="cuda"):
 
 
 def surfel_forward(Cmod, scene, cam, bg=(0.0, 0.0, 0.0), sh_degree=3, mask=None, scale_modifier=1.0,
-                   colors_precomp=None, transMat_precomp=None, debug=False, prefiltered=False, exact=None, cull_audit=False):
+                   colors_precomp=None, transMat_precomp=None, debug=False, prefiltered=False, exact=None, cull_audit=False,
+                   depth_slices=None, slice_fractions=None):
     """scene/cam: dicts of CUDA tensors (see scenes.py).  Returns the 9-tuple as a dict."""
     dev = scene["means3D"].device
     e = torch.empty((0,), dtype=torch.float32, device=dev)
@@ -85,7 +87,8 @@ def surfel_forward(Cmod, scene, cam, bg=(0.0, 0.0, 0.0), sh_degree=3, mask=None,
     use_sh = colors_precomp is None
     kw = {}
     if _is_new(Cmod):
-        kw = dict(exact_lists=_EXACT[0] if exact is None else bool(exact), cull_audit=cull_audit)
+        kw = dict(exact_lists=_EXACT[0] if exact is None else bool(exact), cull_audit=cull_audit,
+                  depth_slices=_SLICES[0] if depth_slices is None else depth_slices, slice_fractions=slice_fractions)
     out = Cmod.rasterize_gaussians(
         bgt, scene["means3D"], mask, e if use_sh else colors_precomp, scene["refl"], scene["opacities"],
         e if transMat_precomp is not None else scene["scales"], e if transMat_precomp is not None else scene["rotations"],
