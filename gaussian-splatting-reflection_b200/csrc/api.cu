@@ -70,6 +70,10 @@ SurfelGeom SurfelGeom::carve(void* base, size_t P, size_t* bytes) {
   g.scan_state = c.take<uint32_t>(scan_state_words((int)P));
   g.flags = c.take<int>(4);
   g.plan = c.take<int>(PLAN_INTS);
+  g.rows.capacity = (uint32_t)(ROWS_PER_GAUSSIAN * P + (1u << 20));
+  g.rows.rows = c.take<uint4>(g.rows.capacity);
+  g.rows.base = c.take<uint32_t>(P);
+  g.rows.cursor = g.flags ? reinterpret_cast<uint32_t*>(g.flags + 1) : nullptr;
   if (bytes) *bytes = c.used + 128;
   return g;
 }
@@ -197,7 +201,7 @@ int b200gs_surfel_forward_stage1(const b200gs_surfel_fwd* a, int* plan, void* st
   const bool exact = a->exact_lists != 0;
   const uint32_t* counts = g.tiles_touched;
   if (!exact) {
-    rc = surfel_count_kept(a->P, g.tiles_touched, g.rects, g.cull, g.tiles_kept, s, a->debug != 0);
+    rc = surfel_count_kept(a->P, g.tiles_touched, g.rects, g.cull, g.tiles_kept, &g.rows, s, a->debug != 0);
     if (rc) return rc;
     counts = g.tiles_kept;
   }
@@ -232,7 +236,7 @@ int b200gs_surfel_forward_stage2(const b200gs_surfel_fwd* a, const int* plan, vo
   Binning b = Binning::carve(R > 0 ? align128(a->binning) : nullptr, R, nullptr);
   BinJob j{};
   j.order = g.order.vals_a; j.rects = g.rects; j.offsets = g.point_offsets;
-  j.cull = a->exact_lists != 0 ? nullptr : g.cull; j.cull_for_hits = g.cull;
+  j.cull = a->exact_lists != 0 ? nullptr : g.cull; j.cull_for_hits = g.cull; j.rows = &g.rows;
   j.P = a->P; j.W = a->width; j.H = a->height; j.R = R;
   j.slices = S; j.g = plan + PLAN_G; j.off = plan + PLAN_OFF;
   j.ranges = im.ranges; j.cranges = im.cranges; j.tile_done = im.tile_done; j.live = im.live;

@@ -242,12 +242,16 @@ struct EmitHist {
   uint32_t mask0, mask1;
 };
 
+constexpr int SMALL_RECT_TILES = 32;
+
 struct KeptArgs {
   int P, gx;
   int g0, g1;                     // emit: the Gaussians [g0, g1) of the depth order (one depth slice)
+  int lpg_shift;                  // emit: log2 of the lanes per Gaussian (0: 32 Gaussians per warp ... 5: one per warp)
   const uint8_t* done;            // emit, slices > 0: tiles whose pixels all saturated in an earlier slice ...
   uint32_t sentinel;              // ... get this key instead (sorts behind every tile, never read)
   const uint32_t* live;           // emit: number of unfinished tiles; 0 -> this slice is not needed at all
+  RowCache rows;                  // rows.base == nullptr: no cache
   const uint32_t* tiles_touched;  // count: [P] in id order
   const uint32_t* order;          // emit: ids in depth order
   const uint32_t* offsets;        // emit: inclusive scan of the kept counts, depth order
@@ -266,16 +270,22 @@ __global__ void __launch_bounds__(256) kept_rows_kernel(const KeptArgs a) {
   __shared__ uint32_t s_pref[256];       // inclusive prefix of rows within the warp
   __shared__ uint32_t s_run[256];        // count: kept tiles so far; emit: next free slot
   __shared__ uint2 s_ie[EMIT ? 256 : 1]; // emit: id, end of the Gaussian's slots
+  __shared__ uint32_t s_rb[256];         // first cached row of the Gaussian (ROW_NONE: compute)
   __shared__ uint32_t s_h[2][EMIT ? RS_RADIX : 1];
   const int t = threadIdx.x, lane = t & 31, wb = t & ~31;
-  const int i = (EMIT ? a.g0 : 0) + blockIdx.x * 256 + t;
+  // The front depth slices hold few Gaussians with very many rows each (splats close to the camera): with 32 of them
+  // per warp only a handful of SMs would work, one row stream after the other.  There the Gaussians are spread out,
+  // one per 2^lpg_shift lanes; the lanes in between own nothing and only help with the rows and tiles.
+  const int gt = blockIdx.x * 256 + t;
+  const bool owner = !EMIT || (gt & ((1 << a.lpg_shift) - 1)) == 0;
+  const int i = EMIT ? a.g0 + (gt >> a.lpg_shift) : gt;
   if (EMIT && a.live != nullptr && *a.live == 0u) return;
   const bool hist = EMIT && a.eh.hist != nullptr;
   if (hist) { s_h[0][t] = 0u; s_h[1][t] = 0u; __syncthreads(); }
 
   uint32_t id = 0, off = 0, end = 0;
   bool vis = false;
-  if (i < (EMIT ? a.g1 : a.P)) {
+  if (owner && i < (EMIT ? a.g1 : a.P)) {
     if (EMIT) {
       off = i == 0 ? 0u : a.offsets[i - 1]; end = a.offsets[i];
       vis = end > off;
@@ -286,14 +296,31 @@ __global__ void __launch_bounds__(256) kept_rows_kernel(const KeptArgs a) {
     }
   }
   int rows = 0;
+  const bool cached = a.rows.base != nullptr;
+  uint32_t rb = ROW_NONE;
+  uint32_t run0 = off;                    // 0 when counting
   if (vis) {
     const uint2 rc = a.rects[id];
     const int x0 = rc.x & 0xffff, x1 = rc.x >> 16, y0 = rc.y & 0xffff, y1 = rc.y >> 16;
-    rowcull_init(a.cull[id], s_rc[t]);
-    rows = (s_rc[t].mode == 0) ? 0 : (y1 - y0);
+    // Small rects keep all their tiles: the row test costs ~1300 fp64-heavy instructions per Gaussian and takes an
+    // ordinary splat of 5 x 5 tiles down to ~19; the emitted list only has to be a superset of the reachable
+    // instances (tile_hits_kernel drops the rest) and, with depth slices, the far part of it is never emitted anyway.
+    // What the test is for are the splats that cross the camera plane and would land in every tile of the screen.
+    if ((x1 - x0) * (y1 - y0) <= SMALL_RECT_TILES) {
+      if (EMIT) { s_rc[t].mode = 1; rows = y1 - y0; }
+      else run0 = (uint32_t)((x1 - x0) * (y1 - y0));
+    } else {
+      if (EMIT && cached) rb = a.rows.base[id];
+      if (rb == ROW_NONE) {                    // count, or a Gaussian whose rows did not fit the cache
+        rowcull_init(a.cull[id], s_rc[t]);
+        rows = (s_rc[t].mode == 0) ? 0 : (y1 - y0);
+      } else {
+        rows = rb == ROW_EMPTY ? 0 : (y1 - y0);
+      }
+    }
     s_box[t] = make_int4(x0, x1, y0, rows);
   }
-  s_run[t] = off;                         // 0 when counting
+  s_run[t] = run0;
   if (EMIT) s_ie[t] = make_uint2(id, end);
   uint32_t pref = (uint32_t)rows;
 #pragma unroll
@@ -303,6 +330,15 @@ __global__ void __launch_bounds__(256) kept_rows_kernel(const KeptArgs a) {
   }
   s_pref[t] = pref;
   const uint32_t total = __shfl_sync(0xffffffffu, pref, 31);
+  // row cache: the count hands out `total` consecutive rows to the warp and notes where each Gaussian's rows start
+  if (cached && !EMIT) {
+    uint32_t wbase = 0u;
+    if (lane == 0 && total) wbase = atomicAdd(a.rows.cursor, total);
+    wbase = __shfl_sync(0xffffffffu, wbase, 0);
+    if (total && wbase + total <= a.rows.capacity) rb = wbase + (pref - (uint32_t)rows);
+    if (i < a.P) a.rows.base[i] = rows ? rb : ROW_EMPTY;
+  }
+  s_rb[t] = rows ? rb : ROW_NONE;
   __syncwarp();
 
   auto put = [&](uint32_t o, uint32_t key, uint32_t v) {
@@ -322,9 +358,22 @@ __global__ void __launch_bounds__(256) kept_rows_kernel(const KeptArgs a) {
       for (int st = 16; st > 0; st >>= 1)
         if (s_pref[wb + g + st - 1] <= k) g += st;
       const int4 bx = s_box[wb + g];
-      y = bx.z + (int)(k - (s_pref[wb + g] - (uint32_t)bx.w));
-      rowcull_ranges(s_rc[wb + g], y, bx.x, bx.y, a1, b1, a2, b2, d0, d1);
-      n = (uint32_t)rowcull_count(a1, b1, a2, b2, d0, d1);
+      const uint32_t r = k - (s_pref[wb + g] - (uint32_t)bx.w);         // row of the Gaussian's rect
+      y = bx.z + (int)r;
+      const uint32_t grb = s_rb[wb + g];
+      if (EMIT && grb != ROW_NONE) {                                    // the count pass already did this row
+        const uint4 c = a.rows.rows[grb + r];
+        a1 = (int)(c.x & 0xffffu); b1 = (int)(c.x >> 16) - 1; a2 = (int)(c.y & 0xffffu); b2 = (int)(c.y >> 16) - 1;
+        d0 = (int)(c.z & 0xffffu); d1 = (int)(c.z >> 16) - 1;
+        n = c.w;
+      } else {
+        rowcull_ranges(s_rc[wb + g], y, bx.x, bx.y, a1, b1, a2, b2, d0, d1);
+        n = (uint32_t)rowcull_count(a1, b1, a2, b2, d0, d1);
+        if (!EMIT && grb != ROW_NONE)
+          a.rows.rows[grb + r] = make_uint4(((uint32_t)(a1 & 0xffff)) | ((uint32_t)((b1 + 1) & 0xffff) << 16),
+                                            ((uint32_t)(a2 & 0xffff)) | ((uint32_t)((b2 + 1) & 0xffff) << 16),
+                                            ((uint32_t)(d0 & 0xffff)) | ((uint32_t)((d1 + 1) & 0xffff) << 16), n);
+      }
     }
     uint32_t o = 0;
     if (n) o = atomicAdd(&s_run[wb + g], n);
@@ -398,11 +447,12 @@ __global__ void __launch_bounds__(256) kept_rows_kernel(const KeptArgs a) {
 }
 
 int surfel_count_kept(int P, const uint32_t* tiles_touched, const uint2* rects, const CullRec* cull, uint32_t* kept,
-                      cudaStream_t s, bool debug) {
+                      const RowCache* rows, cudaStream_t s, bool debug) {
   if (P <= 0) return B200GS_OK;
   StageScope _t(ST_COUNT_KEPT, s);
   KeptArgs a{};
   a.P = P; a.tiles_touched = tiles_touched; a.rects = rects; a.cull = cull; a.kept = kept;
+  if (rows) a.rows = *rows;
   kept_rows_kernel<false><<<(P + 255) / 256, 256, 0, s>>>(a);
   B200GS_LAUNCHED("kept_rows_kernel<count>", debug, s);
   return B200GS_OK;
@@ -885,9 +935,13 @@ int bin_slice(const BinJob& j, int k, const Binning& b, size_t& zcursor, cudaStr
       ea.g0 = j.g[k]; ea.g1 = j.g[k + 1];
       ea.done = sliced && k > 0 ? j.tile_done : nullptr; ea.sentinel = (uint32_t)tiles; ea.live = live;
       ea.keys = ka; ea.vals = va; ea.eh = eh;     // slots are absolute positions (offsets is the global prefix sum)
+      if (j.rows) ea.rows = *j.rows;
       const int ng = ea.g1 - ea.g0;
       if (ng > 0) {
-        kept_rows_kernel<true><<<(ng + 255) / 256, 256, 0, s>>>(ea);
+        const long long per = (long long)n / ng;                 // instances per Gaussian of this slice
+        ea.lpg_shift = per >= 64 ? 5 : (per >= 24 ? 3 : 0);
+        const long long threads = (long long)ng << ea.lpg_shift;
+        kept_rows_kernel<true><<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(ea);
         B200GS_LAUNCHED("kept_rows_kernel<emit>", j.debug, s);
       }
     } else {

@@ -119,6 +119,20 @@ struct DepthOrder {
   static DepthOrder carve(Carver& c, size_t P);
 };
 
+// Row cache: the count pass stores, per (Gaussian, tile row of its rect), the reachable column ranges it computed
+// (cull_rows.cuh, fp64) so that the emission of the same forward reads 16 B per row instead of repeating the
+// arithmetic.  Rows of the 32 Gaussians of a warp are allocated with one atomicAdd on `cursor`; a Gaussian whose rows
+// did not fit (capacity is a fixed multiple of P) is marked and recomputed by the emission.
+struct RowCache {
+  uint4* rows;            // [capacity] {a1 | (b1+1) << 16, a2 | (b2+1) << 16, d0 | (d1+1) << 16, tiles in the row}
+  uint32_t* base;         // [P] first row of Gaussian id, or ROW_NONE / ROW_EMPTY
+  uint32_t* cursor;       // rows handed out so far (zeroed with the flags by the preprocess)
+  uint32_t capacity;
+};
+constexpr uint32_t ROW_NONE = 0xffffffffu;    // not cached: compute
+constexpr uint32_t ROW_EMPTY = 0xfffffffeu;   // the Gaussian reaches no tile at all
+constexpr int ROWS_PER_GAUSSIAN = 4;   // capacity = ROWS_PER_GAUSSIAN * P + 2^20
+
 struct SurfelGeom {
   float* depths;            // [P]
   uint32_t* tiles_touched;  // [P] the reference's count (rect area)
@@ -132,6 +146,7 @@ struct SurfelGeom {
   uint32_t* scan_state;     // decoupled look-back tile states
   int* flags;               // [4] error flags (prefiltered violation, ...)
   int* plan;                // [PLAN_INTS] the slice plan of this forward (device copy; the backward reads S from it)
+  RowCache rows;            // reachable tile columns per (Gaussian, tile row): written by the count, read by the emission
   static SurfelGeom carve(void* base, size_t P, size_t* bytes);
 };
 
@@ -170,6 +185,7 @@ struct BinJob {
   const uint32_t* offsets;        // inclusive prefix sum of the per-Gaussian instance counts, depth order
   const CullRec* cull;            // culled emission: the cull records; nullptr: the reference's full lists
   const CullRec* cull_for_hits;   // the cull records (block masks are computed in both modes)
+  const RowCache* rows;           // culled emission: the count pass's per-row ranges, or nullptr
   int P, W, H, R;
   int slices;
   const int* g;                   // [slices+1] host
@@ -281,7 +297,7 @@ int inclusive_scan_u32(const uint32_t* in, uint32_t* out, int n, uint32_t* state
 int depth_order_and_scan(const float* depths, const uint32_t* tiles_touched, int P, const DepthOrder& o,
                          uint32_t* point_offsets, uint32_t* scan_state, cudaStream_t s, bool debug);
 int surfel_count_kept(int P, const uint32_t* tiles_touched, const uint2* rects, const CullRec* cull, uint32_t* kept,
-                      cudaStream_t s, bool debug);
+                      const RowCache* rows, cudaStream_t s, bool debug);
 size_t tile_hits_state_words(size_t R);
 // slice k of S (S == 1: the whole list in one go, no state carried)
 int surfel_composite_forward(const b200gs_surfel_fwd& a, const SurfelGeom& g, const SurfelImage& im,

@@ -116,7 +116,7 @@ int b200gs_gauss_forward_stage1(const b200gs_gauss_fwd* a, int* num_rendered, vo
   if (rc) return rc;
   const uint32_t* counts = g.tiles_touched;
   if (a->exact_lists == 0) {   // culled emission (include/b200gs.h: exact_lists)
-    rc = surfel_count_kept(a->P, g.tiles_touched, g.rects, g.cull, g.tiles_kept, s, a->debug != 0);
+    rc = surfel_count_kept(a->P, g.tiles_touched, g.rects, g.cull, g.tiles_kept, nullptr, s, a->debug != 0);
     if (rc) return rc;
     counts = g.tiles_kept;
   }
@@ -144,7 +144,7 @@ int b200gs_gauss_forward_stage2(const b200gs_gauss_fwd* a, int R, void* stream) 
   BinJob j{};
   const int g01[2] = {0, a->P}, off01[2] = {0, R};           // one depth slice
   j.order = g.order.vals_a; j.rects = g.rects; j.offsets = g.point_offsets;
-  j.cull = a->exact_lists != 0 ? nullptr : g.cull; j.cull_for_hits = g.cull;
+  j.cull = a->exact_lists != 0 ? nullptr : g.cull; j.cull_for_hits = g.cull; j.rows = nullptr;
   j.P = a->P; j.W = a->width; j.H = a->height; j.R = R;
   j.slices = 1; j.g = g01; j.off = off01;
   j.ranges = im.ranges; j.cranges = im.cranges; j.tile_done = nullptr; j.live = nullptr;

@@ -63,6 +63,16 @@ __global__ void __launch_bounds__(256, B200GS_PREBWD_CTAS) surfel_preprocess_bwd
       g[4 * k] = v.x; g[4 * k + 1] = v.y; g[4 * k + 2] = v.z; g[4 * k + 3] = v.w;
     }
   }
+  // A visible Gaussian no pixel blended (occluded, or below the 1/255 cut everywhere) has an all-zero accumulator
+  // row: every gradient this kernel would derive from it is an exact zero, which the zero-filled outputs (or, when
+  // accumulating, the sums so far) already hold.  On scenes with occlusion that is most visible Gaussians, and it
+  // saves their input reads (237 B) and gradient rows (248 B).
+  {
+    bool any = false;
+#pragma unroll
+    for (int k = 0; k < ACC_STRIDE; ++k) any = any || (g[k] != 0.0f);
+    if (!any) return;
+  }
   // plain per-Gaussian sums straight through
   a.dL_dopacity[idx] = ACC ? a.dL_dopacity[idx] + g[11] : g[11];
   a.dL_dcolors[3 * idx + 0] = g[12]; a.dL_dcolors[3 * idx + 1] = g[13]; a.dL_dcolors[3 * idx + 2] = g[14];
