@@ -80,7 +80,7 @@ __global__ void __launch_bounds__(AR_THREADS) p2p_allreduce_kernel(const PeerPtr
 using namespace b200gs;
 
 extern "C" int b200gs_peer_allreduce_f32(void* multicast_ptr, void* const* peer_ptrs, int rank, int world, size_t n_floats,
-                                         void* stream) {
+                                         int ctas, void* stream) {
   if (world < 1 || world > AR_MAX_WORLD || rank < 0 || rank >= world) { set_error("peer_allreduce: bad rank %d / world %d", rank, world); return B200GS_EINVAL; }
   if (world == 1 || n_floats == 0) return B200GS_OK;
   if (n_floats % 4 != 0) { set_error("peer_allreduce: the buffer must hold a multiple of 4 floats (pad it)"); return B200GS_EINVAL; }
@@ -95,7 +95,8 @@ extern "C" int b200gs_peer_allreduce_f32(void* multicast_ptr, void* const* peer_
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   size_t want = (end - begin + AR_THREADS - 1) / AR_THREADS;
-  const int blocks = (int)(want < (size_t)sms * 4 ? want : (size_t)sms * 4);   // 4 CTAs of 512 threads per SM: every SM keeps 8192 B x 4 in flight
+  const size_t cap = ctas > 0 ? (size_t)ctas : (size_t)sms * 4;
+  const int blocks = (int)(want < cap ? want : cap);
   if (multicast_ptr) {
     if (reinterpret_cast<uintptr_t>(multicast_ptr) & 15u) { set_error("peer_allreduce: multicast address not 16-B aligned"); return B200GS_EINVAL; }
     nvls_allreduce_kernel<<<blocks, AR_THREADS, 0, s>>>(reinterpret_cast<float4*>(multicast_ptr), begin, end);

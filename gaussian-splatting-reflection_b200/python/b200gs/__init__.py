@@ -192,7 +192,7 @@ adam_step = _sig("b200gs_adam_step", _i, C.POINTER(Adam), _p)
 densify_stats = _sig("b200gs_densify_stats", _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p)
 
 
-peer_allreduce_f32 = _sig("b200gs_peer_allreduce_f32", _i, _p, C.POINTER(_p), _i, _i, _sz, _p)
+peer_allreduce_f32 = _sig("b200gs_peer_allreduce_f32", _i, _p, C.POINTER(_p), _i, _i, _sz, _i, _p)
 
 
 ssim_forward = _sig("b200gs_ssim_forward", _i, _f, _f, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p)

@@ -62,8 +62,15 @@ class GradArena:
         # where this tensor sits inside the handle's buffer (the multicast mapping covers the same range)
         self._offset = buf.data_ptr() - int(self._hdl.buffer_ptrs[self._rank])
         self._mc = int(self._hdl.multicast_ptr) + self._offset if int(self._hdl.multicast_ptr) else 0
+        # Measured on 8 x B200 / NVSwitch, 708 MB (tests/run_dp_check.py, profiles/r2i_dp_check_n*.json): two ranks --
+        # peer-to-peer loads / stores 1.09 ms, ncclAllReduce 1.31, multimem 1.75 (nothing for the switch to reduce);
+        # eight ranks -- multimem 1.60 ms with 16-64 CTAs (more CTAs only contend in the switch: 1.70-1.75),
+        # ncclAllReduce 1.76, peer-to-peer 2.04.
+        if self._world == 2 and self._world in (2, 4, 8):
+            self._mc = 0
+        self.ctas = 32 if self._mc else 0
         self.algo = ("own kernel: NVLS multimem.ld_reduce + multimem.st over the multicast mapping" if self._mc
-                     else "own kernel: peer-to-peer loads / stores over NVLink (no multicast object on this system)")
+                     else "own kernel: peer-to-peer loads / stores over NVLink")
 
     @property
     def floats_per_gaussian(self):
@@ -130,7 +137,7 @@ class GradArena:
             peers = (C.c_void_p * self._world)(*[int(p) + self._offset for p in h.buffer_ptrs])
             h.barrier(channel=0)
             b200gs.check(b200gs.peer_allreduce_f32(self._mc or None, peers, self._rank, self._world, self._buf.numel(),
-                                                   torch.cuda.current_stream().cuda_stream))
+                                                   int(getattr(self, "ctas", 0)), torch.cuda.current_stream().cuda_stream))
             h.barrier(channel=1)
             return None
         return dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group, async_op=async_op)

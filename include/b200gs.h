@@ -375,10 +375,11 @@ int b200gs_densify_stats(int P, const int* radii, const float* dL_dmeans2D, cons
  *     multimem.ld_reduce and broadcasts it with multimem.st -- the adds happen in the switch;
  *   multicast_ptr == NULL: peer_ptrs (HOST array of `world` device pointers, entry i = rank i's copy as mapped in
  *     this process) are read and written directly; world in {2, 4, 8}.
- * n_floats must be a multiple of 4 and the addresses 16-B aligned.  The caller orders the ranks: a device-side
- * barrier over all ranks on `stream` before this call (all arenas complete) and one after it (all slices landed). */
+ * n_floats must be a multiple of 4 and the addresses 16-B aligned.  `ctas`: thread blocks to launch (0: the library's
+ * choice).  The caller orders the ranks: a device-side barrier over all ranks on `stream` before this call (all
+ * arenas complete) and one after it (all slices landed). */
 int b200gs_peer_allreduce_f32(void* multicast_ptr, void* const* peer_ptrs, int rank, int world, size_t n_floats,
-                              void* stream);
+                              int ctas, void* stream);
 
 /* ------------------------------------------------------------------------ */
 /* SSIM image loss ("next" row 3): replaces fusedssim / fusedssim_backward of
