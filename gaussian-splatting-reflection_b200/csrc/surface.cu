@@ -19,7 +19,12 @@ struct SurfCam {
   float ratio;     // pipe.depth_ratio
 };
 
-__device__ __forceinline__ float nan_to_zero(float v) { return (isnan(v) || isinf(v)) ? 0.0f : v; }
+// torch.nan_to_num(x, 0, 0) as the renderer calls it (gaussian_renderer/__init__.py:152,:158: nan=0, posinf=0, neginf
+// left at its default): NaN and +inf become 0, -inf becomes the lowest finite float.
+__device__ __forceinline__ float nan_to_zero(float v) {
+  if (isnan(v) || v == __int_as_float(0x7f800000)) return 0.0f;
+  return v == __int_as_float(0xff800000) ? -3.402823466e+38f : v;
+}
 
 __device__ __forceinline__ float surf_depth_of(const float* __restrict__ allmap, size_t N, size_t n, float ratio) {
   const float D = allmap[n], alpha = allmap[N + n], med = allmap[5 * N + n];

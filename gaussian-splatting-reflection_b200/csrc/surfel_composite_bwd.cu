@@ -8,8 +8,13 @@
 // every lane, and sums them over the warp with a 21-shuffle recursive-halving
 // reduce-scatter, so that 19 lanes each own one component and flush the warp's
 // contribution with ONE vector RED.ADD.F32 into a contiguous 80-B accumulator
-// row (ACC_STRIDE floats per Gaussian).  Warps none of whose pixels touch a
-// Gaussian skip the reduction altogether.
+// row (ACC_STRIDE floats per Gaussian).
+//
+// The kernel is bound by instruction issue (ncu: 79-83 % of the issue slots, DRAM 1 %), and a quarter of its
+// instructions per (warp, Gaussian) visit were that reduction plus the per-entry loop overhead
+// (profiles/r2_ncu_summary.md: 84 of 342).  Every thread therefore owns TWO pixels -- a warp covers an 8x8 pixel
+// block, a CTA of four warps the 16x16 tile (surfel_composite.cuh: pair_pixel) -- so one reduction, one RED and one
+// trip through the entry loop serve 64 pixels.
 #include "surfel_composite.cuh"
 
 namespace b200gs {
@@ -33,27 +38,132 @@ struct CompBwdArgs {
   float* acc;                 // [P, ACC_STRIDE]
 };
 
-constexpr int BATCH = 256;
+constexpr int BATCH = PAIR_THREADS;   // threads per CTA = entries staged per batch
 
-// Register allocation bounded for 3 resident CTAs per SM.  Measured on the bench workload (round 1):
-// 2 CTAs (98 registers) 1.87 ms, 3 (77 registers, no spills) 1.63 ms, 4 (64 registers, 48 B of spills) 1.61 ms.
-__global__ void __launch_bounds__(BATCH, 3) surfel_composite_bwd_kernel(const CompBwdArgs a) {
+// Everything the backward keeps per pixel: the forward's final values, the upstream gradients and the recurrences.
+struct PixelBwd {
+  float fx, fy;
+  uint32_t last_contributor, median_contributor;     // last_contributor == 0 for pixels outside the image
+  float T_final, T, final_D, final_D2, final_A;
+  float dpix0, dpix1, dpix2, drefl, ddepth, daccum, dreg, dn0, dn1, dn2, dmedian, bg_dot;
+  float acc_q, last_q, last_dL_dT, last_alpha;
+
+  __device__ __forceinline__ void load(const CompBwdArgs& a, int pxi, int pyi) {
+    const bool inside = pxi < a.W && pyi < a.H;
+    fx = (float)pxi; fy = (float)pyi;
+    const size_t N = (size_t)a.W * a.H;
+    const size_t pix_id = (size_t)a.W * pyi + pxi;
+    T_final = inside ? a.accum[pix_id] : 0.0f;
+    T = T_final;
+    last_contributor = inside ? a.n_contrib[pix_id] : 0u;
+    median_contributor = inside ? a.n_contrib[pix_id + N] : 0u;
+    final_D = inside ? a.accum[pix_id + N] : 0.0f;
+    final_D2 = inside ? a.accum[pix_id + 2 * N] : 0.0f;
+    final_A = 1.0f - T_final;
+    dpix0 = dpix1 = dpix2 = drefl = ddepth = daccum = dreg = dn0 = dn1 = dn2 = dmedian = 0.0f;
+    if (inside) {
+      dpix0 = a.dL_dpix[pix_id]; dpix1 = a.dL_dpix[pix_id + N]; dpix2 = a.dL_dpix[pix_id + 2 * N];
+      drefl = a.dL_drefl ? a.dL_drefl[pix_id] : 0.0f;
+      ddepth = a.dL_dothers[pix_id + 0 * N];
+      daccum = a.dL_dothers[pix_id + 1 * N];
+      dn0 = a.dL_dothers[pix_id + 2 * N]; dn1 = a.dL_dothers[pix_id + 3 * N]; dn2 = a.dL_dothers[pix_id + 4 * N];
+      dmedian = a.dL_dothers[pix_id + 5 * N];
+      dreg = a.dL_dothers[pix_id + 6 * N];
+    }
+    bg_dot = 0.0f;
+    bg_dot += a.bg[0] * dpix0;
+    bg_dot += a.bg[1] * dpix1;
+    bg_dot += a.bg[2] * dpix2;
+    acc_q = last_q = last_dL_dT = last_alpha = 0.0f;
+  }
+
+  // One contributing (pixel, Gaussian) pair: advances the recurrences and ADDS the pair's 19 partials to g.
+  __device__ __forceinline__ void contribute(const SurfelHit& h, const float4& q3, const float4& q4, uint32_t contributor,
+                                             float* g) {
+    const float alpha = h.alpha, G = h.G;
+    // One reciprocal for (1 - alpha) and one for p.z instead of the reference's divisions
+    // (backward.cu:341,:412,:437-438): nothing cancels behind them.
+    const float inv_1ma = __frcp_rn(__fsub_rn(1.0f, alpha));
+    T = T * inv_1ma;
+    const float w = alpha * T;
+    const float om = 1.0f - last_alpha;
+    const float c_d = h.depth;
+    // Colour, reflection strength, depth, alpha and normal (backward.cu:346-364,:392-402) all
+    // enter dL_dalpha as (value - value accumulated behind) * upstream gradient.  The recurrence
+    // is linear, so the nine per-channel recurrences of the reference collapse into ONE on
+    // q = sum_ch value_ch * upstream_ch.
+    const float qv = q4.x * dpix0 + q4.y * dpix1 + q4.z * dpix2 + q3.w * drefl + c_d * ddepth + daccum +
+                     q3.x * dn0 + q3.y * dn1 + q3.z * dn2;
+    acc_q = last_alpha * last_q + om * acc_q;
+    last_q = qv;
+    float dL_dalpha = qv - acc_q;
+    g[12] += w * dpix0; g[13] += w * dpix1; g[14] += w * dpix2;
+    g[15] += w * drefl;
+    g[16] += w * dn0; g[17] += w * dn1; g[18] += w * dn2;
+    // distortion (:366-390).  final_D2 + m^2 final_A - 2 m final_D and m final_A - final_D cancel in fp32, so
+    // m_d and both expressions are written in exactly the rounding shape of the reference build (SASS of
+    // renderCUDA<3>, nvcc 12.9: IEEE -0.2/c_d, +1, *far/(far-near); fma(2m, -D, fma(A, m*m, D2)); fma(A, m, -D)):
+    // with the forward's final_* bit-identical, dL_dweight and the last_dL_dT recurrence are then the reference's
+    // bit for bit, and only T (reciprocal instead of division, nothing cancels there) differs in the last place.
+    const float m_d = ndc_depth(c_d);
+    const float dmd_dd = __fdiv_rn(FAR_N * NEAR_N, __fmul_rn(c_d, __fmul_rn(c_d, FAR_N - NEAR_N)));
+    float dL_dz = 0.0f;
+    if (contributor == median_contributor - 1u) dL_dz = dmedian;
+    const float dL_dweight =
+        __fmul_rn(dreg, __fmaf_rn(__fadd_rn(m_d, m_d), -final_D, __fmaf_rn(final_A, __fmul_rn(m_d, m_d), final_D2)));
+    dL_dalpha += __fsub_rn(dL_dweight, last_dL_dT);
+    last_dL_dT = __fmaf_rn(alpha, dL_dweight, __fmul_rn(last_dL_dT, __fsub_rn(1.0f, alpha)));
+    const float dL_dmd = __fmul_rn(dreg, __fmul_rn(__fadd_rn(w, w), __fmaf_rn(final_A, m_d, -final_D)));
+    dL_dz = __fmaf_rn(dL_dmd, dmd_dd, dL_dz);
+
+    dL_dalpha *= T;
+    last_alpha = alpha;
+    dL_dalpha += (-T_final * inv_1ma) * bg_dot;  // :411-414
+    const float dL_dG = h.opa * dL_dalpha;
+    dL_dz += w * ddepth;
+    if (h.rho3d <= h.rho2d) {  // :423-453
+      const float dsx = dL_dG * -G * h.sx + dL_dz * h.Twx;
+      const float dsy = dL_dG * -G * h.sy + dL_dz * h.Twy;
+      const float dsx_pz = dsx * h.rpz, dsy_pz = dsy * h.rpz;
+      const float dpx = dsx_pz, dpy = dsy_pz, dpz = -(dsx_pz * h.sx + dsy_pz * h.sy);
+      // dL_dk = cross(l, dL_dp), dL_dl = cross(dL_dp, k)
+      const float dkx = h.ly * dpz - h.lz * dpy, dky = h.lz * dpx - h.lx * dpz, dkz = h.lx * dpy - h.ly * dpx;
+      const float dlx = dpy * h.kz - dpz * h.ky, dly = dpz * h.kx - dpx * h.kz, dlz = dpx * h.ky - dpy * h.kx;
+      g[0] -= dkx; g[1] -= dky; g[2] -= dkz;
+      g[3] -= dlx; g[4] -= dly; g[5] -= dlz;
+      g[6] += fx * dkx + fy * dlx + dL_dz * h.sx;
+      g[7] += fx * dky + fy * dly + dL_dz * h.sy;
+      g[8] += fx * dkz + fy * dlz + dL_dz * 1.0f;
+    } else {  // :454-464
+      g[9] += dL_dG * (-G * FILTER_INV_SQUARE * h.dx);
+      g[10] += dL_dG * (-G * FILTER_INV_SQUARE * h.dy);
+      g[6] += h.sx * dL_dz;
+      g[7] += h.sy * dL_dz;
+      g[8] += dL_dz;
+    }
+    g[11] += G * dL_dalpha;  // :467
+  }
+};
+
+// Register allocation bounded for 4 resident CTAs of 128 threads per SM.
+__global__ void __launch_bounds__(BATCH, 4) surfel_composite_bwd_kernel(const CompBwdArgs a) {
   __shared__ SurfelRec s_rec[2][BATCH];
   __shared__ int s_id[2][BATCH];
   __shared__ uint32_t s_pos[2][BATCH];
-  __shared__ uint8_t s_hit[2][BATCH];   // bit w: the entry can reach alpha >= 1/255 in warp w's 8x4 pixel block
-  __shared__ int s_n;                   // live prefix of the tile's compacted list
+  __shared__ uint8_t s_hit[2][BATCH];   // bit b: the entry can reach alpha >= 1/255 in 8x4 pixel block b of the tile
+  __shared__ int s_n;                   // live prefix of the slice's compacted list
+  __shared__ uint32_t s_last[BATCH / 32];
+  __shared__ uint32_t s_tile_last;
 
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const int tile = blockIdx.x;
   const int tile_x = tile % a.gx, tile_y = tile / a.gx;
   int lx, ly;
-  tile_pixel(t, lx, ly);
-  const int pxi = tile_x * TILE_X + lx, pyi = tile_y * TILE_Y + ly;
-  const bool inside = pxi < a.W && pyi < a.H;
-  const float fx = (float)pxi, fy = (float)pyi;
-  const size_t N = (size_t)a.W * a.H;
-  const size_t pix_id = (size_t)a.W * pyi + pxi;
+  pair_pixel(t, lx, ly);
+  PixelBwd px[2];
+  px[0].load(a, tile_x * TILE_X + lx, tile_y * TILE_Y + ly);
+  px[1].load(a, tile_x * TILE_X + lx, tile_y * TILE_Y + ly + 4);
+  const unsigned warp_bits = pair_hit_bits(warp);       // the two 8x4 blocks of this warp's 8x8 pixels
 
   // lane -> accumulator component owned after the reduce-scatter
   const int b16 = (lane >> 4) & 1, b8 = (lane >> 3) & 1, b4 = (lane >> 2) & 1, b2 = (lane >> 1) & 1, b1 = lane & 1;
@@ -61,49 +171,16 @@ __global__ void __launch_bounds__(BATCH, 3) surfel_composite_bwd_kernel(const Co
   const int comp = b16 * 10 + b8 * 5 + loc5;
   const bool comp_valid = loc3 <= 2 && loc5 <= 4 && comp < 19;
 
-  const float T_final = inside ? a.accum[pix_id] : 0.0f;
-  float T = T_final;
-  const uint32_t last_contributor = inside ? a.n_contrib[pix_id] : 0u;
-  const uint32_t median_contributor = inside ? a.n_contrib[pix_id + N] : 0u;
-  const float final_D = inside ? a.accum[pix_id + N] : 0.0f;
-  const float final_D2 = inside ? a.accum[pix_id + 2 * N] : 0.0f;
-  const float final_A = 1.0f - T_final;
-
-  float dpix0 = 0.f, dpix1 = 0.f, dpix2 = 0.f, drefl = 0.f;
-  float ddepth = 0.f, daccum = 0.f, dreg = 0.f, dn0 = 0.f, dn1 = 0.f, dn2 = 0.f, dmedian = 0.f;
-  if (inside) {
-    dpix0 = a.dL_dpix[pix_id]; dpix1 = a.dL_dpix[pix_id + N]; dpix2 = a.dL_dpix[pix_id + 2 * N];
-    drefl = a.dL_drefl ? a.dL_drefl[pix_id] : 0.0f;
-    ddepth = a.dL_dothers[pix_id + 0 * N];
-    daccum = a.dL_dothers[pix_id + 1 * N];
-    dn0 = a.dL_dothers[pix_id + 2 * N]; dn1 = a.dL_dothers[pix_id + 3 * N]; dn2 = a.dL_dothers[pix_id + 4 * N];
-    dmedian = a.dL_dothers[pix_id + 5 * N];
-    dreg = a.dL_dothers[pix_id + 6 * N];
-  }
-  float bg_dot_dpixel = 0.0f;
-  bg_dot_dpixel += a.bg[0] * dpix0;
-  bg_dot_dpixel += a.bg[1] * dpix1;
-  bg_dot_dpixel += a.bg[2] * dpix2;
-
-  float acc_q = 0.f, last_q = 0.f;
-  float last_dL_dT = 0.f, last_alpha = 0.f;
-
-  // The reference leaves the entry loop per thread (`!done`); here `done` pixels
-  // (outside the image) simply never contribute.
-  const bool live = inside;
-
   // Entries at or behind the last contributor of every pixel of the tile are never used
   // (backward.cu:290: `contributor >= last_contributor` -> continue).
-  const uint32_t warp_last = __reduce_max_sync(0xffffffffu, inside ? last_contributor : 0u);
-  __shared__ uint32_t s_last[BATCH / 32];
-  __shared__ uint32_t s_tile_last;
+  const uint32_t warp_last = __reduce_max_sync(0xffffffffu, max(px[0].last_contributor, px[1].last_contributor));
   if (lane == 0) s_last[warp] = warp_last;
   __syncthreads();
   if (t == 0) {
-    uint32_t tile_last = 0;
+    uint32_t tl = 0;
 #pragma unroll
-    for (int w = 0; w < BATCH / 32; ++w) tile_last = max(tile_last, s_last[w]);
-    s_tile_last = tile_last;
+    for (int w = 0; w < BATCH / 32; ++w) tl = max(tl, s_last[w]);
+    s_tile_last = tl;
   }
   __syncthreads();
   const uint32_t tile_last = s_tile_last;
@@ -113,162 +190,98 @@ __global__ void __launch_bounds__(BATCH, 3) surfel_composite_bwd_kernel(const Co
   // the slices back to front, each slice's entries back to front.  The per-pixel recurrences simply carry on.
   const int S = a.plan[1];
   for (int sl = S - 1; sl >= 0; --sl) {
-  const uint32_t base = sl == 0 ? 0u : a.tile_base[(size_t)sl * a.tiles + tile];     // list position of the slice's first entry
-  if (base >= tile_last) continue;
-  const uint2 range = a.ranges[(size_t)sl * (a.tiles + 1) + tile];
-  if (range.y == range.x) continue;
-  const uint32_t* pl = a.point_list + range.x;
-  const uint8_t* ph = a.hit + range.x;
-  const uint32_t* pp = a.list_pos + range.x;
-  // list positions ascend, so the live part is a prefix of the slice's compacted list; find its length by bisection
-  __syncthreads();                                  // everyone has left the previous slice's shared buffers
-  if (t == 0) {
-    const uint32_t lim = tile_last - base;
-    int lo = 0, hi = (int)(range.y - range.x);     // first index with pos >= lim
-    while (lo < hi) {
-      const int mid = (lo + hi) >> 1;
-      if (pp[mid] < lim) lo = mid + 1; else hi = mid;
+    const uint32_t base = sl == 0 ? 0u : a.tile_base[(size_t)sl * a.tiles + tile];   // list position of the slice's first entry
+    if (base >= tile_last) continue;
+    const uint2 range = a.ranges[(size_t)sl * (a.tiles + 1) + tile];
+    if (range.y == range.x) continue;
+    const uint32_t* pl = a.point_list + range.x;
+    const uint8_t* ph = a.hit + range.x;
+    const uint32_t* pp = a.list_pos + range.x;
+    // list positions ascend, so the live part is a prefix of the slice's compacted list; find its length by bisection
+    __syncthreads();                                  // everyone has left the previous slice's shared buffers
+    if (t == 0) {
+      const uint32_t lim = tile_last - base;
+      int lo = 0, hi = (int)(range.y - range.x);     // first index with pos >= lim
+      while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (pp[mid] < lim) lo = mid + 1; else hi = mid;
+      }
+      s_n = lo;
     }
-    s_n = lo;
-  }
-  __syncthreads();
-  const int n = s_n;
-  const int rounds = (n + BATCH - 1) / BATCH;
-  if (n == 0) continue;
-
-  unsigned hit_cur = 0u, hit_next = 0u;
-  uint32_t pos_next = 0u;
-  auto stage = [&](int buf, int id) {
-    hit_cur = hit_next;
-    if (id >= 0) {
-      s_pos[buf][t] = pos_next;
-      const SurfelRec* g = a.rec + id;
-      SurfelRec* d = &s_rec[buf][t];
-#pragma unroll
-      for (int k = 0; k < 5; ++k) cp_async16(&d->q[k], &g->q[k]);
-      s_id[buf][t] = id;
-    }
-    cp_async_commit();
-  };
-  int id_next = -1;
-  if (t < n) { id_next = (int)pl[n - 1 - t]; hit_next = ph[n - 1 - t]; pos_next = pp[n - 1 - t]; }
-  stage(0, id_next);
-  id_next = -1; hit_next = 0u;
-  if (BATCH + t < n) { const int q = n - 1 - (BATCH + t); id_next = (int)pl[q]; hit_next = ph[q]; pos_next = pp[q]; }
-
-  // Warps whose pixels all have last_contributor == 0 have nothing to do, but they
-  // still take part in the staging and barriers.
-
-  for (int i = 0; i < rounds; ++i) {
-    cp_async_wait_all();
-    s_hit[i & 1][t] = (uint8_t)hit_cur;
     __syncthreads();
-    if (i + 1 < rounds) {
-      stage((i + 1) & 1, id_next);
-      const int nx = (i + 2) * BATCH + t;
-      id_next = -1; hit_next = 0u;
-      if (nx < n) { const int q = n - 1 - nx; id_next = (int)pl[q]; hit_next = ph[q]; pos_next = pp[q]; }
-    }
-    const int buf = i & 1;
-    const int count = min(BATCH, n - i * BATCH);
-    const SurfelRec* rb = s_rec[buf];
-#pragma unroll 1
-    for (int r = 0; r < (count + 31) >> 5; ++r) {
-      // entries of other warp blocks, and entries behind every pixel's last contributor, are skipped
-      const int e = r * 32 + lane;
-      unsigned m = __ballot_sync(0xffffffffu, e < count && ((s_hit[buf][e] >> warp) & 1u) && base + s_pos[buf][e] < warp_last);
-      while (m) {
-      const int j = r * 32 + __ffs(m) - 1;
-      m &= m - 1;
-      const uint32_t contributor = base + s_pos[buf][j];   // 0-based position in the tile's full list
-      const float4 q0 = rb[j].q[0], q1 = rb[j].q[1], q2 = rb[j].q[2];
-      SurfelHit h;
-      bool c = live && contributor < last_contributor;
-      c = surfel_eval<true>(q0, q1, q2, fx, fy, h) && c;
-      if (!__any_sync(0xffffffffu, c)) continue;   // next set bit of m
+    const int n = s_n;
+    const int rounds = (n + BATCH - 1) / BATCH;
+    if (n == 0) continue;
 
-      float g[20];
+    unsigned hit_cur = 0u, hit_next = 0u;
+    uint32_t pos_next = 0u;
+    auto stage = [&](int buf, int id) {
+      hit_cur = hit_next;
+      if (id >= 0) {
+        s_pos[buf][t] = pos_next;
+        const SurfelRec* g = a.rec + id;
+        SurfelRec* d = &s_rec[buf][t];
 #pragma unroll
-      for (int k = 0; k < 20; ++k) g[k] = 0.0f;
-      if (c) {
-        const float4 q3 = rb[j].q[3], q4 = rb[j].q[4];
-        const float alpha = h.alpha, G = h.G;
-        // One reciprocal for (1 - alpha) and one for p.z instead of the reference's divisions
-        // (backward.cu:341,:412,:437-438): nothing cancels behind them.
-        const float inv_1ma = __frcp_rn(__fsub_rn(1.0f, alpha));
-        T = T * inv_1ma;
-        const float w = alpha * T;
-        const float om = 1.0f - last_alpha;
-        const float c_d = h.depth;
-        // Colour, reflection strength, depth, alpha and normal (backward.cu:346-364,:392-402) all
-        // enter dL_dalpha as (value - value accumulated behind) * upstream gradient.  The recurrence
-        // is linear, so the nine per-channel recurrences of the reference collapse into ONE on
-        // q = sum_ch value_ch * upstream_ch.
-        const float qv = q4.x * dpix0 + q4.y * dpix1 + q4.z * dpix2 + q3.w * drefl + c_d * ddepth + daccum +
-                         q3.x * dn0 + q3.y * dn1 + q3.z * dn2;
-        acc_q = last_alpha * last_q + om * acc_q;
-        last_q = qv;
-        float dL_dalpha = qv - acc_q;
-        g[12] = w * dpix0; g[13] = w * dpix1; g[14] = w * dpix2;
-        g[15] = w * drefl;
-        g[16] = w * dn0; g[17] = w * dn1; g[18] = w * dn2;
-        // distortion (:366-390).  final_D2 + m^2 final_A - 2 m final_D and m final_A - final_D cancel in fp32, so
-        // m_d and both expressions are written in exactly the rounding shape of the reference build (SASS of
-        // renderCUDA<3>, nvcc 12.9: IEEE -0.2/c_d, +1, *far/(far-near); fma(2m, -D, fma(A, m*m, D2)); fma(A, m, -D)):
-        // with the forward's final_* bit-identical, dL_dweight and the last_dL_dT recurrence are then the reference's
-        // bit for bit, and only T (reciprocal instead of division, nothing cancels there) differs in the last place.
-        const float m_d = ndc_depth(c_d);
-        const float dmd_dd = __fdiv_rn(FAR_N * NEAR_N, __fmul_rn(c_d, __fmul_rn(c_d, FAR_N - NEAR_N)));
-        float dL_dz = 0.0f;
-        if (contributor == median_contributor - 1u) dL_dz = dmedian;
-        const float dL_dweight =
-            __fmul_rn(dreg, __fmaf_rn(__fadd_rn(m_d, m_d), -final_D, __fmaf_rn(final_A, __fmul_rn(m_d, m_d), final_D2)));
-        dL_dalpha += __fsub_rn(dL_dweight, last_dL_dT);
-        last_dL_dT = __fmaf_rn(alpha, dL_dweight, __fmul_rn(last_dL_dT, __fsub_rn(1.0f, alpha)));
-        const float dL_dmd = __fmul_rn(dreg, __fmul_rn(__fadd_rn(w, w), __fmaf_rn(final_A, m_d, -final_D)));
-        dL_dz = __fmaf_rn(dL_dmd, dmd_dd, dL_dz);
-
-        dL_dalpha *= T;
-        last_alpha = alpha;
-        dL_dalpha += (-T_final * inv_1ma) * bg_dot_dpixel;  // :411-414
-        const float dL_dG = h.opa * dL_dalpha;
-        dL_dz += w * ddepth;
-        if (h.rho3d <= h.rho2d) {  // :423-453
-          const float dsx = dL_dG * -G * h.sx + dL_dz * h.Twx;
-          const float dsy = dL_dG * -G * h.sy + dL_dz * h.Twy;
-          const float dsx_pz = dsx * h.rpz, dsy_pz = dsy * h.rpz;
-          const float dpx = dsx_pz, dpy = dsy_pz, dpz = -(dsx_pz * h.sx + dsy_pz * h.sy);
-          // dL_dk = cross(l, dL_dp), dL_dl = cross(dL_dp, k)
-          const float dkx = h.ly * dpz - h.lz * dpy, dky = h.lz * dpx - h.lx * dpz, dkz = h.lx * dpy - h.ly * dpx;
-          const float dlx = dpy * h.kz - dpz * h.ky, dly = dpz * h.kx - dpx * h.kz, dlz = dpx * h.ky - dpy * h.kx;
-          g[0] = -dkx; g[1] = -dky; g[2] = -dkz;
-          g[3] = -dlx; g[4] = -dly; g[5] = -dlz;
-          g[6] = fx * dkx + fy * dlx + dL_dz * h.sx;
-          g[7] = fx * dky + fy * dly + dL_dz * h.sy;
-          g[8] = fx * dkz + fy * dlz + dL_dz * 1.0f;
-        } else {  // :454-464
-          g[9] = dL_dG * (-G * FILTER_INV_SQUARE * h.dx);
-          g[10] = dL_dG * (-G * FILTER_INV_SQUARE * h.dy);
-          g[6] = h.sx * dL_dz;
-          g[7] = h.sy * dL_dz;
-          g[8] = dL_dz;
-        }
-        g[11] = G * dL_dalpha;  // :467
+        for (int k = 0; k < 5; ++k) cp_async16(&d->q[k], &g->q[k]);
+        s_id[buf][t] = id;
       }
+      cp_async_commit();
+    };
+    int id_next = -1;
+    if (t < n) { id_next = (int)pl[n - 1 - t]; hit_next = ph[n - 1 - t]; pos_next = pp[n - 1 - t]; }
+    stage(0, id_next);
+    id_next = -1; hit_next = 0u;
+    if (BATCH + t < n) { const int q = n - 1 - (BATCH + t); id_next = (int)pl[q]; hit_next = ph[q]; pos_next = pp[q]; }
 
-      // warp reduce-scatter 20 -> 10 -> 5 -> 3 -> 2 -> 1
-      rs_step<10>(g, 16, b16);
-      rs_step<5>(g, 8, b8);
-      g[5] = 0.0f;
-      rs_step<3>(g, 4, b4);
-      g[3] = 0.0f;
-      rs_step<2>(g, 2, b2);
-      rs_step<1>(g, 1, b1);
-      if (comp_valid) atomicAdd(a.acc + (size_t)s_id[buf][j] * ACC_STRIDE + comp, g[0]);
+    for (int i = 0; i < rounds; ++i) {
+      cp_async_wait_all();
+      s_hit[i & 1][t] = (uint8_t)hit_cur;
+      __syncthreads();
+      if (i + 1 < rounds) {
+        stage((i + 1) & 1, id_next);
+        const int nx = (i + 2) * BATCH + t;
+        id_next = -1; hit_next = 0u;
+        if (nx < n) { const int q = n - 1 - nx; id_next = (int)pl[q]; hit_next = ph[q]; pos_next = pp[q]; }
+      }
+      const int buf = i & 1;
+      const int count = min(BATCH, n - i * BATCH);
+      const SurfelRec* rb = s_rec[buf];
+#pragma unroll 1
+      for (int r = 0; r < (count + 31) >> 5; ++r) {
+        // entries of other warp blocks, and entries behind every pixel's last contributor, are skipped
+        const int e = r * 32 + lane;
+        unsigned m = __ballot_sync(0xffffffffu, e < count && (s_hit[buf][e] & warp_bits) && base + s_pos[buf][e] < warp_last);
+        while (m) {
+          const int j = r * 32 + __ffs(m) - 1;
+          m &= m - 1;
+          const uint32_t contributor = base + s_pos[buf][j];   // 0-based position in the tile's full list
+          const float4 q0 = rb[j].q[0], q1 = rb[j].q[1], q2 = rb[j].q[2], q3 = rb[j].q[3], q4 = rb[j].q[4];
+
+          float g[20];
+#pragma unroll
+          for (int k = 0; k < 20; ++k) g[k] = 0.0f;
+#pragma unroll
+          for (int p = 0; p < 2; ++p) {
+            SurfelHit h;
+            bool c = contributor < px[p].last_contributor;
+            c = surfel_eval<true>(q0, q1, q2, px[p].fx, px[p].fy, h) && c;
+            if (c) px[p].contribute(h, q3, q4, contributor, g);
+          }
+
+          // warp reduce-scatter 20 -> 10 -> 5 -> 3 -> 2 -> 1 (a visit without any contributing pixel -- 3 % of them on
+          // the bench scene -- adds zeros: cheaper than a vote and a branch on every visit)
+          rs_step<10>(g, 16, b16);
+          rs_step<5>(g, 8, b8);
+          g[5] = 0.0f;
+          rs_step<3>(g, 4, b4);
+          g[3] = 0.0f;
+          rs_step<2>(g, 2, b2);
+          rs_step<1>(g, 1, b1);
+          if (comp_valid) atomicAdd(a.acc + (size_t)s_id[buf][j] * ACC_STRIDE + comp, g[0]);
+        }
       }
     }
-  }
-  cp_async_wait_all();
+    cp_async_wait_all();
   }   // slices
 }
 

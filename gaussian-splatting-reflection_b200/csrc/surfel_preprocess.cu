@@ -43,6 +43,7 @@ struct SurfelPreArgs {
   const float* projmatrix;
   const float* campos;
   int* radii;
+  float* gaussian_weights;   // zeroed here: the compositing takes an atomicMax on it
   float* depths;
   uint32_t* tiles_touched;
   uint8_t* clamped;
@@ -215,6 +216,7 @@ __global__ void __launch_bounds__(256, B200GS_PRE_CTAS) surfel_preprocess_kernel
   }
 
   a.radii[idx] = radius_out;
+  a.gaussian_weights[idx] = 0.0f;
   a.tiles_touched[idx] = alive ? tiles : 0u;
   if (!alive) return;
 
@@ -256,7 +258,7 @@ int surfel_preprocess(const b200gs_surfel_fwd& a, const SurfelGeom& g, cudaStrea
   k.shs = a.shs; k.colors_precomp = a.colors_precomp; k.transMat_precomp = a.transMat_precomp;
   k.refl = a.refl_strengths; k.mask = a.env_scope_mask;
   k.viewmatrix = a.viewmatrix; k.projmatrix = a.projmatrix; k.campos = a.campos;
-  k.radii = a.radii; k.depths = g.depths; k.tiles_touched = g.tiles_touched; k.clamped = g.clamped;
+  k.radii = a.radii; k.gaussian_weights = a.gaussian_weights; k.depths = g.depths; k.tiles_touched = g.tiles_touched; k.clamped = g.clamped;
   k.rects = g.rects; k.rec = g.rec; k.cull = g.cull; k.flags = g.flags;
   StageScope _t(ST_PREPROCESS, s);
   B200GS_CUDA(cudaMemsetAsync(g.flags, 0, 4 * sizeof(int), s));

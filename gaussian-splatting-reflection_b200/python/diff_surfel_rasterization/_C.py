@@ -65,12 +65,14 @@ def rasterize_gaussians(background, means3D, env_scope_mask, colors, refl_streng
     with torch.cuda.device(dev):
         # the reference zero-fills these (S/rasterize_points.cu:88-95); the kernels write every pixel and
         # every radius themselves, so only the P == 0 short-circuit and the atomicMax target need zeros
+        # One allocation for the 12 output planes and one for the per-Gaussian outputs (views are handed out): on
+        # small scenes the call is launch-bound and every allocation / fill is a launch or a host round trip.
         new = torch.zeros if P == 0 else torch.empty
-        out_color = new((NUM_CHANNELS, H, W), **f32)
-        out_others = new((3 + 3 + 1 + 1, H, W), **f32)
-        out_refl = new((1, H, W), **f32)
-        radii = new((P,), dtype=torch.int32, device=dev)
-        gaussian_weights = torch.zeros((P,), **f32)
+        planes = new((NUM_CHANNELS + 8 + 1, H, W), **f32)
+        out_color, out_others, out_refl = planes[:NUM_CHANNELS], planes[NUM_CHANNELS:NUM_CHANNELS + 8], planes[NUM_CHANNELS + 8:]
+        per_gaussian = new((2, P), **f32)
+        radii = per_gaussian[0].view(torch.int32)
+        gaussian_weights = per_gaussian[1]              # zeroed by stage 1 (the atomicMax target of the compositing)
         u8 = dict(dtype=torch.uint8, device=dev)
         geom = torch.empty((0,), **u8)
         binning = torch.empty((0,), **u8)
@@ -150,20 +152,23 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, refl_streng
             if not arena.accumulate:
                 arena.zero_()
             av = arena.views()
-        dL_dmeans3D = av["means3D"] if arena is not None else torch.zeros((P, 3), **o)
-        dL_dmeans2D = torch.zeros((P, 3), **o)
-        dL_dcolors = torch.zeros((P, NUM_CHANNELS), **o)
-        dL_dnormal = torch.zeros((P, 3), **o)
-        dL_dtransMat = torch.zeros((P, 9), **o)
+        # The kernels only write the rows of Gaussians a pixel blended; everything else must read 0
+        # (S/rasterize_points.cu:186-197 zero-fills ten tensors).  One zero-filled allocation, ten views.
+        widths = [3, NUM_CHANNELS, 3, 9] + ([] if arena is not None else [3, 1, 3 * M, 2, 4, 1 if has_refl else 0])
+        flat = torch.zeros((P * sum(widths),), **o)
+        blocks, off = [], 0
+        for wd in widths:
+            blocks.append(flat[off:off + P * wd].view(P, wd))
+            off += P * wd
+        dL_dmeans2D, dL_dcolors, dL_dnormal, dL_dtransMat = blocks[:4]
         if arena is not None:
-            dL_dopacity, dL_dsh, dL_dscales = av["opacity"], av["sh"], av["scales"]
+            dL_dmeans3D, dL_dopacity, dL_dsh, dL_dscales = av["means3D"], av["opacity"], av["sh"], av["scales"]
             dL_drotations, dL_drefl = av["rotations"], av["refl"]
         else:
-            dL_dopacity = torch.zeros((P, 1), **o)
-            dL_dsh = torch.zeros((P, M, 3), **o)
-            dL_dscales = torch.zeros((P, 2), **o)
-            dL_drotations = torch.zeros((P, 4), **o)
-            dL_drefl = torch.zeros((P, 1) if has_refl else (0, 1), **o)
+            dL_dmeans3D, dL_dopacity, dL_dsh, dL_dscales, dL_drotations, dL_drefl = blocks[4:]
+            dL_dsh = dL_dsh.view(P, M, 3)
+            if not has_refl:
+                dL_drefl = dL_drefl.view(0, 1)
         if P != 0:
             accum = torch.empty((_b.surfel_accum_bytes(P),), dtype=torch.uint8, device=means3D.device)
             a = _b.SurfelBwd(

@@ -126,7 +126,7 @@ typedef struct b200gs_surfel_fwd {
   float* out_others;       /* [8,H,W] depth,alpha,normal xyz,median,distortion,mask */
   float* out_refl;         /* [1,H,W]                                         */
   int* radii;              /* [P]                                             */
-  float* gaussian_weights; /* [P], must be zero-filled by the caller          */
+  float* gaussian_weights; /* [P], zeroed by stage 1, maximised by stage 2    */
   int exact_lists;         /* instance-list mode of this call, see above      */
   int cull_audit;          /* != 0: audit pass (test infrastructure), see above */
   int depth_slices;        /* culled emission only.  0: automatic; 1: one slice (no occlusion-aware binning);
