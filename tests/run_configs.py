@@ -62,7 +62,7 @@ def surfel_config(name, n_views=1, with_cubemap=False):
     sc_np, cam0 = scenes.build(name, view=0, n_views=32)
     sc = hz.to_dev(sc_np)
     P, W, H = sc_np["means3D"].shape[0], cam0["width"], cam0["height"]
-    cams = [hz.to_dev(scenes.build(name, view=v, n_views=32)[1]) if v else hz.to_dev(cam0) for v in range(n_views)]
+    cams = [hz.to_dev(scenes.camera(name, v, 32)) if v else hz.to_dev(cam0) for v in range(n_views)]
     grads = hz.to_dev(scenes.upstream_grads(W, H))
     out.update(P=P, W=W, H=H)
 
