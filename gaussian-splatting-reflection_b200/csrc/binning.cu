@@ -252,6 +252,7 @@ struct KeptArgs {
   int P, gx;
   int g0, g1;                     // emit: the Gaussians [g0, g1) of the depth order (one depth slice)
   int lpg_shift;                  // emit: log2 of the lanes per Gaussian (0: 32 Gaussians per warp ... 5: one per warp)
+  int nchunks;                    // groups of 256 threads' worth of work; the (capped) grid strides over them
   const uint8_t* done;            // emit, slices > 0: tiles whose pixels all saturated in an earlier slice ...
   uint32_t sentinel;              // ... get this key instead (sorts behind every tile, never read)
   const uint32_t* live;           // emit: number of unfinished tiles; 0 -> this slice is not needed at all
@@ -281,12 +282,15 @@ __global__ void __launch_bounds__(256) kept_rows_kernel(const KeptArgs a) {
   // The front depth slices hold few Gaussians with very many rows each (splats close to the camera): with 32 of them
   // per warp only a handful of SMs would work, one row stream after the other.  There the Gaussians are spread out,
   // one per 2^lpg_shift lanes; the lanes in between own nothing and only help with the rows and tiles.
-  const int gt = blockIdx.x * 256 + t;
-  const bool owner = !EMIT || (gt & ((1 << a.lpg_shift) - 1)) == 0;
-  const int i = EMIT ? a.g0 + (gt >> a.lpg_shift) : gt;
   if (EMIT && a.live != nullptr && *a.live == 0u) return;
   const bool hist = EMIT && a.eh.hist != nullptr;
   if (hist) { s_h[0][t] = 0u; s_h[1][t] = 0u; __syncthreads(); }
+  // the grid is capped (slice_grid): a slice nobody needs is one small launch; everything below is warp-private
+  for (int chunk = blockIdx.x; chunk < a.nchunks; chunk += gridDim.x) {
+  __syncwarp();
+  const int gt = chunk * 256 + t;
+  const bool owner = !EMIT || (gt & ((1 << a.lpg_shift) - 1)) == 0;
+  const int i = EMIT ? a.g0 + (gt >> a.lpg_shift) : gt;
 
   uint32_t id = 0, off = 0, end = 0;
   bool vis = false;
@@ -442,12 +446,13 @@ __global__ void __launch_bounds__(256) kept_rows_kernel(const KeptArgs a) {
       const int4 bx = s_box[t];
       for (uint32_t o = s_run[t]; o < end; ++o) put(o, (uint32_t)(bx.z * a.gx + bx.x), id);
     }
-    if (hist) {
-      __syncthreads();
-      const uint32_t h0 = s_h[0][t], h1 = s_h[1][t];
-      if (h0) atomicAdd(a.eh.hist + t, h0);
-      if (h1) atomicAdd(a.eh.hist + RS_RADIX + t, h1);
-    }
+  }
+  }   // next chunk
+  if (hist) {
+    __syncthreads();
+    const uint32_t h0 = s_h[0][t], h1 = s_h[1][t];
+    if (h0) atomicAdd(a.eh.hist + t, h0);
+    if (h1) atomicAdd(a.eh.hist + RS_RADIX + t, h1);
   }
 }
 
@@ -459,7 +464,8 @@ int surfel_count_kept(int P, const uint32_t* tiles_touched, const uint2* rects, 
   a.P = P; a.tiles_touched = tiles_touched; a.rects = rects; a.cull = cull; a.kept = kept;
   if (rows) a.rows = *rows;
   a.small_rect = rows ? SMALL_RECT_SLICED : SMALL_RECT_UNSLICED;     // the surfel path hands in its row cache
-  kept_rows_kernel<false><<<(P + 255) / 256, 256, 0, s>>>(a);
+  a.nchunks = (P + 255) / 256;
+  kept_rows_kernel<false><<<a.nchunks, 256, 0, s>>>(a);
   B200GS_LAUNCHED("kept_rows_kernel<count>", debug, s);
   return B200GS_OK;
 }
@@ -469,16 +475,24 @@ int surfel_count_kept(int P, const uint32_t* tiles_touched, const uint2* rects, 
 __global__ void __launch_bounds__(256) tile_ranges_kernel(int first, int L, const uint32_t* __restrict__ keys, uint2* ranges,
                                                           const uint32_t* __restrict__ live) {
   if (live != nullptr && *live == 0u) return;
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= L) return;
-  const uint32_t cur = keys[first + idx];
-  if (idx == 0) {
-    ranges[cur].x = first;
-  } else {
-    const uint32_t prev = keys[first + idx - 1];
-    if (cur != prev) { ranges[prev].y = first + idx; ranges[cur].x = first + idx; }
+  // grid-stride: the grid is capped (slice_grid) so that a slice nobody needs costs one small launch, not one CTA per
+  // 256 instances of it
+  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < L; idx += gridDim.x * blockDim.x) {
+    const uint32_t cur = keys[first + idx];
+    if (idx == 0) {
+      ranges[cur].x = first;
+    } else {
+      const uint32_t prev = keys[first + idx - 1];
+      if (cur != prev) { ranges[prev].y = first + idx; ranges[cur].x = first + idx; }
+    }
+    if (idx == L - 1) ranges[cur].y = first + L;
   }
-  if (idx == L - 1) ranges[cur].y = first + L;
+}
+
+// Launch width of the per-slice kernels: enough CTAs to fill the GPU several times over, never one per work item.
+static inline int slice_grid(long long work_items) {
+  const long long cap = 148 * 16;
+  return (int)(work_items < cap ? (work_items > 0 ? work_items : 1) : cap);
 }
 
 // ------------------------------------------------------------------ tile hits
@@ -668,9 +682,15 @@ __global__ void __launch_bounds__(TH_THREADS) tile_hits_kernel(int first, int R,
   __shared__ uint16_t s_queue[TH_TILE];  // items that reach their tile and need the per-block refinement
   __shared__ uint32_t s_qn;
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const uint32_t nblocks = (uint32_t)((R + TH_TILE - 1) / TH_TILE);
+  // persistent CTAs: blocks of TH_TILE items are taken in ticket order until none is left (the look-back below only
+  // ever waits for tickets that were handed out before, i.e. for CTAs that are running)
+  while (true) {
+  __syncthreads();                                   // the previous block's shared state is no longer read
   if (t == 0) { s_tile = atomicAdd(state, 1u); s_qn = 0u; }
   __syncthreads();
   const uint32_t blk = s_tile;
+  if (blk >= nblocks) return;
   const int base = (int)blk * TH_TILE;
 
   unsigned mask[TH_ITEMS];
@@ -775,6 +795,7 @@ __global__ void __launch_bounds__(TH_THREADS) tile_hits_kernel(int first, int R,
     if (ia == rg.x) cranges[tile[k]].x = off;
     if (ia + 1u == rg.y) cranges[tile[k]].y = off + (keep[k] ? 1u : 0u);
   }
+  }   // next ticket
 }
 
 // ------------------------------------------------------------------ slice plan
@@ -950,7 +971,8 @@ int bin_slice(const BinJob& j, int k, const Binning& b, size_t& zcursor, cudaStr
         // idle helper lanes would just be more warps to schedule
         ea.lpg_shift = (per >= 64 && ng < (1 << 17)) ? 5 : ((per >= 24 && ng < (1 << 19)) ? 3 : 0);
         const long long threads = (long long)ng << ea.lpg_shift;
-        kept_rows_kernel<true><<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(ea);
+        ea.nchunks = (int)((threads + 255) / 256);
+        kept_rows_kernel<true><<<slice_grid(ea.nchunks), 256, 0, s>>>(ea);
         B200GS_LAUNCHED("kept_rows_kernel<emit>", j.debug, s);
       }
     } else {
@@ -969,7 +991,7 @@ int bin_slice(const BinJob& j, int k, const Binning& b, size_t& zcursor, cudaStr
   }
   {
     StageScope _t(ST_RANGES, s);
-    tile_ranges_kernel<<<(n + 255) / 256, 256, 0, s>>>(first, n, b.tile_ids, ranges, live);
+    tile_ranges_kernel<<<slice_grid((n + 255) / 256), 256, 0, s>>>(first, n, b.tile_ids, ranges, live);
     B200GS_LAUNCHED("tile_ranges_kernel", j.debug, s);
   }
   StageScope _t(ST_TILE_HITS, s);
@@ -977,10 +999,10 @@ int bin_slice(const BinJob& j, int k, const Binning& b, size_t& zcursor, cudaStr
   const int blocks = (n + TH_TILE - 1) / TH_TILE;
   if (j.cull_for_hits == nullptr) { set_error("bin_slice: no cull records"); return B200GS_EINVAL; }
   if (j.cull == nullptr)     // exact lists: most instances miss their tile, test the whole tile first
-    tile_hits_kernel<true><<<blocks, TH_THREADS, 0, s>>>(first, n, b.tile_ids, b.point_list, j.cull_for_hits, gx, (uint32_t)tiles, ranges,
+    tile_hits_kernel<true><<<slice_grid(blocks), TH_THREADS, 0, s>>>(first, n, b.tile_ids, b.point_list, j.cull_for_hits, gx, (uint32_t)tiles, ranges,
                                                          cranges, b.comp_id, b.comp_pos, b.comp_hit, hit_state, keep_all, live);
   else
-    tile_hits_kernel<false><<<blocks, TH_THREADS, 0, s>>>(first, n, b.tile_ids, b.point_list, j.cull_for_hits, gx, (uint32_t)tiles, ranges,
+    tile_hits_kernel<false><<<slice_grid(blocks), TH_THREADS, 0, s>>>(first, n, b.tile_ids, b.point_list, j.cull_for_hits, gx, (uint32_t)tiles, ranges,
                                                           cranges, b.comp_id, b.comp_pos, b.comp_hit, hit_state, keep_all, live);
   B200GS_LAUNCHED("tile_hits_kernel", j.debug, s);
   return B200GS_OK;

@@ -168,8 +168,6 @@ __global__ void __launch_bounds__(THREADS, 3) radix_pass_kernel(const PassArgs a
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   if (a.live != nullptr && *a.live == 0u) return;
   const uint32_t dmask = (1u << a.nbits) - 1u;
-  if (t == 0) s_blk = atomicAdd(a.ticket, 1u);
-  for (int e = t; e < WARPS * RS_RADIX; e += THREADS) (&s_cnt[0][0])[e] = (cnt_t)0;
   // exclusive bucket base of digit t over all n keys (the histogram is small and L2-resident)
   uint32_t dbase = 0u;
   {
@@ -188,7 +186,17 @@ __global__ void __launch_bounds__(THREADS, 3) radix_pass_kernel(const PassArgs a
 #pragma unroll
     for (int w = 0; w < RS_RADIX / 32; ++w) if (w < warp) dbase += s_hsum[w];
   }
+  // Persistent CTAs: tiles of RS_TILE pairs are taken in ticket order until none is left.  The look-back only waits
+  // for tickets handed out earlier, i.e. for CTAs that are running, so a capped grid cannot deadlock -- and a pass
+  // nobody needs (`live`) is one small launch instead of one CTA per tile.
+  const uint32_t nblocks = (uint32_t)((a.n + RS_TILE - 1) / RS_TILE);
+  while (true) {
+  __syncthreads();                                   // the previous tile's shared state is no longer read
+  if (t == 0) s_blk = atomicAdd(a.ticket, 1u);
+  for (int e = t; e < WARPS * RS_RADIX; e += THREADS) (&s_cnt[0][0])[e] = (cnt_t)0;
+  __syncthreads();
   const uint32_t blk = s_blk;
+  if (blk >= nblocks) return;
   const int blk_base = (int)blk * RS_TILE;
   const int wbase = blk_base + warp * (32 * ITEMS);
 
@@ -303,6 +311,7 @@ __global__ void __launch_bounds__(THREADS, 3) radix_pass_kernel(const PassArgs a
     a.keys_out[g] = k;
     a.vals_out[g] = s_vals[p];
   }
+  }   // next ticket
 }
 
 int radix_sort_pairs_u32(uint32_t* keys_a, uint32_t* vals_a, uint32_t* keys_b, uint32_t* vals_b, int n,
@@ -321,7 +330,7 @@ int radix_sort_pairs_u32(uint32_t* keys_a, uint32_t* vals_a, uint32_t* keys_b, u
     // Measured on the bench workload (round 1; tile sort of 33.8M pairs, two passes): ranking inside the counter loop
     // 0.76 ms, independent match.any 0.64, ballots per digit bit 0.64; look-back batch 1 0.66, 4 0.61, 8 0.65;
     // 512 threads x 8 keys 0.70-0.85.  Kept: independent match.any, 4-wide look-back.
-    radix_pass_kernel<1, 256, 16, 4><<<blocks, 256, 0, s>>>(a);
+    radix_pass_kernel<1, 256, 16, 4><<<blocks < 148 * 6 ? blocks : 148 * 6, 256, 0, s>>>(a);
     B200GS_LAUNCHED("radix_pass_kernel", debug, s);
     uint32_t* x;
     x = ki; ki = ko; ko = x;

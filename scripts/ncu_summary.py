@@ -16,7 +16,10 @@ COLS = [("gpu__time_duration.sum", "time"), ("dram__bytes_read.sum", "DRAM rd"),
         ("gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "DRAM %"),
         ("lts__throughput.avg.pct_of_peak_sustained_elapsed", "L2 %"),
         ("smsp__inst_executed.sum", "warp inst"), ("smsp__thread_inst_executed_per_inst_executed.ratio", "lanes/inst"),
-        ("sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active", "fp64 pipe %")]
+        ("sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active", "fp64 pipe %"),
+        ("lts__t_sectors_op_red.sum", "L2 RED sectors"), ("lts__t_sectors_op_atom.sum", "L2 ATOM sectors"),
+        ("l1tex__data_pipe_lsu_wavefronts_mem_shared.sum", "smem wavefronts")]
+HBM_PEAK_GBS = 6543.7   # MEASURED_PEAKS.json hbm_gbs
 
 
 def short(name):
@@ -48,11 +51,21 @@ def launches(path):
 
 
 def rep(path):
-    out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    if path.endswith(".csv"):       # `ncu -i X.ncu-rep --page raw --csv` exported on the GPU box
+        out = open(path).read()
+    else:
+        out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(out.splitlines()))
     h, u = rows[0], rows[1]
-    print("| # | kernel | " + " | ".join(f"{lab} [{u[h.index(m)]}]" if u[h.index(m)] else lab for m, lab in COLS if m in h) + " |")
-    print("|---|---|" + "---|" * sum(1 for m, _ in COLS if m in h))
+    print("| # | kernel | " + " | ".join(f"{lab} [{u[h.index(m)]}]" if u[h.index(m)] else lab for m, lab in COLS if m in h) + " | DRAM GB/s | of HBM peak |")
+    print("|---|---|" + "---|" * (2 + sum(1 for m, _ in COLS if m in h)))
+
+    def num(r, m):
+        v = float(r[h.index(m)].replace(",", ""))
+        unit = u[h.index(m)]
+        scale = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0, "ms": 1e-3, "us": 1e-6, "ns": 1e-9, "s": 1.0,
+                 "msecond": 1e-3, "usecond": 1e-6, "nsecond": 1e-9, "second": 1.0}.get(unit, 1.0)
+        return v * scale
     for n, r in enumerate(rows[2:]):
         vals = []
         for m, _ in COLS:
@@ -61,16 +74,22 @@ def rep(path):
                     vals.append(f"{float(r[h.index(m)].replace(',', '')):.4g}")
                 except ValueError:
                     vals.append(r[h.index(m)])
-        print(f"| {n} | `{short(r[h.index('Kernel Name')])}` | " + " | ".join(vals) + " |")
+        try:
+            gbs = (num(r, "dram__bytes_read.sum") + num(r, "dram__bytes_write.sum")) / num(r, "gpu__time_duration.sum") / 1e9
+            extra = f" {gbs:.0f} | {gbs / HBM_PEAK_GBS:.2f} |"
+        except Exception:  # noqa: BLE001
+            extra = " - | - |"
+        print(f"| {n} | `{short(r[h.index('Kernel Name')])}` | " + " | ".join(vals) + " |" + extra)
 
 
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--launches")
-    ap.add_argument("--rep")
+    ap.add_argument("--rep", action="append")
     a = ap.parse_args()
     if a.launches:
         launches(a.launches)
         print()
-    if a.rep:
-        rep(a.rep)
+    for path in a.rep or []:
+        print(f"\n### {path}\n")
+        rep(path)
