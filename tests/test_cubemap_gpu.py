@@ -38,6 +38,26 @@ def _close(a, b, atol, rtol, max_bad_frac=0.0):
     assert float(bad.double().mean()) <= max_bad_frac, (float((a - b).abs().max()), int(bad.sum()))
 
 
+def _near_tap_boundary(d, L, interp, tol_texels=2e-3):
+    """Rays whose tap selection hangs on the last bits of the direction: the face choice is (nearly) a tie between two
+    axes, or a texel coordinate lies within `tol_texels` of the value at which floor / trunc / the edge tests of the
+    lookup flip (C/src/cubemapencoder.cu:66-263; both builds are -use_fast_math, their coordinates differ by ~1e-4
+    texels at L = 128).  There -- and only there -- the two builds may pick neighbouring texels, and the direction
+    gradient, which is discontinuous across a texel boundary, legitimately differs."""
+    from oracle import cubemap_oracle as co
+    d64 = np.asarray(d, np.float64)
+    a = np.sort(np.abs(d64), axis=1)
+    tie = (a[:, 2] - a[:, 1]) <= 1e-5 * np.maximum(a[:, 2], 1e-30)
+    _, u, v = co.face_uv(d64)
+    fu, fv = (u * 0.5 + 0.5) * L, (-v * 0.5 + 0.5) * L
+    off = 0.5 if interp else 0.0
+
+    def near(x):
+        f = x - off
+        return np.abs(f - np.round(f)) <= tol_texels
+    return torch.from_numpy(tie | near(fu) | near(fv))
+
+
 @pytest.mark.parametrize("interp,seamless", MODES)
 @pytest.mark.parametrize("B,C,L", [(4096, 3, 16), (100000, 3, 128), (777, 6, 8), (5000, 5, 32)])
 def test_matches_reference(ref, interp, seamless, B, C, L):
@@ -47,7 +67,15 @@ def test_matches_reference(ref, interp, seamless, B, C, L):
     _close(o_n, o_r, 1e-5, 1e-5)
     _close(gt_n, gt_r, 1e-4, 1e-4)          # scatter sums: atomics order differs
     _close(gf_n, gf_r, 1e-5, 1e-5)
-    _close(gi_n, gi_r, 1e-3, 1e-4, max_bad_frac=1e-3)
+    # direction gradient: EVERY ray away from a tap boundary within 1e-4 (of the largest entry / relative); the rays
+    # on a boundary are few, are identified from the geometry alone, and only they may differ
+    edge = _near_tap_boundary(d, L, interp).to(gi_r.device)
+    # (the first 301 rays of a case are constructed ON cube vertices / edges; of the random ones a per cent or two
+    # fall within the band at L = 128, fewer at small L)
+    assert float(edge[301:].double().mean()) <= 0.03, float(edge[301:].double().mean())
+    scale = float(gi_r.abs().max())
+    _close(gi_n[~edge], gi_r[~edge], 1e-4 * scale, 1e-4)
+    _close(gi_n, gi_r, 1e-4 * scale, 1e-4, max_bad_frac=float(edge.double().mean()))
 
 
 @pytest.mark.parametrize("interp,seamless", MODES)

@@ -113,3 +113,35 @@ def test_two_rank_densify_stats_allreduce(tmp_path):
     assert np.array_equal(r0[1], one["denom"]) and np.array_equal(r0[3], one["denom_w"])
     assert np.array_equal(r0[4], one["max_radii2D"])
     assert np.allclose(r0[0], one["xyz_gradient_accum"], rtol=1e-6) and np.allclose(r0[2], one["accum_w"], rtol=1e-6)
+
+
+def test_arena_lands_in_model_gradients():
+    """The two ways an all-reduced arena reaches the optimizer (b200gs.dp.GradArena): bind_grads -- the leaves'
+    .grad ARE the arena blocks -- and backward_through -- the chain rule through the model's activations
+    (sigmoid / exp / normalize, scene/gaussian_model.py:124-147) applied once to the batch sum."""
+    P = 7
+    a = GradArena(P, 16, "cpu", accumulate=True)
+    leaves = {"means3D": torch.zeros(P, 3, requires_grad=True), "sh": torch.zeros(P, 16, 3, requires_grad=True),
+              "opacity": torch.zeros(P, 1, requires_grad=True)}
+    a.bind_grads(leaves)
+    a.view("opacity").add_(2.0)                       # what a backward kernel does
+    assert leaves["opacity"].grad.data_ptr() == a.view("opacity").data_ptr()
+    assert float(leaves["opacity"].grad.sum()) == 2.0 * P
+    a.zero_()
+    assert float(leaves["opacity"].grad.abs().sum()) == 0.0
+    with pytest.raises(ValueError):
+        a.bind_grads({"scales": torch.zeros(P, 3, requires_grad=True)})
+    # activations in between: d/d raw = Jacobian^T x (gradient with respect to the activated value)
+    raw_o = torch.randn(P, 1, requires_grad=True)
+    raw_s = torch.randn(P, 2, requires_grad=True)
+    raw_r = torch.randn(P, 4, requires_grad=True)
+    act = {"opacity": torch.sigmoid(raw_o), "scales": torch.exp(raw_s), "rotations": torch.nn.functional.normalize(raw_r)}
+    g = {k: torch.randn_like(v) for k, v in act.items()}
+    for k in act:
+        a.view(k).copy_(g[k])
+    a.backward_through(act)
+    so = torch.sigmoid(raw_o.detach())
+    assert torch.allclose(raw_o.grad, g["opacity"] * so * (1 - so), atol=1e-6)
+    assert torch.allclose(raw_s.grad, g["scales"] * torch.exp(raw_s.detach()), atol=1e-6)
+    want = torch.autograd.grad(torch.nn.functional.normalize(raw_r), raw_r, g["rotations"])[0]
+    assert torch.allclose(raw_r.grad, want, atol=1e-6)

@@ -273,3 +273,49 @@ def test_gradient_arena_accumulates_a_batch_of_views():
     b1 = hz.surfel_backward(C, sc, cams[0], f, grads)                    # no arena: fresh tensors
     assert b1["sh"].data_ptr() != arena.view("sh").data_ptr()
     assert hz.rel_l2(arena.view("sh"), b1["sh"]) <= 1e-5    # run-to-run atomic order only
+
+
+def test_autograd_module_with_arena_over_several_views(refC):
+    """the drop-in GaussianRasterizer + loss.backward() with a gradient arena over several views.  The
+    backward adds each view's parameter gradients into the arena and hands autograd nothing for those inputs, so
+    nothing aliases, nothing is added twice, and the leaves' .grad (bound to the arena blocks) hold exactly the sum
+    of the per-view gradients the plain autograd path accumulates -- which is also what the reference's own package
+    accumulates on the reference extension."""
+    import diff_surfel_rasterization as d
+    from b200gs.dp import GradArena
+    sc_np, _ = scenes.build("small")
+    sc = hz.to_dev(sc_np)
+    P, M = sc["means3D"].shape[0], sc["shs"].shape[1]
+    cams = [hz.to_dev(scenes.camera("small", v, 32)) for v in (0, 7, 19)]
+    names = {"means3D": "means3D", "shs": "sh", "opacities": "opacity", "scales": "scales", "rotations": "rotations", "refl": "refl"}
+    mask = torch.ones((P, 3), dtype=torch.bool, device="cuda")
+
+    def run(arena):
+        leaves = {k: sc[k].clone().requires_grad_(True) for k in names}
+        if arena is not None:
+            arena.zero_()
+            arena.bind_grads({names[k]: v for k, v in leaves.items()})
+        m2d_grads = []
+        for c in cams:
+            rs = d.GaussianRasterizationSettings(
+                image_height=c["height"], image_width=c["width"], tanfovx=c["tanfovx"], tanfovy=c["tanfovy"],
+                bg=torch.zeros(3, device="cuda"), scale_modifier=1.0, viewmatrix=c["viewmatrix"],
+                projmatrix=c["projmatrix"], sh_degree=3, campos=c["campos"], prefiltered=False, debug=False)
+            m2d = torch.zeros_like(leaves["means3D"], requires_grad=True)
+            color, radii, allmap, refl_map, _ = d.GaussianRasterizer(rs, grad_arena=arena)(
+                means3D=leaves["means3D"], means2D=m2d, opacities=leaves["opacities"], shs=leaves["shs"],
+                refl_strengths=leaves["refl"], scales=leaves["scales"], rotations=leaves["rotations"], env_scope_mask=mask)
+            (color.square().mean() + allmap[:6].mean() + refl_map.mean()).backward()
+            m2d_grads.append(m2d.grad.clone())
+        torch.cuda.synchronize()
+        return {k: v.grad.clone() for k, v in leaves.items()}, m2d_grads
+
+    plain, m_plain = run(None)
+    arena = GradArena(P, M, "cuda", accumulate=True)
+    got, m_got = run(arena)
+    got2, _ = run(arena)                               # a second batch on the same arena: zero_() starts it afresh
+    for k in plain:
+        assert hz.rel_l2(got[k], plain[k]) <= 1e-5, (k, hz.rel_l2(got[k], plain[k]))
+        assert hz.rel_l2(got2[k], plain[k]) <= 1e-5, k
+    for a, b in zip(m_got, m_plain):                   # the per-view densification gradient stays an ordinary tensor
+        assert hz.rel_l2(a, b) <= 1e-5
