@@ -1,7 +1,7 @@
 set -x
 cd $GRAFT_REPO_ROOT
-timeout 600 python -m pytest tests/test_configs_gpu.py tests/test_surfel_gpu.py -x -q -m gpu -k "depth_sliced or baseline_config or surfel_gpu" > gpurun_out/r2e_pytest_gpu.log 2>&1; tail -5 gpurun_out/r2e_pytest_gpu.log
-timeout 600 python scripts/gpu_slices.py bench > gpurun_out/r2e_slices.jsonl 2> gpurun_out/r2e_slices.err; cut -c1-900 gpurun_out/r2e_slices.jsonl | head -3; tail -3 gpurun_out/r2e_slices.err
+timeout 600 python -m pytest tests/test_configs_gpu.py tests/test_surfel_gpu.py -x -q -m gpu -k "depth_sliced or baseline_config or surfel_gpu" > gpurun_out/dev_pytest_gpu.log 2>&1; tail -5 gpurun_out/dev_pytest_gpu.log
+timeout 600 python scripts/gpu_slices.py bench > gpurun_out/dev_slices.jsonl 2> gpurun_out/dev_slices.err; cut -c1-900 gpurun_out/dev_slices.jsonl | head -3; tail -3 gpurun_out/dev_slices.err
 python - <<'PY'
 import sys, os
 sys.path.insert(0, "tests")
