@@ -152,6 +152,10 @@ MAX_SLICES, PLAN_INTS = 8, 24
 surfel_forward_stage1 = _sig("b200gs_surfel_forward_stage1", _i, C.POINTER(SurfelFwd), C.POINTER(_i), _p)
 surfel_forward_stage2 = _sig("b200gs_surfel_forward_stage2", _i, C.POINTER(SurfelFwd), C.POINTER(_i), _p)
 surfel_backward = _sig("b200gs_surfel_backward", _i, C.POINTER(SurfelBwd), _p)
+# the same backward with its accumulator in a static device array inside the library (no allocation anywhere on the
+# call; P <= STATIC_ACCUM_MAX_POINTS; calls on one device share the array and must not overlap on the GPU)
+STATIC_ACCUM_MAX_POINTS = 131072
+surfel_backward_static = _sig("b200gs_surfel_backward_static", _i, C.POINTER(SurfelBwd), _p)
 surfel_inspect_geom = _sig("b200gs_surfel_inspect_geom", _i, _p, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p)
 inspect_binning = _sig("b200gs_inspect_binning", _i, _p, _i, _p, _p, _p, _p)
 surfel_inspect_image = _sig("b200gs_surfel_inspect_image", _i, _p, _i, _i, _p, _p, _p, _p)

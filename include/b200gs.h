@@ -205,6 +205,17 @@ typedef struct b200gs_surfel_bwd {
 size_t b200gs_surfel_accum_bytes(int P);
 int b200gs_surfel_backward(const b200gs_surfel_bwd* a, void* stream);
 
+/* The same backward for callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid
+ * cudaMalloc).  No counterpart in the reference.
+ * `a->accum` / `a->accum_bytes` are IGNORED; the accumulator lives in a file-scope __device__ array inside the
+ * library (csrc/static_scratch.cu), sized for at most B200GS_STATIC_ACCUM_MAX_POINTS Gaussians (10 MiB, held by
+ * every GPU that loads the library until the process exits).  P beyond that maximum -> B200GS_ESIZE with a message.
+ * Calls no cudaMalloc / cudaFree / allocating routine.  All calls on a device share the one array (the rows a call
+ * uses are cleared on its stream first), so calls that overlap on the GPU race: serialise them.  Inputs, outputs
+ * and everything else are as for b200gs_surfel_backward.                                                        */
+#define B200GS_STATIC_ACCUM_MAX_POINTS 131072
+int b200gs_surfel_backward_static(const b200gs_surfel_bwd* a, void* stream);
+
 /* Parity-check helpers: unpack the private scratch layouts into the SoA arrays
  * the reference keeps in GeometryState / BinningState / ImageState
  * (S/cuda_rasterizer/rasterizer_impl.h:33-69).  Any output may be NULL.      */
