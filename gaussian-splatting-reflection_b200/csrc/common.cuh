@@ -229,14 +229,21 @@ struct GaussGeom {
   CullRec* cull;            // [P] {alpha >= 1/255} as a point conic (an ellipse here), same record as the surfel path
   uint32_t* scan_state;
   int* flags;
+  int* plan;                // [PLAN_INTS] slice plan of this forward, as in SurfelGeom
+  RowCache rows;            // as in SurfelGeom
   static GaussGeom carve(void* base, size_t P, size_t* bytes);
 };
 
+constexpr int GSTATE_PLANES = 10;  // T (sign = done), colour, normal, refl, inverse depth, last contributor
 struct GaussImage {
   float* accum;         // [N] final T
   uint32_t* n_contrib;  // [N]
-  uint2* ranges;        // [tiles+1]
-  uint2* cranges;       // [tiles+1] ranges into the compacted instance list
+  uint2* ranges;        // [MAX_SLICES][tiles+1]   (depth slices: same bookkeeping as SurfelImage)
+  uint2* cranges;       // [MAX_SLICES][tiles+1] ranges into the compacted instance list
+  uint32_t* tile_base;  // [MAX_SLICES+1][tiles]
+  uint8_t* tile_done;   // [tiles]
+  uint32_t* live;       // [4]
+  float* state;         // [GSTATE_PLANES,N]
   static GaussImage carve(void* base, int W, int H, size_t* bytes);
 };
 
@@ -247,7 +254,7 @@ constexpr int GACC_STRIDE = 16;
 
 int gauss_preprocess(const b200gs_gauss_fwd& a, const GaussGeom& g, cudaStream_t s);
 int gauss_composite_forward(const b200gs_gauss_fwd& a, const GaussGeom& g, const GaussImage& im, const Binning& b,
-                            cudaStream_t s);
+                            int k, int S, cudaStream_t s);
 int gauss_composite_backward(const b200gs_gauss_bwd& a, const GaussGeom& g, const GaussImage& im, const Binning& b,
                              float* acc, cudaStream_t s);
 int gauss_preprocess_backward(const b200gs_gauss_bwd& a, const GaussGeom& g, const float* acc, cudaStream_t s);

@@ -21,6 +21,11 @@ GaussGeom GaussGeom::carve(void* base, size_t P, size_t* bytes) {
   g.cull = c.take<CullRec>(P);
   g.scan_state = c.take<uint32_t>(scan_state_words((int)P));
   g.flags = c.take<int>(4);
+  g.plan = c.take<int>(PLAN_INTS);
+  g.rows.capacity = (uint32_t)(ROWS_PER_GAUSSIAN * P + (1u << 20));
+  g.rows.rows = c.take<uint4>(g.rows.capacity);
+  g.rows.base = c.take<uint32_t>(P);
+  g.rows.cursor = g.flags ? reinterpret_cast<uint32_t*>(g.flags + 1) : nullptr;
   if (bytes) *bytes = c.used + 128;
   return g;
 }
@@ -32,8 +37,12 @@ GaussImage GaussImage::carve(void* base, int W, int H, size_t* bytes) {
   const size_t tiles = (size_t)((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
   im.accum = c.take<float>(N);
   im.n_contrib = c.take<uint32_t>(N);
-  im.ranges = c.take<uint2>(tiles + 1);
-  im.cranges = c.take<uint2>(tiles + 1);
+  im.ranges = c.take<uint2>((size_t)MAX_SLICES * (tiles + 1));
+  im.cranges = c.take<uint2>((size_t)MAX_SLICES * (tiles + 1));
+  im.tile_base = c.take<uint32_t>((size_t)(MAX_SLICES + 1) * tiles);
+  im.tile_done = c.take<uint8_t>(tiles);
+  im.live = c.take<uint32_t>(4);
+  im.state = c.take<float>((size_t)GSTATE_PLANES * N);
   if (bytes) *bytes = c.used + 128;
   return im;
 }
@@ -104,59 +113,77 @@ size_t b200gs_gauss_image_bytes(int width, int height) {
 }
 size_t b200gs_gauss_accum_bytes(int P) { return (size_t)(P > 0 ? P : 0) * GACC_STRIDE * sizeof(float) + 128; }
 
-int b200gs_gauss_forward_stage1(const b200gs_gauss_fwd* a, int* num_rendered, void* stream) {
+int b200gs_gauss_forward_stage1(const b200gs_gauss_fwd* a, int* plan, void* stream) {
   int rc = check_fwd(a);
   if (rc) return rc;
-  if (!num_rendered) { set_error("num_rendered is null"); return B200GS_EINVAL; }
+  if (!plan) { set_error("plan is null"); return B200GS_EINVAL; }
   cudaStream_t s = (cudaStream_t)stream;
-  *num_rendered = 0;
+  for (int i = 0; i < PLAN_INTS; ++i) plan[i] = 0;
+  plan[1] = 1;
   if (a->P == 0) return B200GS_OK;
   GaussGeom g = GaussGeom::carve(align128(a->geom), a->P, nullptr);
   rc = gauss_preprocess(*a, g, s);
   if (rc) return rc;
+  const bool exact = a->exact_lists != 0;
   const uint32_t* counts = g.tiles_touched;
-  if (a->exact_lists == 0) {   // culled emission (include/b200gs.h: exact_lists)
-    rc = surfel_count_kept(a->P, g.tiles_touched, g.rects, g.cull, g.tiles_kept, nullptr, s, a->debug != 0);
+  if (!exact) {   // culled emission (include/b200gs.h: exact_lists)
+    rc = surfel_count_kept(a->P, g.tiles_touched, g.rects, g.cull, g.tiles_kept, &g.rows, s, a->debug != 0);
     if (rc) return rc;
     counts = g.tiles_kept;
   }
   rc = depth_order_and_scan(g.depths, counts, a->P, g.order, g.point_offsets, g.scan_state, s, a->debug != 0);
   if (rc) return rc;
-  int host[2] = {0, 0};
-  B200GS_CUDA(cudaMemcpyAsync(&host[0], g.point_offsets + a->P - 1, sizeof(int), cudaMemcpyDeviceToHost, s));
-  B200GS_CUDA(cudaMemcpyAsync(&host[1], g.flags, sizeof(int), cudaMemcpyDeviceToHost, s));
+  rc = slice_plan(g.point_offsets, a->P, exact ? 1 : a->depth_slices, a->slice_frac, g.plan, s, a->debug != 0);
+  if (rc) return rc;
+  int flag = 0;
+  B200GS_CUDA(cudaMemcpyAsync(plan, g.plan, PLAN_INTS * sizeof(int), cudaMemcpyDeviceToHost, s));
+  B200GS_CUDA(cudaMemcpyAsync(&flag, g.flags, sizeof(int), cudaMemcpyDeviceToHost, s));
   B200GS_CUDA(cudaStreamSynchronize(s));
-  *num_rendered = host[0];
-  if (host[1]) { set_error("Point is filtered although prefiltered is set. This shouldn't happen!"); return B200GS_EINVAL; }
+  if (flag) { set_error("Point is filtered although prefiltered is set. This shouldn't happen!"); return B200GS_EINVAL; }
   return B200GS_OK;
 }
 
-int b200gs_gauss_forward_stage2(const b200gs_gauss_fwd* a, int R, void* stream) {
+int b200gs_gauss_forward_stage2(const b200gs_gauss_fwd* a, const int* plan, void* stream) {
   int rc = check_fwd(a);
   if (rc) return rc;
   cudaStream_t s = (cudaStream_t)stream;
   if (a->P == 0) return B200GS_OK;
-  if (R < 0) { set_error("negative num_rendered"); return B200GS_EINVAL; }
+  if (!plan) { set_error("plan is null"); return B200GS_EINVAL; }
+  const int R = plan[0], S = plan[1];
+  if (R < 0 || S < 1 || S > MAX_SLICES || plan[PLAN_G] != 0 || plan[PLAN_OFF] != 0 || plan[PLAN_G + S] != a->P || plan[PLAN_OFF + S] != R) {
+    set_error("bad slice plan (num_rendered %d, %d slices)", R, S); return B200GS_EINVAL; }
+  for (int k = 0; k < S; ++k)
+    if (plan[PLAN_G + k + 1] < plan[PLAN_G + k] || plan[PLAN_OFF + k + 1] < plan[PLAN_OFF + k]) { set_error("slice plan not ascending"); return B200GS_EINVAL; }
+  if (S > 1 && a->exact_lists) { set_error("depth slices need the culled emission"); return B200GS_EINVAL; }
   if (R > 0 && (!a->binning || a->binning_bytes < b200gs_binning_bytes(R))) { set_error("binning scratch too small"); return B200GS_ESIZE; }
   GaussGeom g = GaussGeom::carve(align128(a->geom), a->P, nullptr);
   GaussImage im = GaussImage::carve(align128(a->img), a->width, a->height, nullptr);
   Binning b = Binning::carve(R > 0 ? align128(a->binning) : nullptr, R, nullptr);
   BinJob j{};
-  const int g01[2] = {0, a->P}, off01[2] = {0, R};           // one depth slice
   j.order = g.order.vals_a; j.rects = g.rects; j.offsets = g.point_offsets;
-  j.cull = a->exact_lists != 0 ? nullptr : g.cull; j.cull_for_hits = g.cull; j.rows = nullptr;
+  j.cull = a->exact_lists != 0 ? nullptr : g.cull; j.cull_for_hits = g.cull; j.rows = &g.rows;
   j.P = a->P; j.W = a->width; j.H = a->height; j.R = R;
-  j.slices = 1; j.g = g01; j.off = off01;
-  j.ranges = im.ranges; j.cranges = im.cranges; j.tile_done = nullptr; j.live = nullptr;
+  j.slices = S; j.g = plan + PLAN_G; j.off = plan + PLAN_OFF;
+  j.ranges = im.ranges; j.cranges = im.cranges; j.tile_done = im.tile_done; j.live = im.live;
   j.debug = a->debug != 0; j.audit = false;
   rc = bin_clear(b, j, s);
   if (rc) return rc;
-  if (R > 0) {
-    size_t zcursor = 0;
-    rc = bin_slice(j, 0, b, zcursor, s);
+  if (S > 1) {
+    const uint32_t tiles = (uint32_t)j.tiles();
+    B200GS_CUDA(cudaMemsetAsync(im.tile_done, 0, tiles, s));
+    const uint32_t live0[4] = {tiles, 0u, 0u, 0u};
+    B200GS_CUDA(cudaMemcpyAsync(im.live, live0, sizeof(live0), cudaMemcpyHostToDevice, s));
+  }
+  size_t zcursor = 0;
+  for (int k = 0; k < S; ++k) {
+    if (R > 0) {
+      rc = bin_slice(j, k, b, zcursor, s);
+      if (rc) return rc;
+    }
+    rc = gauss_composite_forward(*a, g, im, b, k, S, s);
     if (rc) return rc;
   }
-  return gauss_composite_forward(*a, g, im, b, s);
+  return B200GS_OK;
 }
 
 int b200gs_gauss_backward(const b200gs_gauss_bwd* a, void* stream) {

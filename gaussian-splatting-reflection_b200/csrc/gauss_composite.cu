@@ -52,6 +52,14 @@ struct GCompFwdArgs {
   float* out_normal;
   float* out_refl;
   float* out_invdepth;
+  // depth slices (common.cuh, as in surfel_composite_fwd.cu): this launch composites slice k of S
+  int k, S;
+  const uint2* uranges;       // slice k's ranges in the UNcompacted list (their lengths number the contributors)
+  const uint32_t* base_k;     // [tiles] list position at which slice k starts in every tile
+  uint32_t* base_next;        // [tiles] the same for slice k+1 (written here)
+  uint8_t* tile_done;         // [tiles] set when every pixel of the tile has saturated
+  uint32_t* live;             // [0] tiles not done
+  float* state;               // [GSTATE_PLANES,N] compositing state of unfinished pixels between slices
 };
 
 __global__ void __launch_bounds__(GBATCH) gauss_composite_fwd_kernel(const GCompFwdArgs a) {
@@ -69,6 +77,9 @@ __global__ void __launch_bounds__(GBATCH) gauss_composite_fwd_kernel(const GComp
   const float fx = (float)pxi, fy = (float)pyi;
   const size_t N = (size_t)a.W * a.H;
   const size_t pix_id = (size_t)a.W * pyi + pxi;
+  const bool sliced = a.S > 1;
+  if (sliced && a.k > 0 && a.tile_done[tile]) return;      // finished (and its outputs written) by an earlier slice
+  const uint32_t base = a.k > 0 ? a.base_k[tile] : 0u;     // contributors are numbered through all slices of the tile
   const uint2 range = a.ranges[tile];
   const int n = (int)(range.y - range.x);
   const int rounds = (n + GBATCH - 1) / GBATCH;
@@ -77,6 +88,15 @@ __global__ void __launch_bounds__(GBATCH) gauss_composite_fwd_kernel(const GComp
   float T = 1.0f;
   uint32_t last_contributor = 0;
   float C0 = 0.f, C1 = 0.f, C2 = 0.f, N0 = 0.f, N1 = 0.f, N2 = 0.f, refl = 0.f, invd = 0.f;
+  if (sliced && a.k > 0 && inside) {                        // pick up where the previous slice left this pixel
+    const float* st = a.state + pix_id;
+    const float Ts = st[0];
+    done = Ts < 0.0f; T = fabsf(Ts);                        // T >= 1e-4 > 0: the sign carries `done`
+    C0 = st[1 * N]; C1 = st[2 * N]; C2 = st[3 * N];
+    N0 = st[4 * N]; N1 = st[5 * N]; N2 = st[6 * N];
+    refl = st[7 * N]; invd = st[8 * N];
+    last_contributor = __float_as_uint(st[9 * N]);
+  }
 
   const uint32_t* pl = a.point_list + range.x;
   const uint8_t* ph = a.hit + range.x;
@@ -135,13 +155,33 @@ __global__ void __launch_bounds__(GBATCH) gauss_composite_fwd_kernel(const GComp
         refl = __fmaf_rn(T, __fmul_rn(e.alpha, q1.w), refl);
         invd = __fmaf_rn(T, __fmul_rn(e.alpha, q1.z), invd);
         T = test_T;
-        last_contributor = s_pos[buf][j] + 1u;   // 1-based position in the tile's (full) list
+        last_contributor = base + s_pos[buf][j] + 1u;   // 1-based position in the tile's (full) list
       }
     }
   }
   cp_async_wait_all();
 
-  if (inside) {  // forward.cu:395-410
+  bool finalize = true;
+  if (sliced) {
+    const bool last = a.k == a.S - 1;
+    const bool all_done = __syncthreads_count(done) == GBATCH;
+    finalize = last || all_done;
+    if (t == 0 && !last) {
+      const uint2 ur = a.uranges[tile];
+      a.base_next[tile] = base + (ur.y - ur.x);
+      if (all_done) { a.tile_done[tile] = 1; atomicSub(a.live, 1u); }   // later slices emit nothing into this tile
+    }
+    if (!finalize && inside) {
+      float* st = a.state + pix_id;
+      st[0] = done ? -T : T;
+      st[1 * N] = C0; st[2 * N] = C1; st[3 * N] = C2;
+      st[4 * N] = N0; st[5 * N] = N1; st[6 * N] = N2;
+      st[7 * N] = refl; st[8 * N] = invd;
+      st[9 * N] = __uint_as_float(last_contributor);
+    }
+  }
+
+  if (finalize && inside) {  // forward.cu:395-410
     a.accum[pix_id] = T;
     a.n_contrib[pix_id] = last_contributor;
     a.out_color[pix_id] = __fmaf_rn(T, a.bg[0], C0);
@@ -156,12 +196,17 @@ __global__ void __launch_bounds__(GBATCH) gauss_composite_fwd_kernel(const GComp
 }
 
 int gauss_composite_forward(const b200gs_gauss_fwd& f, const GaussGeom& g, const GaussImage& im, const Binning& b,
-                            cudaStream_t s) {
+                            int k, int S, cudaStream_t s) {
   GCompFwdArgs a;
   a.W = f.width; a.H = f.height;
   a.gx = (f.width + TILE_X - 1) / TILE_X;
   const int gy = (f.height + TILE_Y - 1) / TILE_Y;
-  a.ranges = im.cranges; a.point_list = b.comp_id; a.list_pos = b.comp_pos; a.rec = g.rec; a.hit = b.comp_hit; a.bg = f.background;
+  const size_t tiles = (size_t)a.gx * gy;
+  a.k = k; a.S = S;
+  a.uranges = im.ranges + (size_t)k * (tiles + 1);
+  a.base_k = im.tile_base + (size_t)k * tiles; a.base_next = im.tile_base + (size_t)(k + 1) * tiles;
+  a.tile_done = im.tile_done; a.live = im.live; a.state = im.state;
+  a.ranges = im.cranges + (size_t)k * (tiles + 1); a.point_list = b.comp_id; a.list_pos = b.comp_pos; a.rec = g.rec; a.hit = b.comp_hit; a.bg = f.background;
   a.accum = im.accum; a.n_contrib = im.n_contrib;
   a.out_color = f.out_color; a.out_normal = f.out_normal; a.out_refl = f.out_refl; a.out_invdepth = f.out_invdepth;
   StageScope _t(ST_COMPOSITE_FWD, s);
@@ -186,6 +231,9 @@ struct GCompBwdArgs {
   const float* dL_drefl;     // [N] or NULL
   const float* dL_dinvd;     // [N] or NULL
   float* acc;                // [P, GACC_STRIDE]
+  int tiles;
+  const int* plan;            // device copy of the forward's slice plan ([1] = S)
+  const uint32_t* tile_base;  // [MAX_SLICES+1][tiles]
 };
 
 __global__ void __launch_bounds__(GBATCH, B200GS_GBWD_CTAS) gauss_composite_bwd_kernel(const GCompBwdArgs a) {
@@ -194,7 +242,8 @@ __global__ void __launch_bounds__(GBATCH, B200GS_GBWD_CTAS) gauss_composite_bwd_
   __shared__ uint32_t s_pos[2][GBATCH];
   __shared__ uint8_t s_hit[2][GBATCH];
   __shared__ uint32_t s_last[GBATCH / 32];
-  __shared__ int s_n;                   // live prefix of the tile's compacted list
+  __shared__ uint32_t s_tile_last;
+  __shared__ int s_n;                   // live prefix of the slice's compacted list
 
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const int tile = blockIdx.x;
@@ -206,8 +255,6 @@ __global__ void __launch_bounds__(GBATCH, B200GS_GBWD_CTAS) gauss_composite_bwd_
   const float fx = (float)pxi, fy = (float)pyi;
   const size_t N = (size_t)a.W * a.H;
   const size_t pix_id = (size_t)a.W * pyi + pxi;
-  const uint2 range = a.ranges[tile];
-  if (range.y == range.x) return;
 
   // lane -> accumulator component owned after the reduce-scatter (16 values, 32 lanes)
   const int b16 = (lane >> 4) & 1, b8 = (lane >> 3) & 1, b4 = (lane >> 2) & 1, b2 = (lane >> 1) & 1;
@@ -234,31 +281,47 @@ __global__ void __launch_bounds__(GBATCH, B200GS_GBWD_CTAS) gauss_composite_bwd_
 
   float acc_q = 0.f, last_q = 0.f, acc_m = 0.f, last_m = 0.f, last_alpha = 0.f;
 
-  const uint32_t* pl = a.point_list + range.x;
-  const uint8_t* ph = a.hit + range.x;
-  const uint32_t* pp = a.list_pos + range.x;
-
   // Entries at or behind the last contributor of every pixel of the tile are never used
-  // (backward.cu:560: `contributor >= last_contributor` -> continue): list positions ascend, so
-  // the live part is a prefix of the compacted list; find its length by bisection.
+  // (backward.cu:560: `contributor >= last_contributor` -> continue).
   const uint32_t warp_last = __reduce_max_sync(0xffffffffu, inside ? last_contributor : 0u);
   if (lane == 0) s_last[warp] = warp_last;
   __syncthreads();
   if (t == 0) {
-    uint32_t tile_last = 0;
+    uint32_t tl = 0;
 #pragma unroll
-    for (int w = 0; w < GBATCH / 32; ++w) tile_last = max(tile_last, s_last[w]);
-    int lo = 0, hi = (int)(range.y - range.x);     // first index with pos >= tile_last
+    for (int w = 0; w < GBATCH / 32; ++w) tl = max(tl, s_last[w]);
+    s_tile_last = tl;
+  }
+  __syncthreads();
+  const uint32_t tile_last = s_tile_last;
+  if (tile_last == 0u) return;
+
+  // The tile's list is the concatenation of its depth slices' lists (one slice unless the forward was sliced): walk
+  // the slices back to front, each slice's entries back to front.  The per-pixel recurrences simply carry on.
+  const int S = a.plan[1];
+  for (int sl = S - 1; sl >= 0; --sl) {
+  const uint32_t base = sl == 0 ? 0u : a.tile_base[(size_t)sl * a.tiles + tile];   // list position of the slice's first entry
+  if (base >= tile_last) continue;
+  const uint2 range = a.ranges[(size_t)sl * (a.tiles + 1) + tile];
+  if (range.y == range.x) continue;
+  const uint32_t* pl = a.point_list + range.x;
+  const uint8_t* ph = a.hit + range.x;
+  const uint32_t* pp = a.list_pos + range.x;
+  // list positions ascend, so the live part is a prefix of the slice's compacted list; find its length by bisection
+  __syncthreads();                                  // everyone has left the previous slice's shared buffers
+  if (t == 0) {
+    const uint32_t lim = tile_last - base;
+    int lo = 0, hi = (int)(range.y - range.x);     // first index with pos >= lim
     while (lo < hi) {
       const int mid = (lo + hi) >> 1;
-      if (pp[mid] < tile_last) lo = mid + 1; else hi = mid;
+      if (pp[mid] < lim) lo = mid + 1; else hi = mid;
     }
     s_n = lo;
   }
   __syncthreads();
   const int n = s_n;
   const int rounds = (n + GBATCH - 1) / GBATCH;
-  if (n == 0) return;
+  if (n == 0) continue;
 
   unsigned hit_cur = 0u, hit_next = 0u;
   uint32_t pos_next = 0u;
@@ -297,11 +360,11 @@ __global__ void __launch_bounds__(GBATCH, B200GS_GBWD_CTAS) gauss_composite_bwd_
     for (int r = 0; r < (count + 31) >> 5; ++r) {
       // entries of other warp blocks, and entries behind every pixel's last contributor, are skipped
       const int en = r * 32 + lane;
-      unsigned m = __ballot_sync(0xffffffffu, en < count && ((s_hit[buf][en] >> warp) & 1u) && s_pos[buf][en] < warp_last);
+      unsigned m = __ballot_sync(0xffffffffu, en < count && ((s_hit[buf][en] >> warp) & 1u) && base + s_pos[buf][en] < warp_last);
       while (m) {
         const int j = r * 32 + __ffs(m) - 1;
         m &= m - 1;
-        const uint32_t contributor = s_pos[buf][j];   // 0-based position in the tile's full list
+        const uint32_t contributor = base + s_pos[buf][j];   // 0-based position in the tile's full list
         const float4 q0 = rb[j].q[0], q1 = rb[j].q[1];
         GaussEval e;
         bool c = inside && contributor < last_contributor;
@@ -359,6 +422,7 @@ __global__ void __launch_bounds__(GBATCH, B200GS_GBWD_CTAS) gauss_composite_bwd_
     }
   }
   cp_async_wait_all();
+  }   // slices
 }
 
 int gauss_composite_backward(const b200gs_gauss_bwd& f, const GaussGeom& g, const GaussImage& im, const Binning& b,
@@ -371,6 +435,7 @@ int gauss_composite_backward(const b200gs_gauss_bwd& f, const GaussGeom& g, cons
   a.accum = im.accum; a.n_contrib = im.n_contrib;
   a.dL_dpix = f.dL_dout_color; a.dL_dnormal = f.dL_dout_normal; a.dL_drefl = f.dL_dout_refl; a.dL_dinvd = f.dL_dout_invdepth;
   a.acc = acc;
+  a.tiles = a.gx * gy; a.plan = g.plan; a.tile_base = im.tile_base;
   StageScope _t(ST_COMPOSITE_BWD, s);
   B200GS_CUDA(cudaMemsetAsync(acc, 0, (size_t)f.P * GACC_STRIDE * sizeof(float), s));
   gauss_composite_bwd_kernel<<<a.gx * gy, GBATCH, 0, s>>>(a);

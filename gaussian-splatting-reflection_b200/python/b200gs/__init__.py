@@ -76,7 +76,7 @@ class GaussFwd(C.Structure):
         ("viewmatrix", _p), ("projmatrix", _p), ("campos", _p),
         ("geom", _p), ("geom_bytes", _sz), ("img", _p), ("img_bytes", _sz), ("binning", _p), ("binning_bytes", _sz),
         ("out_color", _p), ("out_invdepth", _p), ("out_normal", _p), ("out_refl", _p), ("radii", _p),
-        ("exact_lists", _i),
+        ("exact_lists", _i), ("depth_slices", _i), ("slice_frac", _f * 7),
     ]
 
 
@@ -168,7 +168,7 @@ gauss_geom_bytes = _sig("b200gs_gauss_geom_bytes", _sz, _i)
 gauss_image_bytes = _sig("b200gs_gauss_image_bytes", _sz, _i, _i)
 gauss_accum_bytes = _sig("b200gs_gauss_accum_bytes", _sz, _i)
 gauss_forward_stage1 = _sig("b200gs_gauss_forward_stage1", _i, C.POINTER(GaussFwd), C.POINTER(_i), _p)
-gauss_forward_stage2 = _sig("b200gs_gauss_forward_stage2", _i, C.POINTER(GaussFwd), _i, _p)
+gauss_forward_stage2 = _sig("b200gs_gauss_forward_stage2", _i, C.POINTER(GaussFwd), C.POINTER(_i), _p)
 gauss_backward = _sig("b200gs_gauss_backward", _i, C.POINTER(GaussBwd), _p)
 gauss_inspect_geom = _sig("b200gs_gauss_inspect_geom", _i, _p, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p)
 gauss_inspect_image = _sig("b200gs_gauss_inspect_image", _i, _p, _i, _i, _p, _p, _p, _p)

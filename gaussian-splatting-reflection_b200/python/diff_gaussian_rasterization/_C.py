@@ -26,9 +26,13 @@ def _stream():
 
 def rasterize_gaussians(background, means3D, colors, normals, refl_strengths, opacity, scales, rotations, scale_modifier,
                         cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh,
-                        degree, campos, prefiltered, antialiasing, debug, *, exact_lists=False):
+                        degree, campos, prefiltered, antialiasing, debug, *, exact_lists=False, depth_slices=0,
+                        slice_fractions=None):
     """-> (rendered, out_color[3,H,W], radii[P], geomBuffer, binningBuffer, imgBuffer, out_invdepth[1,H,W],
-    normal_map[3,H,W], refl_strength_map[1,H,W])   (G/rasterize_points.cu:39-141)"""
+    normal_map[3,H,W], refl_strength_map[1,H,W])   (G/rasterize_points.cu:39-141)
+
+    Keyword-only, per call (no reference counterpart): exact_lists, depth_slices, slice_fractions -- the fields of the
+    same names of b200gs_gauss_fwd (include/b200gs.h), as in diff_surfel_rasterization._C.rasterize_gaussians."""
     if means3D.dim() != 2 or means3D.size(1) != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")
     background = _cuda_f32("background", background)
@@ -71,15 +75,18 @@ def rasterize_gaussians(background, means3D, colors, normals, refl_strengths, op
                 geom=geom.data_ptr(), geom_bytes=geom.numel(), img=img.data_ptr(), img_bytes=img.numel(),
                 binning=None, binning_bytes=0, out_color=out_color.data_ptr(), out_invdepth=out_invdepth.data_ptr(),
                 out_normal=out_normal.data_ptr(), out_refl=out_refl.data_ptr(), radii=radii.data_ptr(),
-                exact_lists=int(bool(exact_lists)))
-            n = C.c_int(0)
+                exact_lists=int(bool(exact_lists)), depth_slices=int(depth_slices))
+            if slice_fractions:
+                for i, fr in enumerate(list(slice_fractions)[:7]):
+                    a.slice_frac[i] = float(fr)
+            plan = (C.c_int * _b.PLAN_INTS)()
             st = _stream()
-            _b.check(_b.gauss_forward_stage1(C.byref(a), C.byref(n), st))
-            rendered = n.value
+            _b.check(_b.gauss_forward_stage1(C.byref(a), plan, st))
+            rendered = plan[0]
             binning = torch.empty((_b.binning_bytes(rendered),), **u8)
             a.binning = binning.data_ptr()
             a.binning_bytes = binning.numel()
-            _b.check(_b.gauss_forward_stage2(C.byref(a), rendered, st))
+            _b.check(_b.gauss_forward_stage2(C.byref(a), plan, st))
     return rendered, out_color, radii, geom, binning, img, out_invdepth, out_normal, out_refl
 
 

@@ -269,12 +269,15 @@ typedef struct b200gs_gauss_fwd {
   float* out_refl;        /* [1,H,W] */
   int* radii;             /* [P]     */
   int exact_lists;        /* instance-list mode of this call (see b200gs_surfel_fwd) */
+  int depth_slices;       /* as in b200gs_surfel_fwd: 0 automatic, 1 one slice, n <= B200GS_MAX_SLICES at most n slices */
+  float slice_frac[7];    /* as in b200gs_surfel_fwd */
 } b200gs_gauss_fwd;
 
 size_t b200gs_gauss_geom_bytes(int P);
 size_t b200gs_gauss_image_bytes(int width, int height);
-int b200gs_gauss_forward_stage1(const b200gs_gauss_fwd* a, int* num_rendered, void* stream);
-int b200gs_gauss_forward_stage2(const b200gs_gauss_fwd* a, int num_rendered, void* stream);
+/* The plan is the surfel path's: plan[0] = num_rendered, plan[1] = depth slices, ... (B200GS_PLAN_INTS ints). */
+int b200gs_gauss_forward_stage1(const b200gs_gauss_fwd* a, int* plan, void* stream);
+int b200gs_gauss_forward_stage2(const b200gs_gauss_fwd* a, const int* plan, void* stream);
 
 /* All dL_d* outputs must be zero-filled by the caller (G/rasterize_points.cu:196-226). */
 typedef struct b200gs_gauss_bwd {

@@ -229,12 +229,16 @@ def gauss_scene(scene):
 
 
 def gauss_forward(Cmod, scene, cam, bg=(0.0, 0.0, 0.0), sh_degree=3, scale_modifier=1.0, antialiasing=False,
-                  colors_precomp=None, cov3D_precomp=None, debug=False):
+                  colors_precomp=None, cov3D_precomp=None, debug=False, exact=None, depth_slices=None,
+                  slice_fractions=None):
     dev = scene["means3D"].device
     e = torch.empty((0,), dtype=torch.float32, device=dev)
     bgt = _bg(bg, dev)
     use_sh = colors_precomp is None
-    kw = dict(exact_lists=_EXACT[0]) if _is_new(Cmod) else {}
+    kw = {}
+    if _is_new(Cmod):
+        kw = dict(exact_lists=_EXACT[0] if exact is None else bool(exact),
+                  depth_slices=_SLICES[0] if depth_slices is None else depth_slices, slice_fractions=slice_fractions)
     out = Cmod.rasterize_gaussians(
         bgt, scene["means3D"], e if use_sh else colors_precomp, scene["normals"], scene["refl"], scene["opacities"],
         e if cov3D_precomp is not None else scene["scales3"], e if cov3D_precomp is not None else scene["rotations"],
