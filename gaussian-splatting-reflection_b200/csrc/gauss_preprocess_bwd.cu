@@ -61,6 +61,15 @@ __global__ void __launch_bounds__(256) gauss_preprocess_bwd_kernel(const GPreBwd
       g[4 * k] = v.x; g[4 * k + 1] = v.y; g[4 * k + 2] = v.z; g[4 * k + 3] = v.w;
     }
   }
+  // A visible Gaussian no pixel blended (occluded, or below the 1/255 cut everywhere) has an all-zero accumulator
+  // row: every gradient derived from it below is an exact zero (finite factors times 0), which the caller's
+  // zero-filled outputs (G/rasterize_points.cu:186-199 does torch::zeros) already hold -- as in the surfel kernel.
+  {
+    bool any = false;
+#pragma unroll
+    for (int k = 0; k < GACC_STRIDE; ++k) any = any || (g[k] != 0.0f);
+    if (!any) return;
+  }
   a.dL_dmeans2D[3 * idx] = g[2]; a.dL_dmeans2D[3 * idx + 1] = g[3];
   if (a.dL_dconic) reinterpret_cast<float4*>(a.dL_dconic)[idx] = make_float4(g[4], g[5], 0.f, g[6]);
   a.dL_dcolors[3 * idx] = g[8]; a.dL_dcolors[3 * idx + 1] = g[9]; a.dL_dcolors[3 * idx + 2] = g[10];

@@ -53,11 +53,13 @@ def rasterize_gaussians(background, means3D, colors, normals, refl_strengths, op
     f32 = dict(dtype=torch.float32, device=dev)
     u8 = dict(dtype=torch.uint8, device=dev)
     with torch.cuda.device(dev):
-        out_color = torch.zeros((NUM_CHANNELS, H, W), **f32)
-        out_normal = torch.zeros((3, H, W), **f32)
-        out_invdepth = torch.zeros((1, H, W), **f32)
-        out_refl = torch.zeros((1, H, W), **f32)
-        radii = torch.zeros((P,), dtype=torch.int32, device=dev)
+        # the reference zero-fills these (G/rasterize_points.cu:78-84); the kernels write every pixel and every radius
+        # themselves, so only the P == 0 short-circuit needs zeros.  One allocation for the eight output planes.
+        new = torch.zeros if P == 0 else torch.empty
+        planes = new((NUM_CHANNELS + 3 + 1 + 1, H, W), **f32)
+        out_color, out_normal = planes[:NUM_CHANNELS], planes[NUM_CHANNELS:NUM_CHANNELS + 3]
+        out_invdepth, out_refl = planes[NUM_CHANNELS + 3:NUM_CHANNELS + 4], planes[NUM_CHANNELS + 4:]
+        radii = new((P,), dtype=torch.int32, device=dev)
         geom, binning, img = torch.empty((0,), **u8), torch.empty((0,), **u8), torch.empty((0,), **u8)
         rendered = 0
         if P != 0:
@@ -119,17 +121,17 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, normals, re
     M = sh.size(1) if sh.numel() else 0
     o = dict(dtype=torch.float32, device=means3D.device)
     with torch.cuda.device(means3D.device):
-        dL_dmeans3D = torch.zeros((P, 3), **o)
-        dL_dmeans2D = torch.zeros((P, 3), **o)
-        dL_dcolors = torch.zeros((P, NUM_CHANNELS), **o)
-        dL_dnormals = torch.zeros((P, 3), **o)
-        dL_dopacity = torch.zeros((P, 1), **o)
-        dL_dcov3D = torch.zeros((P, 6), **o)
-        dL_dsh = torch.zeros((P, M, 3), **o)
-        dL_dscales = torch.zeros((P, 3), **o)
-        dL_drotations = torch.zeros((P, 4), **o)
-        dL_dinvdepths = torch.zeros((P, 1) if has_inv else (0, 1), **o)
-        dL_drefl = torch.zeros((P, 1) if has_refl else (0, 1), **o)
+        # The kernels only write the rows of Gaussians a pixel blended; everything else must read 0
+        # (G/rasterize_points.cu:186-199 zero-fills eleven tensors).  One zero-filled allocation, eleven views.
+        widths = [3, 3, NUM_CHANNELS, 3, 1, 6, 3 * M, 3, 4, 1 if has_inv else 0, 1 if has_refl else 0]
+        flat = torch.zeros((P * sum(widths),), **o)
+        blocks, off = [], 0
+        for wd in widths:
+            blocks.append(flat[off:off + P * wd].view(P if wd else 0, max(wd, 1)))
+            off += P * wd
+        (dL_dmeans3D, dL_dmeans2D, dL_dcolors, dL_dnormals, dL_dopacity, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations,
+         dL_dinvdepths, dL_drefl) = blocks
+        dL_dsh = dL_dsh.view(P, M, 3) if M else torch.zeros((P, 0, 3), **o)
         if P != 0:
             accum = torch.empty((_b.gauss_accum_bytes(P),), dtype=torch.uint8, device=means3D.device)
             a = _b.GaussBwd(

@@ -10,17 +10,18 @@ import scenes
 
 N = 50
 for name in sys.argv[1:] or ["c1", "c2"]:
-    sc_np, cam_np = scenes.build(name)
+    gauss = name.endswith("g")             # c3g: c3 through the 3DGS (EWA) rasterizer
+    sc_np, cam_np = scenes.build(name[:-1] if gauss else name)
     sc, cam = hz.to_dev(sc_np), hz.to_dev(cam_np)
     W, H = cam_np["width"], cam_np["height"]
-    grads = hz.to_dev(scenes.upstream_grads(W, H))
-    C = hz.new_surfel_C()
-
-    def fwd():
-        return hz.surfel_forward(C, sc, cam)
-
-    def fb():
-        hz.surfel_backward(C, sc, cam, fwd(), grads)
+    if gauss:
+        sc, grads, C = hz.gauss_scene(sc), hz.to_dev(hz.gauss_grads(W, H)), hz.new_gauss_C()
+        fwd = lambda: hz.gauss_forward(C, sc, cam)                          # noqa: E731
+        fb = lambda: hz.gauss_backward(C, sc, cam, fwd(), grads)            # noqa: E731
+    else:
+        grads, C = hz.to_dev(scenes.upstream_grads(W, H)), hz.new_surfel_C()
+        fwd = lambda: hz.surfel_forward(C, sc, cam)                         # noqa: E731
+        fb = lambda: hz.surfel_backward(C, sc, cam, fwd(), grads)           # noqa: E731
 
     out = {"config": name}
     for label, fn in (("fwd", fwd), ("fwd_bwd", fb)):
