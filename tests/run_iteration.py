@@ -3,7 +3,7 @@ per-iteration device step through this repo's sm_100a kernels, next to the same 
 pieces on the same GPU:
 
   step                          this repo                                  reference arm
-  rasterize fwd + bwd           diff_surfel_rasterization (libb200gs)      the same autograd class on oracle/_ref/ref_surfel_C
+  rasterize fwd + bwd           diff_surfel_rasterization (libb200gs)      the reference's own package on oracle/_ref/ref_surfel_C
   surface attributes            b200gs.shade.surface_attributes            the torch lines (oracle/shade_oracle.py on the device)
   reflection pass               b200gs.shade.reflect_shade                 torch lines + oracle/_ref/ref_cubemap_C
   L1 + SSIM                     fused_ssim (libb200gs)                     oracle/_ref/ref_ssim_C through the same autograd shape
@@ -61,8 +61,15 @@ def make_model(sc_np):
 
 
 def build_arm(arm, sc_np, cam_np):
-    import diff_surfel_rasterization as dsr
     from oracle import shade_oracle as so
+    if arm == "new":
+        import diff_surfel_rasterization as dsr
+    else:      # the reference's own python package on its own extension (tests/refpy.py)
+        import refpy
+        ref_arm = refpy.load_arm("ref")
+        if ref_arm is None:
+            return None
+        dsr = ref_arm.diff_surfel_rasterization
     view = View(cam_np)
     W, H = view.image_width, view.image_height
     P = sc_np["means3D"].shape[0]
@@ -138,7 +145,6 @@ def build_arm(arm, sc_np, cam_np):
     state = {"loss": None}
 
     def iteration(do_step=True):
-        dsr._C = C_new if new else C_ref
         try:
             m2d = torch.zeros_like(params["xyz"], requires_grad=True)
             shs = torch.cat((params["f_dc"], params["f_rest"]), dim=1)                    # get_features
@@ -198,7 +204,7 @@ def build_arm(arm, sc_np, cam_np):
                     opt.zero_grad(set_to_none=True)
             state["loss"] = loss.detach()
         finally:
-            dsr._C = C_new
+            pass
     return iteration, params, state
 
 
