@@ -69,6 +69,8 @@ def parse():
     ap.add_argument("--exact-lists", action="store_true",
                     help="time the exact-lists mode (the reference's instance lists bit for bit) instead of the "
                          "default culled emission")
+    ap.add_argument("--no-pipeline", action="store_true",
+                    help="diagnosis: every view start to end on one stream (no stage-1 prefetch of the next view)")
     ap.add_argument("--nccl-allreduce", action="store_true",
                     help="N > 1: reduce the arena with ncclAllReduce instead of the library's NVLS multimem kernel")
     return ap.parse_args()
@@ -264,6 +266,8 @@ def main():
         from b200gs.dp import GradArena
         arena = GradArena(P, M, "cuda", accumulate=True, symmetric=(world > 1 and not a.nccl_allreduce))
 
+    pipelined = new and not a.no_pipeline and len(cams) > 1
+    side = torch.cuda.Stream() if pipelined else None
     ev = {}                                                # optional event marks of the scale pass
 
     def mark(name):
@@ -278,7 +282,21 @@ def main():
         if arena is not None:
             arena.zero_()
         f = b = None
-        for vi, c in enumerate(cams):
+        if new and pipelined:
+            # software pipeline over the batch's views: stage 1 of view i+1 (preprocess, depth order, scan, plan and
+            # the forward's host sync) runs on a side stream while stage 2 + backward of view i occupy the SMs
+            main = torch.cuda.current_stream()
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
+                prep = hz.surfel_prepare(Cmod, sc, cams[0], exact=exact)
+            for vi, c in enumerate(cams):
+                f = hz.surfel_finish(Cmod, prep)
+                b = hz.surfel_backward(Cmod, sc, c, f, grads, grad_arena=arena)
+                if vi + 1 < len(cams):
+                    with torch.cuda.stream(side):
+                        prep = hz.surfel_prepare(Cmod, sc, cams[vi + 1], exact=exact)
+            main.wait_stream(side)
+        for vi, c in enumerate(cams if not (new and pipelined) else []):
             if new:
                 f = hz.surfel_forward(Cmod, sc, c, exact=exact)
                 b = hz.surfel_backward(Cmod, sc, c, f, grads, grad_arena=arena)
@@ -474,26 +492,48 @@ def main():
                     for t in list(leaves.values()) + [m2d]:
                         t.grad = None
                 total = None
-                nxt = upload(hosts[0])
-                for vi in range(len(hosts)):             # this rank's views of the batch; the gradients are summed
-                    dev, e = nxt
-                    if vi + 1 < len(hosts):
-                        nxt = upload(hosts[vi + 1])      # the next view's inputs travel while this one renders
-                    cur = torch.cuda.current_stream()
-                    cur.wait_event(e)
-                    for t in dev.values():
-                        t.record_stream(cur)
+                inputs = dict(means3D=leaves["means3D"], means2D=m2d, opacities=leaves["opacities"], shs=leaves["shs"],
+                              refl_strengths=leaves["refl"], scales=leaves["scales"], rotations=leaves["rotations"],
+                              env_scope_mask=mask)
+
+                def module(dev):
                     rs = dsr.GaussianRasterizationSettings(
                         image_height=H, image_width=W, tanfovx=cam_np["tanfovx"], tanfovy=cam_np["tanfovy"], bg=dev["bg"],
                         scale_modifier=1.0, viewmatrix=dev["viewmatrix"], projmatrix=dev["projmatrix"], sh_degree=3,
                         campos=dev["campos"], prefiltered=False, debug=False)
-                    color, radii, allmap, refl_map, _ = dsr.GaussianRasterizer(rs, **kw)(
-                        means3D=leaves["means3D"], means2D=m2d, opacities=leaves["opacities"], shs=leaves["shs"],
-                        refl_strengths=leaves["refl"], scales=leaves["scales"], rotations=leaves["rotations"],
-                        env_scope_mask=mask)
+                    return dsr.GaussianRasterizer(rs, **kw)
+
+                def prepared(view):
+                    """this library only: stage 1 of that view's forward on the side stream, now"""
+                    dev, e = view
+                    side.wait_event(e)
+                    for t in dev.values():
+                        t.record_stream(side)
+                    with torch.cuda.stream(side):
+                        return module(dev).prepare(**inputs)
+
+                cur = torch.cuda.current_stream()
+                nxt = upload(hosts[0])
+                mod_next = None
+                if pipelined:
+                    side.wait_stream(cur)
+                    mod_next = prepared(nxt)
+                for vi in range(len(hosts)):             # this rank's views of the batch; the gradients are summed
+                    dev, e = nxt
+                    if vi + 1 < len(hosts):
+                        nxt = upload(hosts[vi + 1])      # the next view's inputs travel while this one renders
+                    cur.wait_event(e)
+                    for t in dev.values():
+                        t.record_stream(cur)
+                    mod = mod_next if pipelined else module(dev)
+                    color, radii, allmap, refl_map, _ = mod(**inputs)
                     loss = (color - dev["target"]).abs().mean() + 1e-3 * allmap[:7].mean() + 1e-3 * refl_map.mean()
                     loss.backward()
+                    if pipelined and vi + 1 < len(hosts):
+                        mod_next = prepared(nxt)         # stage 1 of the next view next to this view's kernels
                     total = loss.detach() if total is None else total + loss.detach()
+                if pipelined:
+                    cur.wait_stream(side)
                 if world > 1:
                     if new:
                         arena.all_reduce()
@@ -508,7 +548,8 @@ def main():
             e2e = {"value": VB * N / (e2e_ms * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": e2e_ms, "ms_per_view": e2e_ms * world / VB,
                    "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4,
                    "api": "diff_surfel_rasterization.GaussianRasterizer (autograd) + L1 loss"
-                          + (", gradients accumulated in the GradArena the leaves' .grad are bound to" if new else "")}
+                          + (", gradients accumulated in the GradArena the leaves' .grad are bound to" if new else "")
+                          + (", stage 1 of the next view prefetched on a side stream (GaussianRasterizer.prepare)" if pipelined else "")}
 
     if rank != 0:
         if world > 1:
@@ -600,7 +641,9 @@ def main():
                    "parallelism": f"view-parallel x{world}, replicated Gaussians" + (", one all-reduce of the [P,59] fp32 gradients per batch" if world > 1 else "")},
         "impl_detail": {"implementation": impl_desc, "instances_emitted": R,
                         "lists": ("exact (reference's lists bit for bit)" if (exact or not new)
-                                  else "culled emission (only instances that can reach alpha >= 1/255)")},
+                                  else "culled emission (only instances that can reach alpha >= 1/255)"),
+                        "view_pipeline": ("stage 1 of view i+1 on a side stream next to stage 2 + backward of view i"
+                                          if pipelined else "none: every view start to end on one stream")},
         "clocks": clocks, "e2e": e2e, "gpu_launches": (int(launches) if launches is not None else None),
         "roofline": roofline, "roofline_hbm": roofline_hbm, "cpu_baseline": cpu, "stages": stage_table,
         "scale": scale, "forward_only": fwd_only,

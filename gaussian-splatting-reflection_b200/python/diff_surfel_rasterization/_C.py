@@ -26,17 +26,16 @@ def _stream():
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
-def rasterize_gaussians(background, means3D, env_scope_mask, colors, refl_strengths, opacity, scales, rotations,
+def rasterize_gaussians_prepare(background, means3D, env_scope_mask, colors, refl_strengths, opacity, scales, rotations,
                         scale_modifier, transMat_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy,
                         image_height, image_width, sh, degree, campos, prefiltered, debug, *, exact_lists=False,
                         cull_audit=False, depth_slices=0, slice_fractions=None):
-    """-> (rendered, out_color[3,H,W], out_others[8,H,W], radii[P], geomBuffer, binningBuffer,
-    imgBuffer, out_refl_strength_map[1,H,W], gaussian_weights[P])   (S/rasterize_points.cu:39-151)
-
-    The 21 positional arguments are the reference's.  Keyword-only extras of this library, per call (the
-    library keeps no mode of its own): exact_lists -- emit the reference's instance lists bit for bit
-    instead of only the reachable instances (include/b200gs.h); cull_audit -- test infrastructure; depth_slices
-    (0 automatic, 1 off, n at most n) / slice_fractions -- the occlusion-aware binning of b200gs_surfel_forward_stage1."""
+    """Stage 1 of `rasterize_gaussians` (same arguments): checks, output / scratch allocation, preprocess, depth order,
+    prefix sum and slice plan on the CURRENT stream, returning after that stream has drained (the one host sync of
+    the forward) with a PreparedForward for `rasterize_gaussians_finish`.  No reference counterpart: the split lets a
+    caller that knows its next camera run this part of the NEXT view on a second (high-priority) stream while the
+    compositing kernels of the current one occupy the SMs (b200gs.dp.ViewPipeline).  The handle keeps every input
+    tensor alive; the parameters must not change between the two calls."""
     if means3D.dim() != 2 or means3D.size(1) != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")
     background = _cuda_f32("background", background)
@@ -103,11 +102,57 @@ def rasterize_gaussians(background, means3D, env_scope_mask, colors, refl_streng
             st = _stream()
             _b.check(_b.surfel_forward_stage1(C.byref(a), plan, st))
             rendered = plan[0]
-            binning = torch.empty((_b.binning_bytes(rendered),), **u8)
+    prep = PreparedForward()
+    prep.a, prep.plan, prep.P, prep.device = (a if P != 0 else None), (plan if P != 0 else None), P, dev
+    prep.outputs = (planes, per_gaussian, out_color, out_others, out_refl, radii, gaussian_weights)
+    prep.scratch = (geom, img)
+    prep.keep = (background, means3D, env_scope_mask, colors, refl_strengths, opacity, scales, rotations,
+                 transMat_precomp, viewmatrix, projmatrix, sh, campos)
+    prep.rendered = rendered
+    return prep
+
+
+class PreparedForward:
+    """What stage 1 of a forward leaves for stage 2: the argument struct, the plan, outputs and scratch."""
+    __slots__ = ("a", "plan", "P", "device", "outputs", "scratch", "keep", "rendered")
+
+
+def rasterize_gaussians_finish(prep):
+    """Stage 2 of a prepared forward on the CURRENT stream (asynchronous): per depth slice emission, tile sort, tile
+    ranges, block masks, compositing.  -> the 9-tuple of `rasterize_gaussians`."""
+    planes, per_gaussian, out_color, out_others, out_refl, radii, gaussian_weights = prep.outputs
+    geom, img = prep.scratch
+    u8 = dict(dtype=torch.uint8, device=prep.device)
+    binning = torch.empty((0,), **u8)
+    if prep.P != 0:
+        with torch.cuda.device(prep.device):
+            cur = torch.cuda.current_stream()
+            for t in (planes, per_gaussian, geom, img):      # allocated on stage 1's stream, used (and later freed) here
+                t.record_stream(cur)
+            a = prep.a
+            binning = torch.empty((_b.binning_bytes(prep.rendered),), **u8)
             a.binning = binning.data_ptr()
             a.binning_bytes = binning.numel()
-            _b.check(_b.surfel_forward_stage2(C.byref(a), plan, st))
-    return rendered, out_color, out_others, radii, geom, binning, img, out_refl, gaussian_weights
+            _b.check(_b.surfel_forward_stage2(C.byref(a), prep.plan, _stream()))
+    return prep.rendered, out_color, out_others, radii, geom, binning, img, out_refl, gaussian_weights
+
+
+def rasterize_gaussians(background, means3D, env_scope_mask, colors, refl_strengths, opacity, scales, rotations,
+                        scale_modifier, transMat_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy,
+                        image_height, image_width, sh, degree, campos, prefiltered, debug, *, exact_lists=False,
+                        cull_audit=False, depth_slices=0, slice_fractions=None):
+    """-> (rendered, out_color[3,H,W], out_others[8,H,W], radii[P], geomBuffer, binningBuffer,
+    imgBuffer, out_refl_strength_map[1,H,W], gaussian_weights[P])   (S/rasterize_points.cu:39-151)
+
+    The 21 positional arguments are the reference's.  Keyword-only extras of this library, per call (the
+    library keeps no mode of its own): exact_lists -- emit the reference's instance lists bit for bit
+    instead of only the reachable instances (include/b200gs.h); cull_audit -- test infrastructure; depth_slices
+    (0 automatic, 1 off, n at most n) / slice_fractions -- the occlusion-aware binning of b200gs_surfel_forward_stage1."""
+    return rasterize_gaussians_finish(rasterize_gaussians_prepare(
+        background, means3D, env_scope_mask, colors, refl_strengths, opacity, scales, rotations, scale_modifier,
+        transMat_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos,
+        prefiltered, debug, exact_lists=exact_lists, cull_audit=cull_audit, depth_slices=depth_slices,
+        slice_fractions=slice_fractions))
 
 
 def rasterize_gaussians_backward(background, means3D, radii, colors, refl_strengths, scales, rotations, scale_modifier,

@@ -10,8 +10,9 @@ call it unchanged.
 Two keyword-only extras exist for callers that know this library (the reference's callers never pass
 them): `exact_lists` (emit the reference's instance lists bit for bit, include/b200gs.h) and `grad_arena`
 (a b200gs.dp.GradArena the backward accumulates the parameter gradients of a batch of views into, for
-the one NCCL all-reduce of view-parallel training).  Both are per-call state of the module instance;
-the library itself keeps no mode.
+the one all-reduce of view-parallel training).  Both are per-call state of the module instance;
+the library itself keeps no mode.  `GaussianRasterizer.prepare(...)` (optional) runs stage 1 of the module's next
+forward() ahead of time, e.g. on a second stream while the previous view's compositing kernels run.
 """
 from typing import NamedTuple
 
@@ -65,10 +66,16 @@ class _RasterizeGaussians(torch.autograd.Function):
         args = (rs.bg, means3D, env_scope_mask, colors_precomp, refl_strengths, opacities, scales, rotations,
                 rs.scale_modifier, cov3Ds_precomp, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy,
                 rs.image_height, rs.image_width, sh, rs.sh_degree, rs.campos, rs.prefiltered, rs.debug)
-        (num_rendered, color, depth, radii, geomBuffer, binningBuffer, imgBuffer, refl_strength_map,
-         gaussian_weights) = _call_with_dump(_C.rasterize_gaussians, args, rs.debug, "snapshot_fw.dump", "forward",
-                                             exact_lists=bool(opts.get("exact_lists", False)),
-                                             depth_slices=int(opts.get("depth_slices", 0)))
+        prepared = opts.get("prepared")
+        if prepared is not None:      # stage 1 already ran (GaussianRasterizer.prepare), possibly on another stream
+            (num_rendered, color, depth, radii, geomBuffer, binningBuffer, imgBuffer, refl_strength_map,
+             gaussian_weights) = _call_with_dump(_C.rasterize_gaussians_finish, (prepared,), rs.debug, "snapshot_fw.dump",
+                                                 "forward")
+        else:
+            (num_rendered, color, depth, radii, geomBuffer, binningBuffer, imgBuffer, refl_strength_map,
+             gaussian_weights) = _call_with_dump(_C.rasterize_gaussians, args, rs.debug, "snapshot_fw.dump", "forward",
+                                                 exact_lists=bool(opts.get("exact_lists", False)),
+                                                 depth_slices=int(opts.get("depth_slices", 0)))
         ctx.raster_settings = rs
         ctx.grad_arena = opts.get("grad_arena")
         ctx.num_rendered = num_rendered
@@ -114,6 +121,7 @@ class GaussianRasterizer(nn.Module):
         self.exact_lists = bool(exact_lists)
         self.grad_arena = grad_arena
         self.depth_slices = int(depth_slices)
+        self._prepared = None
 
     def markVisible(self, positions):
         """Boolean mask of the points in front of the camera's near plane."""
@@ -121,8 +129,8 @@ class GaussianRasterizer(nn.Module):
             rs = self.raster_settings
             return _C.mark_visible(positions, rs.viewmatrix, rs.projmatrix)
 
-    def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, refl_strengths=None, scales=None,
-                rotations=None, cov3D_precomp=None, env_scope_mask=None):
+    @staticmethod
+    def _normalise(means3D, shs, colors_precomp, scales, rotations, cov3D_precomp, env_scope_mask):
         if (shs is None) == (colors_precomp is None):
             raise Exception('Please provide excatly one of either SHs or precomputed colors!')
         have_sr = scales is not None or rotations is not None
@@ -132,14 +140,40 @@ class GaussianRasterizer(nn.Module):
         def empty():
             return torch.empty((0,), dtype=torch.float32, device=means3D.device)
 
-        shs = empty() if shs is None else shs
-        colors_precomp = empty() if colors_precomp is None else colors_precomp
-        scales = empty() if scales is None else scales
-        rotations = empty() if rotations is None else rotations
-        cov3D_precomp = empty() if cov3D_precomp is None else cov3D_precomp
-        env_scope_mask = empty() if env_scope_mask is None else env_scope_mask
+        return tuple(empty() if t is None else t for t in (shs, colors_precomp, scales, rotations, cov3D_precomp,
+                                                           env_scope_mask))
+
+    def prepare(self, means3D, means2D, opacities, shs=None, colors_precomp=None, refl_strengths=None, scales=None,
+                rotations=None, cov3D_precomp=None, env_scope_mask=None):
+        """Optional, no reference counterpart: run stage 1 of the NEXT forward() of this module (preprocess, depth
+        order, prefix sum, slice plan and the forward's one host sync) now, on the CURRENT stream -- typically a
+        second stream, while the compositing kernels of the previous view still occupy the SMs.  forward() must
+        then be called with the same tensors; it only runs stage 2.  The parameters must not change in between."""
+        shs, colors_precomp, scales, rotations, cov3D_precomp, env_scope_mask = self._normalise(
+            means3D, shs, colors_precomp, scales, rotations, cov3D_precomp, env_scope_mask)
+        rs = self.raster_settings
+        with torch.no_grad():
+            prep = _C.rasterize_gaussians_prepare(
+                rs.bg, means3D, env_scope_mask, colors_precomp, refl_strengths, opacities, scales, rotations,
+                rs.scale_modifier, cov3D_precomp, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height,
+                rs.image_width, shs, rs.sh_degree, rs.campos, rs.prefiltered, rs.debug, exact_lists=self.exact_lists,
+                depth_slices=self.depth_slices)
+        self._prepared = (prep, tuple(t.data_ptr() for t in (means3D, opacities, shs, colors_precomp, scales, rotations,
+                                                             cov3D_precomp)))
+        return self
+
+    def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, refl_strengths=None, scales=None,
+                rotations=None, cov3D_precomp=None, env_scope_mask=None):
+        shs, colors_precomp, scales, rotations, cov3D_precomp, env_scope_mask = self._normalise(
+            means3D, shs, colors_precomp, scales, rotations, cov3D_precomp, env_scope_mask)
         opts = None
-        if self.exact_lists or self.grad_arena is not None or self.depth_slices:
-            opts = {"exact_lists": self.exact_lists, "grad_arena": self.grad_arena, "depth_slices": self.depth_slices}
+        prepared, self._prepared = getattr(self, "_prepared", None), None
+        if prepared is not None:
+            prep, ptrs = prepared
+            if ptrs != tuple(t.data_ptr() for t in (means3D, opacities, shs, colors_precomp, scales, rotations, cov3D_precomp)):
+                raise RuntimeError("forward() was given other tensors than the prepare() call before it")
+        if self.exact_lists or self.grad_arena is not None or self.depth_slices or prepared is not None:
+            opts = {"exact_lists": self.exact_lists, "grad_arena": self.grad_arena, "depth_slices": self.depth_slices,
+                    "prepared": prepared[0] if prepared is not None else None}
         return rasterize_gaussians(means3D, means2D, shs, colors_precomp, refl_strengths, opacities, scales, rotations,
                                    cov3D_precomp, self.raster_settings, env_scope_mask, opts)

@@ -76,7 +76,7 @@ def to_dev(d, device="cuda"):
 
 def surfel_forward(Cmod, scene, cam, bg=(0.0, 0.0, 0.0), sh_degree=3, mask=None, scale_modifier=1.0,
                    colors_precomp=None, transMat_precomp=None, debug=False, prefiltered=False, exact=None, cull_audit=False,
-                   depth_slices=None, slice_fractions=None):
+                   depth_slices=None, slice_fractions=None, prepare_only=False):
     """scene/cam: dicts of CUDA tensors (see scenes.py).  Returns the 9-tuple as a dict."""
     dev = scene["means3D"].device
     e = torch.empty((0,), dtype=torch.float32, device=dev)
@@ -89,16 +89,35 @@ def surfel_forward(Cmod, scene, cam, bg=(0.0, 0.0, 0.0), sh_degree=3, mask=None,
     if _is_new(Cmod):
         kw = dict(exact_lists=_EXACT[0] if exact is None else bool(exact), cull_audit=cull_audit,
                   depth_slices=_SLICES[0] if depth_slices is None else depth_slices, slice_fractions=slice_fractions)
-    out = Cmod.rasterize_gaussians(
+    fn = Cmod.rasterize_gaussians_prepare if prepare_only else Cmod.rasterize_gaussians
+    out = fn(
         bgt, scene["means3D"], mask, e if use_sh else colors_precomp, scene["refl"], scene["opacities"],
         e if transMat_precomp is not None else scene["scales"], e if transMat_precomp is not None else scene["rotations"],
         scale_modifier, e if transMat_precomp is None else transMat_precomp, cam["viewmatrix"], cam["projmatrix"],
         cam["tanfovx"], cam["tanfovy"], cam["height"], cam["width"], scene["shs"] if use_sh else e, sh_degree,
         cam["campos"], prefiltered, debug, **kw)
-    keys = ("rendered", "color", "others", "radii", "geom", "binning", "img", "refl_map", "weights")
-    r = dict(zip(keys, out))
-    r.update(bg=bgt, sh_degree=sh_degree, scale_modifier=scale_modifier, colors_precomp=colors_precomp,
-             transMat_precomp=transMat_precomp)
+    extra = dict(bg=bgt, sh_degree=sh_degree, scale_modifier=scale_modifier, colors_precomp=colors_precomp,
+                 transMat_precomp=transMat_precomp)
+    if prepare_only:
+        return out, extra
+    r = dict(zip(_SURFEL_KEYS, out))
+    r.update(extra)
+    return r
+
+
+_SURFEL_KEYS = ("rendered", "color", "others", "radii", "geom", "binning", "img", "refl_map", "weights")
+
+
+def surfel_prepare(Cmod, scene, cam, **kw):
+    """Stage 1 of surfel_forward on the current stream (this library only): -> handle for surfel_finish."""
+    return surfel_forward(Cmod, scene, cam, prepare_only=True, **kw)
+
+
+def surfel_finish(Cmod, handle):
+    """Stage 2 of a prepared forward on the current stream -> the dict surfel_forward returns."""
+    prep, extra = handle
+    r = dict(zip(_SURFEL_KEYS, Cmod.rasterize_gaussians_finish(prep)))
+    r.update(extra)
     return r
 
 

@@ -319,3 +319,69 @@ def test_autograd_module_with_arena_over_several_views(refC):
         assert hz.rel_l2(got2[k], plain[k]) <= 1e-5, k
     for a, b in zip(m_got, m_plain):                   # the per-view densification gradient stays an ordinary tensor
         assert hz.rel_l2(a, b) <= 1e-5
+
+
+def test_prepared_forward_on_a_second_stream():
+    """GaussianRasterizer.prepare(): stage 1 of view i+1 on a side stream while view i's stage 2 + backward are
+    queued on the main stream (the software pipeline bench.py runs).  Same images bit for bit, gradients equal up to
+    the atomic order, per view, against the plain one-stream call; a forward() with other tensors than its prepare()
+    raises."""
+    import diff_surfel_rasterization as d
+    sc_np, _ = scenes.build("small")
+    sc = hz.to_dev(sc_np)
+    P = sc["means3D"].shape[0]
+    cams = [hz.to_dev(scenes.camera("small", v, 32)) for v in (0, 7, 19, 25)]
+    keys = ("means3D", "shs", "opacities", "scales", "rotations", "refl")
+    mask = torch.ones((P, 3), dtype=torch.bool, device="cuda")
+
+    def module(c):
+        rs = d.GaussianRasterizationSettings(
+            image_height=c["height"], image_width=c["width"], tanfovx=c["tanfovx"], tanfovy=c["tanfovy"],
+            bg=torch.zeros(3, device="cuda"), scale_modifier=1.0, viewmatrix=c["viewmatrix"],
+            projmatrix=c["projmatrix"], sh_degree=3, campos=c["campos"], prefiltered=False, debug=False)
+        return d.GaussianRasterizer(rs)
+
+    def run(pipelined):
+        leaves = {k: sc[k].clone().requires_grad_(True) for k in keys}
+        m2d = torch.zeros_like(leaves["means3D"], requires_grad=True)
+        kw = dict(means3D=leaves["means3D"], means2D=m2d, opacities=leaves["opacities"], shs=leaves["shs"],
+                  refl_strengths=leaves["refl"], scales=leaves["scales"], rotations=leaves["rotations"], env_scope_mask=mask)
+        mods = [module(c) for c in cams]
+        side, main = torch.cuda.Stream(), torch.cuda.current_stream()
+        images, grads = [], []
+        if pipelined:
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
+                mods[0].prepare(**kw)
+        for i, m in enumerate(mods):
+            for t in leaves.values():
+                t.grad = None
+            color, radii, allmap, refl_map, weights = m(**kw)
+            (color.square().mean() + allmap[:6].mean() + refl_map.mean()).backward()
+            if pipelined and i + 1 < len(mods):
+                with torch.cuda.stream(side):
+                    mods[i + 1].prepare(**kw)
+            images.append((color.detach().clone(), allmap.detach().clone(), refl_map.detach().clone(), radii.clone(), weights.clone()))
+            grads.append({k: v.grad.clone() for k, v in leaves.items()})
+        main.wait_stream(side)
+        torch.cuda.synchronize()
+        return images, grads
+
+    img_a, g_a = run(False)
+    img_b, g_b = run(True)
+    for va, vb in zip(img_a, img_b):
+        for x, y in zip(va, vb):
+            assert torch.equal(x, y)
+    for ga, gb in zip(g_a, g_b):
+        for k in ga:
+            assert hz.rel_l2(gb[k], ga[k]) <= 1e-5, (k, hz.rel_l2(gb[k], ga[k]))
+
+    m = module(cams[0])
+    leaves = {k: sc[k].clone() for k in keys}
+    kw = dict(means3D=leaves["means3D"], means2D=None, opacities=leaves["opacities"], shs=leaves["shs"],
+              refl_strengths=leaves["refl"], scales=leaves["scales"], rotations=leaves["rotations"], env_scope_mask=mask)
+    m.prepare(**kw)
+    with pytest.raises(RuntimeError):
+        m(**dict(kw, means3D=leaves["means3D"].clone()))
+    out = m(**kw)                      # the handle was dropped by the failed call: an ordinary forward
+    assert torch.equal(out[0], img_a[0][0])
