@@ -40,7 +40,7 @@ def plain():
         hz.surfel_backward(C, sc, cam, f, grads)
 
 
-def make_pipelined(priority):
+def make_pipelined(priority, before_bwd=False):
     side = torch.cuda.Stream(priority=priority)
 
     def run():
@@ -50,8 +50,11 @@ def make_pipelined(priority):
             prep = prepare(cams[0])
         for i, cam in enumerate(cams):
             f = finish(prep)                           # stage 2 of view i on the main stream (asynchronous)
+            if before_bwd and i + 1 < len(cams):
+                with torch.cuda.stream(side):          # stage 1 of view i+1 next to stage 2 of view i
+                    prep = prepare(cams[i + 1])
             hz.surfel_backward(C, sc, cam, f, grads)   # backward of view i, queued behind it
-            if i + 1 < len(cams):
+            if not before_bwd and i + 1 < len(cams):
                 with torch.cuda.stream(side):          # stage 1 of view i+1 next to them; the host waits for ITS end only
                     prep = prepare(cams[i + 1])
         main.wait_stream(side)
@@ -75,5 +78,39 @@ out = {"config": name, "views": V, "plain_ms_per_view": round(timed(plain), 4)}
 lo, hi = torch.cuda.Stream.priority_range() if hasattr(torch.cuda.Stream, "priority_range") else (0, -1)
 out["pipelined_high_priority"] = round(timed(make_pipelined(-1)), 4)
 out["pipelined_same_priority"] = round(timed(make_pipelined(0)), 4)
+out["pipelined_before_bwd"] = round(timed(make_pipelined(0, True)), 4)
+out["pipelined_before_bwd_high_priority"] = round(timed(make_pipelined(-1, True)), 4)
 out["plain_again"] = round(timed(plain), 4)
 print(json.dumps(out), flush=True)
+
+# ---- timeline of the pipelined batch: event timestamps on both streams, ms from the start of the batch
+def timeline():
+    side = torch.cuda.Stream()
+    main = torch.cuda.current_stream()
+    ev = lambda: torch.cuda.Event(enable_timing=True)   # noqa: E731
+    marks = []
+    t0 = ev(); t0.record(main)
+    side.wait_stream(main)
+    with torch.cuda.stream(side):
+        a = ev(); a.record(side); prep = prepare(cams[0]); b = ev(); b.record(side)
+    marks.append(("prep", 0, a, b))
+    for i, cam in enumerate(cams):
+        a = ev(); a.record(main)
+        f = finish(prep)
+        b = ev(); b.record(main)
+        hz.surfel_backward(C, sc, cam, f, grads)
+        c = ev(); c.record(main)
+        marks.append(("stage2", i, a, b)); marks.append(("bwd", i, b, c))
+        if i + 1 < len(cams):
+            with torch.cuda.stream(side):
+                a = ev(); a.record(side); prep = prepare(cams[i + 1]); b = ev(); b.record(side)
+            marks.append(("prep", i + 1, a, b))
+    main.wait_stream(side)
+    torch.cuda.synchronize()
+    return [(n, i, round(t0.elapsed_time(a), 3), round(t0.elapsed_time(b), 3)) for n, i, a, b in marks]
+
+
+for _ in range(2):
+    timeline()
+tl = timeline()
+print(json.dumps({"timeline_first_6_views": [m for m in tl if m[1] < 6]}), flush=True)
