@@ -260,13 +260,14 @@ __global__ void __launch_bounds__(BATCH, 4) surfel_composite_bwd_kernel(const Co
           float g[20];
 #pragma unroll
           for (int k = 0; k < 20; ++k) g[k] = 0.0f;
+          SurfelHit h[2];
+          bool c[2];
 #pragma unroll
-          for (int p = 0; p < 2; ++p) {
-            SurfelHit h;
-            bool c = contributor < px[p].last_contributor;
-            c = surfel_eval<true>(q0, q1, q2, px[p].fx, px[p].fy, h) && c;
-            if (c) px[p].contribute(h, q3, q4, contributor, g);
-          }
+          for (int p = 0; p < 2; ++p)      // both pixels' tests first, straight-line: two chains in flight
+            c[p] = surfel_eval_straight<true>(q0, q1, q2, px[p].fx, px[p].fy, h[p]) && contributor < px[p].last_contributor;
+#pragma unroll
+          for (int p = 0; p < 2; ++p)
+            if (c[p]) px[p].contribute(h[p], q3, q4, contributor, g);
 
           // warp reduce-scatter 20 -> 10 -> 5 -> 3 -> 2 -> 1 (a visit without any contributing pixel -- 3 % of them on
           // the bench scene -- adds zeros: cheaper than a vote and a branch on every visit)
