@@ -279,14 +279,15 @@ def main():
     def step():
         nonlocal ref_acc
         mark("begin")
+        if new and pipelined:
+            main = torch.cuda.current_stream()
+            side.wait_stream(main)        # everything before this step; NOT the arena memset below, which stage 1 never reads
         if arena is not None:
             arena.zero_()
         f = b = None
         if new and pipelined:
             # software pipeline over the batch's views: stage 1 of view i+1 (preprocess, depth order, scan, plan and
             # the forward's host sync) runs on a side stream while stage 2 + backward of view i occupy the SMs
-            main = torch.cuda.current_stream()
-            side.wait_stream(main)
             with torch.cuda.stream(side):
                 prep = hz.surfel_prepare(Cmod, sc, cams[0], exact=exact)
             for vi, c in enumerate(cams):
