@@ -302,8 +302,11 @@ __device__ __forceinline__ void shade_ray(const ShadeCam& c, int x, int y, float
     const float ro = -(c.rot[3 * i] * c.t[0] + c.rot[3 * i + 1] * c.t[1] + c.rot[3 * i + 2] * c.t[2]);
     w[i] = pw - ro;
   }
-  const float inv = 1.0f / sqrtf(w[0] * w[0] + w[1] * w[1] + w[2] * w[2]);
-  d[0] = w[0] * inv; d[1] = w[1] * inv; d[2] = w[2] * inv;
+  // rays_d / torch.norm(rays_d): an IEEE square root and three IEEE divisions, as the torch lines do it (this file is built
+  // with --use_fast_math for the lookup's sake; an approximate rsqrt here moves ten times as many rays across a texel
+  // boundary of the lookup, where the direction gradient jumps)
+  const float nn = __fsqrt_rn(w[0] * w[0] + w[1] * w[1] + w[2] * w[2]);
+  d[0] = __fdiv_rn(w[0], nn); d[1] = __fdiv_rn(w[1], nn); d[2] = __fdiv_rn(w[2], nn);
 }
 
 template <int MODE>

@@ -32,6 +32,8 @@ from test_update_oracle_cpu import LRS  # noqa: E402
 
 L_ENV, DEPTH_RATIO, LAMBDA_DSSIM, LAMBDA_NORMAL, LAMBDA_DIST = 128, 0.0, 0.2, 0.05, 100.0
 LAMBDA_NORMAL = float(os.environ.get("ITER_LAMBDA_NORMAL", LAMBDA_NORMAL))      # diagnosis switches
+LAMBDA_DIST = float(os.environ.get("ITER_LAMBDA_DIST", LAMBDA_DIST))
+LAMBDA_DSSIM = float(os.environ.get("ITER_LAMBDA_DSSIM", LAMBDA_DSSIM))
 NO_REFL = os.environ.get("ITER_NO_REFL", "0") == "1"
 
 
