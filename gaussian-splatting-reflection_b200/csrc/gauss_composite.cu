@@ -13,7 +13,7 @@
 #include "surfel_composite.cuh"
 
 #ifndef B200GS_GBWD_CTAS
-#define B200GS_GBWD_CTAS 2   // resident CTAs per SM the register allocation is bounded for (3: 72 registers, no change on c3)
+#define B200GS_GBWD_CTAS 6   // resident CTAs (of 128 threads, two pixels each) per SM the register allocation is bounded for
 #endif
 
 namespace b200gs {
@@ -236,12 +236,86 @@ struct GCompBwdArgs {
   const uint32_t* tile_base;  // [MAX_SLICES+1][tiles]
 };
 
-__global__ void __launch_bounds__(GBATCH, B200GS_GBWD_CTAS) gauss_composite_bwd_kernel(const GCompBwdArgs a) {
-  __shared__ GaussRec s_rec[2][GBATCH];
-  __shared__ int s_id[2][GBATCH];
-  __shared__ uint32_t s_pos[2][GBATCH];
-  __shared__ uint8_t s_hit[2][GBATCH];
-  __shared__ uint32_t s_last[GBATCH / 32];
+constexpr int GPAIR = PAIR_THREADS;   // the backward: two pixels per thread, 128 threads per tile (surfel_composite.cuh)
+
+// Everything the backward keeps per pixel.
+struct GaussPixelBwd {
+  float fx, fy;
+  uint32_t last_contributor;          // 0 for pixels outside the image
+  float T_final, T;
+  float dpix0, dpix1, dpix2, dn0, dn1, dn2, drefl, dinv, bg_dot, mpix0, mpix1;
+  float acc_q, last_q, acc_m, last_m, last_alpha;
+
+  __device__ __forceinline__ void load(const GCompBwdArgs& a, int pxi, int pyi) {
+    const bool inside = pxi < a.W && pyi < a.H;
+    fx = (float)pxi; fy = (float)pyi;
+    const size_t N = (size_t)a.W * a.H;
+    const size_t pix_id = (size_t)a.W * pyi + pxi;
+    T_final = inside ? a.accum[pix_id] : 0.0f;
+    T = T_final;
+    last_contributor = inside ? a.n_contrib[pix_id] : 0u;
+    dpix0 = dpix1 = dpix2 = dn0 = dn1 = dn2 = drefl = dinv = 0.f;
+    if (inside) {
+      dpix0 = a.dL_dpix[pix_id]; dpix1 = a.dL_dpix[pix_id + N]; dpix2 = a.dL_dpix[pix_id + 2 * N];
+      dn0 = a.dL_dnormal[pix_id]; dn1 = a.dL_dnormal[pix_id + N]; dn2 = a.dL_dnormal[pix_id + 2 * N];
+      drefl = a.dL_drefl ? a.dL_drefl[pix_id] : 0.0f;
+      dinv = a.dL_dinvd ? a.dL_dinvd[pix_id] : 0.0f;
+    }
+    bg_dot = 0.0f;
+    bg_dot += a.bg[0] * dpix0;
+    bg_dot += a.bg[1] * dpix1;
+    bg_dot += a.bg[2] * dpix2;
+    // the running-sum quirk (backward.cu:614): the mean2D gradient uses 3 t0 + 2 t1 + t2 of the colour terms
+    mpix0 = 3.0f * dpix0; mpix1 = 2.0f * dpix1;
+    acc_q = last_q = acc_m = last_m = last_alpha = 0.f;
+  }
+
+  // One contributing (pixel, Gaussian) pair: advances the recurrences and ADDS the pair's 16 partials to g.
+  __device__ __forceinline__ void contribute(const GaussEval& e, const float4& q0, const float4& q1, const float4& q2,
+                                             const float4& q3, float ddelx_dx, float ddely_dy, float* g) {
+    const float alpha = e.alpha, G = e.G;
+    const float inv_1ma = __frcp_rn(__fsub_rn(1.0f, alpha));
+    T = T * inv_1ma;
+    const float w = alpha * T;                      // dchannel_dcolor
+    const float om = 1.f - last_alpha;
+    // backward.cu:596-650: every channel enters dL_dalpha as (value - value accumulated behind) *
+    // upstream gradient.  The recurrence is linear, so the eight per-channel recurrences collapse
+    // into one on q = sum_ch value_ch * upstream_ch, plus one on the colour-only weighted sum the
+    // mean2D running-sum quirk (:614) needs.
+    const float cm = q2.x * mpix0 + q2.y * mpix1 + q2.z * dpix2;
+    const float qv = q2.x * dpix0 + q2.y * dpix1 + q2.z * dpix2 + q3.x * dn0 + q3.y * dn1 + q3.z * dn2 +
+                     q1.w * drefl + q1.z * dinv;
+    acc_q = last_alpha * last_q + om * acc_q; last_q = qv;
+    acc_m = last_alpha * last_m + om * acc_m; last_m = cm;
+    last_alpha = alpha;
+    g[8] += w * dpix0; g[9] += w * dpix1; g[10] += w * dpix2;
+    g[11] += w * dn0; g[12] += w * dn1; g[13] += w * dn2;
+    g[14] += w * drefl; g[15] += w * dinv;
+    const float bgterm = (-T_final * inv_1ma) * bg_dot;
+    const float dL_dalpha = (qv - acc_q) * T + bgterm;
+    const float dL_dalpha_m = (cm - acc_m) * T + bgterm;
+    const float opa = q1.y;
+    const float dL_dG = opa * dL_dalpha, dL_dG_m = opa * dL_dalpha_m;
+    const float gdx = G * e.dx, gdy = G * e.dy;
+    const float dG_ddelx = -gdx * q0.z - gdy * q0.w;
+    const float dG_ddely = -gdy * q1.x - gdx * q0.w;
+    g[0] += dL_dG * dG_ddelx * ddelx_dx;
+    g[1] += dL_dG * dG_ddely * ddely_dy;
+    g[2] += dL_dG_m * dG_ddelx * ddelx_dx;
+    g[3] += dL_dG_m * dG_ddely * ddely_dy;
+    g[4] += -0.5f * gdx * e.dx * dL_dG;
+    g[5] += -0.5f * gdx * e.dy * dL_dG;
+    g[6] += -0.5f * gdy * e.dy * dL_dG;
+    g[7] += G * dL_dalpha;
+  }
+};
+
+__global__ void __launch_bounds__(GPAIR, B200GS_GBWD_CTAS) gauss_composite_bwd_kernel(const GCompBwdArgs a) {
+  __shared__ GaussRec s_rec[2][GPAIR];
+  __shared__ int s_id[2][GPAIR];
+  __shared__ uint32_t s_pos[2][GPAIR];
+  __shared__ uint8_t s_hit[2][GPAIR];
+  __shared__ uint32_t s_last[GPAIR / 32];
   __shared__ uint32_t s_tile_last;
   __shared__ int s_n;                   // live prefix of the slice's compacted list
 
@@ -249,47 +323,27 @@ __global__ void __launch_bounds__(GBATCH, B200GS_GBWD_CTAS) gauss_composite_bwd_
   const int tile = blockIdx.x;
   const int tile_x = tile % a.gx, tile_y = tile / a.gx;
   int lx, ly;
-  tile_pixel(t, lx, ly);
-  const int pxi = tile_x * TILE_X + lx, pyi = tile_y * TILE_Y + ly;
-  const bool inside = pxi < a.W && pyi < a.H;
-  const float fx = (float)pxi, fy = (float)pyi;
-  const size_t N = (size_t)a.W * a.H;
-  const size_t pix_id = (size_t)a.W * pyi + pxi;
+  pair_pixel(t, lx, ly);
+  GaussPixelBwd px[2];
+  px[0].load(a, tile_x * TILE_X + lx, tile_y * TILE_Y + ly);
+  px[1].load(a, tile_x * TILE_X + lx, tile_y * TILE_Y + ly + 4);
+  const unsigned warp_bits = pair_hit_bits(warp);       // the two 8x4 blocks of this warp's 8x8 pixels
 
   // lane -> accumulator component owned after the reduce-scatter (16 values, 32 lanes)
   const int b16 = (lane >> 4) & 1, b8 = (lane >> 3) & 1, b4 = (lane >> 2) & 1, b2 = (lane >> 1) & 1;
   const int comp = b16 * 8 + b8 * 4 + b4 * 2 + b2;
   const bool writer = (lane & 1) == 0;
-
-  const float T_final = inside ? a.accum[pix_id] : 0.0f;
-  float T = T_final;
-  const uint32_t last_contributor = inside ? a.n_contrib[pix_id] : 0u;
-  float dpix0 = 0.f, dpix1 = 0.f, dpix2 = 0.f, dn0 = 0.f, dn1 = 0.f, dn2 = 0.f, drefl = 0.f, dinv = 0.f;
-  if (inside) {
-    dpix0 = a.dL_dpix[pix_id]; dpix1 = a.dL_dpix[pix_id + N]; dpix2 = a.dL_dpix[pix_id + 2 * N];
-    dn0 = a.dL_dnormal[pix_id]; dn1 = a.dL_dnormal[pix_id + N]; dn2 = a.dL_dnormal[pix_id + 2 * N];
-    drefl = a.dL_drefl ? a.dL_drefl[pix_id] : 0.0f;
-    dinv = a.dL_dinvd ? a.dL_dinvd[pix_id] : 0.0f;
-  }
-  float bg_dot_dpixel = 0.0f;
-  bg_dot_dpixel += a.bg[0] * dpix0;
-  bg_dot_dpixel += a.bg[1] * dpix1;
-  bg_dot_dpixel += a.bg[2] * dpix2;
   const float ddelx_dx = 0.5f * a.W, ddely_dy = 0.5f * a.H;
-  // the running-sum quirk (backward.cu:614): the mean2D gradient uses 3 t0 + 2 t1 + t2 of the colour terms
-  const float mpix0 = 3.0f * dpix0, mpix1 = 2.0f * dpix1;
-
-  float acc_q = 0.f, last_q = 0.f, acc_m = 0.f, last_m = 0.f, last_alpha = 0.f;
 
   // Entries at or behind the last contributor of every pixel of the tile are never used
   // (backward.cu:560: `contributor >= last_contributor` -> continue).
-  const uint32_t warp_last = __reduce_max_sync(0xffffffffu, inside ? last_contributor : 0u);
+  const uint32_t warp_last = __reduce_max_sync(0xffffffffu, max(px[0].last_contributor, px[1].last_contributor));
   if (lane == 0) s_last[warp] = warp_last;
   __syncthreads();
   if (t == 0) {
     uint32_t tl = 0;
 #pragma unroll
-    for (int w = 0; w < GBATCH / 32; ++w) tl = max(tl, s_last[w]);
+    for (int w = 0; w < GPAIR / 32; ++w) tl = max(tl, s_last[w]);
     s_tile_last = tl;
   }
   __syncthreads();
@@ -300,128 +354,95 @@ __global__ void __launch_bounds__(GBATCH, B200GS_GBWD_CTAS) gauss_composite_bwd_
   // the slices back to front, each slice's entries back to front.  The per-pixel recurrences simply carry on.
   const int S = a.plan[1];
   for (int sl = S - 1; sl >= 0; --sl) {
-  const uint32_t base = sl == 0 ? 0u : a.tile_base[(size_t)sl * a.tiles + tile];   // list position of the slice's first entry
-  if (base >= tile_last) continue;
-  const uint2 range = a.ranges[(size_t)sl * (a.tiles + 1) + tile];
-  if (range.y == range.x) continue;
-  const uint32_t* pl = a.point_list + range.x;
-  const uint8_t* ph = a.hit + range.x;
-  const uint32_t* pp = a.list_pos + range.x;
-  // list positions ascend, so the live part is a prefix of the slice's compacted list; find its length by bisection
-  __syncthreads();                                  // everyone has left the previous slice's shared buffers
-  if (t == 0) {
-    const uint32_t lim = tile_last - base;
-    int lo = 0, hi = (int)(range.y - range.x);     // first index with pos >= lim
-    while (lo < hi) {
-      const int mid = (lo + hi) >> 1;
-      if (pp[mid] < lim) lo = mid + 1; else hi = mid;
+    const uint32_t base = sl == 0 ? 0u : a.tile_base[(size_t)sl * a.tiles + tile];   // list position of the slice's first entry
+    if (base >= tile_last) continue;
+    const uint2 range = a.ranges[(size_t)sl * (a.tiles + 1) + tile];
+    if (range.y == range.x) continue;
+    const uint32_t* pl = a.point_list + range.x;
+    const uint8_t* ph = a.hit + range.x;
+    const uint32_t* pp = a.list_pos + range.x;
+    // list positions ascend, so the live part is a prefix of the slice's compacted list; find its length by bisection
+    __syncthreads();                                  // everyone has left the previous slice's shared buffers
+    if (t == 0) {
+      const uint32_t lim = tile_last - base;
+      int lo = 0, hi = (int)(range.y - range.x);     // first index with pos >= lim
+      while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (pp[mid] < lim) lo = mid + 1; else hi = mid;
+      }
+      s_n = lo;
     }
-    s_n = lo;
-  }
-  __syncthreads();
-  const int n = s_n;
-  const int rounds = (n + GBATCH - 1) / GBATCH;
-  if (n == 0) continue;
-
-  unsigned hit_cur = 0u, hit_next = 0u;
-  uint32_t pos_next = 0u;
-  auto stage = [&](int buf, int id) {
-    hit_cur = hit_next;
-    if (id >= 0) {
-      s_pos[buf][t] = pos_next;
-      const GaussRec* g = a.rec + id;
-      GaussRec* d = &s_rec[buf][t];
-#pragma unroll
-      for (int k = 0; k < 4; ++k) cp_async16(&d->q[k], &g->q[k]);
-      s_id[buf][t] = id;
-    }
-    cp_async_commit();
-  };
-  int id_next = -1;
-  if (t < n) { id_next = (int)pl[n - 1 - t]; hit_next = ph[n - 1 - t]; pos_next = pp[n - 1 - t]; }
-  stage(0, id_next);
-  id_next = -1; hit_next = 0u;
-  if (GBATCH + t < n) { const int q = n - 1 - (GBATCH + t); id_next = (int)pl[q]; hit_next = ph[q]; pos_next = pp[q]; }
-
-  for (int i = 0; i < rounds; ++i) {
-    cp_async_wait_all();
-    s_hit[i & 1][t] = (uint8_t)hit_cur;
     __syncthreads();
-    if (i + 1 < rounds) {
-      stage((i + 1) & 1, id_next);
-      const int nx = (i + 2) * GBATCH + t;
-      id_next = -1; hit_next = 0u;
-      if (nx < n) { const int q = n - 1 - nx; id_next = (int)pl[q]; hit_next = ph[q]; pos_next = pp[q]; }
-    }
-    const int buf = i & 1;
-    const int count = min(GBATCH, n - i * GBATCH);
-    const GaussRec* rb = s_rec[buf];
-#pragma unroll 1
-    for (int r = 0; r < (count + 31) >> 5; ++r) {
-      // entries of other warp blocks, and entries behind every pixel's last contributor, are skipped
-      const int en = r * 32 + lane;
-      unsigned m = __ballot_sync(0xffffffffu, en < count && ((s_hit[buf][en] >> warp) & 1u) && base + s_pos[buf][en] < warp_last);
-      while (m) {
-        const int j = r * 32 + __ffs(m) - 1;
-        m &= m - 1;
-        const uint32_t contributor = base + s_pos[buf][j];   // 0-based position in the tile's full list
-        const float4 q0 = rb[j].q[0], q1 = rb[j].q[1];
-        GaussEval e;
-        bool c = inside && contributor < last_contributor;
-        c = gauss_eval(q0, q1, fx, fy, e) && c;
-        if (!__any_sync(0xffffffffu, c)) continue;
+    const int n = s_n;
+    const int rounds = (n + GPAIR - 1) / GPAIR;
+    if (n == 0) continue;
 
-        float g[16];
+    unsigned hit_cur = 0u, hit_next = 0u;
+    uint32_t pos_next = 0u;
+    auto stage = [&](int buf, int id) {
+      hit_cur = hit_next;
+      if (id >= 0) {
+        s_pos[buf][t] = pos_next;
+        const GaussRec* g = a.rec + id;
+        GaussRec* d = &s_rec[buf][t];
 #pragma unroll
-        for (int k = 0; k < 16; ++k) g[k] = 0.0f;
-        if (c) {
-          const float4 q2 = rb[j].q[2], q3 = rb[j].q[3];
-          const float alpha = e.alpha, G = e.G;
-          const float inv_1ma = __frcp_rn(__fsub_rn(1.0f, alpha));
-          T = T * inv_1ma;
-          const float w = alpha * T;                      // dchannel_dcolor
-          const float om = 1.f - last_alpha;
-          // backward.cu:596-650: every channel enters dL_dalpha as (value - value accumulated behind) *
-          // upstream gradient.  The recurrence is linear, so the eight per-channel recurrences collapse
-          // into one on q = sum_ch value_ch * upstream_ch, plus one on the colour-only weighted sum the
-          // mean2D running-sum quirk (:614) needs.
-          const float cm = q2.x * mpix0 + q2.y * mpix1 + q2.z * dpix2;
-          const float qv = q2.x * dpix0 + q2.y * dpix1 + q2.z * dpix2 + q3.x * dn0 + q3.y * dn1 + q3.z * dn2 +
-                           q1.w * drefl + q1.z * dinv;
-          acc_q = last_alpha * last_q + om * acc_q; last_q = qv;
-          acc_m = last_alpha * last_m + om * acc_m; last_m = cm;
-          last_alpha = alpha;
-          g[8] = w * dpix0; g[9] = w * dpix1; g[10] = w * dpix2;
-          g[11] = w * dn0; g[12] = w * dn1; g[13] = w * dn2;
-          g[14] = w * drefl; g[15] = w * dinv;
-          const float bgterm = (-T_final * inv_1ma) * bg_dot_dpixel;
-          const float dL_dalpha = (qv - acc_q) * T + bgterm;
-          const float dL_dalpha_m = (cm - acc_m) * T + bgterm;
-          const float opa = q1.y;
-          const float dL_dG = opa * dL_dalpha, dL_dG_m = opa * dL_dalpha_m;
-          const float gdx = G * e.dx, gdy = G * e.dy;
-          const float dG_ddelx = -gdx * q0.z - gdy * q0.w;
-          const float dG_ddely = -gdy * q1.x - gdx * q0.w;
-          g[0] = dL_dG * dG_ddelx * ddelx_dx;
-          g[1] = dL_dG * dG_ddely * ddely_dy;
-          g[2] = dL_dG_m * dG_ddelx * ddelx_dx;
-          g[3] = dL_dG_m * dG_ddely * ddely_dy;
-          g[4] = -0.5f * gdx * e.dx * dL_dG;
-          g[5] = -0.5f * gdx * e.dy * dL_dG;
-          g[6] = -0.5f * gdy * e.dy * dL_dG;
-          g[7] = G * dL_dalpha;
+        for (int k = 0; k < 4; ++k) cp_async16(&d->q[k], &g->q[k]);
+        s_id[buf][t] = id;
+      }
+      cp_async_commit();
+    };
+    int id_next = -1;
+    if (t < n) { id_next = (int)pl[n - 1 - t]; hit_next = ph[n - 1 - t]; pos_next = pp[n - 1 - t]; }
+    stage(0, id_next);
+    id_next = -1; hit_next = 0u;
+    if (GPAIR + t < n) { const int q = n - 1 - (GPAIR + t); id_next = (int)pl[q]; hit_next = ph[q]; pos_next = pp[q]; }
+
+    for (int i = 0; i < rounds; ++i) {
+      cp_async_wait_all();
+      s_hit[i & 1][t] = (uint8_t)hit_cur;
+      __syncthreads();
+      if (i + 1 < rounds) {
+        stage((i + 1) & 1, id_next);
+        const int nx = (i + 2) * GPAIR + t;
+        id_next = -1; hit_next = 0u;
+        if (nx < n) { const int q = n - 1 - nx; id_next = (int)pl[q]; hit_next = ph[q]; pos_next = pp[q]; }
+      }
+      const int buf = i & 1;
+      const int count = min(GPAIR, n - i * GPAIR);
+      const GaussRec* rb = s_rec[buf];
+#pragma unroll 1
+      for (int r = 0; r < (count + 31) >> 5; ++r) {
+        // entries of other warp blocks, and entries behind every pixel's last contributor, are skipped
+        const int en = r * 32 + lane;
+        unsigned m = __ballot_sync(0xffffffffu, en < count && (s_hit[buf][en] & warp_bits) && base + s_pos[buf][en] < warp_last);
+        while (m) {
+          const int j = r * 32 + __ffs(m) - 1;
+          m &= m - 1;
+          const uint32_t contributor = base + s_pos[buf][j];   // 0-based position in the tile's full list
+          const float4 q0 = rb[j].q[0], q1 = rb[j].q[1], q2 = rb[j].q[2], q3 = rb[j].q[3];
+
+          float g[16];
+#pragma unroll
+          for (int k = 0; k < 16; ++k) g[k] = 0.0f;
+#pragma unroll
+          for (int p = 0; p < 2; ++p) {
+            GaussEval e;
+            bool c = contributor < px[p].last_contributor;
+            c = gauss_eval(q0, q1, px[p].fx, px[p].fy, e) && c;
+            if (c) px[p].contribute(e, q0, q1, q2, q3, ddelx_dx, ddely_dy, g);
+          }
+          // warp reduce-scatter 16 -> 8 -> 4 -> 2 -> 1, then the last butterfly (a visit without any contributing
+          // pixel adds zeros: cheaper than a vote and a branch on every visit)
+          rs_step<8>(g, 16, b16);
+          rs_step<4>(g, 8, b8);
+          rs_step<2>(g, 4, b4);
+          rs_step<1>(g, 2, b2);
+          g[0] += __shfl_xor_sync(0xffffffffu, g[0], 1);
+          if (writer) atomicAdd(a.acc + (size_t)s_id[buf][j] * GACC_STRIDE + comp, g[0]);
         }
-        // warp reduce-scatter 16 -> 8 -> 4 -> 2 -> 1, then the last butterfly
-        rs_step<8>(g, 16, b16);
-        rs_step<4>(g, 8, b8);
-        rs_step<2>(g, 4, b4);
-        rs_step<1>(g, 2, b2);
-        g[0] += __shfl_xor_sync(0xffffffffu, g[0], 1);
-        if (writer) atomicAdd(a.acc + (size_t)s_id[buf][j] * GACC_STRIDE + comp, g[0]);
       }
     }
-  }
-  cp_async_wait_all();
+    cp_async_wait_all();
   }   // slices
 }
 
@@ -438,7 +459,7 @@ int gauss_composite_backward(const b200gs_gauss_bwd& f, const GaussGeom& g, cons
   a.tiles = a.gx * gy; a.plan = g.plan; a.tile_base = im.tile_base;
   StageScope _t(ST_COMPOSITE_BWD, s);
   B200GS_CUDA(cudaMemsetAsync(acc, 0, (size_t)f.P * GACC_STRIDE * sizeof(float), s));
-  gauss_composite_bwd_kernel<<<a.gx * gy, GBATCH, 0, s>>>(a);
+  gauss_composite_bwd_kernel<<<a.gx * gy, GPAIR, 0, s>>>(a);
   B200GS_LAUNCHED("gauss_composite_bwd_kernel", f.debug, s);
   return B200GS_OK;
 }
