@@ -442,6 +442,18 @@ def main():
     if rank == 0 or world > 1:
         with torch.no_grad():
             def fstep():
+                if new and pipelined:      # stage 1 of the next frame on the side stream, as in the training step
+                    main = torch.cuda.current_stream()
+                    side.wait_stream(main)
+                    with torch.cuda.stream(side):
+                        prep = hz.surfel_prepare(Cmod, sc, cams[0], exact=exact)
+                    for vi in range(len(cams)):
+                        hz.surfel_finish(Cmod, prep)
+                        if vi + 1 < len(cams):
+                            with torch.cuda.stream(side):
+                                prep = hz.surfel_prepare(Cmod, sc, cams[vi + 1], exact=exact)
+                    main.wait_stream(side)
+                    return
                 for c in cams:
                     hz.surfel_forward(Cmod, sc, c, **({"exact": exact} if new else {}))
             f_ms = timed(fstep, max(3, a.steps // 4), 2) / max(3, a.steps // 4) / len(cams)

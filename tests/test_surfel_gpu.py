@@ -321,16 +321,17 @@ def test_autograd_module_with_arena_over_several_views(refC):
         assert hz.rel_l2(a, b) <= 1e-5
 
 
-def test_prepared_forward_on_a_second_stream():
+@pytest.mark.parametrize("name", ["small", "c2"])      # c2: 5.4M instances, three depth slices
+def test_prepared_forward_on_a_second_stream(name):
     """GaussianRasterizer.prepare(): stage 1 of view i+1 on a side stream while view i's stage 2 + backward are
     queued on the main stream (the software pipeline bench.py runs).  Same images bit for bit, gradients equal up to
     the atomic order, per view, against the plain one-stream call; a forward() with other tensors than its prepare()
     raises."""
     import diff_surfel_rasterization as d
-    sc_np, _ = scenes.build("small")
+    sc_np, _ = scenes.build(name)
     sc = hz.to_dev(sc_np)
     P = sc["means3D"].shape[0]
-    cams = [hz.to_dev(scenes.camera("small", v, 32)) for v in (0, 7, 19, 25)]
+    cams = [hz.to_dev(scenes.camera(name, v, 32)) for v in (0, 7, 19, 25)]
     keys = ("means3D", "shs", "opacities", "scales", "rotations", "refl")
     mask = torch.ones((P, 3), dtype=torch.bool, device="cuda")
 
