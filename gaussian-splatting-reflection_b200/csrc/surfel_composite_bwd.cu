@@ -218,7 +218,7 @@ __global__ void __launch_bounds__(BATCH, 4) surfel_composite_bwd_kernel(const Co
     auto stage = [&](int buf, int id) {
       hit_cur = hit_next;
       if (id >= 0) {
-        s_pos[buf][t] = pos_next;
+        s_pos[buf][t] = base + pos_next;       // 0-based position in the tile's full list
         const SurfelRec* g = a.rec + id;
         SurfelRec* d = &s_rec[buf][t];
 #pragma unroll
@@ -250,11 +250,11 @@ __global__ void __launch_bounds__(BATCH, 4) surfel_composite_bwd_kernel(const Co
       for (int r = 0; r < (count + 31) >> 5; ++r) {
         // entries of other warp blocks, and entries behind every pixel's last contributor, are skipped
         const int e = r * 32 + lane;
-        unsigned m = __ballot_sync(0xffffffffu, e < count && (s_hit[buf][e] & warp_bits) && base + s_pos[buf][e] < warp_last);
+        unsigned m = __ballot_sync(0xffffffffu, e < count && (s_hit[buf][e] & warp_bits) && s_pos[buf][e] < warp_last);
         while (m) {
           const int j = r * 32 + __ffs(m) - 1;
           m &= m - 1;
-          const uint32_t contributor = base + s_pos[buf][j];   // 0-based position in the tile's full list
+          const uint32_t contributor = s_pos[buf][j];          // 0-based position in the tile's full list
           const float4 q0 = rb[j].q[0], q1 = rb[j].q[1], q2 = rb[j].q[2], q3 = rb[j].q[3], q4 = rb[j].q[4];
 
           float g[20];

@@ -105,7 +105,7 @@ __global__ void __launch_bounds__(BATCH) surfel_composite_fwd_kernel(const CompF
   auto stage = [&](int buf, int id) {
     hit_cur = hit_next;                  // 0 for padding entries: never visited
     if (id >= 0) {
-      s_pos[buf][t] = pos_next;
+      s_pos[buf][t] = base + pos_next + 1u;   // the entry's 1-based position in the tile's (full) list
       const SurfelRec* g = a.rec + id;
       SurfelRec* d = &s_rec[buf][t];
 #pragma unroll
@@ -152,7 +152,7 @@ __global__ void __launch_bounds__(BATCH) surfel_composite_fwd_kernel(const CompF
         if (__all_sync(0xffffffffu, done)) { warp_done = true; break; }
         const int j = r * 32 + __ffs(m) - 1;
         m &= m - 1;
-        const uint32_t contributor = base + s_pos[buf][j] + 1u;  // 1-based position in the tile's (full) list
+        const uint32_t contributor = s_pos[buf][j];              // 1-based position in the tile's (full) list
         const float4 q0 = rb[j].q[0], q1 = rb[j].q[1], q2 = rb[j].q[2];
         SurfelHit h;
         bool c = surfel_eval<false>(q0, q1, q2, fx, fy, h);
