@@ -458,7 +458,8 @@ def main():
                     hz.surfel_forward(Cmod, sc, c, **({"exact": exact} if new else {}))
             f_ms = timed(fstep, max(3, a.steps // 4), 2) / max(3, a.steps // 4) / len(cams)
         fwd_only = {"ms_per_view": round(f_ms, 4), "fps_per_gpu": round(1e3 / f_ms, 1),
-                    "api": "_C.rasterize_gaussians under torch.no_grad(), device-resident inputs"}
+                    "api": "_C.rasterize_gaussians under torch.no_grad(), device-resident inputs"
+                           + (" (stage 1 of the next frame prefetched on a side stream: _prepare / _finish)" if new and pipelined else "")}
 
     # ---- end to end through the drop-in Python API, host inputs ------------------------------
     e2e = None
