@@ -39,7 +39,15 @@ class GradArena:
         self.numel = off
         self.symmetric, self.algo, self._hdl = False, "ncclAllReduce", None
         if symmetric:
-            self._alloc_symmetric(off, device, group)
+            try:
+                self._alloc_symmetric(off, device, group)
+            except Exception as e:  # noqa: BLE001 -- no symmetric memory on this system / torch build (every rank fails alike)
+                import warnings
+                warnings.warn(f"b200gs.dp.GradArena: symmetric memory unavailable ({type(e).__name__}: {e}); "
+                              "the arena is an ordinary tensor and is reduced with ncclAllReduce")
+                self.symmetric, self._hdl = False, None
+                self.algo = "ncclAllReduce (symmetric memory unavailable)"
+                self.flat = torch.zeros(off, dtype=torch.float32, device=device)
         else:
             self.flat = torch.zeros(off, dtype=torch.float32, device=device)
 
@@ -70,7 +78,8 @@ class GradArena:
             self._mc = 0
         self.ctas = 32 if self._mc else 0
         self.algo = ("own kernel: NVLS multimem.ld_reduce + multimem.st over the multicast mapping" if self._mc
-                     else "own kernel: peer-to-peer loads / stores over NVLink")
+                     else "own kernel: peer-to-peer loads / stores over NVLink" if self._world in (2, 4, 8)
+                     else "ncclAllReduce on the symmetric buffer (no multicast object; peer-to-peer kernel built for 2 / 4 / 8 ranks)")
 
     @property
     def floats_per_gaussian(self):
@@ -130,6 +139,9 @@ class GradArena:
         import torch.distributed as dist
         if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
             return None
+        if self.symmetric and not self._mc and self._world not in (2, 4, 8):
+            # no multicast object and a rank count the peer-to-peer kernel is not built for: NCCL on the same memory
+            return dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group, async_op=async_op)
         if self.symmetric:
             import ctypes as C
             import b200gs
