@@ -5,16 +5,17 @@
 // tiling and staging as the forward kernel.  Where the reference issues up to 17
 // global atomicAdds per contributing (pixel, Gaussian) pair, this kernel keeps
 // the per-pixel recurrences in registers, forms the 19 per-Gaussian partials of
-// every lane, and sums them over the warp with a 21-shuffle recursive-halving
-// reduce-scatter, so that 19 lanes each own one component and flush the warp's
-// contribution with ONE vector RED.ADD.F32 into a contiguous 80-B accumulator
-// row (ACC_STRIDE floats per Gaussian).
+// every lane, sums them over the warp (through shared memory: one 80-B row per lane,
+// then lane c adds column c), and 19 lanes flush the warp's contribution with ONE
+// vector RED.ADD.F32 into a contiguous 80-B accumulator row (ACC_STRIDE floats per Gaussian).
 //
-// The kernel is bound by instruction issue (ncu: 79-83 % of the issue slots, DRAM 1 %), and a quarter of its
+// The kernel is bound by instruction issue (ncu: 74-83 % of the issue slots, DRAM 1 %), and a quarter of its
 // instructions per (warp, Gaussian) visit were that reduction plus the per-entry loop overhead
 // (profiles/r2_ncu_summary.md: 84 of 342).  Every thread therefore owns TWO pixels -- a warp covers an 8x8 pixel
 // block, a CTA of four warps the 16x16 tile (surfel_composite.cuh: pair_pixel) -- so one reduction, one RED and one
-// trip through the entry loop serve 64 pixels.
+// trip through the entry loop serve 64 pixels.  The reduction was a 21-shuffle recursive-halving reduce-scatter in
+// registers until the end of round 2 (102 instructions with its selects); the shared-memory form is ~75 and took
+// K4 from 1.52 to 1.49 ms on the bench view.
 #include "surfel_composite.cuh"
 
 namespace b200gs {
@@ -154,6 +155,7 @@ __global__ void __launch_bounds__(BATCH, 4) surfel_composite_bwd_kernel(const Co
   __shared__ int s_n;                   // live prefix of the slice's compacted list
   __shared__ uint32_t s_last[BATCH / 32];
   __shared__ uint32_t s_tile_last;
+  __shared__ __align__(16) float s_red[BATCH / 32][32][ACC_STRIDE];   // per warp: the lanes' partials of one visit
 
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const int tile = blockIdx.x;
@@ -164,12 +166,6 @@ __global__ void __launch_bounds__(BATCH, 4) surfel_composite_bwd_kernel(const Co
   px[0].load(a, tile_x * TILE_X + lx, tile_y * TILE_Y + ly);
   px[1].load(a, tile_x * TILE_X + lx, tile_y * TILE_Y + ly + 4);
   const unsigned warp_bits = pair_hit_bits(warp);       // the two 8x4 blocks of this warp's 8x8 pixels
-
-  // lane -> accumulator component owned after the reduce-scatter
-  const int b16 = (lane >> 4) & 1, b8 = (lane >> 3) & 1, b4 = (lane >> 2) & 1, b2 = (lane >> 1) & 1, b1 = lane & 1;
-  const int loc3 = b2 * 2 + b1, loc5 = b4 * 3 + loc3;
-  const int comp = b16 * 10 + b8 * 5 + loc5;
-  const bool comp_valid = loc3 <= 2 && loc5 <= 4 && comp < 19;
 
   // Entries at or behind the last contributor of every pixel of the tile are never used
   // (backward.cu:290: `contributor >= last_contributor` -> continue).
@@ -269,16 +265,25 @@ __global__ void __launch_bounds__(BATCH, 4) surfel_composite_bwd_kernel(const Co
           for (int p = 0; p < 2; ++p)
             if (c[p]) px[p].contribute(h[p], q3, q4, contributor, g);
 
-          // warp reduce-scatter 20 -> 10 -> 5 -> 3 -> 2 -> 1 (a visit without any contributing pixel -- 3 % of them on
-          // the bench scene -- adds zeros: cheaper than a vote and a branch on every visit)
-          rs_step<10>(g, 16, b16);
-          rs_step<5>(g, 8, b8);
-          g[5] = 0.0f;
-          rs_step<3>(g, 4, b4);
-          g[3] = 0.0f;
-          rs_step<2>(g, 2, b2);
-          rs_step<1>(g, 1, b1);
-          if (comp_valid) atomicAdd(a.acc + (size_t)s_id[buf][j] * ACC_STRIDE + comp, g[0]);
+          // Sum over the warp through shared memory: every lane stores its 20 partials as one 80-B row (five 16-B
+          // stores, conflict-free: the rows of eight lanes cover all 32 banks), then lane c adds column c of the 32
+          // rows (conflict-free: the lanes of one load read consecutive words).  5 STS + 32 LDS + 33 FADD against the
+          // 21 shuffles + 20 adds + 42 selects of a recursive-halving reduce-scatter in registers.
+          {
+            float4* row = reinterpret_cast<float4*>(s_red[warp][lane]);
+#pragma unroll
+            for (int k = 0; k < 5; ++k) row[k] = make_float4(g[4 * k], g[4 * k + 1], g[4 * k + 2], g[4 * k + 3]);
+            __syncwarp();
+            float s0 = 0.0f, s1 = 0.0f;
+            if (lane < ACC_STRIDE) {
+#pragma unroll
+              for (int r = 0; r < 32; r += 2) { s0 += s_red[warp][r][lane]; s1 += s_red[warp][r + 1][lane]; }
+            }
+            __syncwarp();
+            // (16-B column loads by lanes 4 q + g over the rows 4 k + g, then two butterflies: 1.63 ms against 1.49 --
+            // bank conflicts of the strided 16-B loads)
+            if (lane < 19) atomicAdd(a.acc + (size_t)s_id[buf][j] * ACC_STRIDE + lane, s0 + s1);
+          }
         }
       }
     }
