@@ -274,7 +274,7 @@ struct GaussPixelBwd {
   __device__ __forceinline__ void contribute(const GaussEval& e, const float4& q0, const float4& q1, const float4& q2,
                                              const float4& q3, float ddelx_dx, float ddely_dy, float* g) {
     const float alpha = e.alpha, G = e.G;
-    const float inv_1ma = __frcp_rn(__fsub_rn(1.0f, alpha));
+    const float inv_1ma = rcp_newton(__fsub_rn(1.0f, alpha));   // as in the surfel backward
     T = T * inv_1ma;
     const float w = alpha * T;                      // dchannel_dcolor
     const float om = 1.f - last_alpha;

@@ -84,7 +84,8 @@ struct PixelBwd {
     const float alpha = h.alpha, G = h.G;
     // One reciprocal for (1 - alpha) and one for p.z instead of the reference's divisions
     // (backward.cu:341,:412,:437-438): nothing cancels behind them.
-    const float inv_1ma = __frcp_rn(__fsub_rn(1.0f, alpha));
+    // T is a running product over the tile's list: MUFU.RCP plus one Newton step (within half a unit in the last place)
+    const float inv_1ma = rcp_newton(__fsub_rn(1.0f, alpha));
     T = T * inv_1ma;
     const float w = alpha * T;
     const float om = 1.0f - last_alpha;
@@ -107,7 +108,7 @@ struct PixelBwd {
     // with the forward's final_* bit-identical, dL_dweight and the last_dL_dT recurrence are then the reference's
     // bit for bit, and only T (reciprocal instead of division, nothing cancels there) differs in the last place.
     const float m_d = ndc_depth(c_d);
-    const float dmd_dd = __fdiv_rn(FAR_N * NEAR_N, __fmul_rn(c_d, __fmul_rn(c_d, FAR_N - NEAR_N)));
+    const float dmd_dd = (FAR_N * NEAR_N) * rcp_approx(__fmul_rn(c_d, __fmul_rn(c_d, FAR_N - NEAR_N)));   // a plain factor: no cancellation behind it
     float dL_dz = 0.0f;
     if (contributor == median_contributor - 1u) dL_dz = dmedian;
     const float dL_dweight =
