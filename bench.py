@@ -363,7 +363,9 @@ def main():
         torch.cuda.synchronize()
         b200gs.timing_enable(1)
         b200gs.timing_read()
-        step()
+        was_pipelined, pipelined = pipelined, False      # one stream for this pass: an event pair around a stage must not
+        step()                                           # also cover another view's stage 1 running next to it
+        pipelined = was_pipelined
         torch.cuda.synchronize()
         stages_all = b200gs.timing_read()
         b200gs.timing_enable(0)
